@@ -1,0 +1,126 @@
+"""ctypes front-end of the CPU oracle (TEST INFRASTRUCTURE — see oracle/oracle.h).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+may import this module.  The product package (litap_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liblitap_oracle.so")
+_lib = None
+
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+
+
+def build(force=False):
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".h"))]
+    if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liblitap_oracle.so"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        L.oracle_ddir.argtypes = [_f64p, C.c_int64, C.c_int64, _u8p, _u8p, C.c_void_p,
+                                  C.POINTER(C.c_int), C.POINTER(C.c_int64)]
+        L.oracle_get_dir.argtypes = [C.c_int64] * 4 + [C.c_uint]
+        L.oracle_invert.argtypes = [_f64p, C.c_int64, _f64p]
+        L.oracle_invert.restype = None
+        L.oracle_shed.argtypes = [_f64p, _u8p, C.c_int64, C.c_int64, _i32p, _i64p, _u8p, C.POINTER(C.c_int64)]
+        L.oracle_form.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 5 + [C.c_int]
+        L.oracle_weti.argtypes = [_f64p, _u8p, _f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 4
+        L.oracle_r_round.argtypes = [C.c_double, C.c_int]
+        L.oracle_r_round.restype = C.c_double
+        L.oracle_synth_dem.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_uint32,
+                                       C.c_double, C.c_int, C.c_int]
+        L.oracle_synth_dem.restype = None
+        _lib = L
+    return _lib
+
+
+def add_buffer(grid):
+    """R/LITAP_load.R:273-332 add_buffer: wrap an nr x nc grid in a ring of NA."""
+    g = np.asarray(grid, dtype=np.float64)
+    out = np.full((g.shape[0] + 2, g.shape[1] + 2), np.nan)
+    out[1:-1, 1:-1] = g
+    return out
+
+
+def ddir(elev_b):
+    """calc_ddir2 on a buffered grid. Returns dict(ddir u8 [0=NA], flatcell u8 [2=NA], drec i64 [0=NA])."""
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    NR, NC = e.shape
+    d = np.zeros((NR, NC), np.uint8)
+    f = np.zeros((NR, NC), np.uint8)
+    dr = np.zeros((NR, NC), np.int64)
+    rounds, pc = C.c_int(0), C.c_int64(0)
+    lib().oracle_ddir(e, NR, NC, d, f, dr.ctypes.data, C.byref(rounds), C.byref(pc))
+    return dict(ddir=d, flatcell=f, drec=dr, plateau_rounds=rounds.value, patch_cells=pc.value)
+
+
+def get_dir(row, col, row_f, col_f, opts=range(1, 10)):
+    m = 0
+    for o in opts:
+        m |= 1 << int(o)
+    return lib().oracle_get_dir(row, col, row_f, col_f, m)
+
+
+def invert(elev_b):
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    out = np.empty_like(e)
+    lib().oracle_invert(e.ravel(), e.size, out.ravel())
+    return out
+
+
+def shed(elev_b, ddir_b):
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    d = np.ascontiguousarray(ddir_b, dtype=np.uint8)
+    NR, NC = e.shape
+    s = np.zeros((NR, NC), np.int32)
+    u = np.zeros((NR, NC), np.int64)
+    r = np.zeros((NR, NC), np.uint8)
+    n = C.c_int64(0)
+    lib().oracle_shed(e, d, NR, NC, s, u, r, C.byref(n))
+    return dict(shed=s, upslope=u, ridge=r, npits=n.value)
+
+
+def form(elev_b, grid, nthreads=1):
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    NR, NC = e.shape
+    outs = [np.empty((NR, NC)) for _ in range(5)]
+    lib().oracle_form(e, NR, NC, float(grid), *outs, int(nthreads))
+    return dict(zip(("slope_pct", "slope_deg", "aspect", "prof", "plan"), outs))
+
+
+def weti(elev_b, ddir_b, upslope_b, grid):
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    d = np.ascontiguousarray(ddir_b, dtype=np.uint8)
+    u = np.ascontiguousarray(upslope_b, dtype=np.float64)
+    NR, NC = e.shape
+    outs = [np.empty((NR, NC)) for _ in range(4)]
+    lib().oracle_weti(e, d, u, NR, NC, float(grid), *outs)
+    return dict(zip(("qarea1", "qarea2", "qweti1", "qweti2"), outs))
+
+
+def r_round(x, digits):
+    return lib().oracle_r_round(float(x), int(digits))
+
+
+def synth_dem(nr, nc, seed=20261104, quant=1000.0, na_permille=0, row0=0, gnr=None, nthreads=0):
+    """Buffered (nr+2) x (nc+2) synthetic hash-fBm DEM (rows row0..row0+nr-1 of a gnr-row DEM)."""
+    gnr = nr if gnr is None else gnr
+    out = np.empty((nr + 2, nc + 2))
+    if nthreads <= 0:
+        nthreads = os.cpu_count() or 1
+    lib().oracle_synth_dem(out, nr, nc, row0, gnr, seed, float(quant), int(na_permille), nthreads)
+    return out

@@ -1,0 +1,142 @@
+"""Pins the CPU oracle against every golden the reference ships for the hot path.
+
+Sources (decoded by tests/golden/make_golden.py from /root/reference):
+  G1 tests/testthat/_snaps/02_flow_internal.md blocks 0,1,8,9  (test_02_flow_internal.R:9-66)
+  G2 tests/testthat/test_02_flow_internal.R:70-163             (upslope KATs, transcribed below)
+  G3 tests/testthat/test_00_utility.R:2-70                     (get_dir table, transcribed below)
+  G4 inst/extdata/testELEV/{flow/dem_fill,flow/dem_inverted,form/dem_form}.rds
+"""
+import numpy as np
+import pytest
+
+import oracle
+from conftest import eq_na
+
+
+def _sampled(arr, seq, na=None):
+    v = arr.ravel()[seq].astype(np.float64)
+    if na is not None:
+        v[v == na] = np.nan
+    return v
+
+
+@pytest.mark.parametrize("inverted", [False, True])
+def test_snapshot_ddir_shed(golden, inverted):
+    snap = golden["snap_02_flow_internal"]
+    e = oracle.add_buffer(golden["dems"]["testELEV"])
+    td, ts = ("inv_ddir", "inv_shed") if inverted else ("ddir", "shed")
+    if inverted:
+        e = oracle.invert(e)
+    r = oracle.ddir(e)
+    seq = snap[td + "__seqno"].astype(int) - 1
+    assert len(seq) == 500
+    # snapshot numerics were rounded to 5 dp by sub_dem (tests/testthat/setup.R:4-8)
+    assert np.nanmax(np.abs(snap[td + "__elev"] - e.ravel()[seq])) < 1e-5
+    assert eq_na(_sampled(r["ddir"], seq, 0), snap[td + "__ddir"]).all()
+    assert eq_na(_sampled(r["drec"], seq, 0), snap[td + "__drec"]).all()
+    assert eq_na(_sampled(r["flatcell"], seq, 2), snap[td + "__flatcell"]).all()
+    if inverted:  # exercises the plateau loop and one flat-pit patch
+        assert r["plateau_rounds"] == 2 and r["patch_cells"] == 2
+    s = oracle.shed(e, r["ddir"])
+    seq = snap[ts + "__seqno"].astype(int) - 1
+    assert eq_na(_sampled(s["shed"], seq, 0), snap[ts + "__initial_shed"]).all()
+    assert eq_na(_sampled(s["upslope"], seq), snap[ts + "__upslope"]).all()
+    assert eq_na(_sampled(s["ridge"], seq, 2), snap[ts + "__ridge"]).all()
+    assert s["npits"] == (11 if inverted else 10)
+
+
+def test_fullgrid_shed_ridge(golden):
+    e = oracle.add_buffer(golden["dems"]["testELEV"])
+    s = oracle.shed(e, oracle.ddir(e)["ddir"])
+    fill = golden["dem_fill"]
+    assert (fill["elev"] == golden["dems"]["testELEV"].ravel()).all()
+    assert (s["shed"][1:-1, 1:-1].ravel() == fill["initial_shed"]).all()
+    assert (s["ridge"][1:-1, 1:-1].ravel() == fill["ridge"]).all()
+    ei = oracle.invert(e)
+    si = oracle.shed(ei, oracle.ddir(ei)["ddir"])
+    inv = golden["dem_inverted"]
+    assert (si["shed"][1:-1, 1:-1].ravel() == inv["inv_initial_shed"]).all()
+    assert (si["ridge"][1:-1, 1:-1].ravel() == inv["ridge"]).all()
+
+
+def test_fullgrid_form_bit_exact(golden):
+    fill, frm = golden["dem_fill"], golden["dem_form"]
+    e = oracle.add_buffer(fill["elev"].reshape(90, 90))
+    f = oracle.form(e, 5.0)
+    for k in ("slope_pct", "slope_deg", "aspect", "prof", "plan"):
+        assert (f[k][1:-1, 1:-1].ravel() == frm[k]).all(), k
+    # OpenMP leg gives the same bits
+    f2 = oracle.form(e, 5.0, nthreads=4)
+    for k in f:
+        assert eq_na(f[k], f2[k]).all()
+
+
+def test_fullgrid_weti_bit_exact(golden):
+    fill, frm = golden["dem_fill"], golden["dem_form"]
+    e = oracle.add_buffer(fill["elev"].reshape(90, 90))
+    dd = np.nan_to_num(oracle.add_buffer(fill["ddir"].reshape(90, 90)), nan=0).astype(np.uint8)
+    up = np.nan_to_num(oracle.add_buffer(fill["upslope"].reshape(90, 90)), nan=0.0)
+    w = oracle.weti(e, dd, up, 5.0)
+    for k in ("qarea1", "qarea2", "qweti1", "qweti2"):
+        assert (w[k][1:-1, 1:-1].ravel() == frm[k]).all(), k
+
+
+KATS = [
+    ([[99, 98, 99], [98, 97, 98], [97, 96, 97]],
+     [1, 1, 1, 1, 4, 1, 1, 9, 1]),
+    ([[99, 98, 99, 98], [98, 97, 98, 96], [97, 96, 97, 90], [90, 95, 92, 91]],
+     [1, 1, 1, 1, 1, 3, 1, 3, 1, 5, 1, 8, 8, 1, 1, 1]),
+    ([[99, 98, 99, 98, 111, 107], [98, 97, 98, 96, 110, 109], [97, 96, 97, 90, 109, 110],
+      [90, 95, 92, 91, 93, 95], [89, 90, 94, 99, 94, 95], [99, 99, 97, 101, 103, 101]],
+     [1, 1, 1, 2, 1, 2, 1, 3, 1, 4, 1, 1, 1, 5, 1, 18, 1, 1, 7, 1, 1, 4, 5, 2, 16, 7, 2, 1, 2, 2,
+      1, 1, 1, 1, 1, 1]),
+]
+
+
+@pytest.mark.parametrize("dem,upslope", KATS)
+def test_upslope_kats(dem, upslope):
+    """tests/testthat/test_02_flow_internal.R:70-163 (first_pitr1 with max_area=0,max_depth=0 is a no-op)."""
+    e = oracle.add_buffer(np.array(dem, dtype=float))
+    s = oracle.shed(e, oracle.ddir(e)["ddir"])
+    assert s["upslope"][1:-1, 1:-1].ravel().tolist() == upslope
+
+
+def test_get_dir_table():
+    """tests/testthat/test_00_utility.R:2-70."""
+    g = oracle.get_dir
+    base = {1: (1, 2, 2, 1), 2: (1, 1, 2, 1), 3: (1, 1, 2, 2), 4: (1, 2, 1, 1), 5: (2, 2, 2, 2),
+            6: (1, 1, 1, 2), 7: (2, 2, 1, 1), 8: (2, 1, 1, 1), 9: (2, 1, 1, 2)}
+    for d, a in base.items():
+        assert g(*a) == d
+        for i in (1, 2, 3, 4, 6, 7, 8, 9):
+            assert g(*a, [i]) == (5 if d == 5 else i)
+    restricted = {
+        1: [((2, 3), 2), ((4, 7), 4), ((8, 6), 8)], 2: [((3, 6), 3), ((1, 4), 1), ((7, 8), 7)],
+        3: [((2, 1), 2), ((6, 9), 6), ((4, 8), 8)], 4: [((7, 8), 7), ((1, 2), 1), ((9, 3), 9)],
+        5: [((1, 2), 5), ((3, 4), 5), ((8, 9), 5)], 6: [((8, 9), 9), ((2, 3), 3), ((7, 1), 7)],
+        7: [((4, 1), 4), ((8, 9), 8), ((2, 6), 6)], 8: [((4, 7), 7), ((9, 6), 9), ((1, 3), 1)],
+        9: [((7, 8), 8), ((3, 6), 6), ((4, 2), 4)]}
+    for d, cases in restricted.items():
+        for opts, want in cases:
+            assert g(*base[d], opts) == want, (d, opts)
+
+
+def test_r_round_rule():
+    assert oracle.r_round(2.0055, 3) == 2.006     # rint(x*1000)/1000 would give 2.005
+    assert oracle.r_round(0.15, 1) == 0.1 and oracle.r_round(2.5, 0) == 2.0
+    assert oracle.r_round(-1.0005, 3) == -oracle.r_round(1.0005, 3)
+    rng = np.random.default_rng(1)
+    for x in rng.uniform(-60, 60, 20000):
+        assert oracle.r_round(x, 3) == round(float(x), 3)
+
+
+def test_synth_dem_bands_bit_identical():
+    full = oracle.synth_dem(96, 80, seed=7)
+    top = oracle.synth_dem(40, 80, seed=7, row0=0, gnr=96)
+    bot = oracle.synth_dem(56, 80, seed=7, row0=40, gnr=96)
+    assert eq_na(top[:-1], full[:41]).all()          # band + south halo row
+    assert eq_na(bot[1:], full[41:]).all() and eq_na(bot[0], full[40]).all()
+    assert np.isnan(full[0]).all() and np.isnan(full[:, 0]).all()
+    assert (np.round(full[1:-1, 1:-1] * 1000) / 1000 == full[1:-1, 1:-1]).all()
+    na = oracle.synth_dem(64, 64, seed=7, na_permille=10)
+    assert 5 < np.isnan(na[1:-1, 1:-1]).sum() < 100
