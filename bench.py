@@ -1,0 +1,276 @@
+#!/usr/bin/env python3
+"""bench.py — Mcells/s of the LITAP raster hot path (ddir + shed + upslope + form) on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--size S] [--impl reference]
+
+A step = one pass of calc_ddir2 -> calc_shed4 (labels, upslope, ridge) + calc_form over one
+synthetic hash-fBm DEM (BASELINE.json configs[2]: 8192 x 8192, 0.001 m quantisation, grid = 5,
+seed 20261104) that is already resident in HBM.  `value` = cells of the whole job / device time
+(CUDA events, max over ranks).  `e2e` = the same composite through the host-buffer C-ABI call
+litap_flow_form (pinned host arrays, H2D + D2H inside the timed region).
+`--impl reference` times the CPU restatement of the reference's R code (the oracle; R itself is
+not installed) on a bounded sample of the same DEM with all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED, QUANT, GRID_M = 20261104, 1000.0, 5.0
+METRIC = "Mcells/s (ddir+shed+upslope+form)"
+# algorithmic bytes per cell of each hot kernel
+ALG_BYTES = {"k_d8": 9, "k_form": 48, "k_shed_local": 9, "k_shed_final": 10}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        self.t.join(timeout=2)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_port_pass(e, nthreads):
+    """One pass of the oracle (CPU port of the reference's R code) over a buffered DEM."""
+    import oracle
+    d = oracle.ddir(e)
+    oracle.shed(e, d["ddir"])
+    oracle.form(e, GRID_M, nthreads=nthreads)
+
+
+def cpu_sample(size, rows):
+    import numpy as np
+
+    import oracle
+    rows = min(rows, size)
+    e = oracle.synth_dem(rows, size, seed=SEED, quant=QUANT, row0=0, gnr=size)
+    e[-1, :] = np.nan  # the band is processed as a DEM of its own: close the ring
+    return e, rows * size, f"rows 0-{rows - 1} of the same {size}x{size} DEM ({rows * size / 1e6:.1f} Mcells)"
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    nthreads = os.cpu_count() or 1
+    e, cells, what = cpu_sample(a.size, a.cpu_rows)
+    for _ in range(min(a.warmup, 1)):
+        cpu_port_pass(e, nthreads)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        cpu_port_pass(e, nthreads)
+    dt = (time.perf_counter() - t0) / a.steps
+    v = cells / dt / 1e6
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "Mcells/s", "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": min(a.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"hash-fBm DEM {a.size}x{a.size}, quant 0.001 m, grid 5 m, seed {SEED}",
+                   "note": "R is not installed: CPU port of the reference's R algorithm (oracle/), "
+                           "OpenMP where the algorithm is data-parallel (D8 stencil, form), serial elsewhere"},
+        "cpu_baseline": {"value": v, "unit": "Mcells/s", "cores": nthreads, "kind": "port", "sample": what},
+        "e2e": {"value": v, "unit": "Mcells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def run_ours(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import litap_b200 as lb
+    from litap_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.check(lb.lib().litap_init(local))
+    stream = torch.cuda.current_stream()
+    _lib.set_stream(stream.cuda_stream)
+
+    n = a.size
+    NR = NC = n + 2
+    g = lb.DeviceGrid(NR, NC)
+    g.synth(seed=SEED + (rank if world > 1 else 0), quant=QUANT)
+
+    def step():
+        g.form(GRID_M)
+        g.ddir()
+        g.shed()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        step()
+    launches0 = None
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    nl = 0
+    ev0.record(stream)
+    for _ in range(a.steps):
+        g.form(GRID_M); nl += lb.timings()["kernel_launches"]
+        g.ddir(); nl += lb.timings()["kernel_launches"]
+        g.shed(); nl += lb.timings()["kernel_launches"]
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    cells_job = n * n * world
+    value = cells_job * a.steps / (ms * 1e-3) / 1e6
+    stage = lb.timings()
+
+    # ---- per-kernel pass (untimed, CUDA events around every launch) -> roofline of the dominant kernel
+    _lib.profile(True)
+    PROF_STEPS = 3
+    for _ in range(PROF_STEPS):
+        step()
+    prof = _lib.profile_report()
+    _lib.profile(False)
+    per_kernel = {k: {"launches_per_step": v[0] / PROF_STEPS, "ms_per_step": v[1] / PROF_STEPS} for k, v in prof.items()}
+    dom = max(prof, key=lambda k: prof[k][1])
+    peak, peak_src = measured_peak()
+    roof = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
+            "traffic": None, "peak_source": peak_src}
+    if dom in ALG_BYTES:
+        avg_ms = prof[dom][1] / prof[dom][0]
+        ach = ALG_BYTES[dom] * n * n / (avg_ms * 1e-3) / 1e9
+        roof.update(achieved=ach, frac=ach / peak, alg_bytes_per_cell=ALG_BYTES[dom], avg_launch_ms=avg_ms)
+    rf_all = {}
+    for k, b in ALG_BYTES.items():
+        if k in prof:
+            avg = prof[k][1] / prof[k][0]
+            rf_all[k] = round(b * n * n / (avg * 1e-3) / 1e9 / peak, 4)
+
+    # ---- end to end through the host-buffer C ABI (pinned host arrays)
+    e2e = None
+    if not a.no_e2e:
+        host_in = torch.empty((NR, NC), dtype=torch.float64).pin_memory()
+        e_np = host_in.numpy()
+        e_np[...] = g.download("elev")
+        dts = {"ddir": torch.uint8, "flatcell": torch.uint8, "shed": torch.int32, "upslope": torch.int32,
+               "ridge": torch.uint8, "slope_pct": torch.float64, "slope_deg": torch.float64,
+               "aspect": torch.float64, "prof": torch.float64, "plan": torch.float64}
+        pinned = {k: torch.empty((NR, NC), dtype=dt).pin_memory() for k, dt in dts.items()}
+        out = {k: (v.numpy().view(np.uint32) if k == "upslope" else v.numpy()) for k, v in pinned.items()}
+        h2d = e_np.nbytes
+        d2h = sum(v.nbytes for v in out.values())
+        for _ in range(1):
+            lb.flow_form(e_np, GRID_M, out=out)
+        barrier()
+        es = max(1, min(a.steps, a.e2e_steps))
+        ev0.record(stream)
+        for _ in range(es):
+            lb.flow_form(e_np, GRID_M, out=out)
+        ev1.record(stream)
+        barrier()
+        t = torch.tensor([ev0.elapsed_time(ev1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item()) / es
+        e2e = {"value": cells_job / (e2e_ms * 1e-3) / 1e6, "unit": "Mcells/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": es,
+               "api": "litap_flow_form (C ABI, pinned host buffers)"}
+        del pinned, host_in
+
+    # ---- CPU baseline (rank 0, N = 1): the oracle on a bounded sample, single thread
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu:
+        e, cells, what = cpu_sample(n, a.cpu_rows)
+        t0 = time.perf_counter()
+        cpu_port_pass(e, 1)
+        dt = time.perf_counter() - t0
+        cpu = {"value": cells / dt / 1e6, "unit": "Mcells/s", "cores": 1, "kind": "port", "sample": what,
+               "seconds": dt}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": "Mcells/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"hash-fBm DEM {n}x{n} per GPU, quant 0.001 m, grid 5 m, seed {SEED}",
+                       "cells_per_gpu": n * n, "l2": "inputs (537 MB elev) larger than L2; no flush needed",
+                       "parallelism": "1 GPU" if world == 1 else f"{world} independent DEM replicas (row-band sharding: see DESIGN.md)",
+                       "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": nl,
+            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel,
+            "cpu_baseline": cpu}))
+    g.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--size", type=int, default=8192)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-rows", type=int, default=2048, help="rows of the DEM in the CPU sample")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,122 @@
+/*
+ * litap.h — C ABI of liblitap_cuda.so: the B200 (sm_100a) implementation of the raster
+ * core of LITAP's flow_mapper() / form_mapper().
+ *
+ * The reference (FRDC-SHL/LITAP, pure R) has no FFI for this path; the boundary is the set of
+ * internal R functions below.  Each entry point replaces one of them and is what the R-side
+ * `.Call` shim (litap_b200/r/src/litap_call.c) binds:
+ *
+ *   litap_ddir   <- calc_ddir2()   R/flow_01_calc_ddir.R:2-118   (called R/flow_mapper.R:157,354)
+ *   litap_shed   <- calc_shed4()   R/flow_02_calc_shed.R:10-58   (called R/flow_mapper.R:180,377)
+ *                   incl. calc_upslopes(type="upslope")  R/flow_02_calc_shed.R:60-116
+ *   litap_form   <- calc_form()    R/form_01_calc_form.R:4-67    (called R/form_mapper.R:103)
+ *   litap_weti   <- calc_weti2()   R/form_02b_calc_weti.R:3-110  (called R/form_mapper.R:127)
+ *   invert flag  <- invert()       R/flow_06_invert.R:1-5        (called R/flow_mapper.R:343-346)
+ *
+ * Grid convention (R/LITAP_load.R:273-332 add_buffer; R/LITAP_functions.R:207-235 nb_values):
+ * every array is the BUFFERED grid, NR = nrow+2 by NC = ncol+2, dense row-major, row 0 = north,
+ * element i <-> R's seqno = i+1.  The outer ring is NA.  NA elevation = any NaN.
+ * Neighbour / direction codes:   7 8 9
+ *                                4 5 6      (5 = pit / self, 0 = NA in the uint8 encoding)
+ *                                1 2 3
+ *
+ * Ownership: the caller allocates every host buffer; the library never keeps a caller pointer
+ * past return.  Device memory is library-owned and pooled between calls (litap_shutdown frees).
+ * Errors: 0 = OK, otherwise a LITAP_E* class; text via litap_last_error() (thread-local).
+ * There is NO CPU fallback: without a usable CUDA device every compute call returns LITAP_ECUDA.
+ * Threading: calls are synchronous; one host thread at a time per process.
+ * Limits: NR*pitch < 2^31 cells per device (32768 x 32768 fits); NC >= 3, NR >= 3.
+ */
+#ifndef LITAP_H
+#define LITAP_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LITAP_OK 0
+#define LITAP_EARG 1   /* bad argument */
+#define LITAP_ECUDA 2  /* CUDA runtime / no device */
+#define LITAP_ENOMEM 3 /* device or host allocation failed */
+#define LITAP_ECOMM 4  /* multi-GPU exchange failed */
+
+/* per-stage device times of the most recent call, milliseconds (CUDA events) */
+typedef struct litap_timings {
+  float h2d_ms, d2h_ms;
+  float ddir_ms;    /* D8 stencil + plateau rounds + flat-pit patches */
+  float shed_ms;    /* labels + canonical numbering + upslope + ridge */
+  float form_ms;
+  float weti_ms;
+  float total_ms;   /* whole call, incl. copies */
+  int plateau_rounds;
+  int64_t flat_cells, patch_cells, npits;
+  int64_t kernel_launches; /* kernels of this library launched by the call */
+} litap_timings;
+
+int litap_init(int device);        /* selects the device and creates the stream; idempotent */
+void litap_shutdown(void);         /* frees pooled device memory */
+const char* litap_last_error(void);
+const char* litap_version(void);
+int litap_get_timings(litap_timings* out);
+/* run on a caller-owned CUDA stream (a cudaStream_t; NULL = back to the library's own stream) */
+int litap_set_stream(void* cuda_stream);
+/* per-kernel CUDA-event timing, off by default: enable, run stages, then fetch a CSV
+ * "kernel,launches,total_ms" (the log is cleared by the report) */
+int litap_profile_enable(int on);
+int litap_profile_report(char* buf, int64_t cap);
+
+/* ---- host-buffer entry points (what the R shim calls) -------------------------------------- */
+
+/* calc_ddir2.  invert != 0 applies invert() first (elev <- max(elev) - elev) on the device.
+ * ddir: 0 = NA, 1..9.  flatcell (may be NULL): 1 = flat after the initial stencil, 0 = not,
+ * 2 = NA.  R derives drec = seqno + offset(ddir) (R/LITAP_functions.R:237-254). */
+int litap_ddir(const double* elev, int64_t NR, int64_t NC, int invert,
+               uint8_t* ddir, uint8_t* flatcell);
+
+/* calc_shed4 (+ calc_upslopes "upslope").  shed: 0 = NA, 1..npits (= initial_shed).
+ * upslope: cells draining through the cell incl. itself; 0 where shed is NA.
+ * ridge: 1/0, 2 = NA (ring).  Any of shed/upslope/ridge/npits may be NULL. */
+int litap_shed(const double* elev, const uint8_t* ddir, int64_t NR, int64_t NC,
+               int32_t* shed, uint32_t* upslope, uint8_t* ridge, int64_t* npits);
+
+/* calc_form.  Outputs NaN = NA.  Any output may be NULL. */
+int litap_form(const double* elev, int64_t NR, int64_t NC, double grid,
+               double* slope_pct, double* slope_deg, double* aspect, double* prof, double* plan);
+
+/* calc_weti2.  upslope as produced by litap_shed (R passes the dem_fill column). */
+int litap_weti(const double* elev, const uint8_t* ddir, const uint32_t* upslope,
+               int64_t NR, int64_t NC, double grid,
+               double* qarea1, double* qarea2, double* qweti1, double* qweti2);
+
+/* Fused composite (ddir -> shed/upslope/ridge -> form) with one upload of elev; the
+ * intermediate ddir never leaves the device.  Any output may be NULL (then not downloaded). */
+int litap_flow_form(const double* elev, int64_t NR, int64_t NC, double grid, int invert,
+                    uint8_t* ddir, uint8_t* flatcell, int32_t* shed, uint32_t* upslope,
+                    uint8_t* ridge, int64_t* npits, double* slope_pct, double* slope_deg,
+                    double* aspect, double* prof, double* plan);
+
+/* ---- device-resident entry points (bench / large DEMs that never exist on the host) -------- */
+
+typedef struct litap_grid litap_grid; /* opaque: one DEM (or one row band) resident in HBM */
+
+int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out);
+void litap_grid_destroy(litap_grid* g);
+/* fill elev with the synthetic hash-fBm DEM; rows row0.. of a gnr-row DEM */
+int litap_grid_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille);
+int litap_grid_upload_elev(litap_grid* g, const double* elev);
+/* run stages on the resident grid; results stay on the device */
+int litap_grid_ddir(litap_grid* g, int invert);
+int litap_grid_shed(litap_grid* g);
+int litap_grid_form(litap_grid* g, double grid_m);
+int litap_grid_weti(litap_grid* g, double grid_m);
+/* copy results out (dense NR*NC); name is one of: elev ddir flatcell shed upslope ridge
+ * slope_pct slope_deg aspect prof plan qarea1 qarea2 qweti1 qweti2 */
+int litap_grid_download(litap_grid* g, const char* name, void* dst);
+int64_t litap_grid_npits(const litap_grid* g);
+/* order-independent checksum (sum of value*index hashes) of a result array, computed on the device */
+int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

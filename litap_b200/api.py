@@ -1,0 +1,248 @@
+"""Host-side mirror of the reference's internal R functions for the hot path.
+
+R is not available here, so the tibble `db` of the reference becomes a dict of numpy columns of
+length NR*NC sorted by seqno (the same "one row per cell of the buffered grid" contract,
+R/LITAP_load.R:273-332), plus the keys "nrow"/"ncol" of the buffered grid.  Function names,
+argument meaning, returned columns and NA conventions follow the R functions; every function
+calls the CUDA library through the C ABI and raises LitapError on failure.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import LitapError, check, lib
+
+_OFF_DR = np.array([0, 1, 1, 1, 0, 0, 0, -1, -1, -1])
+_OFF_DC = np.array([0, -1, 0, 1, -1, 0, 1, -1, 0, 1])
+
+
+def add_buffer(elev):
+    """R/LITAP_load.R:273-332: wrap an nrow x ncol elevation grid in a ring of NA cells and build
+    the seqno-ordered table (seqno, row, col, elev, buffer)."""
+    g = np.asarray(elev, dtype=np.float64)
+    if g.ndim != 2:
+        raise LitapError("add_buffer: elev must be a 2-d grid (north row first)")
+    NR, NC = g.shape[0] + 2, g.shape[1] + 2
+    e = np.full((NR, NC), np.nan)
+    e[1:-1, 1:-1] = g
+    row, col = np.divmod(np.arange(NR * NC), NC)
+    buf = np.ones((NR, NC), bool)
+    buf[1:-1, 1:-1] = False
+    return {"nrow": NR, "ncol": NC, "seqno": np.arange(1, NR * NC + 1), "row": row + 1, "col": col + 1,
+            "elev": e.ravel(), "buffer": buf.ravel()}
+
+
+def remove_buffer(db, cols=None):
+    """R/LITAP_read_write.R:124-166: drop the ring; returns {name: (nrow-2, ncol-2) array}."""
+    NR, NC = db["nrow"], db["ncol"]
+    out = {}
+    for k, v in db.items():
+        if k in ("nrow", "ncol") or (cols and k not in cols):
+            continue
+        out[k] = np.asarray(v).reshape(NR, NC)[1:-1, 1:-1]
+    return out
+
+
+def _dims(db):
+    NR, NC = int(db["nrow"]), int(db["ncol"])
+    if db["elev"].size != NR * NC:
+        raise LitapError("db$elev does not have nrow*ncol rows")
+    return NR, NC
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _ddir_u8(ddir):
+    d = np.asarray(ddir)
+    if d.dtype != np.uint8:
+        d = np.where(np.isnan(d.astype(np.float64)), 0, d).astype(np.uint8)  # NA -> 0
+    return np.ascontiguousarray(d)
+
+
+def invert(db):
+    """R/flow_06_invert.R:1-5.  Kept on the host for callers that need the inverted column itself;
+    calc_ddir2(invert=True) does the same on the device."""
+    out = dict(db)
+    e = _f64(db["elev"])
+    out["elev"] = np.nanmax(e) - e
+    return out
+
+
+def calc_ddir2(db, verbose=False, invert=False):
+    """R/flow_01_calc_ddir.R:2-118.  Returns db + ddir (float, NaN = NA), flatcell, drec."""
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    d = np.empty(NR * NC, np.uint8)
+    f = np.empty(NR * NC, np.uint8)
+    check(lib().litap_ddir(e.ctypes.data, NR, NC, int(bool(invert)), d.ctypes.data, f.ctypes.data))
+    out = dict(db)
+    if invert:
+        out["elev"] = np.nanmax(e) - e
+    out["ddir_u8"] = d
+    dd = d.astype(np.float64)
+    dd[d == 0] = np.nan
+    out["ddir"] = dd
+    fc = f.astype(np.float64)
+    fc[f == 2] = np.nan
+    out["flatcell"] = fc
+    # flow_values / calc_seq, R/LITAP_functions.R:237-254
+    seq = np.arange(1, NR * NC + 1, dtype=np.float64)
+    drec = seq + _OFF_DR[d] * NC + _OFF_DC[d]
+    drec[d == 0] = np.nan
+    out["drec"] = drec
+    return out
+
+
+def calc_shed4(db, verbose=False):
+    """R/flow_02_calc_shed.R:10-58.  Needs elev + ddir; returns db + initial_shed, upslope, ridge."""
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    d = _ddir_u8(db["ddir_u8"] if "ddir_u8" in db else db["ddir"])
+    s = np.empty(NR * NC, np.int32)
+    u = np.empty(NR * NC, np.uint32)
+    r = np.empty(NR * NC, np.uint8)
+    n = C.c_int64(0)
+    check(lib().litap_shed(e.ctypes.data, d.ctypes.data, NR, NC, s.ctypes.data, u.ctypes.data, r.ctypes.data,
+                           C.byref(n)))
+    out = dict(db)
+    sh = s.astype(np.float64)
+    sh[s == 0] = np.nan
+    out["initial_shed"] = sh
+    out["upslope"] = u.astype(np.float64)
+    rg = r.astype(np.float64)
+    rg[r == 2] = np.nan
+    out["ridge"] = rg
+    out["npits"] = n.value
+    return out
+
+
+def calc_form(db, grid, verbose=False):
+    """R/form_01_calc_form.R:4-67.  Returns seqno,row,col,slope_pct,slope_deg,aspect,prof,plan,buffer."""
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    outs = [np.empty(NR * NC) for _ in range(5)]
+    check(lib().litap_form(e.ctypes.data, NR, NC, float(grid), *[o.ctypes.data for o in outs]))
+    res = {k: db[k] for k in ("nrow", "ncol", "seqno", "row", "col", "buffer") if k in db}
+    res.update(zip(("slope_pct", "slope_deg", "aspect", "prof", "plan"), outs))
+    return res
+
+
+def calc_weti2(db, grid, verbose=False):
+    """R/form_02b_calc_weti.R:3-110.  Needs elev, ddir, upslope; returns db + qarea1/2, qweti1/2."""
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    d = _ddir_u8(db["ddir_u8"] if "ddir_u8" in db else db["ddir"])
+    u = np.ascontiguousarray(np.nan_to_num(np.asarray(db["upslope"], dtype=np.float64), nan=0.0), dtype=np.uint32)
+    outs = [np.empty(NR * NC) for _ in range(4)]
+    check(lib().litap_weti(e.ctypes.data, d.ctypes.data, u.ctypes.data, NR, NC, float(grid),
+                           *[o.ctypes.data for o in outs]))
+    out = dict(db)
+    out.update(zip(("qarea1", "qarea2", "qweti1", "qweti2"), outs))
+    return out
+
+
+def flow_form(elev_b, grid, invert=False, want=("ddir", "shed", "upslope", "ridge", "form"), out=None):
+    """Fused composite through litap_flow_form on a buffered 2-d grid (host buffers in, host buffers
+    out).  `out` may carry preallocated (e.g. pinned) arrays keyed like the result."""
+    e = _f64(elev_b)
+    NR, NC = e.shape
+    out = {} if out is None else out
+
+    def buf(name, dt):
+        if name not in out:
+            out[name] = np.empty((NR, NC), dt)
+        return out[name].ctypes.data
+
+    p = {k: None for k in ("ddir", "flatcell", "shed", "upslope", "ridge", "slope_pct", "slope_deg", "aspect",
+                           "prof", "plan")}
+    if "ddir" in want:
+        p["ddir"], p["flatcell"] = buf("ddir", np.uint8), buf("flatcell", np.uint8)
+    if "shed" in want:
+        p["shed"] = buf("shed", np.int32)
+    if "upslope" in want:
+        p["upslope"] = buf("upslope", np.uint32)
+    if "ridge" in want:
+        p["ridge"] = buf("ridge", np.uint8)
+    if "form" in want:
+        for k in ("slope_pct", "slope_deg", "aspect", "prof", "plan"):
+            p[k] = buf(k, np.float64)
+    n = C.c_int64(0)
+    check(lib().litap_flow_form(e.ctypes.data, NR, NC, float(grid), int(bool(invert)), p["ddir"], p["flatcell"],
+                                p["shed"], p["upslope"], p["ridge"], C.byref(n), p["slope_pct"], p["slope_deg"],
+                                p["aspect"], p["prof"], p["plan"]))
+    out["npits"] = n.value
+    return out
+
+
+class DeviceGrid:
+    """A DEM (or row band) resident in HBM: litap_grid_* of include/litap.h."""
+
+    _DT = {"elev": np.float64, "ddir": np.uint8, "flatcell": np.uint8, "shed": np.int32, "upslope": np.uint32,
+           "ridge": np.uint8}
+
+    def __init__(self, NR, NC):
+        self.NR, self.NC = int(NR), int(NC)
+        self._h = C.c_void_p()
+        check(lib().litap_grid_create(self.NR, self.NC, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().litap_grid_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def synth(self, seed=20261104, quant=1000.0, na_permille=0, row0=0, gnr=None):
+        check(lib().litap_grid_synth(self._h, row0, self.NR - 2 if gnr is None else gnr, seed, float(quant),
+                                     int(na_permille)))
+
+    def upload_elev(self, elev_b):
+        e = _f64(elev_b)
+        if e.size != self.NR * self.NC:
+            raise LitapError("upload_elev: wrong size")
+        check(lib().litap_grid_upload_elev(self._h, e.ctypes.data))
+
+    def ddir(self, invert=False):
+        check(lib().litap_grid_ddir(self._h, int(bool(invert))))
+
+    def shed(self):
+        check(lib().litap_grid_shed(self._h))
+
+    def form(self, grid):
+        check(lib().litap_grid_form(self._h, float(grid)))
+
+    def weti(self, grid):
+        check(lib().litap_grid_weti(self._h, float(grid)))
+
+    def download(self, name):
+        a = np.empty((self.NR, self.NC), self._DT.get(name, np.float64))
+        check(lib().litap_grid_download(self._h, name.encode(), a.ctypes.data))
+        return a
+
+    def checksum(self, name):
+        v = C.c_uint64(0)
+        check(lib().litap_grid_checksum(self._h, name.encode(), C.byref(v)))
+        return v.value
+
+    @property
+    def npits(self):
+        return lib().litap_grid_npits(self._h)
+
+
+def checksum_host(a):
+    """Host twin of litap_grid_checksum (tests): sum over cells of a 64-bit mix of (value bits, seqno)."""
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.float64:
+        v = a.view(np.uint64).ravel().copy()
+        v[np.isnan(a.ravel())] = np.uint64(0x7FF8000000000000)
+    else:
+        v = a.ravel().astype(np.int64).astype(np.uint64) if a.dtype == np.int32 else a.ravel().astype(np.uint64)
+        if a.dtype == np.int32:
+            v = a.ravel().view(np.uint32).astype(np.uint64)
+    idx = np.arange(1, v.size + 1, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        h = (v + np.uint64(0x9E3779B97F4A7C15)) * ((idx * np.uint64(0xBF58476D1CE4E5B9)) | np.uint64(1))
+        h ^= h >> np.uint64(29)
+        return int(h.sum(dtype=np.uint64))

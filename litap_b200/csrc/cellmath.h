@@ -1,0 +1,190 @@
+// cellmath.h — per-cell arithmetic of the hot path, shared by the CUDA kernels and by the
+// host-compiled unit test of the same functions (tests/test_cellmath_host.py builds
+// csrc/cellmath_host.cpp).  Everything here must keep the reference's expression trees:
+// compile with -fmad=false (nvcc) / -ffp-contract=off (g++).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define LITAP_HD __host__ __device__ __forceinline__
+#else
+#define LITAP_HD inline
+#endif
+
+// neighbour code n (1..9) -> row / col step; R/LITAP_functions.R:212-220, rows grow southward
+LITAP_HD int nb_dr(int n) { return n <= 3 ? 1 : (n <= 6 ? 0 : -1); }
+LITAP_HD int nb_dc(int n) { return (n - 1) % 3 - 1; }
+
+LITAP_HD bool is_nan(double x) { return x != x; }
+
+// ---------------------------------------------------------------------------------------------
+// finddir2 (R/LITAP_functions.R:257-273): D8 steepest descent with diagonals divided by sqrt(2),
+// exact ties resolved to the lowest direction code.  nb[n] = elevation of neighbour n (nb[5] unused).
+// Returns 0 (NA) for a NaN centre, 5 for a flat cell / pit.
+//
+// The IEEE division by sqrt(2) is only needed to order a diagonal against an orthogonal
+// neighbour (or two unequal diagonals) when they are within a few ulp; otherwise raw
+// differences decide.  The slow path below is the reference's loop verbatim.
+LITAP_HD int d8_slow(double e, const double* nb) {
+  const double sqrt2 = 1.4142135623730951;  // == sqrt(2.0) in binary64
+  double best = 0.0;
+  int d = 5;
+#pragma unroll
+  for (int n = 1; n <= 9; ++n) {
+    if (n == 5) continue;
+    double diff = e - nb[n];
+    if (n == 1 || n == 3 || n == 7 || n == 9) diff = diff / sqrt2;
+    if (diff > best) { best = diff; d = n; }  // NaN compares false: replace_na(.,0) never wins
+  }
+  return d;
+}
+
+LITAP_HD int d8_dir(double e, const double* nb) {
+  if (is_nan(e)) return 0;
+  // orthogonal candidates 2,4,6,8 and diagonal candidates 1,3,7,9, first maximum each
+  double mo = 0.0, md = 0.0, md2 = 0.0;  // md2: largest diagonal difference strictly below md
+  int io = 5, id = 5;
+  {
+    double d2 = e - nb[2], d4 = e - nb[4], d6 = e - nb[6], d8 = e - nb[8];
+    if (d2 > mo) { mo = d2; io = 2; }
+    if (d4 > mo) { mo = d4; io = 4; }
+    if (d6 > mo) { mo = d6; io = 6; }
+    if (d8 > mo) { mo = d8; io = 8; }
+    double d1 = e - nb[1], d3 = e - nb[3], d7 = e - nb[7], d9 = e - nb[9];
+    if (d1 > md) { md = d1; id = 1; }
+    if (d3 > md) { md2 = md; md = d3; id = 3; } else if (d3 > md2 && d3 < md) md2 = d3;
+    if (d7 > md) { md2 = md; md = d7; id = 7; } else if (d7 > md2 && d7 < md) md2 = d7;
+    if (d9 > md) { md2 = md; md = d9; id = 9; } else if (d9 > md2 && d9 < md) md2 = d9;
+  }
+  if (id == 5) return io;  // no descending diagonal (io == 5 -> flat)
+  const double tol = 4e-15;
+  bool ambiguous = (md2 > md * (1.0 - tol));  // two unequal diagonals within a few ulp
+  if (io != 5) {
+    double a = md * 0.70710678118654757;  // ~ md / sqrt(2), within 2 ulp
+    double gap = a - mo;
+    if (gap < 0) gap = -gap;
+    if (gap <= tol * mo) ambiguous = true;
+    else if (!ambiguous) return (a > mo) ? id : io;
+  }
+  if (!ambiguous) return id;
+  return d8_slow(e, nb);
+}
+
+// ---------------------------------------------------------------------------------------------
+// get_dir (R/LITAP_functions.R:576-617) with integer arithmetic.  The reference compares
+// a = atan(|h|/|v|)*180/pi against 22.5 and 67.5; tan(22.5 deg) = sqrt(2)-1 is irrational, so for
+// integer h, v:  a >= 67.5 <=> |v| <= (sqrt(2)-1)|h| <=> (|v|+|h|)^2 <= 2 h^2 ;
+//                a >= 22.5 <=> |h| >= (sqrt(2)-1)|v| <=> (|h|+|v|)^2 >= 2 v^2 (equalities unreachable).
+LITAP_HD int get_dir_int(long long row, long long col, long long row_f, long long col_f, unsigned opts) {
+  long long h = col_f - col, v = row_f - row;
+  if (h == 0 && v == 0) return 5;
+  unsigned long long ah = (unsigned long long)(h < 0 ? -h : h), av = (unsigned long long)(v < 0 ? -v : v);
+  unsigned long long s = ah + av;
+  bool ge675 = (av == 0) || (s * s <= 2 * ah * ah);
+  bool ge225 = (av == 0) || (s * s >= 2 * av * av);
+  int l;
+  if (h > 0 && v <= 0) l = ge675 ? 6 : (ge225 ? 9 : 8);
+  else if (h > 0 && v > 0) l = ge675 ? 6 : (ge225 ? 3 : 2);
+  else if (h <= 0 && v <= 0) l = ge675 ? 4 : (ge225 ? 7 : 8);
+  else l = ge675 ? 4 : (ge225 ? 1 : 2);
+  if (!((opts >> l) & 1u)) {
+    // closest[l], R/LITAP_functions.R:604-611, packed 7 nibbles per entry (first = lowest nibble)
+    const unsigned closest[10] = {0, 0x9683724u, 0x8976431u, 0x7481926u, 0x6392817u, 0,
+                                  0x4172839u, 0x3261948u, 0x2316497u, 0x1243768u};
+    unsigned cl = closest[l];
+    l = 0;
+    for (int k = 0; k < 7; ++k) {
+      int cand = (cl >> (4 * k)) & 15;
+      if ((opts >> cand) & 1u) { l = cand; break; }
+    }
+  }
+  return l;
+}
+
+// ---------------------------------------------------------------------------------------------
+// base R round(x, 3) for R >= 4.0.0 (src/nmath/fround.c): nearer of the two 3-decimal neighbours
+// evaluated in binary64, ties -> even.  NaN passes through.
+LITAP_HD double r_round3(double x) {
+  if (is_nan(x) || x == 0.0) return x;
+  double ax = x < 0 ? -x : x;
+  if (ax >= 1099511627776.0 /* 2^40: log10(2)*(0.5+logb(x)) + 3 > DBL_DIG */ || ax > 1.7976931348623157e308)
+    return x;
+  double x10 = 1000.0 * ax, i10 = floor(x10);
+  double xd = i10 / 1000.0, xu = ceil(x10) / 1000.0;
+  double du = xu - ax, dd = ax - xd;
+  bool even = (((long long)i10) & 1LL) == 0;
+  double r = (dd < du || (dd == du && even)) ? xd : xu;
+  return x < 0 ? -r : r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// calc_form for one cell (R/form_01_calc_form.R:9-47).  e[n] = elev_n (NOT yet *100), n = 1..9,
+// e[5] = centre.  sin_t / cos_t: tables of sin((A*pi)/180), cos((A*pi)/180) for integer A = 0..180,
+// filled by the host libm (the GPU build uses the same table, so both follow glibc exactly).
+// Outputs are the rounded values BEFORE edge replication and the final NA -> 0 step.
+struct FormOut { double slope_pct, slope_deg, aspect, prof, plan; };
+
+LITAP_HD double form_rad_deg(double x) { return (x * 180) / 3.14159265358979323846; }
+
+LITAP_HD double form_curv(int A, const double* z, double grid, double sp, const double* sin_t, const double* cos_t) {
+  double sn = sin_t[A], cs = cos_t[A];
+  double x1 = 2 + sn, y1 = 2 - cs, x2 = 2 - sn, y2 = 2 + cs;
+  double z1, z2;
+  if (A <= 90) {
+    z1 = (2 - y1) * ((z[9] * (x1 - 2)) + (z[8] * (3 - x1)));
+    z1 = z1 + ((y1 - 1) * ((z[6] * (x1 - 2)) + (z[5] * (3 - x1))));
+    z2 = (3 - y2) * ((z[5] * (x2 - 1)) + (z[4] * (2 - x2)));
+    z2 = z2 + ((y2 - 2) * ((z[2] * (x2 - 1)) + (z[1] * (2 - x2))));
+  } else {
+    z1 = (3 - y1) * ((z[6] * (x1 - 2)) + (z[5] * (3 - x1)));
+    z1 = z1 + ((y1 - 2) * ((z[3] * (x1 - 2)) + (z[2] * (3 - x1))));
+    z2 = (2 - y2) * ((z[8] * (x2 - 1)) + (z[7] * (2 - x2)));
+    z2 = z2 + ((y2 - 1) * ((z[5] * (x2 - 1)) + (z[4] * (2 - x2))));
+  }
+  if (sp <= 0) return 0;
+  return form_rad_deg(atan((((2 * z[5]) - z1 - z2) / (grid * grid))));
+}
+
+LITAP_HD FormOut form_cell(const double* e, double grid, const double* sin_t, const double* cos_t) {
+  const double NA = NAN;
+  FormOut o;
+  bool any_na = false;
+  double z[10];
+#pragma unroll
+  for (int n = 1; n <= 9; ++n) {
+    any_na |= is_nan(e[n]);
+    z[n] = e[n] * 100;
+  }
+  if (any_na) {
+    o.slope_pct = NA; o.slope_deg = NA; o.prof = NA; o.plan = NA;
+    o.aspect = is_nan(e[5]) ? NA : 360.0;
+    return o;
+  }
+  double sx = (z[6] - z[4]) / (2 * grid);
+  double sy = (z[2] - z[8]) / (2 * grid);
+  double sp = sqrt(sx * sx + sy * sy);
+  double sd = form_rad_deg(atan(sp / 100));
+  double as;
+  if (sp <= 0) as = 360;
+  else {
+    double la = form_rad_deg(acos(fabs(sx) / sp));
+    if (sx > 0 && sy > 0) as = 270 + la;
+    else if (sx > 0 && sy < 0) as = 270 - la;
+    else if (sx < 0 && sy > 0) as = 90 - la;
+    else if (sx < 0 && sy < 0) as = 90 + la;
+    else if (sx < 0) as = 90;
+    else if (sx > 0) as = 270;
+    else if (sy < 0) as = 180;
+    else as = 360;
+  }
+  as = nearbyint(as);  // round(aspect): ties to even
+  double pa = as > 180 ? as - 180 : as;
+  double pl = (pa + 90) > 180 ? pa + 90 - 180 : pa + 90;
+  o.prof = r_round3(form_curv((int)pa, z, grid, sp, sin_t, cos_t));
+  o.plan = r_round3(form_curv((int)pl, z, grid, sp, sin_t, cos_t));
+  o.slope_pct = r_round3(sp);
+  o.slope_deg = r_round3(sd);
+  o.aspect = as;
+  return o;
+}

@@ -1,0 +1,147 @@
+// form.cu — calc_form on the device (R/form_01_calc_form.R:4-67): slope %, slope deg, aspect,
+// profile and plan curvature as one fused 3x3 stencil, 48 B/cell (8 read + 5 x 8 written).
+//   k_form       : every cell from its own window, with the final NA -> 0 step (:60-65)
+//   k_form_edges : the four replicated lines (:54-57) recomputed from their source cells
+#include <cmath>
+#include "cellmath.h"
+#include "litap_internal.h"
+
+namespace {
+
+constexpr int FORM_ROWS = 16;
+constexpr int FORM_THREADS = 128;
+
+struct FormPtrs { double* o[5]; };
+struct Row3 { double l, m, r; };
+// replicated lines: out(r, c) takes the window of (mapr(r), mapc(c)); the maps differ from the
+// identity on at most two rows and two columns, simulated on the host in the reference's order.
+struct EdgeMap { int dst_c[2], src_c[2], dst_r[2], src_r[2]; };
+
+__device__ __forceinline__ Row3 load_row3(const double* __restrict__ elev, const GridDims& d, int r, int c, int lane) {
+  const double NA = __longlong_as_double(0x7ff8000000000000LL);
+  Row3 w;
+  const bool rv = (r >= 0 && r < d.NR);
+  const double* row = elev + (size_t)(rv ? r : 0) * d.pitch;
+  w.m = (rv && c < d.NC) ? __ldg(row + c) : NA;
+  w.l = __shfl_up_sync(0xffffffffu, w.m, 1);
+  w.r = __shfl_down_sync(0xffffffffu, w.m, 1);
+  if (lane == 0) w.l = (rv && c - 1 >= 0 && c - 1 < d.NC) ? __ldg(row + c - 1) : NA;
+  if (lane == 31) w.r = (rv && c + 1 < d.NC) ? __ldg(row + c + 1) : NA;
+  return w;
+}
+
+__device__ __forceinline__ void store_final(const FormPtrs& P, size_t i, const FormOut& o, bool elev_ok) {
+  // NA -> 0 where the cell itself has an elevation; aspect keeps its value (:60-65)
+  P.o[0][i] = (elev_ok && is_nan(o.slope_pct)) ? 0.0 : o.slope_pct;
+  P.o[1][i] = (elev_ok && is_nan(o.slope_deg)) ? 0.0 : o.slope_deg;
+  P.o[2][i] = o.aspect;
+  P.o[3][i] = (elev_ok && is_nan(o.prof)) ? 0.0 : o.prof;
+  P.o[4][i] = (elev_ok && is_nan(o.plan)) ? 0.0 : o.plan;
+}
+
+__global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict__ elev, GridDims d, double grid,
+                                                       const double* __restrict__ trig, FormPtrs P) {
+  __shared__ double s_sin[181], s_cos[181];
+  for (int i = threadIdx.x; i < 181; i += FORM_THREADS) { s_sin[i] = trig[i]; s_cos[i] = trig[181 + i]; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int c = blockIdx.x * FORM_THREADS + threadIdx.x + 1;
+  const int r0 = blockIdx.y * FORM_ROWS;
+  Row3 p = load_row3(elev, d, r0 - 1, c, lane);
+  Row3 q = load_row3(elev, d, r0, c, lane);
+  const int rend = min(r0 + FORM_ROWS, d.NR);
+  for (int r = r0; r < rend; ++r) {
+    Row3 n = load_row3(elev, d, r + 1, c, lane);
+    double e[10];
+    e[7] = p.l; e[8] = p.m; e[9] = p.r;
+    e[4] = q.l; e[5] = q.m; e[6] = q.r;
+    e[1] = n.l; e[2] = n.m; e[3] = n.r;
+    if (c < d.NC) {
+      FormOut o = form_cell(e, grid, s_sin, s_cos);
+      size_t i = (size_t)r * d.pitch + c;
+      store_final(P, i, o, !is_nan(q.m));
+      if (c == 1) {  // ring column 0: NA everywhere
+        const double NA = __longlong_as_double(0x7ff8000000000000LL);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) P.o[k][i - 1] = NA;
+      }
+    }
+    p = q;
+    q = n;
+  }
+}
+
+__device__ __forceinline__ int map1(int x, const int* dst, const int* src) {
+  // the second assignment reads the state left by the first (R executes them in sequence)
+  if (x == dst[1]) { int s = src[1]; return s == dst[0] ? src[0] : s; }
+  if (x == dst[0]) return src[0];
+  return x;
+}
+
+__global__ void k_form_edges(const double* __restrict__ elev, GridDims d, double grid,
+                             const double* __restrict__ trig, FormPtrs P, EdgeMap em) {
+  // line 0,1: destination columns (all rows); line 2,3: destination rows (all columns)
+  const int line = blockIdx.y;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  int r, c;
+  if (line < 2) { c = em.dst_c[line]; r = t; if (c < 0 || r >= d.NR) return; }
+  else { r = em.dst_r[line - 2]; c = t; if (r < 0 || c >= d.NC) return; }
+  const int sr = map1(r, em.dst_r, em.src_r), sc = map1(c, em.dst_c, em.src_c);
+  const double NA = __longlong_as_double(0x7ff8000000000000LL);
+  double e[10];
+#pragma unroll
+  for (int n = 1; n <= 9; ++n) {
+    int rr = sr + nb_dr(n), cc = sc + nb_dc(n);
+    e[n] = (rr < 0 || rr >= d.NR || cc < 0 || cc >= d.NC) ? NA : elev[(size_t)rr * d.pitch + cc];
+  }
+  FormOut o = form_cell(e, grid, trig, trig + 181);
+  const size_t i = (size_t)r * d.pitch + c;
+  store_final(P, i, o, !is_nan(elev[i]));
+}
+
+double* g_trig = nullptr;  // sin((A*pi)/180), cos((A*pi)/180), A = 0..180, from the host libm
+}  // namespace
+
+int run_form(litap_grid* g, double grid_m) {
+  Ctx& c = ctx();
+  const GridDims d = g->d;
+  cudaStream_t st = c.stream;
+  if (!g_trig) {
+    double h[362];
+    for (int A = 0; A <= 180; ++A) {
+      double t = ((double)A * M_PI) / 180;  // deg_rad(), R/form_01_calc_form.R:115
+      h[A] = std::sin(t);
+      h[181 + A] = std::cos(t);
+    }
+    g_trig = (double*)pool_alloc(sizeof(h));
+    if (!g_trig) return set_error(LITAP_ENOMEM, "device allocation failed (trig table)");
+    CUDA_TRY(cudaMemcpyAsync(g_trig, h, sizeof(h), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+  }
+  FormPtrs P;
+  for (int k = 0; k < 5; ++k) {
+    if (!g->form[k]) g->form[k] = grid_alloc_array<double>(d, -1);
+    if (!g->form[k]) return set_error(LITAP_ENOMEM, "device allocation failed (form outputs)");
+    P.o[k] = g->form[k];
+  }
+  {
+    dim3 grid((d.NC - 1 + FORM_THREADS - 1) / FORM_THREADS, (d.NR + FORM_ROWS - 1) / FORM_ROWS);
+    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, grid_m, g_trig, P));
+  }
+  // R/form_01_calc_form.R:54-57 in buffered 0-based coordinates, in this order:
+  //   col 1 <- col 2 ; col NC-2 <- col NC-3 ; row 1 <- row 2 ; row NR-2 <- row NR-3
+  EdgeMap em;
+  em.dst_c[0] = 1; em.src_c[0] = 2 < d.NC ? 2 : -1;
+  em.dst_c[1] = d.NC - 2; em.src_c[1] = d.NC - 3;
+  em.dst_r[0] = 1; em.src_r[0] = 2 < d.NR ? 2 : -1;
+  em.dst_r[1] = d.NR - 2; em.src_r[1] = d.NR - 3;
+  {
+    int m = d.NR > d.NC ? d.NR : d.NC;
+    dim3 grid((m + 127) / 128, 4);
+    KERNEL("k_form_edges", k_form_edges<<<grid, 128, 0, st>>>(g->elev, d, grid_m, g_trig, P, em));
+  }
+  return LITAP_OK;
+}
+
+// called by litap_shutdown through pool_release_all(): the table is pool-owned
+void form_forget_trig() { g_trig = nullptr; }

@@ -1,0 +1,124 @@
+// litap_internal.h — shared declarations of liblitap_cuda.so (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include "../../include/litap.h"
+
+// ---- HBM layout -------------------------------------------------------------------------------
+// Every per-cell array of a grid uses one pitched layout: buffered cell (r, c), 0 <= r < NR,
+// 0 <= c < NC, lives at element r*pitch + c of a pointer that is XOFF elements past a
+// 256-byte-aligned allocation; pitch is a multiple of 32 elements.  So the first interior
+// column (c = 1) of every row is 32-element aligned for every dtype (32 B for u8, 128 B for
+// u32, 256 B for f64): warp-wide row accesses are sector-aligned and rows are TMA-legal.
+// A "cell id" on the device is that pitched linear index (uint32, < 2^31).
+constexpr int LITAP_XOFF = 31;
+
+struct GridDims {
+  int NR, NC;      // buffered rows / cols
+  int pitch;       // elements per row (multiple of 32)
+  int64_t cells;   // NR * pitch (allocation is cells + 64 elements)
+};
+
+inline GridDims make_dims(int64_t NR, int64_t NC) {
+  GridDims d;
+  d.NR = (int)NR;
+  d.NC = (int)NC;
+  d.pitch = (int)(((NC + LITAP_XOFF + 31) / 32) * 32);
+  d.cells = (int64_t)d.NR * d.pitch;
+  return d;
+}
+
+// ---- shed / upslope tiling --------------------------------------------------------------------
+constexpr int TW = 64, TH = 64;            // interior cells per tile
+constexpr int LW = TW + 2, LH = TH + 2;    // local grid incl. the 1-cell ring
+constexpr int LC = LW * LH;                // 4356 local cells
+constexpr int BSLOTS = 256;                // border slots per tile (252 used)
+constexpr uint32_t ID_NA = 0xFFFFFFFFu;    // "no shed" (NA drec chain / cycle)
+constexpr uint32_t ID_ROOT = 0x80000000u;  // flag: low 31 bits are a pit id (pid)
+
+struct litap_grid {
+  GridDims d;
+  // per-cell arrays (pitched, pointers already offset by XOFF); nullptr until first needed
+  double* elev = nullptr;
+  uint8_t* ddir = nullptr;
+  uint8_t* flat = nullptr;
+  int32_t* shed = nullptr;
+  uint32_t* upslope = nullptr;
+  uint8_t* ridge = nullptr;
+  double* form[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double* weti[4] = {nullptr, nullptr, nullptr, nullptr};
+  int64_t npits = 0;
+  bool have_ddir = false, have_shed = false;
+};
+
+// ---- context ----------------------------------------------------------------------------------
+struct Ctx {
+  bool ready = false;
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};
+  litap_timings tm = {};
+  int64_t launches = 0;
+};
+Ctx& ctx();
+int set_error(int code, const std::string& msg);
+int ensure_init();
+
+// pooled device allocations (freed by litap_shutdown); zero = cudaMemsetAsync to 0
+void* pool_alloc(size_t bytes);
+void pool_free(void* p);
+void pool_release_all();
+
+template <typename T>
+inline T* grid_alloc_array(const GridDims& d, int fill_byte) {
+  size_t n = (size_t)d.cells + 64;
+  T* base = (T*)pool_alloc(n * sizeof(T));
+  if (!base) return nullptr;
+  if (fill_byte >= 0) cudaMemsetAsync(base, fill_byte, n * sizeof(T), ctx().stream);
+  return base + LITAP_XOFF;
+}
+template <typename T>
+inline void grid_free_array(T*& p) {
+  if (p) pool_free((void*)(p - LITAP_XOFF));
+  p = nullptr;
+}
+
+#define CUDA_TRY(expr)                                                                      \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess)                                                                  \
+      return set_error(LITAP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));    \
+  } while (0)
+#define LAUNCH_CHECK()                                                                      \
+  do {                                                                                      \
+    ctx().launches++;                                                                       \
+    cudaError_t _e = cudaGetLastError();                                                    \
+    if (_e != cudaSuccess)                                                                  \
+      return set_error(LITAP_ECUDA, std::string("kernel launch: ") + cudaGetErrorString(_e) + \
+                                        " at " + __FILE__ + ":" + std::to_string(__LINE__)); \
+  } while (0)
+
+// Optional per-kernel timing (litap_profile_enable): CUDA events around every launch, summed
+// per kernel name.  Off by default; the bench turns it on for a separate, untimed pass.
+struct ProfScope {
+  int idx;
+  explicit ProfScope(const char* name);
+  ~ProfScope();
+};
+#define KERNEL(name, ...)   \
+  do {                      \
+    ProfScope _prof(name);  \
+    __VA_ARGS__;            \
+    LAUNCH_CHECK();         \
+  } while (0)
+
+// ---- stage drivers (each enqueues on ctx().stream; host syncs only where stated) --------------
+int run_ddir(litap_grid* g, int invert);               // ddir.cu
+int run_shed(litap_grid* g);                           // shed.cu
+int run_form(litap_grid* g, double grid_m);            // form.cu
+void form_forget_trig();                               // form.cu (pool-owned table dropped at shutdown)
+int run_weti(litap_grid* g, double grid_m);            // weti.cu
+int run_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille);  // synth.cu
+int run_checksum(const void* arr, int elem_size, const GridDims& d, uint64_t* out);                     // synth.cu

@@ -1,0 +1,518 @@
+// shed.cu — calc_shed4 + calc_upslopes("upslope") on the device (R/flow_02_calc_shed.R:10-145).
+//
+//   k_count_pits    pits = cells with ddir == 5                                   (:12-20)
+//   k_shed_local    per tile: local terminals (pointer jumping), per-terminal max-elevation key,
+//                   local flow counts; writes the level-2 edges of the 252 border cells
+//   k_l2_*          level-2 graph over border slots: resolve every border cell to its pit
+//                   (pointer jumping with path compression), accumulate external inflow
+//                   (in-degree + chase with atomics), merge the per-shed keys               (:25-29)
+//   cub radix sort  rank pits by (max elev desc, seqno of that cell asc)                  (:32-38)
+//   k_shed_final    per tile: final shed label, upslope count (local accumulation seeded with
+//                   the external inflow) and ridge flag                                 (:42-57)
+//
+// Algorithmic traffic: ddir is read twice (1 B), elev once (8 B), shed + upslope + ridge written
+// once (9 B) => 19 B/cell; the level-2 arrays are ~1.9 B/cell and stay in L2.
+#include <algorithm>
+#include <vector>
+#include <cub/cub.cuh>
+#include "shed_tile.cuh"
+
+namespace shed {
+
+__device__ __forceinline__ unsigned long long f64_orderable(double x) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(x);
+  return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+
+struct L2 {                    // level-2 arrays, one entry per border slot
+  uint32_t* jump0;             // original edge: entry cell id | ID_ROOT|pid | ID_NA
+  uint32_t* jres;              // resolved (compressed) pointer
+  unsigned long long* pkmax;   // exit cells: max orderable elevation draining through it inside its tile (0 = none)
+  uint32_t* pkidx;             //             lowest cell id attaining pkmax
+  uint32_t* ext;               // external inflow into the border cell (starts as base, accumulated in place)
+  uint32_t* indeg;
+  uint8_t* src;
+};
+struct Pits {                  // one entry per pit id
+  unsigned long long* rootmax; // max orderable elevation of the shed
+  unsigned long long* pitkmax; // the pit tile's own partial
+  uint32_t* pitkidx;
+  uint32_t* rootidx;
+  uint32_t* rank;              // final initial_shed number
+};
+
+__global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsigned long long* count) {
+  unsigned n = 0;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  if (c < d.NC)
+    for (int r = 1 + blockIdx.y; r < d.NR; r += gridDim.y) n += ddir[(size_t)r * d.pitch + c] == 5;
+  for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if ((threadIdx.x & 31) == 0 && n) atomicAdd(count, (unsigned long long)n);
+}
+
+// ------------------------------------------------------------------------------------------------
+constexpr size_t SMEM_A = LC * (1 + 2 + 8 + 4) + 64;
+
+__global__ void __launch_bounds__(NT) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
+                                                   const double* __restrict__ elev, uint32_t* __restrict__ lab,
+                                                   L2 l2, Pits pits, unsigned long long* pit_cursor) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned long long* s_key = reinterpret_cast<unsigned long long*>(smem);       // LC x 8
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);           // LC x 4
+  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 12);          // LC x 2
+  uint8_t* s_dir = smem + (size_t)LC * 14;                                        // LC x 1
+  unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                             // aliases s_key (phase 4)
+  uint8_t* s_deg = smem + (size_t)LC * 4;                                          // aliases s_key (phase 4)
+  __shared__ unsigned s_npit;
+  __shared__ unsigned long long s_pitbase;
+
+  const TileCtx t = tile_ctx();
+  if (threadIdx.x == 0) s_npit = 0;
+  tile_load_dir(g, t, ddir, s_dir);
+  for (int li = threadIdx.x; li < LC; li += NT) { s_key[li] = 0ull; s_idx[li] = 0xFFFFFFFFu; }
+  __syncthreads();
+  tile_pointer_jump(s_dir, s_ptr);
+  __syncthreads();
+
+  // ---- per-terminal key: max elevation, then lowest cell id attaining it
+  int term[CPT];
+  unsigned long long key[CPT];
+  uint32_t cid[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    int ly = i / LW, lx = i - ly * LW;
+    int r = t.r_base + ly, c = t.c_base + lx;
+    term[k] = -1;
+    key[k] = 0;
+    cid[k] = (uint32_t)((size_t)r * g.d.pitch + c);
+    if (in_grid(g, r, c) && s_dir[i] != 0) {
+      int tt = s_ptr[i];
+      if (term_kind(s_dir, s_ptr, tt) != T_NA) {
+        term[k] = tt;
+        key[k] = f64_orderable(elev[cid[k]]);
+        atomicMax(&s_key[tt], key[k]);
+      }
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k)
+    if (term[k] >= 0 && key[k] == s_key[term[k]]) atomicMin(&s_idx[term[k]], cid[k]);
+  __syncthreads();
+
+  // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
+  unsigned rk[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    rk[k] = 0xFFFFFFFFu;
+    if (s_dir[i] == 5) rk[k] = atomicAdd(&s_npit, 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_npit) s_pitbase = atomicAdd(pit_cursor, (unsigned long long)s_npit);
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    if (rk[k] == 0xFFFFFFFFu) continue;
+    int i = owned_local(threadIdx.x, k);
+    uint32_t pid = (uint32_t)(s_pitbase + rk[k]);
+    pits.rootmax[pid] = s_key[i];
+    pits.pitkmax[pid] = s_key[i];
+    pits.pitkidx[pid] = s_idx[i];
+    pits.rootidx[pid] = 0xFFFFFFFFu;
+    lab[cid[k]] = pid;  // read back by k_shed_final of this tile
+    s_idx[i] = pid;     // from here on s_idx[pit] is its pid
+  }
+  __syncthreads();
+
+  // ---- level-2 edges and key partials of the border cells
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    int ly = i / LW, lx = i - ly * LW;
+    int bs = border_slot_local(lx, ly);
+    if (bs < 0) continue;
+    size_t s = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS + bs;
+    uint32_t edge = ID_NA;
+    unsigned long long pk = 0;
+    uint32_t pi = 0xFFFFFFFFu;
+    if (term[k] >= 0) {
+      int tt = term[k];
+      int kind = term_kind(s_dir, s_ptr, tt);
+      if (kind == T_PIT) edge = ID_ROOT | s_idx[tt];
+      else {  // exit: continue at the entry cell of the neighbouring tile
+        int e = tt + loc_off(s_dir[tt]);
+        int er = t.r_base + e / LW, ec = t.c_base + e % LW;
+        edge = (uint32_t)((size_t)er * g.d.pitch + ec);
+        if (tt == i) { pk = s_key[i]; pi = s_idx[i]; }  // this border cell is the exit itself
+      }
+    }
+    l2.jump0[s] = edge;
+    l2.jres[s] = edge;
+    l2.pkmax[s] = pk;
+    l2.pkidx[s] = pi;
+  }
+  __syncthreads();  // s_key / s_idx are dead from here: reuse as s_cnt / s_deg
+
+  // ---- local flow counts; exits hand theirs to the entry cell's slot (base of the level-2 sum)
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    int ly = i / LW, lx = i - ly * LW;
+    s_cnt[i] = (in_grid(g, t.r_base + ly, t.c_base + lx) && s_dir[i] != 0) ? 1u : 0u;
+  }
+  __syncthreads();  // s_cnt aliases s_key, s_deg aliases s_key too but at a disjoint offset
+  unsigned srcmask = tile_in_degree(s_dir, s_deg);
+  __syncthreads();
+  tile_chase(s_dir, s_cnt, s_deg, srcmask);
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    if (term[k] != i) continue;  // not a (valid) terminal
+    int dv = s_dir[i];
+    if (dv == 5) continue;
+    int e = i + loc_off(dv);  // exit (term_kind checked above): entry cell on the local ring
+    long long es = slot_of_rc(t.r_base + e / LW, t.c_base + e % LW, g.tilesX);
+    if (es >= 0) atomicAdd(&l2.ext[es], s_cnt[i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool is_cell(uint32_t v) { return !(v & ID_ROOT); }  // ID_NA has the flag bit too
+
+__global__ void k_l2_resolve(TileGeom g, uint32_t* __restrict__ jres, size_t nslots, unsigned* unresolved) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool open = false;
+  if (s < nslots) {
+    uint32_t v = jres[s];
+    if (is_cell(v)) {
+      for (int hop = 0; hop < 8 && is_cell(v); ++hop) {
+        long long s2 = slot_of_id(v, g);
+        v = s2 < 0 ? ID_NA : jres[s2];
+      }
+      jres[s] = v;
+      open = is_cell(v);
+    }
+  }
+  if (__syncthreads_or(open) && threadIdx.x == 0) atomicAdd(unresolved, 1u);
+}
+__global__ void k_l2_close_cycles(uint32_t* __restrict__ jres, size_t nslots) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots && is_cell(jres[s])) jres[s] = ID_NA;
+}
+__global__ void k_l2_indeg(TileGeom g, const uint32_t* __restrict__ jump0, size_t nslots, uint32_t* __restrict__ indeg) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  uint32_t v = jump0[s];
+  if (!is_cell(v)) return;
+  long long s2 = slot_of_id(v, g);
+  if (s2 >= 0) atomicAdd(&indeg[s2], 1u);
+}
+__global__ void k_l2_src(const uint32_t* __restrict__ indeg, size_t nslots, uint8_t* __restrict__ src) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots) src[s] = indeg[s] == 0;
+}
+__global__ void k_l2_chase(TileGeom g, const uint32_t* __restrict__ jump0, const uint8_t* __restrict__ src,
+                           size_t nslots, uint32_t* ext, uint32_t* indeg) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || !src[s]) return;
+  uint32_t carry = *reinterpret_cast<volatile uint32_t*>(&ext[s]);
+  while (true) {
+    uint32_t v = jump0[s];
+    if (!is_cell(v)) break;
+    long long t = slot_of_id(v, g);
+    if (t < 0) break;
+    if (carry) atomicAdd(&ext[t], carry);
+    __threadfence();
+    if (atomicSub(&indeg[t], 1u) != 1u) break;
+    __threadfence();
+    carry = atomicAdd(&ext[t], 0u);
+    s = (size_t)t;
+  }
+}
+// shed keys: exits' partials merged into their root; then the index among the maxima
+__global__ void k_keys_max(const L2 l2, size_t nslots, Pits pits) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  unsigned long long pk = l2.pkmax[s];
+  uint32_t root = l2.jres[s];
+  if (pk && root != ID_NA && (root & ID_ROOT)) atomicMax(&pits.rootmax[root & ~ID_ROOT], pk);
+}
+__global__ void k_keys_idx(const L2 l2, size_t nslots, Pits pits, unsigned npits) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots) {
+    unsigned long long pk = l2.pkmax[s];
+    uint32_t root = l2.jres[s];
+    if (pk && root != ID_NA && (root & ID_ROOT)) {
+      uint32_t pid = root & ~ID_ROOT;
+      if (pk == pits.rootmax[pid]) atomicMin(&pits.rootidx[pid], l2.pkidx[s]);
+    }
+  }
+  if (s < npits && pits.pitkmax[s] == pits.rootmax[s]) atomicMin(&pits.rootidx[s], pits.pitkidx[s]);
+}
+__global__ void k_iota(uint32_t* a, unsigned n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = i;
+}
+__global__ void k_gather_u64(const unsigned long long* __restrict__ src, const uint32_t* __restrict__ idx,
+                             unsigned long long* __restrict__ dst, unsigned n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[idx[i]];
+}
+__global__ void k_scatter_rank(const uint32_t* __restrict__ order, uint32_t* __restrict__ rank, unsigned n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rank[order[i]] = i + 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+constexpr size_t SMEM_B = LC * (4 + 4 + 2 + 1 + 1) + 64;
+
+__global__ void __launch_bounds__(NT) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
+                                                   const uint32_t* __restrict__ rank, int32_t* shed_out,
+                                                   uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                      // LC x 4
+  uint32_t* s_lab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);     // LC x 4
+  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 8);     // LC x 2
+  uint8_t* s_dir = smem + (size_t)LC * 10;                                  // LC x 1
+  uint8_t* s_deg = smem + (size_t)LC * 11;                                  // LC x 1 (4-aligned: LC % 4 == 0)
+  const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
+
+  const TileCtx t = tile_ctx();
+  tile_load_dir(g, t, ddir, s_dir);
+  __syncthreads();
+  tile_pointer_jump(s_dir, s_ptr);
+  __syncthreads();
+
+  // ---- labels of the terminals (interior) and of the ring cells (for the ridge test)
+  for (int li = threadIdx.x; li < LC; li += NT) {
+    int ly = li / LW, lx = li - ly * LW;
+    int r = t.r_base + ly, c = t.c_base + lx;
+    uint32_t lb = 0;
+    if (r >= 1 && c >= 1 && in_grid(g, r, c)) {
+      if (loc_is_ring(li)) {
+        long long s = slot_of_rc(r, c, g.tilesX);
+        uint32_t v = s >= 0 ? l2.jres[s] : ID_NA;
+        if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
+      } else if (s_ptr[li] == li) {
+        int kind = term_kind(s_dir, s_ptr, li);
+        if (kind == T_PIT) lb = rank[lab_in[(size_t)r * g.d.pitch + c]];
+        else if (kind == T_EXIT) {
+          uint32_t v = l2.jres[(size_t)(t.ty * g.tilesX + t.tx) * BSLOTS + border_slot_local(lx, ly)];
+          if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
+        }
+      }
+    }
+    s_lab[li] = lb;  // non-terminal interior cells: overwritten below
+  }
+  __syncthreads();
+  uint32_t mylab[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    int tt = s_ptr[i];
+    mylab[k] = (s_dir[i] != 0 && term_kind(s_dir, s_ptr, tt) != T_NA) ? s_lab[tt] : 0u;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) s_lab[owned_local(threadIdx.x, k)] = mylab[k];
+
+  // ---- upslope: local accumulation seeded with the external inflow of the border cells
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    int ly = i / LW, lx = i - ly * LW;
+    unsigned w = 0;
+    if (in_grid(g, t.r_base + ly, t.c_base + lx) && s_dir[i] != 0) {
+      w = 1;
+      int bs = border_slot_local(lx, ly);
+      if (bs >= 0) w += l2.ext[(size_t)(t.ty * g.tilesX + t.tx) * BSLOTS + bs];
+    }
+    s_cnt[i] = w;
+  }
+  unsigned srcmask = tile_in_degree(s_dir, s_deg);
+  __syncthreads();
+  tile_chase(s_dir, s_cnt, s_deg, srcmask);
+  __syncthreads();
+
+  // ---- outputs
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(threadIdx.x, k);
+    int ly = i / LW, lx = i - ly * LW;
+    int r = t.r_base + ly, c = t.c_base + lx;
+    if (!in_grid(g, r, c)) continue;
+    size_t o = (size_t)r * g.d.pitch + c;
+    uint32_t lb = mylab[k];
+    uint8_t rg = 2;  // NA on the ring
+    if (r < g.d.NR - 1 && c < g.d.NC - 1) {
+      uint32_t first = 0;
+      bool multi = false;
+#pragma unroll
+      for (int n = 1; n <= 9; ++n) {
+        uint32_t s = s_lab[i + loc_off(n)];
+        if (!s) continue;
+        if (!first) first = s;
+        else if (s != first) multi = true;
+      }
+      rg = multi;
+    }
+    shed_out[o] = (int32_t)lb;
+    upslope[o] = lb ? s_cnt[i] : 0u;
+    ridge[o] = rg;
+  }
+}
+
+// ring row 0 / column 0 (never inside a tile) and, for uniformity, the other two ring lines
+__global__ void k_ring_fill(GridDims d, int32_t* __restrict__ shed_out, uint32_t* __restrict__ upslope,
+                            uint8_t* __restrict__ ridge) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  int line = blockIdx.y;
+  int r, c;
+  if (line == 0) { r = 0; c = t; }
+  else if (line == 1) { r = d.NR - 1; c = t; }
+  else if (line == 2) { r = t; c = 0; }
+  else { r = t; c = d.NC - 1; }
+  if (r >= d.NR || c >= d.NC) return;
+  size_t o = (size_t)r * d.pitch + c;
+  shed_out[o] = 0;
+  upslope[o] = 0;
+  ridge[o] = 2;
+}
+
+}  // namespace shed
+
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct Scratch {
+  std::vector<void*> ptrs;
+  ~Scratch() { for (void* p : ptrs) pool_free(p); }
+  template <typename T> T* get(size_t n) {
+    T* p = (T*)pool_alloc(n * sizeof(T));
+    if (p) ptrs.push_back(p);
+    return p;
+  }
+};
+}  // namespace
+
+int run_shed(litap_grid* g) {
+  using namespace shed;
+  Ctx& c = ctx();
+  const GridDims d = g->d;
+  cudaStream_t st = c.stream;
+  if (!g->shed) g->shed = grid_alloc_array<int32_t>(d, -1);
+  if (!g->upslope) g->upslope = grid_alloc_array<uint32_t>(d, -1);
+  if (!g->ridge) g->ridge = grid_alloc_array<uint8_t>(d, -1);
+  if (!g->shed || !g->upslope || !g->ridge) return set_error(LITAP_ENOMEM, "device allocation failed (shed outputs)");
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(k_shed_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_A));
+    CUDA_TRY(cudaFuncSetAttribute(k_shed_final, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_B));
+    attr_set = true;
+  }
+  TileGeom tg;
+  tg.d = d;
+  tg.tilesX = (d.NC - 1 + TW - 1) / TW;
+  tg.tilesY = (d.NR - 1 + TH - 1) / TH;
+  const size_t nslots = (size_t)tg.tilesX * tg.tilesY * BSLOTS;
+
+  Scratch S;
+  unsigned long long* counters = S.get<unsigned long long>(4);  // [0] npits, [1] pit cursor, [2] flags (2 x u32)
+  if (!counters) return set_error(LITAP_ENOMEM, "device allocation failed (shed scratch)");
+  CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), st));
+  {
+    dim3 grid((d.NC - 1 + 255) / 256, d.NR - 1 < 256 ? d.NR - 1 : 256);
+    KERNEL("k_count_pits", k_count_pits<<<grid, 256, 0, st>>>(g->ddir, d, counters));
+  }
+  unsigned long long npits64 = 0;
+  CUDA_TRY(cudaMemcpyAsync(&npits64, counters, 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  const unsigned npits = (unsigned)npits64;
+  g->npits = (int64_t)npits64;
+  c.tm.npits = g->npits;
+  const size_t np = npits ? npits : 1;
+
+  L2 l2;
+  l2.jump0 = S.get<uint32_t>(nslots);
+  l2.jres = S.get<uint32_t>(nslots);
+  l2.pkmax = S.get<unsigned long long>(nslots);
+  l2.pkidx = S.get<uint32_t>(nslots);
+  l2.ext = S.get<uint32_t>(nslots);
+  l2.indeg = S.get<uint32_t>(nslots);
+  l2.src = S.get<uint8_t>(nslots);
+  Pits pits;
+  pits.rootmax = S.get<unsigned long long>(np);
+  pits.pitkmax = S.get<unsigned long long>(np);
+  pits.pitkidx = S.get<uint32_t>(np);
+  pits.rootidx = S.get<uint32_t>(np);
+  pits.rank = S.get<uint32_t>(np);
+  uint32_t* ord_a = S.get<uint32_t>(np);
+  uint32_t* ord_b = S.get<uint32_t>(np);
+  uint32_t* key32_b = S.get<uint32_t>(np);
+  unsigned long long* key64_a = S.get<unsigned long long>(np);
+  unsigned long long* key64_b = S.get<unsigned long long>(np);
+  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.ext || !l2.indeg || !l2.src || !pits.rootmax ||
+      !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !ord_a || !ord_b || !key32_b || !key64_a || !key64_b)
+    return set_error(LITAP_ENOMEM, "device allocation failed (shed level-2 arrays)");
+  CUDA_TRY(cudaMemsetAsync(l2.ext, 0, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.indeg, 0, nslots * 4, st));
+  // slots 252..255 of every tile are never written by k_shed_local: keep them NA / empty
+  CUDA_TRY(cudaMemsetAsync(l2.jump0, 0xFF, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.jres, 0xFF, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
+
+  dim3 tgrid(tg.tilesX, tg.tilesY);
+  KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, SMEM_A, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), l2, pits,
+                                         counters + 1));
+
+  const unsigned sblk = (unsigned)((nslots + 255) / 256);
+  // ---- resolve border cells to pits; a drec cycle across tiles never resolves -> NA after the cap
+  unsigned* flag = reinterpret_cast<unsigned*>(counters + 2);
+  bool open = true;
+  for (int round = 0; round < 64 && open; ++round) {
+    CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+    KERNEL("k_l2_resolve", k_l2_resolve<<<sblk, 256, 0, st>>>(tg, l2.jres, nslots, flag));
+    unsigned h = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    open = h != 0;
+  }
+  if (open) {
+    KERNEL("k_l2_close_cycles", k_l2_close_cycles<<<sblk, 256, 0, st>>>(l2.jres, nslots));
+  }
+  // ---- external inflow of every border cell
+  KERNEL("k_l2_indeg", k_l2_indeg<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.indeg));
+  KERNEL("k_l2_src", k_l2_src<<<sblk, 256, 0, st>>>(l2.indeg, nslots, l2.src));
+  KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, l2.src, nslots, l2.ext, l2.indeg));
+  // ---- canonical numbering
+  if (npits) {
+    const unsigned kblk = (unsigned)((std::max(nslots, (size_t)npits) + 255) / 256);
+    KERNEL("k_keys_max", k_keys_max<<<sblk, 256, 0, st>>>(l2, nslots, pits));
+    KERNEL("k_keys_idx", k_keys_idx<<<kblk, 256, 0, st>>>(l2, nslots, pits, npits));
+    const unsigned pblk = (npits + 255) / 256;
+    KERNEL("k_iota", k_iota<<<pblk, 256, 0, st>>>(ord_a, npits));
+    size_t tmp1 = 0, tmp2 = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp1, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st);
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp2, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st);
+    size_t tmpn = tmp1 > tmp2 ? tmp1 : tmp2;
+    void* tmp = S.get<unsigned char>(tmpn ? tmpn : 256);
+    if (!tmp) return set_error(LITAP_ENOMEM, "device allocation failed (sort scratch)");
+    // stable LSD: first by the tie-break (cell id asc), then by max elevation desc
+    CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmpn, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st));
+    KERNEL("k_gather_u64", k_gather_u64<<<pblk, 256, 0, st>>>(pits.rootmax, ord_b, key64_a, npits));
+    CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tmpn, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st));
+    KERNEL("k_scatter_rank", k_scatter_rank<<<pblk, 256, 0, st>>>(ord_a, pits.rank, npits));
+    c.launches += 4;  // cub passes (at least)
+  }
+  {
+    int m = d.NR > d.NC ? d.NR : d.NC;
+    dim3 grid((m + 255) / 256, 4);
+    KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge));
+  }
+  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, SMEM_B, st>>>(tg, g->ddir, l2, pits.rank, g->shed, g->upslope, g->ridge));
+  CUDA_TRY(cudaStreamSynchronize(st));  // scratch is returned to the pool when S dies
+  return LITAP_OK;
+}

@@ -1,0 +1,98 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol litap.h
+declares, fails loudly without a device, and the per-cell arithmetic the kernels use (cellmath.h,
+compiled for the host) agrees with the oracle."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from conftest import ROOT
+
+
+def test_library_exports_every_declared_symbol():
+    import litap_b200 as lb
+    L = lb.load()
+    hdr = open(os.path.join(ROOT, "include", "litap.h")).read()
+    declared = set(re.findall(r"\b(litap_[a-z0-9_]+)\s*\(", hdr))
+    assert declared and declared == set(lb._lib.SYMBOLS)
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import litap_b200 as lb
+    with pytest.raises(lb.LitapError, match="no CUDA device"):
+        lb.calc_ddir2(lb.add_buffer(np.ones((5, 5))))
+    with pytest.raises(lb.LitapError):
+        lb.DeviceGrid(10, 10)
+
+
+def test_product_does_not_reference_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "litap_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".c", ".R")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "liblitap_oracle" not in txt and "oracle_" not in txt, f
+
+
+@pytest.fixture(scope="module")
+def cellmath():
+    so = "/tmp/libcellmath_host_%d.so" % os.getpid()
+    src = os.path.join(ROOT, "litap_b200", "csrc", "cellmath_host.cpp")
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-shared", "-o", so, src])
+    L = C.CDLL(so)
+    f64 = np.ctypeslib.ndpointer(np.float64, flags="C")
+    u8 = np.ctypeslib.ndpointer(np.uint8, flags="C")
+    L.host_d8.argtypes = [f64, C.c_longlong, C.c_longlong, u8, C.c_int]
+    L.host_form_raw.argtypes = [f64, C.c_longlong, C.c_longlong, C.c_double, f64]
+    L.host_get_dir.argtypes = [C.c_longlong] * 4 + [C.c_uint]
+    L.host_r_round3.argtypes = [C.c_double]
+    L.host_r_round3.restype = C.c_double
+    yield L
+    os.unlink(so)
+
+
+@pytest.mark.parametrize("kw", [{}, {"quant": 100.0, "na_permille": 10}, {"quant": 0.0}])
+def test_d8_fast_path_equals_reference_loop(cellmath, kw):
+    e = oracle.synth_dem(300, 257, **kw)
+    NR, NC = e.shape
+    a, b = np.zeros((NR, NC), np.uint8), np.zeros((NR, NC), np.uint8)
+    cellmath.host_d8(e, NR, NC, a, 0)
+    cellmath.host_d8(e, NR, NC, b, 1)
+    assert (a == b).all()
+    # the oracle's initial stencil == ddir wherever the cell was not flat
+    o = oracle.ddir(e)
+    nf = o["flatcell"] == 0
+    assert (a[nf] == o["ddir"][nf]).all() and (a[o["flatcell"] == 1] == 5).all()
+
+
+def test_form_cell_equals_oracle(cellmath):
+    e = oracle.synth_dem(200, 240)
+    NR, NC = e.shape
+    raw = np.zeros((5, NR, NC))
+    cellmath.host_form_raw(e, NR, NC, 5.0, raw)
+    o = oracle.form(e, 5.0)
+    sl = (slice(3, -3), slice(3, -3))
+    for i, k in enumerate(("slope_pct", "slope_deg", "aspect", "prof", "plan")):
+        assert (raw[i][sl] == o[k][sl]).all(), k
+
+
+def test_get_dir_integer_form_equals_reference(cellmath):
+    for h in range(-30, 31):
+        for v in range(-30, 31):
+            for opts in (0b1111011110, 0b0000010100, 0b1010000010, 0b0101000100, 0b0000000010):
+                assert cellmath.host_get_dir(50, 50, 50 + v, 50 + h, opts) == \
+                    oracle.lib().oracle_get_dir(50, 50, 50 + v, 50 + h, opts)
+
+
+def test_round3_equals_r_rule(cellmath):
+    rng = np.random.default_rng(3)
+    for x in np.concatenate([rng.uniform(-100, 100, 20000), [2.0055, 0.0005, 1.0005, -2.5005, 1e13, 0.0]]):
+        assert cellmath.host_r_round3(x) == oracle.r_round(x, 3)
