@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "liblitap_cuda.so")
+SO_PATH = os.environ.get("LITAP_SO") or os.path.join(_HERE, "liblitap_cuda.so")  # LITAP_SO: tuning builds only
 _lib = None
 
 # every symbol include/litap.h declares

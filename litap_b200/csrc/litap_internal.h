@@ -30,10 +30,14 @@ inline GridDims make_dims(int64_t NR, int64_t NC) {
 }
 
 // ---- shed / upslope tiling --------------------------------------------------------------------
-constexpr int TW = 64, TH = 64;            // interior cells per tile
+#ifndef LITAP_TILE
+#define LITAP_TILE 32
+#endif
+constexpr int TW = LITAP_TILE, TH = LITAP_TILE;  // interior cells per tile
 constexpr int LW = TW + 2, LH = TH + 2;    // local grid incl. the 1-cell ring
-constexpr int LC = LW * LH;                // 4356 local cells
-constexpr int BSLOTS = 256;                // border slots per tile (252 used)
+constexpr int LC = LW * LH;                // local cells (1156 for 32 x 32)
+constexpr int BUSED = 2 * TW + 2 * (TH - 2);        // border cells per tile (124)
+constexpr int BSLOTS = (BUSED + 31) / 32 * 32;      // border slots per tile (128)
 constexpr uint32_t ID_NA = 0xFFFFFFFFu;    // "no shed" (NA drec chain / cycle)
 constexpr uint32_t ID_ROOT = 0x80000000u;  // flag: low 31 bits are a pit id (pid)
 

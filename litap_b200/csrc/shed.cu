@@ -51,9 +51,9 @@ __global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsig
 }
 
 // ------------------------------------------------------------------------------------------------
-constexpr size_t SMEM_A = LC * (1 + 2 + 8 + 4) + 64;
+constexpr size_t SMEM_A = (size_t)LC * (8 + 4 + 2 + 1) + 64;  // key, idx|cnt, ptr, dir
 
-__global__ void __launch_bounds__(NT) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
+__global__ void __launch_bounds__(NT, 1024 / NT) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
                                                    const double* __restrict__ elev, uint32_t* __restrict__ lab,
                                                    L2 l2, Pits pits, unsigned long long* pit_cursor) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -61,53 +61,66 @@ __global__ void __launch_bounds__(NT) k_shed_local(TileGeom g, const uint8_t* __
   uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);           // LC x 4
   uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 12);          // LC x 2
   uint8_t* s_dir = smem + (size_t)LC * 14;                                        // LC x 1
-  unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                             // aliases s_key (phase 4)
-  uint8_t* s_deg = smem + (size_t)LC * 4;                                          // aliases s_key (phase 4)
+  unsigned* s_cnt = s_idx;                                                        // dead before s_idx is first used
   __shared__ unsigned s_npit;
   __shared__ unsigned long long s_pitbase;
 
   const TileCtx t = tile_ctx();
+  const int lx = owned_lx(), c = t.c_base + lx;
+  const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
   if (threadIdx.x == 0) s_npit = 0;
   tile_load_dir(g, t, ddir, s_dir);
-  for (int li = threadIdx.x; li < LC; li += NT) { s_key[li] = 0ull; s_idx[li] = 0xFFFFFFFFu; }
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) s_key[owned_local(k)] = 0ull;
   __syncthreads();
-  tile_pointer_jump(s_dir, s_ptr);
+  // ---- local terminals + local flow counts; exits hand their count to the entry cell's slot
+  // (base of the level-2 sum)
+  {
+    unsigned w[CPT];
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) w[k] = s_dir[owned_local(k)] != 0 ? 1u : 0u;  // out-of-grid cells have ddir 0
+    tile_jump_accumulate(s_dir, s_ptr, s_cnt, w);
+  }
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int ly = owned_ly(k), i = ly * LW + lx;
+    int dv = s_dir[i];
+    if (s_ptr[i] == i && dv != 5) {  // valid exit: entry cell on the local ring
+      long long es = slot_of_rc(t.r_base + ly + nb_dr(dv), c + nb_dc(dv), g.tilesX);
+      if (es >= 0) atomicAdd(&l2.ext[es], s_cnt[i]);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) s_idx[owned_local(k)] = 0xFFFFFFFFu;  // s_cnt is dead: same memory
   __syncthreads();
 
   // ---- per-terminal key: max elevation, then lowest cell id attaining it
   int term[CPT];
   unsigned long long key[CPT];
-  uint32_t cid[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int ly = i / LW, lx = i - ly * LW;
-    int r = t.r_base + ly, c = t.c_base + lx;
-    term[k] = -1;
+    int i = owned_local(k);
+    term[k] = s_ptr[i];  // 0 = NA
     key[k] = 0;
-    cid[k] = (uint32_t)((size_t)r * g.d.pitch + c);
-    if (in_grid(g, r, c) && s_dir[i] != 0) {
-      int tt = s_ptr[i];
-      if (term_kind(s_dir, s_ptr, tt) != T_NA) {
-        term[k] = tt;
-        key[k] = f64_orderable(elev[cid[k]]);
-        atomicMax(&s_key[tt], key[k]);
-      }
+    if (term[k]) {
+      key[k] = f64_orderable(elev[(size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c]);
+      atomicMax(&s_key[term[k]], key[k]);
     }
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if (term[k] >= 0 && key[k] == s_key[term[k]]) atomicMin(&s_idx[term[k]], cid[k]);
+    if (term[k] && key[k] == s_key[term[k]])
+      atomicMin(&s_idx[term[k]], (uint32_t)((size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c));
   __syncthreads();
 
   // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
   unsigned rk[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
     rk[k] = 0xFFFFFFFFu;
-    if (s_dir[i] == 5) rk[k] = atomicAdd(&s_npit, 1u);
+    if (s_dir[owned_local(k)] == 5) rk[k] = atomicAdd(&s_npit, 1u);
   }
   __syncthreads();
   if (threadIdx.x == 0 && s_npit) s_pitbase = atomicAdd(pit_cursor, (unsigned long long)s_npit);
@@ -115,67 +128,41 @@ __global__ void __launch_bounds__(NT) k_shed_local(TileGeom g, const uint8_t* __
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     if (rk[k] == 0xFFFFFFFFu) continue;
-    int i = owned_local(threadIdx.x, k);
+    int i = owned_local(k);
     uint32_t pid = (uint32_t)(s_pitbase + rk[k]);
     pits.rootmax[pid] = s_key[i];
     pits.pitkmax[pid] = s_key[i];
     pits.pitkidx[pid] = s_idx[i];
     pits.rootidx[pid] = 0xFFFFFFFFu;
-    lab[cid[k]] = pid;  // read back by k_shed_final of this tile
-    s_idx[i] = pid;     // from here on s_idx[pit] is its pid
+    lab[(size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c] = pid;  // read back by k_shed_final of this tile
+    s_idx[i] = pid;                                                // from here on s_idx[pit] is its pid
   }
   __syncthreads();
 
   // ---- level-2 edges and key partials of the border cells
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int ly = i / LW, lx = i - ly * LW;
+    int ly = owned_ly(k);
     int bs = border_slot_local(lx, ly);
     if (bs < 0) continue;
-    size_t s = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS + bs;
+    int i = ly * LW + lx;
     uint32_t edge = ID_NA;
     unsigned long long pk = 0;
     uint32_t pi = 0xFFFFFFFFu;
-    if (term[k] >= 0) {
-      int tt = term[k];
-      int kind = term_kind(s_dir, s_ptr, tt);
-      if (kind == T_PIT) edge = ID_ROOT | s_idx[tt];
+    int tt = term[k];
+    if (tt) {
+      int dv = s_dir[tt];
+      if (dv == 5) edge = ID_ROOT | s_idx[tt];
       else {  // exit: continue at the entry cell of the neighbouring tile
-        int e = tt + loc_off(s_dir[tt]);
-        int er = t.r_base + e / LW, ec = t.c_base + e % LW;
-        edge = (uint32_t)((size_t)er * g.d.pitch + ec);
+        int ty_ = tt / LW, tx_ = tt - ty_ * LW;
+        edge = (uint32_t)((size_t)(t.r_base + ty_ + nb_dr(dv)) * g.d.pitch + (t.c_base + tx_ + nb_dc(dv)));
         if (tt == i) { pk = s_key[i]; pi = s_idx[i]; }  // this border cell is the exit itself
       }
     }
-    l2.jump0[s] = edge;
-    l2.jres[s] = edge;
-    l2.pkmax[s] = pk;
-    l2.pkidx[s] = pi;
-  }
-  __syncthreads();  // s_key / s_idx are dead from here: reuse as s_cnt / s_deg
-
-  // ---- local flow counts; exits hand theirs to the entry cell's slot (base of the level-2 sum)
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int ly = i / LW, lx = i - ly * LW;
-    s_cnt[i] = (in_grid(g, t.r_base + ly, t.c_base + lx) && s_dir[i] != 0) ? 1u : 0u;
-  }
-  __syncthreads();  // s_cnt aliases s_key, s_deg aliases s_key too but at a disjoint offset
-  unsigned srcmask = tile_in_degree(s_dir, s_deg);
-  __syncthreads();
-  tile_chase(s_dir, s_cnt, s_deg, srcmask);
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    if (term[k] != i) continue;  // not a (valid) terminal
-    int dv = s_dir[i];
-    if (dv == 5) continue;
-    int e = i + loc_off(dv);  // exit (term_kind checked above): entry cell on the local ring
-    long long es = slot_of_rc(t.r_base + e / LW, t.c_base + e % LW, g.tilesX);
-    if (es >= 0) atomicAdd(&l2.ext[es], s_cnt[i]);
+    l2.jump0[tile_slot0 + bs] = edge;
+    l2.jres[tile_slot0 + bs] = edge;
+    l2.pkmax[tile_slot0 + bs] = pk;
+    l2.pkidx[tile_slot0 + bs] = pi;
   }
 }
 
@@ -267,9 +254,9 @@ __global__ void k_scatter_rank(const uint32_t* __restrict__ order, uint32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------
-constexpr size_t SMEM_B = LC * (4 + 4 + 2 + 1 + 1) + 64;
+constexpr size_t SMEM_B = (size_t)LC * (4 + 4 + 2 + 1) + 64;  // cnt, lab, ptr, dir
 
-__global__ void __launch_bounds__(NT) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
+__global__ void __launch_bounds__(NT, 1024 / NT) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
                                                    const uint32_t* __restrict__ rank, int32_t* shed_out,
                                                    uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -277,72 +264,77 @@ __global__ void __launch_bounds__(NT) k_shed_final(TileGeom g, const uint8_t* __
   uint32_t* s_lab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);     // LC x 4
   uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 8);     // LC x 2
   uint8_t* s_dir = smem + (size_t)LC * 10;                                  // LC x 1
-  uint8_t* s_deg = smem + (size_t)LC * 11;                                  // LC x 1 (4-aligned: LC % 4 == 0)
   const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
 
   const TileCtx t = tile_ctx();
+  const int lx = owned_lx(), c = t.c_base + lx;
+  const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
   tile_load_dir(g, t, ddir, s_dir);
   __syncthreads();
-  tile_pointer_jump(s_dir, s_ptr);
-  __syncthreads();
-
-  // ---- labels of the terminals (interior) and of the ring cells (for the ridge test)
-  for (int li = threadIdx.x; li < LC; li += NT) {
-    int ly = li / LW, lx = li - ly * LW;
-    int r = t.r_base + ly, c = t.c_base + lx;
-    uint32_t lb = 0;
-    if (r >= 1 && c >= 1 && in_grid(g, r, c)) {
-      if (loc_is_ring(li)) {
-        long long s = slot_of_rc(r, c, g.tilesX);
-        uint32_t v = s >= 0 ? l2.jres[s] : ID_NA;
-        if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
-      } else if (s_ptr[li] == li) {
-        int kind = term_kind(s_dir, s_ptr, li);
-        if (kind == T_PIT) lb = rank[lab_in[(size_t)r * g.d.pitch + c]];
-        else if (kind == T_EXIT) {
-          uint32_t v = l2.jres[(size_t)(t.ty * g.tilesX + t.tx) * BSLOTS + border_slot_local(lx, ly)];
-          if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
-        }
+  // ---- local terminals + upslope: in-tile accumulation seeded with the external inflow of the
+  // border cells (level-2 result)
+  {
+    unsigned w[CPT];
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+      int ly = owned_ly(k);
+      w[k] = 0;
+      if (s_dir[ly * LW + lx] != 0) {
+        w[k] = 1;
+        int bs = border_slot_local(lx, ly);
+        if (bs >= 0) w[k] += l2.ext[tile_slot0 + bs];
       }
     }
-    s_lab[li] = lb;  // non-terminal interior cells: overwritten below
+    tile_jump_accumulate(s_dir, s_ptr, s_cnt, w);
+  }
+
+  // ---- labels of the ring cells (for the ridge test): border cells of the neighbouring tiles
+  for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
+    int ry, rx;
+    if (q < LW) { ry = 0; rx = q; }
+    else if (q < 2 * LW) { ry = LH - 1; rx = q - LW; }
+    else if (q < 2 * LW + TH) { ry = q - 2 * LW + 1; rx = 0; }
+    else { ry = q - 2 * LW - TH + 1; rx = LW - 1; }
+    int r = t.r_base + ry, cc = t.c_base + rx;
+    uint32_t lb = 0;
+    if (r >= 1 && cc >= 1 && in_grid(g, r, cc)) {
+      long long s = slot_of_rc(r, cc, g.tilesX);
+      uint32_t v = s >= 0 ? l2.jres[s] : ID_NA;
+      if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
+    }
+    s_lab[ry * LW + rx] = lb;
+  }
+  // ---- labels of the terminals: pits look up their own rank, exits the rank of their resolved root
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int ly = owned_ly(k), i = ly * LW + lx;
+    if (s_ptr[i] != i) continue;
+    uint32_t lb = 0;
+    if (s_dir[i] == 5) lb = rank[lab_in[(size_t)(t.r_base + ly) * g.d.pitch + c]];
+    else {
+      uint32_t v = l2.jres[tile_slot0 + border_slot_local(lx, ly)];
+      if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
+    }
+    s_lab[i] = lb;
   }
   __syncthreads();
   uint32_t mylab[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int tt = s_ptr[i];
-    mylab[k] = (s_dir[i] != 0 && term_kind(s_dir, s_ptr, tt) != T_NA) ? s_lab[tt] : 0u;
+    int tt = s_ptr[owned_local(k)];
+    mylab[k] = tt ? s_lab[tt] : 0u;
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < CPT; ++k) s_lab[owned_local(threadIdx.x, k)] = mylab[k];
+  for (int k = 0; k < CPT; ++k) s_lab[owned_local(k)] = mylab[k];
 
-  // ---- upslope: local accumulation seeded with the external inflow of the border cells
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int ly = i / LW, lx = i - ly * LW;
-    unsigned w = 0;
-    if (in_grid(g, t.r_base + ly, t.c_base + lx) && s_dir[i] != 0) {
-      w = 1;
-      int bs = border_slot_local(lx, ly);
-      if (bs >= 0) w += l2.ext[(size_t)(t.ty * g.tilesX + t.tx) * BSLOTS + bs];
-    }
-    s_cnt[i] = w;
-  }
-  unsigned srcmask = tile_in_degree(s_dir, s_deg);
-  __syncthreads();
-  tile_chase(s_dir, s_cnt, s_deg, srcmask);
   __syncthreads();
 
   // ---- outputs
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int ly = i / LW, lx = i - ly * LW;
-    int r = t.r_base + ly, c = t.c_base + lx;
+    int ly = owned_ly(k), i = ly * LW + lx;
+    int r = t.r_base + ly;
     if (!in_grid(g, r, c)) continue;
     size_t o = (size_t)r * g.d.pitch + c;
     uint32_t lb = mylab[k];
@@ -352,7 +344,7 @@ __global__ void __launch_bounds__(NT) k_shed_final(TileGeom g, const uint8_t* __
       bool multi = false;
 #pragma unroll
       for (int n = 1; n <= 9; ++n) {
-        uint32_t s = s_lab[i + loc_off(n)];
+        uint32_t s = s_lab[i + nb_dr(n) * LW + nb_dc(n)];
         if (!s) continue;
         if (!first) first = s;
         else if (s != first) multi = true;

@@ -6,34 +6,36 @@
 //     pit   (ddir == 5)                       -> a root of the forest
 //     exit  (ddir points out of the tile)     -> continues at the entry cell of the next tile
 //     NA    (ddir NA, chain leaves the grid, or a cycle)
-// and flow is accumulated inside the tile by chasing from the source cells with shared-memory
-// atomics (each cell forwards its count once all its in-tile donors have arrived).  Only the tile
-// border cells (4 x 63 = 252 "slots" per tile) take part in the global, level-2 graph.
+// and flow is accumulated inside the tile in the same pointer-doubling loop.  Only the tile
+// border cells (BUSED "slots" per tile) take part in the global, level-2 graph.
 #pragma once
 #include "cellmath.h"
 #include "litap_internal.h"
 
 namespace shed {
 
-constexpr int NT = 512;            // threads per tile CTA
+constexpr int NT = TW * TH / 8;    // threads per tile CTA: 8 interior cells per thread
 constexpr int CPT = TW * TH / NT;  // interior cells per thread (8)
-static_assert(TW * TH % NT == 0, "tile must divide evenly over the CTA");
+constexpr int RPK = NT / TW;       // tile rows covered by one pass of the CTA
+static_assert(NT % TW == 0 && (TW & (TW - 1)) == 0, "row-wise ownership needs a power-of-two tile width");
+constexpr uint8_t RING = 0x80;     // s_dir flag of the local ring cells
 
 struct TileGeom {
   GridDims d;
   int tilesX, tilesY;
 };
 
-__device__ __forceinline__ int loc_off(int dir) { return nb_dr(dir) * LW + nb_dc(dir); }
-__device__ __forceinline__ bool loc_is_ring(int li) {
-  int ly = li / LW, lx = li - ly * LW;
-  return lx == 0 || lx == LW - 1 || ly == 0 || ly == LH - 1;
+// local index step of direction code 1..9 (0 for 5): rows grow southward, R/LITAP_functions.R:212-220
+__device__ __forceinline__ int loc_off(int dir) {
+  int dr = (dir < 4) - (dir > 6);
+  int dc = (int)((0x92490u >> (2 * dir)) & 3u) - 1;  // 2-bit table of (dir-1)%3 for dir 0..9 (dir 0 -> unused)
+  return dr * LW + dc;
 }
-// k-th interior cell owned by thread t: consecutive threads take consecutive columns of one row
-__device__ __forceinline__ int owned_local(int t, int k) {
-  int ii = k * NT + t;  // 0..TW*TH-1
-  return (ii / TW + 1) * LW + (ii % TW + 1);
-}
+// k-th interior cell owned by this thread: consecutive threads take consecutive columns of a row
+__device__ __forceinline__ int owned_ly(int k) { return k * RPK + (int)(threadIdx.x / TW) + 1; }
+__device__ __forceinline__ int owned_lx() { return (int)(threadIdx.x % TW) + 1; }
+__device__ __forceinline__ int owned_local(int k) { return owned_ly(k) * LW + owned_lx(); }
+
 __device__ __forceinline__ int border_slot_local(int lx, int ly) {
   if (ly == 1) return lx - 1;
   if (ly == TH) return TW + lx - 1;
@@ -52,9 +54,6 @@ __device__ __forceinline__ long long slot_of_id(uint32_t id, const TileGeom& g) 
   return slot_of_rc(r, c, g.tilesX);
 }
 
-// terminal kinds
-enum { T_NA = 0, T_PIT = 1, T_EXIT = 2 };
-
 struct TileCtx {
   int tx, ty, r_base, c_base;  // global (r, c) of local (0, 0)
 };
@@ -68,16 +67,25 @@ __device__ __forceinline__ TileCtx tile_ctx() {
 }
 __device__ __forceinline__ bool in_grid(const TileGeom& g, int r, int c) { return r < g.d.NR && c < g.d.NC; }
 
-// Phase 0: stage ddir of the local grid (0 outside the grid and on buffered row 0 / column 0, which
-// belong to no tile: they are the NA ring).  Cells whose ddir points outside the grid or onto
-// row 0 / column 0 become NA themselves (their chain has an NA drec).
+// Phase 0: stage ddir of the interior (0 outside the grid; buffered row 0 / column 0 belong to no
+// tile: they are the NA ring) and flag the local ring.  A cell whose ddir points outside the grid
+// or onto row 0 / column 0 becomes NA itself (its chain has an NA drec).
 __device__ __forceinline__ void tile_load_dir(const TileGeom& g, const TileCtx& t, const uint8_t* __restrict__ ddir,
                                               uint8_t* s_dir) {
-  for (int li = threadIdx.x; li < LC; li += NT) {
-    int ly = li / LW, lx = li - ly * LW;
-    int r = t.r_base + ly, c = t.c_base + lx;
+  for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
+    int li;
+    if (q < LW) li = q;
+    else if (q < 2 * LW) li = (LH - 1) * LW + (q - LW);
+    else if (q < 2 * LW + TH) li = (q - 2 * LW + 1) * LW;
+    else li = (q - 2 * LW - TH + 1) * LW + LW - 1;
+    s_dir[li] = RING;
+  }
+  const int lx = owned_lx(), c = t.c_base + lx;
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int ly = owned_ly(k), r = t.r_base + ly;
     uint8_t dv = 0;
-    if (r >= 1 && c >= 1 && in_grid(g, r, c)) {
+    if (in_grid(g, r, c)) {
       dv = ddir[(size_t)r * g.d.pitch + c];
       if (dv > 9) dv = 0;
       if (dv != 0 && dv != 5) {
@@ -85,92 +93,75 @@ __device__ __forceinline__ void tile_load_dir(const TileGeom& g, const TileCtx& 
         if (rr < 1 || cc < 1 || !in_grid(g, rr, cc)) dv = 0;
       }
     }
-    s_dir[li] = dv;
+    s_dir[ly * LW + lx] = dv;
   }
 }
 
-// Phase 1: local terminals by pointer jumping.  On return s_ptr[i] (interior i) is self-pointing
-// for terminals; use term_kind() to classify.  Cells caught in a cycle are classified T_NA.
-__device__ __forceinline__ void tile_pointer_jump(const uint8_t* s_dir, uint16_t* s_ptr) {
-  for (int li = threadIdx.x; li < LC; li += NT) {
-    int p = li;
-    if (!loc_is_ring(li)) {
-      int dv = s_dir[li];
-      if (dv != 0 && dv != 5) {
-        int t = li + loc_off(dv);
-        if (!loc_is_ring(t)) p = t;  // else: exit cell, stays self-pointing
-      }
+// Phase 1: local terminals AND in-tile flow accumulation in one pointer-doubling loop, no
+// divergent walks and no return-value atomics.  p_k(c) is the cell 2^k steps downstream of c inside
+// the tile, flagged OVER once the walk would pass the local terminal; S_k(c) is the weight of all
+// cells at distance < 2^k upstream of c (S_0 = own weight).  One round does
+//     S_{k+1}(p_k(y)) += S_k(y)   for every y whose p_k is not OVER      (32-bit shared RED)
+//     p_{k+1}(y) = p_k(p_k(y))
+// because the cells at distance 2^k .. 2^(k+1)-1 above c are exactly the S_k sets of the cells y
+// sitting 2^k steps above c.  ceil(log2(longest in-tile path)) rounds, two barriers per round.
+// On return, for every interior cell i: s_cnt[i] = weight draining through i inside the tile
+// (itself included) and s_ptr[i] = local index of its valid terminal (a pit or an exit cell), or
+// 0 (the ring corner, never a terminal) when the chain is NA: NA ddir, leaves the grid, or a cycle.
+constexpr int OVER = 0x8000;
+constexpr int MAX_ROUNDS = LC > 2048 ? 14 : 12;  // 2^(MAX_ROUNDS-1) > LC: only cycles are still live after that
+
+__device__ __forceinline__ void tile_jump_accumulate(const uint8_t* s_dir, uint16_t* s_ptr, unsigned* s_cnt,
+                                                     const unsigned* w) {
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    int i = owned_local(k);
+    int dv = s_dir[i], p = i | OVER;
+    if (dv != 0 && dv != 5) {
+      int t = i + loc_off(dv);
+      if (!(s_dir[t] & RING)) p = t;  // else: exit cell, a terminal
     }
-    s_ptr[li] = (uint16_t)p;
+    s_ptr[i] = (uint16_t)p;
+    s_cnt[i] = w[k];
   }
   __syncthreads();
-  for (int round = 0; round < 14; ++round) {  // 2^13 > LC: chains converge in <= 13 rounds
-    bool changed = false;
+  for (int round = 0; round < MAX_ROUNDS; ++round) {
+    int a[CPT], b[CPT];
+    unsigned sv[CPT];
+    bool any = false;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
-      int i = owned_local(threadIdx.x, k);
-      int p = s_ptr[i];
-      int pp = s_ptr[p];
-      if (pp != p) { s_ptr[i] = (uint16_t)pp; changed = true; }
+      int i = owned_local(k);
+      a[k] = s_ptr[i];
+      if (!(a[k] & OVER)) {
+        b[k] = s_ptr[a[k]];
+        sv[k] = s_cnt[i];
+        any = true;
+      }
     }
-    if (!__syncthreads_or(changed)) break;
+    if (!__syncthreads_or(any)) break;  // also separates this round's reads from its writes
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+      if (a[k] & OVER) continue;
+      s_ptr[owned_local(k)] = (uint16_t)b[k];
+      atomicAdd(&s_cnt[a[k]], sv[k]);
+    }
+    __syncthreads();
   }
-}
-__device__ __forceinline__ int term_kind(const uint8_t* s_dir, const uint16_t* s_ptr, int t) {
-  if (s_ptr[t] != t) return T_NA;  // never converged: on / behind a cycle
-  int dv = s_dir[t];
-  if (dv == 0) return T_NA;
-  if (dv == 5) return T_PIT;
-  return loc_is_ring(t + loc_off(dv)) ? T_EXIT : T_NA;  // self-pointing non-exit = 2-cycle
-}
-
-// In-tile donors of each interior cell (pull, no atomics) and the source mask of the owned cells.
-__device__ __forceinline__ unsigned tile_in_degree(const uint8_t* s_dir, uint8_t* s_deg) {
-  unsigned srcmask = 0;
+  // classify: a valid terminal was reached (OVER) and is a pit or an exit
+  int res[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(threadIdx.x, k);
-    int deg = 0;
-#pragma unroll
-    for (int n = 1; n <= 9; ++n) {
-      if (n == 5) continue;
-      int j = i + loc_off(n);
-      if (loc_is_ring(j)) continue;
-      int dj = s_dir[j];
-      // neighbour n of i flows into i iff its direction is the opposite code 10 - n
-      deg += (dj == 10 - n);
-    }
-    s_deg[i] = (uint8_t)deg;
-    if (deg == 0 && s_dir[i] != 0) srcmask |= 1u << k;
+    int pv = s_ptr[owned_local(k)];
+    int tt = pv & (OVER - 1);
+    int dv = s_dir[tt];
+    bool ok = (pv & OVER) && dv != 0 && (dv == 5 || (s_dir[tt + loc_off(dv)] & RING));
+    res[k] = ok ? tt : 0;
   }
-  return srcmask;
-}
-
-// Chase: every source cell pushes its count downstream; a cell continues the walk only when it
-// was the last donor to arrive (its in-degree byte drops from 1 to 0).  Integer adds: exact in
-// any order.  s_cnt must hold the initial weights; s_deg the in-degrees (4 per 32-bit word).
-__device__ __forceinline__ void tile_chase(const uint8_t* s_dir, unsigned* s_cnt, uint8_t* s_deg, unsigned srcmask) {
-  unsigned* deg32 = reinterpret_cast<unsigned*>(s_deg);
+  __syncthreads();
 #pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    if (!((srcmask >> k) & 1u)) continue;
-    int cur = owned_local(threadIdx.x, k);
-    unsigned carry = s_cnt[cur];
-    while (true) {
-      int dv = s_dir[cur];
-      if (dv == 5 || dv == 0) break;
-      int t = cur + loc_off(dv);
-      if (loc_is_ring(t)) break;  // exit cell: its count leaves the tile
-      atomicAdd(&s_cnt[t], carry);
-      __threadfence_block();
-      unsigned sh = 8u * (t & 3);
-      unsigned old = atomicSub(&deg32[t >> 2], 1u << sh);
-      if (((old >> sh) & 0xFFu) != 1u) break;
-      __threadfence_block();
-      carry = *reinterpret_cast<volatile unsigned*>(&s_cnt[t]);
-      cur = t;
-    }
-  }
+  for (int k = 0; k < CPT; ++k) s_ptr[owned_local(k)] = (uint16_t)res[k];
+  __syncthreads();
 }
 
 }  // namespace shed
