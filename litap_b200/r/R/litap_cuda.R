@@ -1,0 +1,88 @@
+# litap_cuda.R -- drop-in replacements for the four hot internals of LITAP, same names, same
+# arguments, same returned columns (SURVEY.md 8b):
+#
+#   calc_ddir2(db, verbose)        replaces R/flow_01_calc_ddir.R:2-118   (callers R/flow_mapper.R:157,354)
+#   calc_shed4(db, verbose)        replaces R/flow_02_calc_shed.R:10-58   (callers R/flow_mapper.R:180,377)
+#   calc_form(db, grid, verbose)   replaces R/form_01_calc_form.R:4-67    (caller  R/form_mapper.R:103)
+#   calc_weti2(db, grid, verbose)  replaces R/form_02b_calc_weti.R:3-110  (caller  R/form_mapper.R:127)
+#
+# Every function calls the CUDA library through .Call unconditionally: there is no CPU fallback
+# (an error from the library, e.g. "no CUDA device", surfaces as an R error).  flow_mapper() and
+# form_mapper() keep their signatures and their output column layout; pit removal (flow_03/04),
+# slope_gc, relief and the I/O stay the reference's R code.
+#
+# `db` is the reference's buffered tibble: one row per cell of the (nrow+2) x (ncol+2) grid,
+# sorted by seqno (R/LITAP_load.R:273-332).
+
+litap_dims <- function(db) {
+  nr <- max(db$row); nc <- max(db$col)
+  if (nrow(db) != nr * nc || is.unsorted(db$seqno))
+    stop("litap: db must hold the full buffered grid sorted by seqno", call. = FALSE)
+  c(nr, nc)
+}
+
+calc_ddir2 <- function(db, verbose = FALSE) {
+  d <- litap_dims(db)
+  if (verbose) message("  Calculating directions on the GPU")
+  r <- .Call("litap_R_ddir", as.double(db$elev), d[1], d[2], FALSE)
+  db$ddir <- r$ddir
+  db$flatcell <- r$flatcell
+  db$drec <- r$drec
+  db
+}
+
+calc_shed4 <- function(db, verbose = FALSE) {
+  d <- litap_dims(db)
+  if (verbose) message("  Labelling watersheds and accumulating upslope cells on the GPU")
+  r <- .Call("litap_R_shed", as.double(db$elev), db$ddir, d[1], d[2])
+  db$initial_shed <- r$initial_shed
+  db$upslope <- r$upslope
+  db$ridge <- r$ridge
+  # side columns the reference's calc_upslopes() leaves in its result
+  # (R/flow_02_calc_shed.R:62-68); not saved (cols_order) but part of its own snapshot test
+  ok <- !is.na(db$initial_shed)
+  db$seqno_shed <- NA_integer_
+  db$seqno_shed[ok] <- stats::ave(db$seqno[ok], db$initial_shed[ok], FUN = seq_along)
+  db$drec_shed <- db$seqno_shed[db$drec]
+  db
+}
+
+calc_form <- function(db, grid, verbose = FALSE) {
+  d <- litap_dims(db)
+  if (verbose) message("  Calculating slope, aspect and curvature on the GPU")
+  r <- .Call("litap_R_form", as.double(db$elev), d[1], d[2], as.double(grid))
+  tibble::tibble(seqno = db$seqno, row = db$row, col = db$col,
+                 slope_pct = r$slope_pct, slope_deg = r$slope_deg, aspect = r$aspect,
+                 prof = r$prof, plan = r$plan, buffer = db$buffer)
+}
+
+calc_weti2 <- function(db, grid, verbose = FALSE) {
+  d <- litap_dims(db)
+  if (verbose) message("  Calculating wetness indices on the GPU")
+  r <- .Call("litap_R_weti", as.double(db$elev), db$ddir, db$upslope, d[1], d[2], as.double(grid))
+  db$qarea1 <- r$qarea1
+  db$qarea2 <- r$qarea2
+  db$qweti1 <- r$qweti1
+  db$qweti2 <- r$qweti2
+  db
+}
+
+# The second traversal of flow_mapper() (R/flow_mapper.R:343-377) may skip the R-side invert()
+# round trip for the direction step: calc_ddir2_inverted(db) == calc_ddir2(invert(db)) with the
+# subtraction max(elev) - elev done on the device.  invert() itself (R/flow_06_invert.R) is still
+# called by flow_mapper() because the inverted elevations are saved with dem_inverted.
+calc_ddir2_inverted <- function(db, verbose = FALSE) {
+  d <- litap_dims(db)
+  r <- .Call("litap_R_ddir", as.double(db$elev), d[1], d[2], TRUE)
+  db$elev <- max(db$elev, na.rm = TRUE) - db$elev
+  db$ddir <- r$ddir
+  db$flatcell <- r$flatcell
+  db$drec <- r$drec
+  db
+}
+
+.onLoad <- function(libname, pkgname) {
+  dev <- as.integer(Sys.getenv("LITAP_CUDA_DEVICE", "-1"))
+  .Call("litap_R_init", dev)
+}
+.onUnload <- function(libpath) .Call("litap_R_shutdown")

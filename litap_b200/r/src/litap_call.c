@@ -1,0 +1,179 @@
+/*
+ * litap_call.c — the R side of the boundary: `.Call` entry points that hand R-owned vectors to
+ * liblitap_cuda.so (include/litap.h).  This is the ONLY file that includes Rinternals.h; it holds
+ * no algorithm.  It is what a LITAP maintainer adds as src/litap_call.c (plus
+ * `useDynLib(LITAP, .registration = TRUE)` in NAMESPACE and `PKG_LIBS = -llitap_cuda` in
+ * src/Makevars); see INTEGRATION.md.  R is not installed in the build image, so this file is
+ * compiled only where R exists (R CMD SHLIB litap_call.c -llitap_cuda).
+ *
+ * Conventions
+ *   - every column arrives as the full buffered grid in seqno order (length NR*NC), exactly the
+ *     tibble columns the reference's internals receive (R/LITAP_load.R:273-332);
+ *   - NA_real_ is a NaN, so REAL() pointers go to the library unchanged;
+ *   - ddir travels as uint8 (0 = NA); R's numeric ddir column is converted here;
+ *   - results are returned as a named list of R vectors with the reference's column types
+ *     (ddir/upslope/initial_shed numeric, drec integer (numeric above 2^31), ridge/flatcell logical);
+ *   - errors: every non-zero status becomes Rf_error() AFTER all temporary buffers are released
+ *     (R_alloc memory is reclaimed by R itself, so nothing leaks across the longjmp).
+ */
+#include <R.h>
+#include <Rinternals.h>
+#include <R_ext/Rdynload.h>
+#include <stdint.h>
+#include <string.h>
+#include "litap.h"
+
+static void fail_if(int rc, const char* what) {
+  if (rc != LITAP_OK) Rf_error("%s: %s (liblitap_cuda status %d)", what, litap_last_error(), rc);
+}
+
+static SEXP named_list(int n, const char** names) {
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, n));
+  SEXP nm = PROTECT(Rf_allocVector(STRSXP, n));
+  for (int i = 0; i < n; ++i) SET_STRING_ELT(nm, i, Rf_mkChar(names[i]));
+  Rf_setAttrib(out, R_NamesSymbol, nm);
+  UNPROTECT(2);
+  return out;
+}
+
+static uint8_t* ddir_to_u8(SEXP ddir, R_xlen_t n) {
+  uint8_t* d = (uint8_t*)R_alloc((size_t)n, 1);
+  if (TYPEOF(ddir) == REALSXP) {
+    const double* p = REAL(ddir);
+    for (R_xlen_t i = 0; i < n; ++i) d[i] = (ISNAN(p[i]) || p[i] < 1 || p[i] > 9) ? 0 : (uint8_t)p[i];
+  } else {
+    const int* p = INTEGER(ddir);
+    for (R_xlen_t i = 0; i < n; ++i) d[i] = (p[i] == NA_INTEGER || p[i] < 1 || p[i] > 9) ? 0 : (uint8_t)p[i];
+  }
+  return d;
+}
+
+/* offsets of direction codes 1..9 on a grid with NC columns (R/LITAP_functions.R:237-254 calc_seq) */
+static double drec_of(R_xlen_t seqno, int d, R_xlen_t NC) {
+  static const int dr[10] = {0, 1, 1, 1, 0, 0, 0, -1, -1, -1};
+  static const int dc[10] = {0, -1, 0, 1, -1, 0, 1, -1, 0, 1};
+  return (double)(seqno + (R_xlen_t)dr[d] * NC + dc[d]);
+}
+
+/* calc_ddir2(db): .Call("litap_R_ddir", db$elev, nrow, ncol, invert) -> list(ddir, flatcell, drec) */
+SEXP litap_R_ddir(SEXP elev, SEXP nrow, SEXP ncol, SEXP invert) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n) Rf_error("litap_R_ddir: elev must be a double vector of nrow*ncol");
+  uint8_t* d = (uint8_t*)R_alloc((size_t)n, 1);
+  uint8_t* f = (uint8_t*)R_alloc((size_t)n, 1);
+  fail_if(litap_ddir(REAL(elev), NR, NC, Rf_asLogical(invert) == TRUE, d, f), "calc_ddir2");
+  const char* nm[3] = {"ddir", "flatcell", "drec"};
+  SEXP out = PROTECT(named_list(3, nm));
+  SEXP s_d = PROTECT(Rf_allocVector(REALSXP, n)), s_f = PROTECT(Rf_allocVector(LGLSXP, n));
+  const int big = n > 2147483647;  /* seqno does not fit INTSXP: emit doubles (SURVEY.md 8b Limits) */
+  SEXP s_r = PROTECT(Rf_allocVector(big ? REALSXP : INTSXP, n));
+  for (R_xlen_t i = 0; i < n; ++i) {
+    REAL(s_d)[i] = d[i] ? (double)d[i] : NA_REAL;
+    LOGICAL(s_f)[i] = f[i] == 2 ? NA_LOGICAL : (int)f[i];
+    if (big) REAL(s_r)[i] = d[i] ? drec_of(i + 1, d[i], NC) : NA_REAL;
+    else INTEGER(s_r)[i] = d[i] ? (int)drec_of(i + 1, d[i], NC) : NA_INTEGER;
+  }
+  SET_VECTOR_ELT(out, 0, s_d);
+  SET_VECTOR_ELT(out, 1, s_f);
+  SET_VECTOR_ELT(out, 2, s_r);
+  UNPROTECT(4);
+  return out;
+}
+
+/* calc_shed4(db): .Call("litap_R_shed", db$elev, db$ddir, nrow, ncol) -> list(initial_shed, upslope, ridge) */
+SEXP litap_R_shed(SEXP elev, SEXP ddir, SEXP nrow, SEXP ncol) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n || XLENGTH(ddir) != n)
+    Rf_error("litap_R_shed: elev/ddir must have nrow*ncol entries");
+  uint8_t* d = ddir_to_u8(ddir, n);
+  int32_t* sh = (int32_t*)R_alloc((size_t)n, sizeof(int32_t));
+  uint32_t* up = (uint32_t*)R_alloc((size_t)n, sizeof(uint32_t));
+  uint8_t* rg = (uint8_t*)R_alloc((size_t)n, 1);
+  int64_t npits = 0;
+  fail_if(litap_shed(REAL(elev), d, NR, NC, sh, up, rg, &npits), "calc_shed4");
+  const char* nm[3] = {"initial_shed", "upslope", "ridge"};
+  SEXP out = PROTECT(named_list(3, nm));
+  SEXP s_s = PROTECT(Rf_allocVector(REALSXP, n)), s_u = PROTECT(Rf_allocVector(REALSXP, n));
+  SEXP s_r = PROTECT(Rf_allocVector(LGLSXP, n));
+  for (R_xlen_t i = 0; i < n; ++i) {
+    REAL(s_s)[i] = sh[i] ? (double)sh[i] : NA_REAL;
+    REAL(s_u)[i] = (double)up[i];
+    LOGICAL(s_r)[i] = rg[i] == 2 ? NA_LOGICAL : (int)rg[i];
+  }
+  SET_VECTOR_ELT(out, 0, s_s);
+  SET_VECTOR_ELT(out, 1, s_u);
+  SET_VECTOR_ELT(out, 2, s_r);
+  UNPROTECT(4);
+  return out;
+}
+
+/* calc_form(db, grid): results are written straight into freshly allocated REALSXPs */
+SEXP litap_R_form(SEXP elev, SEXP nrow, SEXP ncol, SEXP grid) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n) Rf_error("litap_R_form: elev must be a double vector of nrow*ncol");
+  const char* nm[5] = {"slope_pct", "slope_deg", "aspect", "prof", "plan"};
+  SEXP out = PROTECT(named_list(5, nm));
+  double* p[5];
+  for (int k = 0; k < 5; ++k) {
+    SEXP v = Rf_allocVector(REALSXP, n);
+    SET_VECTOR_ELT(out, k, v);  /* protected through `out` */
+    p[k] = REAL(v);
+  }
+  fail_if(litap_form(REAL(elev), NR, NC, Rf_asReal(grid), p[0], p[1], p[2], p[3], p[4]), "calc_form");
+  UNPROTECT(1);
+  return out;
+}
+
+/* calc_weti2(db, grid) */
+SEXP litap_R_weti(SEXP elev, SEXP ddir, SEXP upslope, SEXP nrow, SEXP ncol, SEXP grid) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n || XLENGTH(ddir) != n || XLENGTH(upslope) != n)
+    Rf_error("litap_R_weti: elev/ddir/upslope must have nrow*ncol entries");
+  uint8_t* d = ddir_to_u8(ddir, n);
+  uint32_t* up = (uint32_t*)R_alloc((size_t)n, sizeof(uint32_t));
+  SEXP upr = PROTECT(Rf_coerceVector(upslope, REALSXP));
+  for (R_xlen_t i = 0; i < n; ++i) up[i] = ISNAN(REAL(upr)[i]) ? 0u : (uint32_t)REAL(upr)[i];
+  const char* nm[4] = {"qarea1", "qarea2", "qweti1", "qweti2"};
+  SEXP out = PROTECT(named_list(4, nm));
+  double* p[4];
+  for (int k = 0; k < 4; ++k) {
+    SEXP v = Rf_allocVector(REALSXP, n);
+    SET_VECTOR_ELT(out, k, v);
+    p[k] = REAL(v);
+  }
+  fail_if(litap_weti(REAL(elev), d, up, NR, NC, Rf_asReal(grid), p[0], p[1], p[2], p[3]), "calc_weti2");
+  UNPROTECT(2);
+  return out;
+}
+
+SEXP litap_R_init(SEXP device) {
+  fail_if(litap_init(Rf_asInteger(device)), "litap_init");
+  return Rf_mkString(litap_version());
+}
+SEXP litap_R_shutdown(void) {
+  litap_shutdown();
+  return R_NilValue;
+}
+SEXP litap_R_timings(void) {
+  litap_timings t;
+  fail_if(litap_get_timings(&t), "litap_get_timings");
+  const char* nm[8] = {"h2d_ms", "d2h_ms", "ddir_ms", "shed_ms", "form_ms", "weti_ms", "total_ms", "kernel_launches"};
+  const double v[8] = {t.h2d_ms, t.d2h_ms, t.ddir_ms, t.shed_ms, t.form_ms, t.weti_ms, t.total_ms, (double)t.kernel_launches};
+  SEXP out = PROTECT(Rf_allocVector(REALSXP, 8));
+  SEXP names = PROTECT(Rf_allocVector(STRSXP, 8));
+  for (int i = 0; i < 8; ++i) { REAL(out)[i] = v[i]; SET_STRING_ELT(names, i, Rf_mkChar(nm[i])); }
+  Rf_setAttrib(out, R_NamesSymbol, names);
+  UNPROTECT(2);
+  return out;
+}
+
+static const R_CallMethodDef call_methods[] = {
+    {"litap_R_ddir", (DL_FUNC)&litap_R_ddir, 4},     {"litap_R_shed", (DL_FUNC)&litap_R_shed, 4},
+    {"litap_R_form", (DL_FUNC)&litap_R_form, 4},     {"litap_R_weti", (DL_FUNC)&litap_R_weti, 6},
+    {"litap_R_init", (DL_FUNC)&litap_R_init, 1},     {"litap_R_shutdown", (DL_FUNC)&litap_R_shutdown, 0},
+    {"litap_R_timings", (DL_FUNC)&litap_R_timings, 0}, {NULL, NULL, 0}};
+
+void R_init_LITAP(DllInfo* dll) {
+  R_registerRoutines(dll, NULL, call_methods, NULL, NULL);
+  R_useDynamicSymbols(dll, FALSE);
+}

@@ -96,3 +96,15 @@ def test_round3_equals_r_rule(cellmath):
     rng = np.random.default_rng(3)
     for x in np.concatenate([rng.uniform(-100, 100, 20000), [2.0055, 0.0005, 1.0005, -2.5005, 1e13, 0.0]]):
         assert cellmath.host_r_round3(x) == oracle.r_round(x, 3)
+
+
+def test_r_shim_compiles_against_stub_headers():
+    """R is not installed: type-check the .Call shim against declaration-only stand-ins for R's
+    headers, so that drift between include/litap.h and the shim is caught."""
+    shim = os.path.join(ROOT, "litap_b200", "r", "src", "litap_call.c")
+    subprocess.check_call(["gcc", "-fsyntax-only", "-Wall", "-Werror=implicit-function-declaration",
+                           "-Werror=incompatible-pointer-types", "-Werror=int-conversion",
+                           "-I", os.path.join(ROOT, "tests", "r_stub"), "-I", os.path.join(ROOT, "include"), shim])
+    src = open(shim).read()
+    for fn in ("litap_ddir", "litap_shed", "litap_form", "litap_weti"):
+        assert fn + "(" in src
