@@ -112,6 +112,8 @@ extern "C" int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out) {
   if (rc) return rc;
   litap_grid* g = new litap_grid();
   g->d = d;
+  g->own_lo = 0;
+  g->own_hi = d.NR;
   g->elev = grid_alloc_array<double>(d, 0xFF);  // pads = NaN
   if (!g->elev) { delete g; return set_error(LITAP_ENOMEM, "device allocation failed (elev)"); }
   *out = g;
@@ -129,6 +131,10 @@ extern "C" void litap_grid_destroy(litap_grid* g) {
   grid_free_array(g->ridge);
   for (auto& p : g->form) grid_free_array(p);
   for (auto& p : g->weti) grid_free_array(p);
+  if (g->dd_list) pool_free(g->dd_list);
+  if (g->dd_cand) pool_free(g->dd_cand);
+  if (g->dd_keys) pool_free(g->dd_keys);
+  if (g->dd_ctr) pool_free(g->dd_ctr);
   delete g;
 }
 

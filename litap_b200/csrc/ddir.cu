@@ -1,14 +1,19 @@
 // ddir.cu — calc_ddir2 on the device (R/flow_01_calc_ddir.R:2-118).
-//   k_elev_max / k_invert : invert()            R/flow_06_invert.R:1-5
-//   k_d8                  : finddir2            R/LITAP_functions.R:257-273  (3x3 stencil, 9 B/cell)
-//   k_collect_flats       : worklist of ddir==5 cells
-//   k_plateau_probe/apply : synchronous plateau rounds   R/flow_01_calc_ddir.R:12-41
-//   k_patch_mark + host   : flat-pit patches + get_dir   R/flow_01_calc_ddir.R:48-107
-#include <algorithm>
-#include <unordered_map>
-#include <vector>
+//   k_elev_max / k_invert : invert()                      R/flow_06_invert.R:1-5
+//   k_d8                  : finddir2 + worklist of flats  R/LITAP_functions.R:257-273  (9 B/cell)
+//   k_plateau_all         : all synchronous plateau rounds in one cooperative launch
+//                                                         R/flow_01_calc_ddir.R:12-41
+//   k_plateau_probe/apply : one round (row-band mode: the host exchanges halo rows between rounds)
+//   k_patch_* + cub sort  : flat-pit patches: components (union-find), median centre, get_dir
+//                                                         R/flow_01_calc_ddir.R:48-107
+// No raster and no result ever goes through the host: it reads three counters per call.
+#include <cooperative_groups.h>
+#include <cub/cub.cuh>
 #include "cellmath.h"
 #include "litap_internal.h"
+#include "stencil.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -21,10 +26,20 @@ __device__ __forceinline__ double f64_from_orderable(unsigned long long k) {
   return __longlong_as_double((long long)b);
 }
 
+// device counters of one calc_ddir2 call
+struct DdirCounters {
+  unsigned long long nflat;    // flat cells after the initial stencil (may exceed the list capacity)
+  unsigned long long elev_max; // orderable max(elev) for invert()
+  unsigned npatch;             // cells of flat-pit patches
+  unsigned rounds;             // plateau rounds that changed something
+  unsigned changed[2];         // per-round "any change" flags (double buffered)
+  unsigned pad[2];
+};
+
 // ---- invert ------------------------------------------------------------------------------------
-__global__ void k_elev_max(const double* __restrict__ elev, GridDims d, unsigned long long* out) {
+__global__ void k_elev_max(const double* __restrict__ elev, GridDims d, int r_lo, int r_hi, unsigned long long* out) {
   unsigned long long best = 0;  // below every orderable finite value
-  for (int r = blockIdx.y; r < d.NR; r += gridDim.y)
+  for (int r = r_lo + blockIdx.y; r < r_hi; r += gridDim.y)
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < d.NC; c += gridDim.x * blockDim.x) {
       double v = elev[(size_t)r * d.pitch + c];
       if (!is_nan(v)) { unsigned long long k = f64_orderable(v); best = k > best ? k : best; }
@@ -42,103 +57,148 @@ __global__ void k_invert(double* __restrict__ elev, GridDims d, const unsigned l
   }
 }
 
-// ---- D8 stencil --------------------------------------------------------------------------------
-// One thread per column, a warp = 32 consecutive columns starting on an aligned interior column,
-// each thread slides a 3-row register window down D8_ROWS rows: one coalesced 256 B row load per
-// warp per row; left/right neighbours come from shuffles (+1 halo load on lanes 0 and 31).
-constexpr int D8_ROWS = 32;
-constexpr int D8_THREADS = 128;
-
-struct Row3 { double l, m, r; };
-
-__device__ __forceinline__ Row3 load_row3(const double* __restrict__ elev, const GridDims& d, int r, int c, int lane) {
-  const double NA = __longlong_as_double(0x7ff8000000000000LL);
-  Row3 w;
-  const bool rv = (r >= 0 && r < d.NR);
-  const double* row = elev + (size_t)(rv ? r : 0) * d.pitch;
-  w.m = (rv && c < d.NC) ? __ldg(row + c) : NA;
-  w.l = __shfl_up_sync(0xffffffffu, w.m, 1);
-  w.r = __shfl_down_sync(0xffffffffu, w.m, 1);
-  if (lane == 0) w.l = (rv && c - 1 >= 0 && c - 1 < d.NC) ? __ldg(row + c - 1) : NA;
-  if (lane == 31) w.r = (rv && c + 1 < d.NC) ? __ldg(row + c + 1) : NA;
-  return w;
-}
+// ---- D8 stencil + flat worklist ------------------------------------------------------------------
+constexpr int D8_CPT = 4;        // columns per thread: 32-byte loads, uchar4 stores
+constexpr int D8_THREADS = 128;  // 512 columns per block
+constexpr int D8_ROWS = 16;
+constexpr int D8_STAGE = 1024;   // flats a block stages in shared memory before appending
 
 __global__ void __launch_bounds__(D8_THREADS) k_d8(const double* __restrict__ elev, GridDims d,
                                                    uint8_t* __restrict__ ddir, uint8_t* __restrict__ flat,
-                                                   unsigned long long* nflat) {
+                                                   uint32_t* __restrict__ list, unsigned long long cap,
+                                                   int own_lo, int own_hi, DdirCounters* ctr) {
+  __shared__ uint32_t s_ids[D8_STAGE];
+  __shared__ unsigned s_n;
+  __shared__ unsigned long long s_base;
+  if (threadIdx.x == 0) s_n = 0;
+  __syncthreads();
   const int lane = threadIdx.x & 31;
-  const int c = blockIdx.x * D8_THREADS + threadIdx.x + 1;  // column 1 is the aligned one
+  const int c0 = (blockIdx.x * D8_THREADS + threadIdx.x) * D8_CPT + 1;  // column 1 is the aligned one
   const int r0 = blockIdx.y * D8_ROWS;
-  Row3 p = load_row3(elev, d, r0 - 1, c, lane);
-  Row3 q = load_row3(elev, d, r0, c, lane);
-  unsigned cnt = 0;
   const int rend = min(r0 + D8_ROWS, d.NR);
+  const bool live = c0 < d.pitch - LITAP_XOFF;  // the whole warp-row stays inside the row allocation
+  RowWin<D8_CPT> p, q, n, f;
+  if (live) {
+    sw_issue(p, elev, d, r0 - 1, c0, lane);
+    sw_issue(q, elev, d, r0, c0, lane);
+    sw_issue(n, elev, d, r0 + 1, c0, lane);
+  } else {
+#pragma unroll
+    for (int k = 0; k < D8_CPT + 2; ++k) p.v[k] = q.v[k] = n.v[k] = sw_nan();
+  }
+  sw_finish(p, lane);
+  sw_finish(q, lane);
+  sw_finish(n, lane);
   for (int r = r0; r < rend; ++r) {
-    Row3 n = load_row3(elev, d, r + 1, c, lane);
-    double nb[10];
-    nb[7] = p.l; nb[8] = p.m; nb[9] = p.r;
-    nb[4] = q.l; nb[5] = q.m; nb[6] = q.r;
-    nb[1] = n.l; nb[2] = n.m; nb[3] = n.r;
-    int dd = d8_dir(q.m, nb);
-    if (c < d.NC) {
-      size_t i = (size_t)r * d.pitch + c;
-      ddir[i] = (uint8_t)dd;
-      flat[i] = dd == 0 ? 2 : (dd == 5);
-      cnt += (dd == 5);
-      if (c == 1) { ddir[i - 1] = 0; flat[i - 1] = 2; }  // ring column 0 (always NA)
+    if (live && r + 1 < rend) sw_issue(f, elev, d, r + 2, c0, lane);
+    else {
+#pragma unroll
+      for (int k = 0; k < D8_CPT + 2; ++k) f.v[k] = sw_nan();
+    }
+    uchar4 od, of;
+    uint8_t* pd = reinterpret_cast<uint8_t*>(&od);
+    uint8_t* pf = reinterpret_cast<uint8_t*>(&of);
+#pragma unroll
+    for (int j = 0; j < D8_CPT; ++j) {
+      double nb[10];
+      nb[7] = p.v[j]; nb[8] = p.v[j + 1]; nb[9] = p.v[j + 2];
+      nb[4] = q.v[j]; nb[5] = q.v[j + 1]; nb[6] = q.v[j + 2];
+      nb[1] = n.v[j]; nb[2] = n.v[j + 1]; nb[3] = n.v[j + 2];
+      int dd = d8_dir(nb[5], nb);
+      pd[j] = (uint8_t)dd;
+      pf[j] = dd == 0 ? 2 : (dd == 5);
+      if (dd == 5 && c0 + j < d.NC && r >= own_lo && r < own_hi) {  // halo rows of a band are not ours
+        const uint32_t id = (uint32_t)((size_t)r * d.pitch + c0 + j);
+        unsigned k = atomicAdd(&s_n, 1u);
+        if (k < D8_STAGE) s_ids[k] = id;
+        else {  // staging buffer full (very flat block): append directly
+          unsigned long long g = atomicAdd(&ctr->nflat, 1ull);
+          if (g < cap) list[g] = id;
+        }
+      }
+    }
+    if (live) {
+      const size_t i = (size_t)r * d.pitch + c0;
+      *reinterpret_cast<uchar4*>(ddir + i) = od;
+      *reinterpret_cast<uchar4*>(flat + i) = of;
+      if (c0 == 1) { ddir[i - 1] = 0; flat[i - 1] = 2; }  // ring column 0 (always NA)
     }
     p = q;
     q = n;
+    n = f;
+    sw_finish(n, lane);
   }
-  for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-  if (lane == 0 && cnt) atomicAdd(nflat, (unsigned long long)cnt);
-}
-
-// ---- flat worklist -----------------------------------------------------------------------------
-__global__ void k_collect_flats(const uint8_t* __restrict__ ddir, GridDims d, uint32_t* __restrict__ list,
-                                unsigned long long* cursor) {
-  const int lane = threadIdx.x & 31;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x + 1;
-  const int r = blockIdx.y;
-  bool f = (c < d.NC) && ddir[(size_t)r * d.pitch + c] == 5;
-  unsigned m = __ballot_sync(0xffffffffu, f);
-  if (!m) return;
-  unsigned long long base = 0;
-  if (lane == 0) base = atomicAdd(cursor, (unsigned long long)__popc(m));
-  base = __shfl_sync(0xffffffffu, base, 0);
-  if (f) list[base + __popc(m & ((1u << lane) - 1))] = (uint32_t)((size_t)r * d.pitch + c);
+  __syncthreads();
+  const unsigned ns = min(s_n, (unsigned)D8_STAGE);
+  if (threadIdx.x == 0 && ns) s_base = atomicAdd(&ctr->nflat, (unsigned long long)ns);
+  __syncthreads();
+  for (unsigned k = threadIdx.x; k < ns; k += D8_THREADS)
+    if (s_base + k < cap) list[s_base + k] = s_ids[k];
 }
 
 // ---- plateau rounds (Jacobi: probe reads the previous round's ddir, apply writes) ---------------
-__global__ void k_plateau_probe(const uint32_t* __restrict__ list, unsigned n, const uint8_t* __restrict__ ddir,
+// R/flow_01_calc_ddir.R:17-41: a flat cell takes the lowest direction n whose neighbour has the
+// same elevation (elev - elev_n >= 0 can only be equality: no neighbour is lower) and already drains.
+// ddir is re-read across rounds of one launch while other SMs write it: L2 loads (ld.cg), never L1 / nc.
+__device__ __forceinline__ uint8_t plateau_probe_cell(uint32_t id, const uint8_t* ddir,
+                                                      const double* __restrict__ elev, const GridDims& d) {
+  if (__ldcg(ddir + id) != 5) return 0;
+  const double e = elev[id];
+  const int r = id / d.pitch, c = id - r * d.pitch;
+#pragma unroll
+  for (int k = 1; k <= 9; ++k) {
+    if (k == 5) continue;
+    int rr = r + nb_dr(k), cc = c + nb_dc(k);
+    if (rr < 0 || rr >= d.NR || cc < 0 || cc >= d.NC) continue;
+    size_t j = (size_t)rr * d.pitch + cc;
+    double en = elev[j];
+    if (is_nan(en) || !(e - en >= 0)) continue;
+    uint8_t dn = __ldcg(ddir + j);
+    if (dn == 5 || dn == 0) continue;
+    return (uint8_t)k;
+  }
+  return 0;
+}
+
+// all rounds in one cooperative launch (single-device path): no host round trip per round
+__global__ void __launch_bounds__(256) k_plateau_all(const uint32_t* __restrict__ list, unsigned long long cap,
+                                                     uint8_t* ddir, const double* __restrict__ elev, GridDims d,
+                                                     uint8_t* __restrict__ cand, DdirCounters* ctr) {
+  cg::grid_group grid = cg::this_grid();
+  const unsigned long long nf = ctr->nflat;
+  const unsigned n = (unsigned)(nf < cap ? nf : cap);
+  const unsigned stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  for (unsigned round = 0;; ++round) {
+    unsigned* flag = &ctr->changed[round & 1];
+    bool any = false;
+    for (unsigned i = t0; i < n; i += stride) {
+      uint8_t res = plateau_probe_cell(list[i], ddir, elev, d);
+      cand[i] = res;
+      any |= res != 0;
+    }
+    if (__syncthreads_or(any) && threadIdx.x == 0) atomicOr(flag, 1u);
+    if (t0 == 0) ctr->changed[(round + 1) & 1] = 0;  // next round's flag (nobody reads it before the sync)
+    grid.sync();
+    if (!*reinterpret_cast<volatile unsigned*>(flag)) break;
+    for (unsigned i = t0; i < n; i += stride)
+      if (cand[i]) ddir[list[i]] = cand[i];
+    if (t0 == 0) ctr->rounds = round + 1;
+    grid.sync();
+  }
+}
+
+// one round as two launches (row-band mode)
+__global__ void k_plateau_probe(const uint32_t* __restrict__ list, unsigned n, const uint8_t* ddir,
                                 const double* __restrict__ elev, GridDims d, uint8_t* __restrict__ cand,
                                 unsigned* changed) {
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   bool any = false;
   if (i < n) {
-    uint32_t id = list[i];
-    uint8_t res = 0;
-    if (ddir[id] == 5) {
-      const double e = elev[id];
-      const int r = id / d.pitch, c = id % d.pitch;
-#pragma unroll
-      for (int k = 1; k <= 9; ++k) {
-        if (k == 5 || res) continue;
-        int rr = r + nb_dr(k), cc = c + nb_dc(k);
-        if (rr < 0 || rr >= d.NR || cc < 0 || cc >= d.NC) continue;
-        size_t j = (size_t)rr * d.pitch + cc;
-        double en = elev[j];
-        if (is_nan(en) || !(e - en >= 0)) continue;
-        uint8_t dn = ddir[j];
-        if (dn == 5 || dn == 0) continue;
-        res = (uint8_t)k;
-      }
-    }
+    uint8_t res = plateau_probe_cell(list[i], ddir, elev, d);
     cand[i] = res;
     any = res != 0;
   }
-  if (__syncthreads_or(any) && threadIdx.x == 0) atomicAdd(changed, 1u);
+  if (__syncthreads_or(any) && threadIdx.x == 0) atomicOr(changed, 1u);
 }
 __global__ void k_plateau_apply(const uint32_t* __restrict__ list, unsigned n, const uint8_t* __restrict__ cand,
                                 uint8_t* __restrict__ ddir) {
@@ -146,163 +206,282 @@ __global__ void k_plateau_apply(const uint32_t* __restrict__ list, unsigned n, c
   if (i < n && cand[i]) ddir[list[i]] = cand[i];
 }
 
-// ---- flat-pit patch cells: ddir==5 with an 8-neighbour ddir==5 ----------------------------------
-__global__ void k_patch_mark(const uint32_t* __restrict__ list, unsigned n, const uint8_t* __restrict__ ddir,
-                             GridDims d, uint32_t* __restrict__ plist, unsigned* pcount) {
+// ---- flat-pit patches ------------------------------------------------------------------------------
+// A patch cell is a cell that is still ddir == 5 after the plateau rounds and has an 8-neighbour that
+// is also still 5 (R/flow_01_calc_ddir.R:48-57).  Patch cells travel as 64-bit keys (row << 32 | col),
+// rows counted in the whole DEM (row_off = first row of a band), so the resolver below is the same
+// for one device and for the gathered patch cells of all row bands.
+__device__ __forceinline__ unsigned long long pkey(long long r, long long c) {
+  return ((unsigned long long)r << 32) | (unsigned long long)(uint32_t)c;
+}
+
+__global__ void k_patch_mark(const uint32_t* __restrict__ list, unsigned long long cap, const uint8_t* __restrict__ ddir,
+                             GridDims d, long long row_off, unsigned long long* __restrict__ keys, DdirCounters* ctr) {
+  const unsigned long long nf = ctr->nflat;
+  const unsigned n = (unsigned)(nf < cap ? nf : cap);
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    uint32_t id = list[i];
+    if (ddir[id] != 5) continue;
+    const int r = id / d.pitch, c = id - r * d.pitch;
+    bool hit = false;
+#pragma unroll
+    for (int k = 1; k <= 9; ++k) {
+      if (k == 5) continue;
+      int rr = r + nb_dr(k), cc = c + nb_dc(k);
+      if (rr < 0 || rr >= d.NR || cc < 0 || cc >= d.NC) continue;
+      hit |= ddir[(size_t)rr * d.pitch + cc] == 5;
+    }
+    if (hit) keys[atomicAdd(&ctr->npatch, 1u)] = pkey(row_off + r, c);
+  }
+}
+
+// index of `key` in the sorted array K[0..n), or -1
+__device__ __forceinline__ int pfind(const unsigned long long* __restrict__ K, unsigned n, unsigned long long key) {
+  unsigned lo = 0, hi = n;
+  while (lo < hi) {
+    unsigned mid = (lo + hi) >> 1;
+    if (K[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  return (lo < n && K[lo] == key) ? (int)lo : -1;
+}
+
+// lock-free union-find over list positions; the larger root is hooked under the smaller one, so the
+// root of a component is its first cell in (row, col) order = lowest seqno
+__device__ __forceinline__ uint32_t uf_find(uint32_t* parent, uint32_t x) {
+  uint32_t p = *reinterpret_cast<volatile uint32_t*>(parent + x);
+  while (p != x) {
+    uint32_t gp = *reinterpret_cast<volatile uint32_t*>(parent + p);
+    if (gp != p) parent[x] = gp;  // path halving (x is not a root and never becomes one again)
+    x = p;
+    p = gp;
+  }
+  return x;
+}
+__device__ __forceinline__ void uf_unite(uint32_t* parent, uint32_t a, uint32_t b) {
+  while (true) {
+    a = uf_find(parent, a);
+    b = uf_find(parent, b);
+    if (a == b) return;
+    if (a < b) { uint32_t t = a; a = b; b = t; }
+    if (atomicCAS(parent + a, a, b) == a) return;
+  }
+}
+
+__global__ void k_patch_init(unsigned n, uint32_t* parent, unsigned long long* bestd, uint32_t* bestid) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { parent[i] = i; bestd[i] = ~0ull; bestid[i] = 0xFFFFFFFFu; }
+}
+__global__ void k_patch_union(const unsigned long long* __restrict__ K, unsigned n, uint32_t* parent,
+                              uint16_t* __restrict__ opts) {
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t id = list[i];
-  if (ddir[id] != 5) return;
-  const int r = id / d.pitch, c = id % d.pitch;
-  bool hit = false;
+  const long long r = (long long)(K[i] >> 32), c = (long long)(uint32_t)K[i];
+  unsigned o = 0;
 #pragma unroll
   for (int k = 1; k <= 9; ++k) {
     if (k == 5) continue;
-    int rr = r + nb_dr(k), cc = c + nb_dc(k);
-    if (rr < 0 || rr >= d.NR || cc < 0 || cc >= d.NC) continue;
-    hit |= ddir[(size_t)rr * d.pitch + cc] == 5;
+    long long rr = r + nb_dr(k), cc = c + nb_dc(k);
+    if (rr < 0 || cc < 0) continue;
+    int j = pfind(K, n, pkey(rr, cc));
+    if (j < 0) continue;
+    o |= 1u << k;
+    if (k == 6 || k <= 3) uf_unite(parent, i, (uint32_t)j);  // E, SW, S, SE: every adjacency once
   }
-  if (hit) plist[atomicAdd(pcount, 1u)] = id;
+  opts[i] = (uint16_t)o;
 }
-__global__ void k_patch_apply(const uint32_t* __restrict__ ids, const uint8_t* __restrict__ dirs, unsigned n,
-                              uint8_t* __restrict__ ddir) {
+__global__ void k_patch_flatten(const unsigned long long* __restrict__ K, unsigned n, uint32_t* parent,
+                                unsigned long long* __restrict__ kc, unsigned long long* __restrict__ kr) {
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) ddir[ids[i]] = dirs[i];
+  if (i >= n) return;
+  const uint32_t root = uf_find(parent, i);
+  kc[i] = ((unsigned long long)root << 32) | (uint32_t)K[i];          // (component, col)
+  kr[i] = ((unsigned long long)root << 32) | (uint32_t)(K[i] >> 32);  // (component, row); rows < 2^32
 }
-
-// Host part of the patch step: components, median centre, get_dir.  The patch cell set is tiny
-// (a few cells per 10^5) and the reference's rule is a per-patch sequential one
-// (R/flow_01_calc_ddir.R:59-106); only the cell ids travel, never a raster.
-void resolve_patches_host(std::vector<uint32_t>& P, int pitch, std::vector<uint8_t>& newdir) {
-  std::sort(P.begin(), P.end());
-  const size_t n = P.size();
-  newdir.assign(n, 5);
-  std::unordered_map<uint32_t, uint32_t> pos;
-  pos.reserve(n * 2);
-  for (size_t i = 0; i < n; ++i) pos[P[i]] = (uint32_t)i;
-  std::vector<int> comp(n, -1);
-  std::vector<uint32_t> stack, members;
-  std::vector<long long> cols, rows;
-  auto nbr = [&](uint32_t id, int k) -> long long {
-    return (long long)id + (long long)nb_dr(k) * pitch + nb_dc(k);
-  };
-  for (size_t s = 0; s < n; ++s) {
-    if (comp[s] >= 0) continue;
-    members.clear();
-    stack.assign(1, (uint32_t)s);
-    comp[s] = (int)s;
-    while (!stack.empty()) {
-      uint32_t k = stack.back();
-      stack.pop_back();
-      members.push_back(k);
-      for (int dn = 1; dn <= 9; ++dn) {
-        if (dn == 5) continue;
-        auto it = pos.find((uint32_t)nbr(P[k], dn));
-        if (it != pos.end() && comp[it->second] < 0) { comp[it->second] = (int)s; stack.push_back(it->second); }
-      }
-    }
-    std::sort(members.begin(), members.end());  // ascending cell id == ascending seqno
-    cols.clear(); rows.clear();
-    for (uint32_t k : members) { cols.push_back(P[k] % pitch + 1); rows.push_back(P[k] / pitch + 1); }
-    auto ceil_median2 = [](std::vector<long long> v) {  // ceiling(median(v)) for integers
-      std::sort(v.begin(), v.end());
-      size_t m = v.size();
-      if (m % 2) return v[m / 2];
-      long long s2 = v[m / 2 - 1] + v[m / 2];  // median = s2/2; coordinates are positive
-      return (s2 + 1) / 2;
-    };
-    long long cc = ceil_median2(cols), cr = ceil_median2(rows);
-    long long best = -1;
-    uint32_t centre = members[0];
-    for (size_t t = 0; t < members.size(); ++t) {
-      long long dd = (cols[t] - cc) * (cols[t] - cc) + (rows[t] - cr) * (rows[t] - cr);
-      if (best < 0 || dd < best) { best = dd; centre = members[t]; }  // first minimum = lowest seqno
-    }
-    long long row_f = P[centre] / pitch + 1, col_f = P[centre] % pitch + 1;
-    for (uint32_t k : members) {
-      unsigned opts = 0;
-      for (int dn = 1; dn <= 9; ++dn) {
-        if (dn == 5) continue;
-        if (pos.count((uint32_t)nbr(P[k], dn))) opts |= 1u << dn;
-      }
-      newdir[k] = (uint8_t)get_dir_int(P[k] / pitch + 1, P[k] % pitch + 1, row_f, col_f, opts);
-    }
+// ceiling(median(.)) of the cols and of the rows of every component (R/flow_01_calc_ddir.R:78)
+__global__ void k_patch_median(const unsigned long long* __restrict__ kc, const unsigned long long* __restrict__ kr,
+                               unsigned n, uint32_t* __restrict__ medc, uint32_t* __restrict__ medr) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t root = (uint32_t)(kc[i] >> 32);
+  if (i > 0 && (uint32_t)(kc[i - 1] >> 32) == root) return;  // not the head of its segment
+  unsigned lo = i, hi = n;  // first index whose component is > root
+  while (lo < hi) {
+    unsigned mid = (lo + hi) >> 1;
+    if ((uint32_t)(kc[mid] >> 32) <= root) lo = mid + 1; else hi = mid;
   }
+  const unsigned m = lo - i, a = i + (m - 1) / 2, b = i + m / 2;
+  // median of an even count = mean of the middle two; coordinates are non-negative integers
+  medc[root] = (uint32_t)(((unsigned long long)(uint32_t)kc[a] + (uint32_t)kc[b] + 1) / 2);
+  medr[root] = (uint32_t)(((unsigned long long)(uint32_t)kr[a] + (uint32_t)kr[b] + 1) / 2);
+}
+__device__ __forceinline__ unsigned long long pdist2(unsigned long long key, uint32_t cc, uint32_t cr) {
+  long long dc = (long long)(uint32_t)key - (long long)cc, dr = (long long)(key >> 32) - (long long)cr;
+  return (unsigned long long)(dc * dc + dr * dr);
+}
+// centre cell = smallest Euclidean distance to (medc, medr), first in seqno order (R/flow_01_calc_ddir.R:80-86)
+__global__ void k_patch_best(const unsigned long long* __restrict__ K, unsigned n, uint32_t* parent,
+                             const uint32_t* __restrict__ medc, const uint32_t* __restrict__ medr,
+                             unsigned long long* bestd, uint32_t* bestid, int pass) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t root = uf_find(parent, i);
+  const unsigned long long d2 = pdist2(K[i], medc[root], medr[root]);
+  if (pass == 0) atomicMin(bestd + root, d2);
+  else if (d2 == bestd[root]) atomicMin(bestid + root, i);
+}
+__global__ void k_patch_dirs(const unsigned long long* __restrict__ K, unsigned n, uint32_t* parent,
+                             const uint32_t* __restrict__ bestid, const uint16_t* __restrict__ opts,
+                             uint8_t* __restrict__ newdir) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long kf = K[bestid[uf_find(parent, i)]];
+  newdir[i] = (uint8_t)get_dir_int((long long)(K[i] >> 32) + 1, (long long)(uint32_t)K[i] + 1,
+                                   (long long)(kf >> 32) + 1, (long long)(uint32_t)kf + 1, opts[i]);
+}
+__global__ void k_patch_apply(const unsigned long long* __restrict__ K, const uint8_t* __restrict__ newdir, unsigned n,
+                              uint8_t* __restrict__ ddir, GridDims d, long long row_off, int own_lo, int own_hi) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long r = (long long)(K[i] >> 32) - row_off;
+  if (r < own_lo || r >= own_hi) return;  // another band's cell
+  ddir[(size_t)r * d.pitch + (uint32_t)K[i]] = newdir[i];
 }
 
 }  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// host side
+namespace {
+inline unsigned nblk(size_t n, unsigned t = 256) { return (unsigned)((n + t - 1) / t); }
+
+// per-grid worklists of calc_ddir2 (kept on the grid between the steps of the row-band protocol)
+int ddir_ensure(litap_grid* g, size_t cap) {
+  const GridDims d = g->d;
+  if (!g->ddir) g->ddir = grid_alloc_array<uint8_t>(d, 0);
+  if (!g->flat) g->flat = grid_alloc_array<uint8_t>(d, 2);
+  if (!g->ddir || !g->flat) return set_error(LITAP_ENOMEM, "device allocation failed (ddir)");
+  if (!g->dd_ctr) g->dd_ctr = pool_alloc(sizeof(DdirCounters));
+  if (!g->dd_ctr) return set_error(LITAP_ENOMEM, "device allocation failed (ddir counters)");
+  if (cap > g->dd_cap) {
+    if (g->dd_list) pool_free(g->dd_list);
+    if (g->dd_cand) pool_free(g->dd_cand);
+    if (g->dd_keys) pool_free(g->dd_keys);
+    g->dd_list = (uint32_t*)pool_alloc(cap * sizeof(uint32_t));
+    g->dd_cand = (uint8_t*)pool_alloc(cap);
+    g->dd_keys = (unsigned long long*)pool_alloc(cap * sizeof(unsigned long long));
+    g->dd_cap = (g->dd_list && g->dd_cand && g->dd_keys) ? cap : 0;
+    if (!g->dd_cap) return set_error(LITAP_ENOMEM, "device allocation failed (flat worklist)");
+  }
+  return LITAP_OK;
+}
+inline size_t ddir_default_cap(const GridDims& d) { return (size_t)d.cells / 8 + 4096; }
+
+int launch_d8(litap_grid* g) {
+  const GridDims d = g->d;
+  dim3 grid(nblk((size_t)(d.pitch - LITAP_XOFF + D8_CPT - 1) / D8_CPT, D8_THREADS), (d.NR + D8_ROWS - 1) / D8_ROWS);
+  KERNEL("k_d8", k_d8<<<grid, D8_THREADS, 0, ctx().stream>>>(g->elev, d, g->ddir, g->flat, g->dd_list,
+                                                              (unsigned long long)g->dd_cap, g->own_lo, g->own_hi,
+                                                              (DdirCounters*)g->dd_ctr));
+  return LITAP_OK;
+}
+}  // namespace
+
+// Resolve flat-pit patches given the UNSORTED keys of all patch cells (device array, np entries);
+// on return *K_out / *dirs_out (scratch-owned device arrays) hold the sorted keys and the new
+// direction of every patch cell.
+int ddir_patch_resolve(const unsigned long long* keys, unsigned np, PoolScratch& S, unsigned long long** K_out,
+                       uint8_t** dirs_out) {
+  cudaStream_t st = ctx().stream;
+  unsigned long long* K = S.get<unsigned long long>(np);
+  unsigned long long* kc = S.get<unsigned long long>(np);
+  unsigned long long* kr = S.get<unsigned long long>(np);
+  unsigned long long* kc2 = S.get<unsigned long long>(np);
+  unsigned long long* kr2 = S.get<unsigned long long>(np);
+  unsigned long long* bestd = S.get<unsigned long long>(np);
+  uint32_t* parent = S.get<uint32_t>(np);
+  uint32_t* bestid = S.get<uint32_t>(np);
+  uint32_t* medc = S.get<uint32_t>(np);
+  uint32_t* medr = S.get<uint32_t>(np);
+  uint16_t* opts = S.get<uint16_t>(np);
+  uint8_t* newdir = S.get<uint8_t>(np);
+  size_t tmpn = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, tmpn, keys, K, (int)np, 0, 64, st);
+  void* tmp = S.get<unsigned char>(tmpn + 256);
+  if (!K || !kc || !kr || !kc2 || !kr2 || !bestd || !parent || !bestid || !medc || !medr || !opts || !newdir || !tmp)
+    return set_error(LITAP_ENOMEM, "device allocation failed (patch scratch)");
+  const unsigned nb = nblk(np);
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, keys, K, (int)np, 0, 64, st));
+  KERNEL("k_patch_init", k_patch_init<<<nb, 256, 0, st>>>(np, parent, bestd, bestid));
+  KERNEL("k_patch_union", k_patch_union<<<nb, 256, 0, st>>>(K, np, parent, opts));
+  KERNEL("k_patch_flatten", k_patch_flatten<<<nb, 256, 0, st>>>(K, np, parent, kc, kr));
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, kc, kc2, (int)np, 0, 64, st));
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, kr, kr2, (int)np, 0, 64, st));
+  KERNEL("k_patch_median", k_patch_median<<<nb, 256, 0, st>>>(kc2, kr2, np, medc, medr));
+  KERNEL("k_patch_best", k_patch_best<<<nb, 256, 0, st>>>(K, np, parent, medc, medr, bestd, bestid, 0));
+  KERNEL("k_patch_best", k_patch_best<<<nb, 256, 0, st>>>(K, np, parent, medc, medr, bestd, bestid, 1));
+  KERNEL("k_patch_dirs", k_patch_dirs<<<nb, 256, 0, st>>>(K, np, parent, bestid, opts, newdir));
+  ctx().launches += 3;  // cub sorts (at least)
+  *K_out = K;
+  *dirs_out = newdir;
+  return LITAP_OK;
+}
 
 int run_ddir(litap_grid* g, int invert) {
   Ctx& c = ctx();
   const GridDims d = g->d;
   cudaStream_t st = c.stream;
-  if (!g->ddir) g->ddir = grid_alloc_array<uint8_t>(d, 0);
-  if (!g->flat) g->flat = grid_alloc_array<uint8_t>(d, 2);
-  if (!g->ddir || !g->flat) return set_error(LITAP_ENOMEM, "device allocation failed (ddir)");
-  // scratch: [0] flat count, [1] cursor, [2] elev max, [3] changed/pcount (as 2 x u32)
-  unsigned long long* scr = (unsigned long long*)pool_alloc(8 * sizeof(unsigned long long));
-  if (!scr) return set_error(LITAP_ENOMEM, "device allocation failed (scratch)");
-  struct Free { void* p; ~Free() { if (p) pool_free(p); } } f_scr{scr};
-  CUDA_TRY(cudaMemsetAsync(scr, 0, 8 * sizeof(unsigned long long), st));
-
+  int rc = ddir_ensure(g, g->dd_cap ? g->dd_cap : ddir_default_cap(d));
+  if (rc) return rc;
+  DdirCounters* ctr = (DdirCounters*)g->dd_ctr;
   if (invert) {
-    dim3 gb((d.NC + 255) / 256 < 64 ? (d.NC + 255) / 256 : 64, d.NR < 1024 ? d.NR : 1024);
-    KERNEL("k_elev_max", k_elev_max<<<gb, 256, 0, st>>>(g->elev, d, scr + 2));
-    dim3 gi((d.NC + 31 + 255) / 256, d.NR);
-    KERNEL("k_invert", k_invert<<<gi, 256, 0, st>>>(g->elev, d, scr + 2));
+    CUDA_TRY(cudaMemsetAsync(ctr, 0, sizeof(DdirCounters), st));
+    dim3 gb(nblk(d.NC) < 64 ? nblk(d.NC) : 64, d.NR < 1024 ? d.NR : 1024);
+    KERNEL("k_elev_max", k_elev_max<<<gb, 256, 0, st>>>(g->elev, d, 0, d.NR, &ctr->elev_max));
+    dim3 gi(nblk((size_t)d.NC + 31), d.NR);
+    KERNEL("k_invert", k_invert<<<gi, 256, 0, st>>>(g->elev, d, &ctr->elev_max));
   }
-  {
-    dim3 grid((d.NC - 1 + D8_THREADS - 1) / D8_THREADS, (d.NR + D8_ROWS - 1) / D8_ROWS);
-    KERNEL("k_d8", k_d8<<<grid, D8_THREADS, 0, st>>>(g->elev, d, g->ddir, g->flat, scr));
+  static int coop_blocks = 0;
+  if (!coop_blocks) {
+    int per_sm = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plateau_all, 256, 0));
+    if (per_sm < 1) return set_error(LITAP_ECUDA, "k_plateau_all cannot be made resident");
+    coop_blocks = c.sm_count * (per_sm < 2 ? per_sm : 2);
   }
-  unsigned long long nflat = 0;
-  CUDA_TRY(cudaMemcpyAsync(&nflat, scr, sizeof(nflat), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  c.tm.flat_cells = (int64_t)nflat;
-  c.tm.plateau_rounds = 0;
-  c.tm.patch_cells = 0;
-  if (nflat == 0) return LITAP_OK;
-  if (nflat > 0xFFFFFFF0ull) return set_error(LITAP_EARG, "too many flat cells");
-  const unsigned n = (unsigned)nflat;
-  uint32_t* list = (uint32_t*)pool_alloc((size_t)n * sizeof(uint32_t));
-  uint32_t* plist = (uint32_t*)pool_alloc((size_t)n * sizeof(uint32_t));
-  uint8_t* cand = (uint8_t*)pool_alloc((size_t)n);
-  Free f1{list}, f2{plist}, f3{cand};
-  if (!list || !plist || !cand) return set_error(LITAP_ENOMEM, "device allocation failed (flat worklist)");
-  {
-    dim3 grid((d.NC - 1 + 255) / 256, d.NR);
-    KERNEL("k_collect_flats", k_collect_flats<<<grid, 256, 0, st>>>(g->ddir, d, list, scr + 1));
-  }
-  unsigned* changed = (unsigned*)(scr + 3);
-  const unsigned nblk = (n + 255) / 256;
-  // Every flat cell that can drain is at BFS distance <= nflat from a draining cell.
-  for (unsigned round = 0; round <= n; ++round) {
-    CUDA_TRY(cudaMemsetAsync(changed, 0, sizeof(unsigned), st));
-    KERNEL("k_plateau_probe", k_plateau_probe<<<nblk, 256, 0, st>>>(list, n, g->ddir, g->elev, d, cand, changed));
-    unsigned h = 0;
-    CUDA_TRY(cudaMemcpyAsync(&h, changed, sizeof(h), cudaMemcpyDeviceToHost, st));
+  DdirCounters h;
+  for (int attempt = 0;; ++attempt) {
+    CUDA_TRY(cudaMemsetAsync(ctr, 0, sizeof(DdirCounters), st));
+    rc = launch_d8(g);
+    if (rc) return rc;
+    {
+      unsigned long long cap = g->dd_cap;
+      GridDims dd = d;
+      void* args[] = {(void*)&g->dd_list, (void*)&cap, (void*)&g->ddir, (void*)&g->elev, (void*)&dd,
+                      (void*)&g->dd_cand, (void*)&ctr};
+      ProfScope prof("k_plateau_all");
+      CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_plateau_all, dim3(coop_blocks), dim3(256), args, 0, st));
+      c.launches++;
+    }
+    KERNEL("k_patch_mark", k_patch_mark<<<c.sm_count * 4, 256, 0, st>>>(g->dd_list, (unsigned long long)g->dd_cap, g->ddir,
+                                                                       d, g->row_off, g->dd_keys, ctr));
+    CUDA_TRY(cudaMemcpyAsync(&h, ctr, sizeof(h), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    if (!h) break;
-    KERNEL("k_plateau_apply", k_plateau_apply<<<nblk, 256, 0, st>>>(list, n, cand, g->ddir));
-    c.tm.plateau_rounds++;
+    if (h.nflat <= g->dd_cap) break;
+    if (attempt) return set_error(LITAP_ECUDA, "internal: flat worklist overflow after regrowth");
+    rc = ddir_ensure(g, (size_t)h.nflat + 4096);  // unusually flat DEM: regrow the worklist and redo
+    if (rc) return rc;
   }
-  unsigned* pcount = changed + 1;
-  KERNEL("k_patch_mark", k_patch_mark<<<nblk, 256, 0, st>>>(list, n, g->ddir, d, plist, pcount));
-  unsigned np = 0;
-  CUDA_TRY(cudaMemcpyAsync(&np, pcount, sizeof(np), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  c.tm.patch_cells = np;
-  if (np) {
-    std::vector<uint32_t> P(np);
-    std::vector<uint8_t> nd;
-    CUDA_TRY(cudaMemcpyAsync(P.data(), plist, (size_t)np * 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
-    resolve_patches_host(P, d.pitch, nd);
-    // ids are relative to the XOFF-shifted pointer on both sides (plist was built from it)
-    CUDA_TRY(cudaMemcpyAsync(plist, P.data(), (size_t)np * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(cand, nd.data(), (size_t)np, cudaMemcpyHostToDevice, st));
-    KERNEL("k_patch_apply", k_patch_apply<<<(np + 255) / 256, 256, 0, st>>>(plist, cand, np, g->ddir));
-    CUDA_TRY(cudaStreamSynchronize(st));  // P / nd are stack-owned
+  c.tm.flat_cells = (int64_t)h.nflat;
+  c.tm.plateau_rounds = (int)h.rounds;
+  c.tm.patch_cells = h.npatch;
+  if (h.npatch) {
+    PoolScratch S;
+    unsigned long long* K = nullptr;
+    uint8_t* nd = nullptr;
+    rc = ddir_patch_resolve(g->dd_keys, h.npatch, S, &K, &nd);
+    if (rc) return rc;
+    KERNEL("k_patch_apply", k_patch_apply<<<nblk(h.npatch), 256, 0, st>>>(K, nd, h.npatch, g->ddir, d, g->row_off,
+                                                                         g->own_lo, g->own_hi));
+    CUDA_TRY(cudaStreamSynchronize(st));  // scratch goes back to the pool
   }
   return LITAP_OK;
 }

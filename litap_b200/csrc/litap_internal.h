@@ -54,6 +54,17 @@ struct litap_grid {
   double* weti[4] = {nullptr, nullptr, nullptr, nullptr};
   int64_t npits = 0;
   bool have_ddir = false, have_shed = false;
+  // row-band geometry: rows [own_lo, own_hi) are this grid's own cells; row 0 / NR-1 are the NA ring
+  // of the DEM or halo rows of the neighbouring bands; row_off = DEM row of local row 0
+  int own_lo = 0, own_hi = 0;
+  long long row_off = 0;
+  bool halo_top = false, halo_bot = false;
+  // calc_ddir2 worklists (ddir.cu)
+  uint32_t* dd_list = nullptr;
+  uint8_t* dd_cand = nullptr;
+  unsigned long long* dd_keys = nullptr;
+  void* dd_ctr = nullptr;
+  size_t dd_cap = 0;
 };
 
 // ---- context ----------------------------------------------------------------------------------
@@ -88,6 +99,18 @@ inline void grid_free_array(T*& p) {
   if (p) pool_free((void*)(p - LITAP_XOFF));
   p = nullptr;
 }
+
+// scope-owned pool allocations (returned to the pool when the scope dies; sync the stream first)
+#include <vector>
+struct PoolScratch {
+  std::vector<void*> ptrs;
+  ~PoolScratch() { for (void* p : ptrs) pool_free(p); }
+  template <typename T> T* get(size_t n) {
+    T* p = (T*)pool_alloc((n ? n : 1) * sizeof(T));
+    if (p) ptrs.push_back(p);
+    return p;
+  }
+};
 
 #define CUDA_TRY(expr)                                                                      \
   do {                                                                                      \
