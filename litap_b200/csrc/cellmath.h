@@ -127,6 +127,24 @@ struct FormOut { double slope_pct, slope_deg, aspect, prof, plan; };
 
 LITAP_HD double form_rad_deg(double x) { return (x * 180) / 3.14159265358979323846; }
 
+// numerator (2*z5 - z1 - z2) of the curvature along aspect line A (R/form_01_calc_form.R:87-106)
+LITAP_HD double form_curv_num(int A, const double* z, const double* sin_t, const double* cos_t) {
+  double sn = sin_t[A], cs = cos_t[A];
+  double x1 = 2 + sn, y1 = 2 - cs, x2 = 2 - sn, y2 = 2 + cs;
+  // the two branches of the reference (A <= 90 / A > 90) are the same expression tree on different
+  // operands: select the operands, evaluate the tree once (no divergence between lanes)
+  const bool lo = A <= 90;
+  const double a9 = lo ? z[9] : z[6], a8 = lo ? z[8] : z[5], a6 = lo ? z[6] : z[3], a5 = lo ? z[5] : z[2];
+  const double w1 = (lo ? 2 : 3) - y1, w2 = y1 - (lo ? 1 : 2);
+  const double b5 = lo ? z[5] : z[8], b4 = lo ? z[4] : z[7], b2 = lo ? z[2] : z[5], b1 = lo ? z[1] : z[4];
+  const double v1 = (lo ? 3 : 2) - y2, v2 = y2 - (lo ? 2 : 1);
+  double z1 = w1 * ((a9 * (x1 - 2)) + (a8 * (3 - x1)));
+  z1 = z1 + (w2 * ((a6 * (x1 - 2)) + (a5 * (3 - x1))));
+  double z2 = v1 * ((b5 * (x2 - 1)) + (b4 * (2 - x2)));
+  z2 = z2 + (v2 * ((b2 * (x2 - 1)) + (b1 * (2 - x2))));
+  return (2 * z[5]) - z1 - z2;
+}
+
 LITAP_HD double form_curv(int A, const double* z, double grid, double sp, const double* sin_t, const double* cos_t) {
   double sn = sin_t[A], cs = cos_t[A];
   double x1 = 2 + sn, y1 = 2 - cs, x2 = 2 - sn, y2 = 2 + cs;
@@ -187,4 +205,144 @@ LITAP_HD FormOut form_cell(const double* e, double grid, const double* sin_t, co
   o.slope_deg = r_round3(sd);
   o.aspect = as;
   return o;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fast path of calc_form.  Every output of calc_form is a rounded number (3 decimals, or an integer
+// for aspect), so the reference's value is determined by the INTEGER k = round(1000 v) (or
+// round(aspect)).  The fast path evaluates v with cheap fp64 arithmetic (reciprocal multiplies, a
+// degree-9 arctangent polynomial; relative error < 1e-13, far below the margins used here), decides
+// k, and returns false ("in doubt") whenever v is so close to a rounding boundary that the reference
+// expression tree could decide differently; the caller then runs form_cell() (the reference's
+// tree) for that cell.  When it returns true the outputs are bit-identical with form_cell():
+// k/1000 is produced with the IEEE-correct quotient (div1000, verified exhaustively for k < 2^32).
+#if defined(__CUDA_ARCH__)
+#define LITAP_WARP_ANY(c) __any_sync(__activemask(), (c))
+#else
+#define LITAP_WARP_ANY(c) (c)
+#endif
+struct FormK {
+  double grid, inv2g, invg2;  // grid, 1/(2 grid), 1/(grid*grid)
+};
+
+// RN(k / 1000) for an integer-valued double 0 <= k < 2^32, without a division
+LITAP_HD double div1000(double k) {
+  double q = k * 0.001;
+  double r = fma(-q, 1000.0, k);
+  return fma(r, 0.001, q);
+}
+// reciprocal with relative error ~1e-16 for 1e-30 <= x <= 1e30
+LITAP_HD double fast_rcp(double x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"((float)x));
+#else
+  float r = 1.0f / (float)x;
+#endif
+  double y = (double)r;
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  return y;
+}
+// atan(y) for |y| <= tan(pi/8) * 1.01: y * P(y^2), P of degree 9 (max relative error 1.3e-15)
+LITAP_HD double fast_atan_core(double y) {
+  double t = y * y;
+  double p = -0.02496927912537512;
+  p = fma(p, t, 0.04999137488007895);
+  p = fma(p, t, -0.0649812787648163);
+  p = fma(p, t, 0.0767224153108192);
+  p = fma(p, t, -0.09089406239578209);
+  p = fma(p, t, 0.11111041936867709);
+  p = fma(p, t, -0.14285712445599388);
+  p = fma(p, t, 0.1999999997503182);
+  p = fma(p, t, -0.33333333333201454);
+  p = fma(p, t, 0.9999999999999989);
+  return y * p;
+}
+// atan(a) for 0 <= a <= 1e30
+LITAP_HD double fast_atan_pos(double a) {
+  // slope and curvature arguments are almost always below tan(pi/8): the two reductions sit behind
+  // warp-uniform branches so that they cost nothing when no lane needs them
+  bool inv = false;
+  double off = 0.0;
+  if (LITAP_WARP_ANY(a > 0.41421356237309503)) {
+    if (LITAP_WARP_ANY(a > 1.0)) {
+      inv = a > 1.0;
+      if (inv) a = fast_rcp(a);
+    }
+    if (a > 0.41421356237309503) {
+      a = (a - 1.0) * fast_rcp(a + 1.0);
+      off = 0.78539816339744831;
+    }
+  }
+  double r = off + fast_atan_core(a);
+  return inv ? 1.5707963267948966 - r : r;
+}
+// round(v, 3) when v is safely away from a rounding boundary; false = in doubt
+LITAP_HD bool fast_round3(double v, double* out) {
+  const double a = fabs(v);
+  const double t = a * 1000.0;
+  const double k = rint(t);
+  const double dist = fabs(t - k);
+  // in doubt: near a half, beyond the verified range of div1000, or NaN (every comparison false)
+  if (!(dist <= 0.5 - (1e-9 + t * 2e-11) && t < 4.0e9)) return false;
+  *out = copysign(div1000(k), v);  // v == 0 keeps its sign like the reference (returns x itself)
+  return true;
+}
+
+LITAP_HD bool form_cell_fast(const double* e, const FormK& K, const double* sin_t, const double* cos_t, FormOut* o) {
+  const double NA = NAN;
+  bool any_na = false;
+  double z[10];
+#pragma unroll
+  for (int n = 1; n <= 9; ++n) {
+    any_na |= is_nan(e[n]);
+    z[n] = e[n] * 100;
+  }
+  if (any_na) {
+    o->slope_pct = NA; o->slope_deg = NA; o->prof = NA; o->plan = NA;
+    o->aspect = is_nan(e[5]) ? NA : 360.0;
+    return true;
+  }
+  const double sx = (z[6] - z[4]) * K.inv2g, sy = (z[2] - z[8]) * K.inv2g;
+  const double ax = sx < 0 ? -sx : sx, ay = sy < 0 ? -sy : sy;
+  const double mn = ax < ay ? ax : ay, mx = ax < ay ? ay : ax;
+  if (!(mx > 1e-30 && mx < 1e30)) return false;  // flat window (slope 0) or absurd values: reference tree
+  const double sp = sqrt(sx * sx + sy * sy);
+  const double DEG = 57.295779513082323;
+  if (!fast_round3(sp, &o->slope_pct)) return false;
+  if (!fast_round3(fast_atan_pos(sp * 0.01) * DEG, &o->slope_deg)) return false;
+  // aspect (R/form_01_calc_form.R:71-80): la = acos(|sx|/sp) = atan(|sy|/|sx|); with sx or sy exactly 0
+  // (common on quantised DEMs) the table gives 90 / 270 / 180 / 360 = the same formula with la = 0 or 90
+  double la = 0.0;
+  if (mn > 0) la = fast_atan_pos(mn * fast_rcp(mx));
+  if (ay > ax) la = 1.5707963267948966 - la;
+  la *= DEG;
+  double as_hat = sx > 0 ? (sy > 0 ? 270 + la : 270 - la) : (sy > 0 ? 90 - la : 90 + la);
+  if (sx == 0) as_hat = sy < 0 ? 180 : 360;
+  if (sy == 0) as_hat = sx < 0 ? 90 : 270;
+  const double as = rint(as_hat);
+  double da = as_hat - as;
+  if (da < 0) da = -da;
+  if (da > 0.5 - 1e-6) return false;
+  const double pa = as > 180 ? as - 180 : as;
+  const double pl = (pa + 90) > 180 ? pa + 90 - 180 : pa + 90;
+  {
+    double c = form_curv_num((int)pa, z, sin_t, cos_t) * K.invg2;
+    double a = c < 0 ? -c : c;
+    if (!(a < 1e30)) return false;
+    double v = fast_atan_pos(a) * DEG;
+    if (!fast_round3(c < 0 ? -v : v, &o->prof)) return false;
+  }
+  {
+    double c = form_curv_num((int)pl, z, sin_t, cos_t) * K.invg2;
+    double a = c < 0 ? -c : c;
+    if (!(a < 1e30)) return false;
+    double v = fast_atan_pos(a) * DEG;
+    if (!fast_round3(c < 0 ? -v : v, &o->plan)) return false;
+  }
+  o->aspect = as;
+  return true;
 }

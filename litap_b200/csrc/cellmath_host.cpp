@@ -46,4 +46,31 @@ void host_form_raw(const double* elev, long long NR, long long NC, double grid, 
       out5[3 * NB + i] = o.prof; out5[4 * NB + i] = o.plan;
     }
 }
+// fast path vs reference tree on every window: out[0] = windows the fast path decided, out[1] = of those,
+// windows whose outputs differ in any bit from form_cell()
+void host_form_fast_check(const double* elev, long long NR, long long NC, double grid, long long* out) {
+  double st[181], ct[181];
+  host_fill_trig(st, ct);
+  FormK K;
+  K.grid = grid; K.inv2g = 1.0 / (2 * grid); K.invg2 = 1.0 / (grid * grid);
+  long long nfast = 0, nbad = 0;
+  for (long long r = 0; r < NR; ++r)
+    for (long long c = 0; c < NC; ++c) {
+      double e[10];
+      for (int n = 1; n <= 9; ++n) {
+        long long rr = r + nb_dr(n), cc = c + nb_dc(n);
+        e[n] = (rr < 0 || cc < 0 || rr >= NR || cc >= NC) ? NAN : elev[rr * NC + cc];
+      }
+      FormOut a, b = form_cell(e, grid, st, ct);
+      if (!form_cell_fast(e, K, st, ct, &a)) continue;
+      ++nfast;
+      const double av[5] = {a.slope_pct, a.slope_deg, a.aspect, a.prof, a.plan};
+      const double bv[5] = {b.slope_pct, b.slope_deg, b.aspect, b.prof, b.plan};
+      bool same = true;
+      for (int k = 0; k < 5; ++k) same &= (av[k] == bv[k]) || (av[k] != av[k] && bv[k] != bv[k]);
+      nbad += !same;
+    }
+  out[0] = nfast;
+  out[1] = nbad;
+}
 }

@@ -5,69 +5,91 @@
 #include <cmath>
 #include "cellmath.h"
 #include "litap_internal.h"
+#include "stencil.cuh"
 
 namespace {
 
+constexpr int FORM_CPT = 2;       // columns per thread: 16-byte loads and stores
 constexpr int FORM_ROWS = 16;
-constexpr int FORM_THREADS = 128;
+constexpr int FORM_THREADS = 128;  // 256 columns per block
 
 struct FormPtrs { double* o[5]; };
-struct Row3 { double l, m, r; };
 // replicated lines: out(r, c) takes the window of (mapr(r), mapc(c)); the maps differ from the
 // identity on at most two rows and two columns, simulated on the host in the reference's order.
 struct EdgeMap { int dst_c[2], src_c[2], dst_r[2], src_r[2]; };
 
-__device__ __forceinline__ Row3 load_row3(const double* __restrict__ elev, const GridDims& d, int r, int c, int lane) {
-  const double NA = __longlong_as_double(0x7ff8000000000000LL);
-  Row3 w;
-  const bool rv = (r >= 0 && r < d.NR);
-  const double* row = elev + (size_t)(rv ? r : 0) * d.pitch;
-  w.m = (rv && c < d.NC) ? __ldg(row + c) : NA;
-  w.l = __shfl_up_sync(0xffffffffu, w.m, 1);
-  w.r = __shfl_down_sync(0xffffffffu, w.m, 1);
-  if (lane == 0) w.l = (rv && c - 1 >= 0 && c - 1 < d.NC) ? __ldg(row + c - 1) : NA;
-  if (lane == 31) w.r = (rv && c + 1 < d.NC) ? __ldg(row + c + 1) : NA;
-  return w;
+// NA -> 0 where the cell itself has an elevation; aspect keeps its value (:60-65)
+__device__ __forceinline__ void finalise(FormOut& o, bool elev_ok) {
+  if (elev_ok) {
+    if (is_nan(o.slope_pct)) o.slope_pct = 0.0;
+    if (is_nan(o.slope_deg)) o.slope_deg = 0.0;
+    if (is_nan(o.prof)) o.prof = 0.0;
+    if (is_nan(o.plan)) o.plan = 0.0;
+  }
 }
-
-__device__ __forceinline__ void store_final(const FormPtrs& P, size_t i, const FormOut& o, bool elev_ok) {
-  // NA -> 0 where the cell itself has an elevation; aspect keeps its value (:60-65)
-  P.o[0][i] = (elev_ok && is_nan(o.slope_pct)) ? 0.0 : o.slope_pct;
-  P.o[1][i] = (elev_ok && is_nan(o.slope_deg)) ? 0.0 : o.slope_deg;
+__device__ __forceinline__ void store_final(const FormPtrs& P, size_t i, FormOut o, bool elev_ok) {
+  finalise(o, elev_ok);
+  P.o[0][i] = o.slope_pct;
+  P.o[1][i] = o.slope_deg;
   P.o[2][i] = o.aspect;
-  P.o[3][i] = (elev_ok && is_nan(o.prof)) ? 0.0 : o.prof;
-  P.o[4][i] = (elev_ok && is_nan(o.plan)) ? 0.0 : o.plan;
+  P.o[3][i] = o.prof;
+  P.o[4][i] = o.plan;
 }
 
-__global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict__ elev, GridDims d, double grid,
+__global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict__ elev, GridDims d, FormK K,
                                                        const double* __restrict__ trig, FormPtrs P) {
   __shared__ double s_sin[181], s_cos[181];
   for (int i = threadIdx.x; i < 181; i += FORM_THREADS) { s_sin[i] = trig[i]; s_cos[i] = trig[181 + i]; }
   __syncthreads();
   const int lane = threadIdx.x & 31;
-  const int c = blockIdx.x * FORM_THREADS + threadIdx.x + 1;
+  const int c0 = (blockIdx.x * FORM_THREADS + threadIdx.x) * FORM_CPT + 1;  // column 1 is the aligned one
   const int r0 = blockIdx.y * FORM_ROWS;
-  Row3 p = load_row3(elev, d, r0 - 1, c, lane);
-  Row3 q = load_row3(elev, d, r0, c, lane);
   const int rend = min(r0 + FORM_ROWS, d.NR);
-  for (int r = r0; r < rend; ++r) {
-    Row3 n = load_row3(elev, d, r + 1, c, lane);
-    double e[10];
-    e[7] = p.l; e[8] = p.m; e[9] = p.r;
-    e[4] = q.l; e[5] = q.m; e[6] = q.r;
-    e[1] = n.l; e[2] = n.m; e[3] = n.r;
-    if (c < d.NC) {
-      FormOut o = form_cell(e, grid, s_sin, s_cos);
-      size_t i = (size_t)r * d.pitch + c;
-      store_final(P, i, o, !is_nan(q.m));
-      if (c == 1) {  // ring column 0: NA everywhere
-        const double NA = __longlong_as_double(0x7ff8000000000000LL);
+  const bool live = c0 < d.pitch - LITAP_XOFF;
+  RowWin<FORM_CPT> p, q, n, f;
+  if (live) {
+    sw_issue(p, elev, d, r0 - 1, c0, lane);
+    sw_issue(q, elev, d, r0, c0, lane);
+    sw_issue(n, elev, d, r0 + 1, c0, lane);
+  } else {
 #pragma unroll
-        for (int k = 0; k < 5; ++k) P.o[k][i - 1] = NA;
+    for (int k = 0; k < FORM_CPT + 2; ++k) p.v[k] = q.v[k] = n.v[k] = sw_nan();
+  }
+  sw_finish(p, lane);
+  sw_finish(q, lane);
+  sw_finish(n, lane);
+  for (int r = r0; r < rend; ++r) {
+    if (live && r + 1 < rend) sw_issue(f, elev, d, r + 2, c0, lane);
+    else {
+#pragma unroll
+      for (int k = 0; k < FORM_CPT + 2; ++k) f.v[k] = sw_nan();
+    }
+    FormOut o[FORM_CPT];
+#pragma unroll
+    for (int j = 0; j < FORM_CPT; ++j) {
+      double e[10];
+      e[7] = p.v[j]; e[8] = p.v[j + 1]; e[9] = p.v[j + 2];
+      e[4] = q.v[j]; e[5] = q.v[j + 1]; e[6] = q.v[j + 2];
+      e[1] = n.v[j]; e[2] = n.v[j + 1]; e[3] = n.v[j + 2];
+      if (!form_cell_fast(e, K, s_sin, s_cos, &o[j])) o[j] = form_cell(e, K.grid, s_sin, s_cos);
+      finalise(o[j], !is_nan(e[5]));
+    }
+    if (live) {
+      const size_t i = (size_t)r * d.pitch + c0;
+      *reinterpret_cast<double2*>(P.o[0] + i) = make_double2(o[0].slope_pct, o[1].slope_pct);
+      *reinterpret_cast<double2*>(P.o[1] + i) = make_double2(o[0].slope_deg, o[1].slope_deg);
+      *reinterpret_cast<double2*>(P.o[2] + i) = make_double2(o[0].aspect, o[1].aspect);
+      *reinterpret_cast<double2*>(P.o[3] + i) = make_double2(o[0].prof, o[1].prof);
+      *reinterpret_cast<double2*>(P.o[4] + i) = make_double2(o[0].plan, o[1].plan);
+      if (c0 == 1) {  // ring column 0: NA everywhere
+#pragma unroll
+        for (int k = 0; k < 5; ++k) P.o[k][i - 1] = sw_nan();
       }
     }
     p = q;
     q = n;
+    n = f;
+    sw_finish(n, lane);
   }
 }
 
@@ -125,8 +147,13 @@ int run_form(litap_grid* g, double grid_m) {
     P.o[k] = g->form[k];
   }
   {
-    dim3 grid((d.NC - 1 + FORM_THREADS - 1) / FORM_THREADS, (d.NR + FORM_ROWS - 1) / FORM_ROWS);
-    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, grid_m, g_trig, P));
+    const int cols = (d.pitch - LITAP_XOFF + FORM_CPT - 1) / FORM_CPT;  // threads across a row
+    dim3 grid((cols + FORM_THREADS - 1) / FORM_THREADS, (d.NR + FORM_ROWS - 1) / FORM_ROWS);
+    FormK K;
+    K.grid = grid_m;
+    K.inv2g = 1.0 / (2 * grid_m);
+    K.invg2 = 1.0 / (grid_m * grid_m);
+    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, K, g_trig, P));
   }
   // R/form_01_calc_form.R:54-57 in buffered 0-based coordinates, in this order:
   //   col 1 <- col 2 ; col NC-2 <- col NC-3 ; row 1 <- row 2 ; row NR-2 <- row NR-3
@@ -135,6 +162,9 @@ int run_form(litap_grid* g, double grid_m) {
   em.dst_c[1] = d.NC - 2; em.src_c[1] = d.NC - 3;
   em.dst_r[0] = 1; em.src_r[0] = 2 < d.NR ? 2 : -1;
   em.dst_r[1] = d.NR - 2; em.src_r[1] = d.NR - 3;
+  // a row band replicates rows only where it touches the edge of the DEM
+  if (g->halo_top) em.dst_r[0] = -1;
+  if (g->halo_bot) em.dst_r[1] = -1;
   {
     int m = d.NR > d.NC ? d.NR : d.NC;
     dim3 grid((m + 127) / 128, 4);

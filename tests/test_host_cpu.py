@@ -108,3 +108,18 @@ def test_r_shim_compiles_against_stub_headers():
     src = open(shim).read()
     for fn in ("litap_ddir", "litap_shed", "litap_form", "litap_weti"):
         assert fn + "(" in src
+
+
+@pytest.mark.parametrize("kw,grid", [({}, 5.0), ({"quant": 0.0}, 5.0), ({"quant": 100.0, "na_permille": 10}, 1.0),
+                                     ({"seed": 4, "quant": 10.0}, 2.5)])
+def test_form_fast_path_is_bit_identical_where_it_decides(cellmath, kw, grid):
+    """The fast path of calc_form (cellmath.h form_cell_fast) either declines a window or returns exactly
+    what the reference expression tree (form_cell) returns."""
+    i64 = np.ctypeslib.ndpointer(np.int64, flags="C")
+    cellmath.host_form_fast_check.argtypes = [np.ctypeslib.ndpointer(np.float64, flags="C"), C.c_longlong,
+                                              C.c_longlong, C.c_double, i64]
+    e = oracle.synth_dem(700, 700, **kw)
+    out = np.zeros(2, np.int64)
+    cellmath.host_form_fast_check(e, e.shape[0], e.shape[1], grid, out)
+    assert out[1] == 0
+    assert out[0] > 0.9 * e.size
