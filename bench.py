@@ -45,7 +45,7 @@ class ClockSampler:
         self.rows, self.p = [], None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                       "--format=csv,noheader,nounits", "-lms", "20"],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -54,13 +54,24 @@ class ClockSampler:
 
     def _read(self):
         for line in self.p.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
-    def stop(self):
+    def wait_first(self, timeout=5.0):
+        """nvidia-smi needs ~1 s before its first line: wait for it so that short timed regions are covered."""
+        t0 = time.perf_counter()
+        while self.p and not self.rows and time.perf_counter() - t0 < timeout:
+            time.sleep(0.02)
+
+    def stop(self, t_lo=None, t_hi=None):
+        """Summary of the samples taken in [t_lo, t_hi] (perf_counter times; the loaded region)."""
         if not self.p:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.p.terminate()
         self.t.join(timeout=2)
+        allrows = self.rows
+        self.rows = [r for t, r in allrows if (t_lo is None or t >= t_lo) and (t_hi is None or t <= t_hi)]
+        if not self.rows:  # region shorter than the sampling period: nearest samples
+            self.rows = [r for _, r in allrows[-3:]]
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         reasons = set()
         for r in self.rows:
@@ -150,11 +161,13 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.wait_first()
+    t_load0 = time.perf_counter()
     for _ in range(a.warmup):
         step()
-    launches0 = None
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     nl = 0
     ev0.record(stream)
@@ -165,7 +178,9 @@ def run_ours(a):
     ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.stop(t_load0, time.perf_counter()) if sampler else None
+    if clocks:
+        clocks["window"] = "warm-up + timed steps"
     t = torch.tensor([ms], device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -49,6 +49,7 @@ typedef struct litap_timings {
   float weti_ms;
   float total_ms;   /* whole call, incl. copies */
   int plateau_rounds;
+  int weti_waves;   /* dependency waves of the last calc_weti2 (depth of the flow DAG) */
   int64_t flat_cells, patch_cells, npits;
   int64_t kernel_launches; /* kernels of this library launched by the call */
 } litap_timings;

@@ -346,3 +346,131 @@ LITAP_HD bool form_cell_fast(const double* e, const FormK& K, const double* sin_
   o->aspect = as;
   return true;
 }
+
+// ---------------------------------------------------------------------------------------------
+// R's sum() accumulates in long double (x87 80-bit extended, 64-bit significand) and rounds the
+// result to double once (src/main/summary.c rsum; call site R/form_02b_calc_weti.R:67).  The terms
+// summed on this path are all >= 0, so the emulation only needs the addition of non-negative
+// values: round-to-nearest-even at 64 bits after every add, then 64 -> 53 bits at the end.
+struct Ld80 {          // value = m * 2^(e - 63), m normalised (bit 63 set) or 0
+  unsigned long long m;
+  int e;
+};
+LITAP_HD int ld80_clz64(unsigned long long x) {
+#if defined(__CUDA_ARCH__)
+  return __clzll((long long)x);
+#else
+  return __builtin_clzll(x);
+#endif
+}
+LITAP_HD unsigned long long ld80_bits(double x) {
+#if defined(__CUDA_ARCH__)
+  return (unsigned long long)__double_as_longlong(x);
+#else
+  unsigned long long b;
+  __builtin_memcpy(&b, &x, 8);
+  return b;
+#endif
+}
+LITAP_HD double ld80_from_bits(unsigned long long b) {
+#if defined(__CUDA_ARCH__)
+  return __longlong_as_double((long long)b);
+#else
+  double x;
+  __builtin_memcpy(&x, &b, 8);
+  return x;
+#endif
+}
+// x must be finite and >= 0
+LITAP_HD Ld80 ld80_from_double(double x) {
+  Ld80 r;
+  unsigned long long b = ld80_bits(x);
+  int ex = (int)((b >> 52) & 0x7FF);
+  unsigned long long fr = b & 0x000FFFFFFFFFFFFFull;
+  if (ex == 0) {
+    if (fr == 0) { r.m = 0; r.e = 0; return r; }
+    int s = ld80_clz64(fr);  // subnormal: value = fr * 2^-1074
+    r.m = fr << s;
+    r.e = 63 - s - 1074;
+    return r;
+  }
+  r.m = 0x8000000000000000ull | (fr << 11);
+  r.e = ex - 1023;
+  return r;
+}
+LITAP_HD Ld80 ld80_add(Ld80 a, Ld80 b) {
+  if (b.m == 0) return a;
+  if (a.m == 0) return b;
+  if (a.e < b.e) { Ld80 t = a; a = b; b = t; }
+  const int sh = a.e - b.e;
+  unsigned long long hi, lo;
+  bool sticky = false;
+  if (sh == 0) { hi = b.m; lo = 0; }
+  else if (sh < 64) { hi = b.m >> sh; lo = b.m << (64 - sh); }
+  else if (sh == 64) { hi = 0; lo = b.m; }
+  else if (sh < 128) { hi = 0; lo = b.m >> (sh - 64); sticky = (b.m << (128 - sh)) != 0; }
+  else { hi = 0; lo = 0; sticky = true; }
+  unsigned long long sh_ = a.m + hi;
+  int e = a.e;
+  if (sh_ < a.m) {  // carry out of bit 63
+    sticky = sticky || (lo & 1ull);
+    lo = (lo >> 1) | (sh_ << 63);
+    sh_ = (sh_ >> 1) | 0x8000000000000000ull;
+    ++e;
+  }
+  const unsigned long long half = 0x8000000000000000ull;
+  if (lo > half || (lo == half && (sticky || (sh_ & 1ull)))) {
+    ++sh_;
+    if (sh_ == 0) { sh_ = half; ++e; }
+  }
+  Ld80 r;
+  r.m = sh_;
+  r.e = e;
+  return r;
+}
+// (double) of the extended value, round to nearest even; normal range only (the sums here are
+// slopes times cell sizes)
+LITAP_HD double ld80_to_double(Ld80 a) {
+  if (a.m == 0) return 0.0;
+  unsigned long long m53 = a.m >> 11, rem = a.m & 0x7FFull;
+  int e = a.e;
+  if (rem > 0x400ull || (rem == 0x400ull && (m53 & 1ull))) {
+    ++m53;
+    if (m53 == (1ull << 53)) { m53 >>= 1; ++e; }
+  }
+  if (e > 1023) return ld80_from_bits(0x7FF0000000000000ull);
+  if (e < -1022) return 0.0;  // not reachable for this path's magnitudes
+  return ld80_from_bits(((unsigned long long)(e + 1023) << 52) | (m53 & 0x000FFFFFFFFFFFFFull));
+}
+
+// ---------------------------------------------------------------------------------------------
+// calc_weti2 per-cell pieces (R/form_02b_calc_weti.R:47-67).  Window visit order of the reference:
+// NW,N,NE,W,self,E,SW,S,SE = neighbour codes 7,8,9,4,5,6,1,2,3.
+struct WetiK { double l1, l2, orth, diag, g2; };  // grid*0.5, grid*0.354, grid, grid*sqrt(2), grid^2
+LITAP_HD bool weti_is_diag(int n) { return n == 1 || n == 3 || n == 7 || n == 9; }
+// tan_k of a cell at elevation f towards a neighbour at elevation nv in direction n (:64-65);
+// NaN neighbour -> NaN, neighbour not lower -> 0
+LITAP_HD double weti_tan(double f, double nv, int n, const WetiK& K) {
+  const bool dg = weti_is_diag(n);
+  double t = ((f - nv) / (dg ? K.diag : K.orth)) * (dg ? K.l2 : K.l1);
+  if (nv >= f) t = 0;
+  return t;
+}
+// S = sum(tan, na.rm = TRUE) with R's long double accumulator; e[n] = elevation of neighbour n
+// (e[5] = the cell itself).  *lower gets bit n set for every strictly lower neighbour.
+LITAP_HD double weti_S(const double* e, const WetiK& K, unsigned* lower) {
+  const int W[9] = {7, 8, 9, 4, 5, 6, 1, 2, 3};
+  Ld80 s;
+  s.m = 0; s.e = 0;
+  unsigned lo = 0;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const int n = W[k];
+    if (n == 5) continue;  // self: tan = 0
+    double t = weti_tan(e[5], e[n], n, K);
+    if (is_nan(t)) continue;
+    if (t > 0) { lo |= 1u << n; s = ld80_add(s, ld80_from_double(t)); }
+  }
+  *lower = lo;
+  return ld80_to_double(s);
+}

@@ -74,3 +74,16 @@ void host_form_fast_check(const double* elev, long long NR, long long NC, double
   out[1] = nbad;
 }
 }
+
+// emulated long-double accumulation vs the host's real long double (x86-64: x87 extended)
+extern "C" double host_ld80_sum(const double* t, int n) {
+  Ld80 s;
+  s.m = 0; s.e = 0;
+  for (int i = 0; i < n; ++i) s = ld80_add(s, ld80_from_double(t[i]));
+  return ld80_to_double(s);
+}
+extern "C" double host_real_ld_sum(const double* t, int n) {
+  long double s = 0.0L;
+  for (int i = 0; i < n; ++i) s += t[i];
+  return (double)s;
+}

@@ -247,6 +247,86 @@ def test_full_size_properties():
     g.close()
 
 
+WETI = ("qarea1", "qarea2", "qweti1", "qweti2")
+
+
+def assert_weti_parity(e, ddir_u8, upslope, grid, tag=""):
+    """calc_weti2 through the C ABI vs the oracle: bit-exact (outputs are truncated to 2 decimals; a
+    1-ulp libm difference in log() could flip a digit, so up to one flip of 0.01 per million cells
+    is tolerated and counted)."""
+    NR, NC = e.shape
+    o = oracle.weti(e, ddir_u8, upslope.astype(np.float64), grid)
+    db = lb.add_buffer(e[1:-1, 1:-1])
+    db["elev"] = np.ascontiguousarray(e).ravel()
+    db["ddir_u8"] = np.ascontiguousarray(ddir_u8).ravel()
+    db["upslope"] = upslope.astype(np.float64).ravel()
+    g = lb.calc_weti2(db, grid)
+    flips = 0
+    for k in WETI:
+        a, b = g[k].reshape(NR, NC), o[k]
+        assert (np.isnan(a) == np.isnan(b)).all(), f"{tag} {k}: NA pattern differs"
+        m = ~np.isnan(b)
+        bad = a[m] != b[m]
+        if bad.any():
+            diff = np.abs(a[m][bad] - b[m][bad])
+            assert (diff <= 0.01 * (1 + 1e-9)).all(), f"{tag} {k}: {bad.sum()} cells differ, max {diff.max()}"
+            flips += int(bad.sum())
+    assert flips <= e.size // 1_000_000, f"{tag}: {flips} truncation flips"
+    return o
+
+
+def test_testELEV_weti_golden(golden):
+    """G4: dem_fill (elev, post-pit-removal ddir, upslope) -> dem_form qarea/qweti, all 8100 cells,
+    including the cells whose qweti comes from the reference's stale qc1/qc2 variables."""
+    fill, frm = golden["dem_fill"], golden["dem_form"]
+    db = lb.add_buffer(fill["elev"].reshape(90, 90))
+    db["ddir"] = oracle.add_buffer(fill["ddir"].reshape(90, 90)).ravel()
+    db["upslope"] = oracle.add_buffer(fill["upslope"].reshape(90, 90)).ravel()
+    g = lb.remove_buffer(lb.calc_weti2(db, 5.0), WETI)
+    for k in WETI:
+        assert (g[k].ravel() == frm[k]).all(), f"{k}: {(g[k].ravel() != frm[k]).sum()} cells differ"
+    assert lb.timings()["weti_waves"] > 10
+
+
+@pytest.mark.parametrize("nr,nc,kw,grid", [
+    (200, 300, {}, 5.0),
+    (513, 515, {"quant": 10.0}, 5.0),              # big plateaus: long chains of B cells
+    (400, 900, {"na_permille": 10}, 2.5),
+    (300, 300, {"quant": 0.0}, 1.0),
+    (1024, 1024, {}, 5.0),
+], ids=["200x300", "q0.1", "na1pct", "noquant", "1024"])
+def test_synthetic_weti(nr, nc, kw, grid):
+    e = oracle.synth_dem(nr, nc, **kw)
+    d = oracle.ddir(e)
+    s = oracle.shed(e, d["ddir"])
+    assert_weti_parity(e, d["ddir"], s["upslope"], grid, f"{nr}x{nc}{kw}")
+
+
+def test_weti_with_reversed_flow_and_degenerate_surfaces():
+    """ddir as it looks after pit removal: some flat cells drain uphill (their receiver was visited
+    earlier, so the push only shows in the receiver's final qarea)."""
+    rng = np.random.default_rng(5)
+    e = oracle.synth_dem(300, 260, quant=100.0)
+    d = oracle.ddir(e)
+    s = oracle.shed(e, d["ddir"])
+    dd = d["ddir"].copy()
+    flat = np.argwhere((d["flatcell"] == 1) & (dd != 0))
+    for r, c in flat[rng.random(len(flat)) < 0.5]:
+        dd[r, c] = rng.choice([1, 2, 3, 4, 6, 7, 8, 9])
+    up = s["upslope"].copy()
+    up[rng.random(up.shape) < 0.3] = 1          # ties on (elev, upslope): seqno decides
+    assert_weti_parity(e, dd, up, 5.0, "reversed")
+    flat = oracle.add_buffer(np.full((40, 50), 7.0))
+    df = oracle.ddir(flat)
+    assert_weti_parity(flat, df["ddir"], oracle.shed(flat, df["ddir"])["upslope"], 5.0, "flat")
+    cone = oracle.add_buffer(-np.hypot(*np.meshgrid(np.arange(-40, 41.0), np.arange(-40, 41.0))))
+    dc = oracle.ddir(cone)
+    assert_weti_parity(cone, dc["ddir"], oracle.shed(cone, dc["ddir"])["upslope"], 5.0, "cone")
+    tiny = oracle.add_buffer(np.array([[3.0]]))
+    dt = oracle.ddir(tiny)
+    assert_weti_parity(tiny, dt["ddir"], oracle.shed(tiny, dt["ddir"])["upslope"], 5.0, "1x1")
+
+
 def test_bad_arguments_raise():
     with pytest.raises(lb.LitapError):
         lb.calc_form(lb.add_buffer(np.ones((4, 4))), 0.0)

@@ -123,3 +123,27 @@ def test_form_fast_path_is_bit_identical_where_it_decides(cellmath, kw, grid):
     cellmath.host_form_fast_check(e, e.shape[0], e.shape[1], grid, out)
     assert out[1] == 0
     assert out[0] > 0.9 * e.size
+
+
+def test_ld80_sum_emulation_equals_x87(cellmath):
+    """R's sum() (long double accumulator, R/form_02b_calc_weti.R:67) as emulated for the GPU."""
+    f64 = np.ctypeslib.ndpointer(np.float64, flags="C")
+    for fn in (cellmath.host_ld80_sum, cellmath.host_real_ld_sum):
+        fn.argtypes = [f64, C.c_int]
+        fn.restype = C.c_double
+    rng = np.random.default_rng(11)
+    nbad = 0
+    for trial in range(60000):
+        n = int(rng.integers(1, 9))
+        mode = trial % 4
+        if mode == 0:
+            t = rng.uniform(0, 1, n)
+        elif mode == 1:
+            t = rng.uniform(0, 1, n) * 2.0 ** rng.integers(-40, 40, n)   # wide exponent spread
+        elif mode == 2:
+            t = np.round(rng.uniform(0, 3, n), 3) / 5.0 * 2.5            # tan-like values
+        else:
+            t = np.ldexp(rng.integers(1, 1 << 53, n).astype(np.float64), rng.integers(-80, -20, n))
+        t = np.ascontiguousarray(t, dtype=np.float64)
+        nbad += cellmath.host_ld80_sum(t, n) != cellmath.host_real_ld_sum(t, n)
+    assert nbad == 0
