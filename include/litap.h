@@ -117,6 +117,31 @@ int64_t litap_grid_npits(const litap_grid* g);
 /* order-independent checksum (sum of value*index hashes) of a result array, computed on the device */
 int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* out);
 
+/* ---- row bands: one DEM sharded over several GPUs ----------------------- */
+/* The DEM (gnr rows x nc cols, unbuffered) is cut into nbands contiguous row bands; band b owns rows
+ * [gnr*b/nbands, gnr*(b+1)/nbands) and keeps one halo row on either side.  A band is a litap_grid.
+ * Two ways to run:
+ *   - one band per process / GPU (torchrun): rank 0 calls litap_comm_unique_id, the 128 bytes are
+ *     broadcast by the host (torch.distributed, MPI, a file ...), every rank calls litap_comm_init
+ *     and passes its single band to the litap_bands_* calls (collective: all ranks must call);
+ *   - all bands in one process on one device, no communicator: pass all nbands bands in band order
+ *     (used to verify that the sharded result equals the unsharded one bit for bit).
+ * calc_weti2 is not sharded (its visiting order couples all bands): run it on a whole-DEM grid. */
+int litap_comm_unique_id(void* id128);
+int litap_comm_init(int rank, int nranks, const void* id128);
+void litap_comm_destroy(void);
+int litap_band_create(int64_t gnr, int64_t nc, int band, int nbands, litap_grid** out);
+int litap_band_synth(litap_grid* band, uint32_t seed, double quant, int na_permille);
+/* elev_full: the whole buffered DEM, (gnr+2) x (nc+2) dense; the band copies its rows and halos */
+int litap_band_upload_elev(litap_grid* band, const double* elev_full);
+int litap_bands_ddir(litap_grid** bands, int n, int invert);
+int litap_bands_shed(litap_grid** bands, int n);
+int litap_bands_form(litap_grid** bands, int n, double grid_m);
+/* the rows of the full buffered DEM this band answers for (own rows; + the NA ring row for the
+ * first / last band): first row and row count; litap_band_download copies exactly those rows */
+int litap_band_rows(const litap_grid* band, int64_t* row0, int64_t* nrows);
+int litap_band_download(litap_grid* band, const char* name, void* dst);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,6 +15,9 @@ SYMBOLS = [
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
     "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
+    "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
+    "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_bands_ddir", "litap_bands_shed",
+    "litap_bands_form", "litap_band_rows", "litap_band_download",
 ]
 
 
@@ -69,6 +72,17 @@ def load():
     L.litap_grid_npits.argtypes = [vp]
     L.litap_grid_npits.restype = i64
     L.litap_grid_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
+    L.litap_comm_unique_id.argtypes = [vp]
+    L.litap_comm_init.argtypes = [ci, ci, vp]
+    L.litap_comm_destroy.restype = None
+    L.litap_band_create.argtypes = [i64, i64, ci, ci, C.POINTER(vp)]
+    L.litap_band_synth.argtypes = [vp, C.c_uint32, dbl, ci]
+    L.litap_band_upload_elev.argtypes = [vp, vp]
+    L.litap_bands_ddir.argtypes = [C.POINTER(vp), ci, ci]
+    L.litap_bands_shed.argtypes = [C.POINTER(vp), ci]
+    L.litap_bands_form.argtypes = [C.POINTER(vp), ci, dbl]
+    L.litap_band_rows.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+    L.litap_band_download.argtypes = [vp, C.c_char_p, vp]
     _lib = L
     return L
 

@@ -114,6 +114,9 @@ extern "C" int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out) {
   g->d = d;
   g->own_lo = 0;
   g->own_hi = d.NR;
+  g->edge_top_row = 1;
+  g->edge_bot_row = d.NR - 2;
+  g->gnr = d.NR - 2;
   g->elev = grid_alloc_array<double>(d, 0xFF);  // pads = NaN
   if (!g->elev) { delete g; return set_error(LITAP_ENOMEM, "device allocation failed (elev)"); }
   *out = g;
@@ -257,6 +260,20 @@ extern "C" int litap_grid_download(litap_grid* g, const char* name, void* dst) {
   else if (a.esize == 4) rc = download2d((uint32_t*)dst, g->d, (const uint32_t*)a.p);
   else rc = download2d((uint8_t*)dst, g->d, (const uint8_t*)a.p);
   if (rc) return rc;
+  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  return LITAP_OK;
+}
+
+// a band's share of the full buffered DEM (see litap_band_rows), copied densely into dst
+extern "C" int litap_band_download(litap_grid* g, const char* name, void* dst) {
+  if (!g || !name || !dst || g->nbands < 1) return set_error(LITAP_EARG, "litap_band_download: bad arguments");
+  ArrRef a = find_array(g, name);
+  if (!a.p) return set_error(LITAP_EARG, std::string("litap_band_download: no such result on the band: ") + name);
+  const int lo = g->halo_top ? g->own_lo : g->own_lo - 1, hi = g->halo_bot ? g->own_hi : g->own_hi + 1;
+  const GridDims& d = g->d;
+  const char* src = (const char*)a.p + (size_t)lo * d.pitch * a.esize;
+  CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)d.NC * a.esize, src, (size_t)d.pitch * a.esize, (size_t)d.NC * a.esize, hi - lo,
+                             cudaMemcpyDeviceToHost, ctx().stream));
   CUDA_TRY(cudaStreamSynchronize(ctx().stream));
   return LITAP_OK;
 }

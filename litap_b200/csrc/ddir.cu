@@ -485,3 +485,57 @@ int run_ddir(litap_grid* g, int invert) {
   }
   return LITAP_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// steps of calc_ddir2 for the row-band driver (bands.cu): same kernels, with the exchanges between
+// bands done by the caller between the steps
+int ddir_band_grow(litap_grid* g, size_t cap) { return ddir_ensure(g, cap); }
+
+int ddir_band_begin(litap_grid* g) {
+  int rc = ddir_ensure(g, g->dd_cap ? g->dd_cap : ddir_default_cap(g->d));
+  if (rc) return rc;
+  CUDA_TRY(cudaMemsetAsync(g->dd_ctr, 0, sizeof(DdirCounters), ctx().stream));
+  return launch_d8(g);
+}
+int ddir_band_counts(litap_grid* g, unsigned long long* nflat, unsigned* npatch) {
+  DdirCounters h;
+  CUDA_TRY(cudaMemcpyAsync(&h, g->dd_ctr, sizeof(h), cudaMemcpyDeviceToHost, ctx().stream));
+  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  if (nflat) *nflat = h.nflat;
+  if (npatch) *npatch = h.npatch;
+  return LITAP_OK;
+}
+int ddir_band_probe(litap_grid* g, unsigned nflat, unsigned* changed_dev) {
+  if (!nflat) return LITAP_OK;
+  KERNEL("k_plateau_probe", k_plateau_probe<<<nblk(nflat), 256, 0, ctx().stream>>>(g->dd_list, nflat, g->ddir, g->elev, g->d,
+                                                                                 g->dd_cand, changed_dev));
+  return LITAP_OK;
+}
+int ddir_band_apply(litap_grid* g, unsigned nflat) {
+  if (!nflat) return LITAP_OK;
+  KERNEL("k_plateau_apply", k_plateau_apply<<<nblk(nflat), 256, 0, ctx().stream>>>(g->dd_list, nflat, g->dd_cand, g->ddir));
+  return LITAP_OK;
+}
+int ddir_band_mark(litap_grid* g) {
+  KERNEL("k_patch_mark", k_patch_mark<<<ctx().sm_count * 4, 256, 0, ctx().stream>>>(
+                             g->dd_list, (unsigned long long)g->dd_cap, g->ddir, g->d, g->row_off, g->dd_keys,
+                             (DdirCounters*)g->dd_ctr));
+  return LITAP_OK;
+}
+int ddir_band_patch_apply(litap_grid* g, const unsigned long long* K, const uint8_t* nd, unsigned np) {
+  KERNEL("k_patch_apply", k_patch_apply<<<nblk(np), 256, 0, ctx().stream>>>(K, nd, np, g->ddir, g->d, g->row_off, g->own_lo,
+                                                                          g->own_hi));
+  return LITAP_OK;
+}
+int ddir_band_elev_max(litap_grid* g, unsigned long long* out_dev) {
+  const GridDims d = g->d;
+  dim3 gb(nblk(d.NC) < 64 ? nblk(d.NC) : 64, d.NR < 1024 ? d.NR : 1024);
+  KERNEL("k_elev_max", k_elev_max<<<gb, 256, 0, ctx().stream>>>(g->elev, d, g->own_lo, g->own_hi, out_dev));
+  return LITAP_OK;
+}
+int ddir_band_invert(litap_grid* g, const unsigned long long* max_dev) {
+  const GridDims d = g->d;
+  dim3 gi(nblk((size_t)d.NC + 31), d.NR);
+  KERNEL("k_invert", k_invert<<<gi, 256, 0, ctx().stream>>>(g->elev, d, max_dev));
+  return LITAP_OK;
+}

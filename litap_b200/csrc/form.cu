@@ -160,11 +160,9 @@ int run_form(litap_grid* g, double grid_m) {
   EdgeMap em;
   em.dst_c[0] = 1; em.src_c[0] = 2 < d.NC ? 2 : -1;
   em.dst_c[1] = d.NC - 2; em.src_c[1] = d.NC - 3;
-  em.dst_r[0] = 1; em.src_r[0] = 2 < d.NR ? 2 : -1;
-  em.dst_r[1] = d.NR - 2; em.src_r[1] = d.NR - 3;
-  // a row band replicates rows only where it touches the edge of the DEM
-  if (g->halo_top) em.dst_r[0] = -1;
-  if (g->halo_bot) em.dst_r[1] = -1;
+  // (a row band replicates rows only where it holds the first / last row of the DEM)
+  em.dst_r[0] = g->edge_top_row; em.src_r[0] = g->edge_top_row + 1 < d.NR ? g->edge_top_row + 1 : -1;
+  em.dst_r[1] = g->edge_bot_row; em.src_r[1] = g->edge_bot_row - 1;
   {
     int m = d.NR > d.NC ? d.NR : d.NC;
     dim3 grid((m + 127) / 128, 4);

@@ -59,6 +59,10 @@ struct litap_grid {
   int own_lo = 0, own_hi = 0;
   long long row_off = 0;
   bool halo_top = false, halo_bot = false;
+  // row band of a larger DEM (bands.cu): nbands == 0 for a whole DEM
+  int band = 0, nbands = 0;
+  long long gnr = 0;                        // rows of the whole DEM
+  int edge_top_row = -1, edge_bot_row = -1; // local row holding the first / last DEM row, -1 if not in this grid
   // calc_ddir2 worklists (ddir.cu)
   uint32_t* dd_list = nullptr;
   uint8_t* dd_cand = nullptr;

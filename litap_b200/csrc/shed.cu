@@ -24,23 +24,6 @@ __device__ __forceinline__ unsigned long long f64_orderable(double x) {
   return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
 }
 
-struct L2 {                    // level-2 arrays, one entry per border slot
-  uint32_t* jump0;             // original edge: entry cell id | ID_ROOT|pid | ID_NA
-  uint32_t* jres;              // resolved (compressed) pointer
-  unsigned long long* pkmax;   // exit cells: max orderable elevation draining through it inside its tile (0 = none)
-  uint32_t* pkidx;             //             lowest cell id attaining pkmax
-  uint32_t* ext;               // external inflow into the border cell (starts as base, accumulated in place)
-  uint32_t* indeg;
-  uint8_t* src;
-};
-struct Pits {                  // one entry per pit id
-  unsigned long long* rootmax; // max orderable elevation of the shed
-  unsigned long long* pitkmax; // the pit tile's own partial
-  uint32_t* pitkidx;
-  uint32_t* rootidx;
-  uint32_t* rank;              // final initial_shed number
-};
-
 __global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsigned long long* count) {
   unsigned n = 0;
   const int c = blockIdx.x * blockDim.x + threadIdx.x + 1;
@@ -81,13 +64,15 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_shed_local(TileGeom g, const 
     for (int k = 0; k < CPT; ++k) w[k] = s_dir[owned_local(k)] != 0 ? 1u : 0u;  // out-of-grid cells have ddir 0
     tile_jump_accumulate(s_dir, s_ptr, s_cnt, w);
   }
+  unsigned pcnt[CPT];  // pits: cells draining into them inside this tile
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     int ly = owned_ly(k), i = ly * LW + lx;
     int dv = s_dir[i];
+    pcnt[k] = s_cnt[i];
     if (s_ptr[i] == i && dv != 5) {  // valid exit: entry cell on the local ring
       long long es = slot_of_rc(t.r_base + ly + nb_dr(dv), c + nb_dc(dv), g.tilesX);
-      if (es >= 0) atomicAdd(&l2.ext[es], s_cnt[i]);
+      if (es >= 0) atomicAdd(&l2.ext[es], pcnt[k]);
     }
   }
   __syncthreads();
@@ -134,6 +119,8 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_shed_local(TileGeom g, const 
     pits.pitkmax[pid] = s_key[i];
     pits.pitkidx[pid] = s_idx[i];
     pits.rootidx[pid] = 0xFFFFFFFFu;
+    pits.cell[pid] = (uint32_t)((size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c);
+    pits.cnt[pid] = pcnt[k];
     lab[(size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c] = pid;  // read back by k_shed_final of this tile
     s_idx[i] = pid;                                                // from here on s_idx[pit] is its pid
   }
@@ -258,7 +245,8 @@ constexpr size_t SMEM_B = (size_t)LC * (4 + 4 + 2 + 1) + 64;  // cnt, lab, ptr, 
 
 __global__ void __launch_bounds__(NT, 1024 / NT) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
                                                    const uint32_t* __restrict__ rank, int32_t* shed_out,
-                                                   uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge) {
+                                                   uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge,
+                                                   BandSeeds seeds) {
   extern __shared__ __align__(16) unsigned char smem[];
   unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                      // LC x 4
   uint32_t* s_lab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);     // LC x 4
@@ -283,6 +271,9 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_shed_final(TileGeom g, const 
         w[k] = 1;
         int bs = border_slot_local(lx, ly);
         if (bs >= 0) w[k] += l2.ext[tile_slot0 + bs];
+        // row band: flow entering from the neighbouring bands at the first / last own row
+        if (seeds.x_top && t.r_base + ly == seeds.row_top) w[k] += seeds.x_top[c];
+        if (seeds.x_bot && t.r_base + ly == seeds.row_bot) w[k] += seeds.x_bot[c];
       }
     }
     tile_jump_accumulate(s_dir, s_ptr, s_cnt, w);
@@ -359,9 +350,10 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_shed_final(TileGeom g, const 
 
 // ring row 0 / column 0 (never inside a tile) and, for uniformity, the other two ring lines
 __global__ void k_ring_fill(GridDims d, int32_t* __restrict__ shed_out, uint32_t* __restrict__ upslope,
-                            uint8_t* __restrict__ ridge) {
+                            uint8_t* __restrict__ ridge, int keep_last_row) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   int line = blockIdx.y;
+  if (line == 1 && keep_last_row) return;  // south halo of a row band: its pit cells still hold their ids
   int r, c;
   if (line == 0) { r = 0; c = t; }
   else if (line == 1) { r = d.NR - 1; c = t; }
@@ -377,19 +369,12 @@ __global__ void k_ring_fill(GridDims d, int32_t* __restrict__ shed_out, uint32_t
 }  // namespace shed
 
 // ------------------------------------------------------------------------------------------------
-namespace {
-struct Scratch {
-  std::vector<void*> ptrs;
-  ~Scratch() { for (void* p : ptrs) pool_free(p); }
-  template <typename T> T* get(size_t n) {
-    T* p = (T*)pool_alloc(n * sizeof(T));
-    if (p) ptrs.push_back(p);
-    return p;
-  }
-};
-}  // namespace
-
-int run_shed(litap_grid* g) {
+// host side: calc_shed4 in phases (the row-band driver in bands.cu runs exchanges between them)
+//   shed_phase_local   tiles + level-2 graph: every border cell resolved to a pit id, external
+//                      inflow of every border cell, per-pit key (max elevation, lowest cell)
+//   shed_phase_rank    single device: canonical numbering of the pits (two radix sorts)
+//   shed_phase_final   labels, upslope, ridge
+int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   using namespace shed;
   Ctx& c = ctx();
   const GridDims d = g->d;
@@ -405,14 +390,14 @@ int run_shed(litap_grid* g) {
     CUDA_TRY(cudaFuncSetAttribute(k_shed_final, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_B));
     attr_set = true;
   }
-  TileGeom tg;
+  TileGeom& tg = W.tg;
   tg.d = d;
   tg.tilesX = (d.NC - 1 + TW - 1) / TW;
   tg.tilesY = (d.NR - 1 + TH - 1) / TH;
-  const size_t nslots = (size_t)tg.tilesX * tg.tilesY * BSLOTS;
+  const size_t nslots = W.nslots = (size_t)tg.tilesX * tg.tilesY * BSLOTS;
 
-  Scratch S;
-  unsigned long long* counters = S.get<unsigned long long>(4);  // [0] npits, [1] pit cursor, [2] flags (2 x u32)
+  PoolScratch& S = W.S;
+  unsigned long long* counters = W.counters = S.get<unsigned long long>(4);
   if (!counters) return set_error(LITAP_ENOMEM, "device allocation failed (shed scratch)");
   CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), st));
   {
@@ -422,12 +407,10 @@ int run_shed(litap_grid* g) {
   unsigned long long npits64 = 0;
   CUDA_TRY(cudaMemcpyAsync(&npits64, counters, 8, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
-  const unsigned npits = (unsigned)npits64;
-  g->npits = (int64_t)npits64;
-  c.tm.npits = g->npits;
+  const unsigned npits = W.npits = (unsigned)npits64;
   const size_t np = npits ? npits : 1;
 
-  L2 l2;
+  L2& l2 = W.l2;
   l2.jump0 = S.get<uint32_t>(nslots);
   l2.jres = S.get<uint32_t>(nslots);
   l2.pkmax = S.get<unsigned long long>(nslots);
@@ -435,23 +418,20 @@ int run_shed(litap_grid* g) {
   l2.ext = S.get<uint32_t>(nslots);
   l2.indeg = S.get<uint32_t>(nslots);
   l2.src = S.get<uint8_t>(nslots);
-  Pits pits;
+  Pits& pits = W.pits;
   pits.rootmax = S.get<unsigned long long>(np);
   pits.pitkmax = S.get<unsigned long long>(np);
   pits.pitkidx = S.get<uint32_t>(np);
   pits.rootidx = S.get<uint32_t>(np);
   pits.rank = S.get<uint32_t>(np);
-  uint32_t* ord_a = S.get<uint32_t>(np);
-  uint32_t* ord_b = S.get<uint32_t>(np);
-  uint32_t* key32_b = S.get<uint32_t>(np);
-  unsigned long long* key64_a = S.get<unsigned long long>(np);
-  unsigned long long* key64_b = S.get<unsigned long long>(np);
+  pits.cell = S.get<uint32_t>(np);
+  pits.cnt = S.get<uint32_t>(np);
   if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.ext || !l2.indeg || !l2.src || !pits.rootmax ||
-      !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !ord_a || !ord_b || !key32_b || !key64_a || !key64_b)
+      !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !pits.cell || !pits.cnt)
     return set_error(LITAP_ENOMEM, "device allocation failed (shed level-2 arrays)");
   CUDA_TRY(cudaMemsetAsync(l2.ext, 0, nslots * 4, st));
   CUDA_TRY(cudaMemsetAsync(l2.indeg, 0, nslots * 4, st));
-  // slots 252..255 of every tile are never written by k_shed_local: keep them NA / empty
+  // slots BUSED.. of every tile are never written by k_shed_local: keep them NA / empty
   CUDA_TRY(cudaMemsetAsync(l2.jump0, 0xFF, nslots * 4, st));
   CUDA_TRY(cudaMemsetAsync(l2.jres, 0xFF, nslots * 4, st));
   CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
@@ -479,32 +459,73 @@ int run_shed(litap_grid* g) {
   KERNEL("k_l2_indeg", k_l2_indeg<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.indeg));
   KERNEL("k_l2_src", k_l2_src<<<sblk, 256, 0, st>>>(l2.indeg, nslots, l2.src));
   KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, l2.src, nslots, l2.ext, l2.indeg));
-  // ---- canonical numbering
+  // ---- per-pit keys
   if (npits) {
     const unsigned kblk = (unsigned)((std::max(nslots, (size_t)npits) + 255) / 256);
     KERNEL("k_keys_max", k_keys_max<<<sblk, 256, 0, st>>>(l2, nslots, pits));
     KERNEL("k_keys_idx", k_keys_idx<<<kblk, 256, 0, st>>>(l2, nslots, pits, npits));
-    const unsigned pblk = (npits + 255) / 256;
-    KERNEL("k_iota", k_iota<<<pblk, 256, 0, st>>>(ord_a, npits));
-    size_t tmp1 = 0, tmp2 = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tmp1, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st);
-    cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp2, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st);
-    size_t tmpn = tmp1 > tmp2 ? tmp1 : tmp2;
-    void* tmp = S.get<unsigned char>(tmpn ? tmpn : 256);
-    if (!tmp) return set_error(LITAP_ENOMEM, "device allocation failed (sort scratch)");
-    // stable LSD: first by the tie-break (cell id asc), then by max elevation desc
-    CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmpn, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st));
-    KERNEL("k_gather_u64", k_gather_u64<<<pblk, 256, 0, st>>>(pits.rootmax, ord_b, key64_a, npits));
-    CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tmpn, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st));
-    KERNEL("k_scatter_rank", k_scatter_rank<<<pblk, 256, 0, st>>>(ord_a, pits.rank, npits));
-    c.launches += 4;  // cub passes (at least)
   }
+  return LITAP_OK;
+}
+
+int shed_phase_rank(shed::ShedWork& W) {
+  using namespace shed;
+  Ctx& c = ctx();
+  cudaStream_t st = c.stream;
+  const unsigned npits = W.npits;
+  if (!npits) return LITAP_OK;
+  PoolScratch& S = W.S;
+  Pits& pits = W.pits;
+  uint32_t* ord_a = S.get<uint32_t>(npits);
+  uint32_t* ord_b = S.get<uint32_t>(npits);
+  uint32_t* key32_b = S.get<uint32_t>(npits);
+  unsigned long long* key64_a = S.get<unsigned long long>(npits);
+  unsigned long long* key64_b = S.get<unsigned long long>(npits);
+  if (!ord_a || !ord_b || !key32_b || !key64_a || !key64_b)
+    return set_error(LITAP_ENOMEM, "device allocation failed (shed sort buffers)");
+  const unsigned pblk = (npits + 255) / 256;
+  KERNEL("k_iota", k_iota<<<pblk, 256, 0, st>>>(ord_a, npits));
+  size_t tmp1 = 0, tmp2 = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp1, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st);
+  cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp2, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st);
+  size_t tmpn = tmp1 > tmp2 ? tmp1 : tmp2;
+  void* tmp = S.get<unsigned char>(tmpn ? tmpn : 256);
+  if (!tmp) return set_error(LITAP_ENOMEM, "device allocation failed (sort scratch)");
+  // stable LSD: first by the tie-break (cell id asc), then by max elevation desc
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmpn, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st));
+  KERNEL("k_gather_u64", k_gather_u64<<<pblk, 256, 0, st>>>(pits.rootmax, ord_b, key64_a, npits));
+  CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tmpn, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st));
+  KERNEL("k_scatter_rank", k_scatter_rank<<<pblk, 256, 0, st>>>(ord_a, pits.rank, npits));
+  c.launches += 4;  // cub passes (at least)
+  return LITAP_OK;
+}
+
+int shed_phase_final(litap_grid* g, shed::ShedWork& W, const shed::BandSeeds& seeds) {
+  using namespace shed;
+  Ctx& c = ctx();
+  const GridDims d = g->d;
+  cudaStream_t st = c.stream;
   {
     int m = d.NR > d.NC ? d.NR : d.NC;
     dim3 grid((m + 255) / 256, 4);
-    KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge));
+    KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge, g->halo_bot ? 1 : 0));
   }
-  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, SMEM_B, st>>>(tg, g->ddir, l2, pits.rank, g->shed, g->upslope, g->ridge));
-  CUDA_TRY(cudaStreamSynchronize(st));  // scratch is returned to the pool when S dies
+  dim3 tgrid(W.tg.tilesX, W.tg.tilesY);
+  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, SMEM_B, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, g->shed, g->upslope,
+                                                                g->ridge, seeds));
+  return LITAP_OK;
+}
+
+int run_shed(litap_grid* g) {
+  shed::ShedWork W;
+  int rc = shed_phase_local(g, W);
+  if (rc) return rc;
+  g->npits = (int64_t)W.npits;
+  ctx().tm.npits = g->npits;
+  rc = shed_phase_rank(W);
+  if (rc) return rc;
+  rc = shed_phase_final(g, W, shed::BandSeeds());
+  if (rc) return rc;
+  CUDA_TRY(cudaStreamSynchronize(ctx().stream));  // scratch is returned to the pool when W dies
   return LITAP_OK;
 }

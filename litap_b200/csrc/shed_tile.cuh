@@ -54,6 +54,43 @@ __device__ __forceinline__ long long slot_of_id(uint32_t id, const TileGeom& g) 
   return slot_of_rc(r, c, g.tilesX);
 }
 
+struct L2 {                    // level-2 arrays, one entry per border slot
+  uint32_t* jump0;             // original edge: entry cell id | ID_ROOT|pid | ID_NA
+  uint32_t* jres;              // resolved (compressed) pointer
+  unsigned long long* pkmax;   // exit cells: max orderable elevation draining through it inside its tile (0 = none)
+  uint32_t* pkidx;             //             lowest cell id attaining pkmax
+  uint32_t* ext;               // external inflow into the border cell (starts as base, accumulated in place)
+  uint32_t* indeg;
+  uint8_t* src;
+};
+struct Pits {                  // one entry per pit id
+  unsigned long long* rootmax; // max orderable elevation of the shed
+  unsigned long long* pitkmax; // the pit tile's own partial
+  uint32_t* pitkidx;
+  uint32_t* rootidx;           // lowest cell id attaining rootmax
+  uint32_t* rank;              // final initial_shed number
+  uint32_t* cell;              // cell id of the pit
+  uint32_t* cnt;               // cells draining into the pit inside its own tile (itself included)
+};
+
+// row band: external inflow of the entry cells (first / last own row), indexed by column; nullptr = none
+struct BandSeeds {
+  const uint32_t* x_top = nullptr;
+  const uint32_t* x_bot = nullptr;
+  int row_top = -1, row_bot = -1;
+};
+
+// everything one calc_shed4 run keeps between its phases (the row-band driver interleaves exchanges)
+struct ShedWork {
+  PoolScratch S;
+  TileGeom tg;
+  size_t nslots = 0;
+  unsigned npits = 0;
+  L2 l2 = {};
+  Pits pits = {};
+  unsigned long long* counters = nullptr;  // [0] npits, [1] pit cursor, [2] flags (2 x u32)
+};
+
 struct TileCtx {
   int tx, ty, r_base, c_base;  // global (r, c) of local (0, 0)
 };

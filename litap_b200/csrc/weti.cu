@@ -30,6 +30,9 @@
 #include <cub/cub.cuh>
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
 #include "cellmath.h"
 #include "litap_internal.h"
 
@@ -213,9 +216,11 @@ __global__ void __launch_bounds__(WT) k_weti_donors(Arrays A, GridDims d, unsign
 
 // ------------------------------------------------------------------------------------------------
 // counters[0..2]: cells appended for wave (w % 3); counters[3]: number of waves (reported);
-// counters[4..6]: begin / end / wave handed back by the single-block tail mode
 __device__ __forceinline__ void notify(const Arrays& A, const Stager& st, size_t tid) {
   const unsigned sh = 8u * (unsigned)(tid & 3);
+  // the successor will be visited soon: pull its descriptor towards L2 while the counter round trip is in flight
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(&A.meta[tid]));
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(&A.elev[tid]));
   const unsigned old = atomicSub(&A.pend32[tid >> 2], 1u << sh);
   if (((old >> sh) & 0xFFu) == 1u) stage_push(st, (uint32_t)tid);
 }
@@ -273,10 +278,18 @@ __device__ __forceinline__ void visit(const Arrays& A, const GridDims& d, const 
   }
 }
 
-constexpr unsigned TAIL_MAX = WT;  // waves of at most this many cells are run by block 0 alone
+// Scheduling.  A cell in the queue is ready: all its donors are done and their state is visible
+// (state store -> __threadfence -> counter decrement).  A grid-wide "wave" hands every block a chunk
+// of the global queue; the successors a block releases go to its own shared-memory queue and the
+// block keeps visiting them (LIFO, depth first) for up to `local_rounds` rounds before it appends
+// what is left to the global queue for the next wave.  The DAG of the bench DEM is ~3900 levels deep
+// with a broad spread of level sizes: chasing locally divides the number of grid barriers by the
+// number of levels a block can advance on its own.
+constexpr int QCAP = STAGE * 3;  // shared queue entries; a visiting round adds at most STAGE
 
-__global__ void __launch_bounds__(WT) k_weti_waves(Arrays A, GridDims d, WetiK K, unsigned* counters) {
-  __shared__ uint32_t s_ids[STAGE];
+__global__ void __launch_bounds__(WT) k_weti_waves(Arrays A, GridDims d, WetiK K, unsigned* counters,
+                                                   unsigned* wavelog, unsigned wavelog_cap, int local_rounds) {
+  __shared__ uint32_t s_ids[QCAP];
   __shared__ unsigned s_n, s_base;
   Stager st{s_ids, &s_n, &s_base};
   cg::grid_group grid = cg::this_grid();
@@ -285,48 +298,33 @@ __global__ void __launch_bounds__(WT) k_weti_waves(Arrays A, GridDims d, WetiK K
   unsigned begin = 0, end = *reinterpret_cast<volatile unsigned*>(&counters[0]);
   unsigned wave = 0;
   while (begin < end) {
-    if (end - begin <= TAIL_MAX) {
-      // ---- tail mode: the deep, thin part of the DAG.  Block 0 runs wave after wave with block
-      // barriers only (the next wave never leaves shared memory) until a wave outgrows the block.
-      if (blockIdx.x == 0) {
-        unsigned n = end - begin;
-        uint32_t my = threadIdx.x < n ? __ldcg(&A.order[begin + threadIdx.x]) : 0xFFFFFFFFu;
-        unsigned n_next;
-        while (true) {
-          if (my != 0xFFFFFFFFu) visit(A, d, K, st, my);
-          __syncthreads();
-          n_next = s_n;
-          ++wave;
-          if (n_next == 0 || n_next > TAIL_MAX) break;
-          my = threadIdx.x < n_next ? s_ids[threadIdx.x] : 0xFFFFFFFFu;
-          __syncthreads();
-          if (threadIdx.x == 0) s_n = 0;
-          __syncthreads();
-        }
-        for (unsigned k = threadIdx.x; k < n_next; k += WT) A.order[end + k] = s_ids[k];
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          s_n = 0;
-          counters[0] = counters[1] = counters[2] = 0;
-          counters[4] = end;
-          counters[5] = end + n_next;
-          counters[6] = wave;
-        }
-      }
-      grid.sync();
-      begin = *reinterpret_cast<volatile unsigned*>(&counters[4]);
-      end = *reinterpret_cast<volatile unsigned*>(&counters[5]);
-      wave = *reinterpret_cast<volatile unsigned*>(&counters[6]);
-      grid.sync();  // everybody has read the hand-back record before block 0 can rewrite it
-      continue;
-    }
     unsigned* next_counter = &counters[(wave + 1) % 3];
-    if (blockIdx.x == 0 && threadIdx.x == 0) counters[(wave + 2) % 3] = 0;  // untouched during this wave
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      counters[(wave + 2) % 3] = 0;  // untouched during this wave
+      if (wavelog && wave < wavelog_cap) wavelog[wave] = end - begin;
+    }
+    // a wave that fits one block leaves every other block idle: let that block run on
+    const int rounds = (end - begin <= WT) ? (1 << 30) : local_rounds;
     for (unsigned base = begin + blockIdx.x * WT; base < end; base += gridDim.x * WT) {
       const unsigned i = base + threadIdx.x;
       if (i < end) visit(A, d, K, st, __ldcg(&A.order[i]));
-      stage_flush(st, A.order, end, next_counter);
+      __syncthreads();
+      const unsigned filled = s_n;
+      __syncthreads();  // nobody pushes before everybody has read
+      if (filled > QCAP - STAGE) stage_flush(st, A.order, end, next_counter);
     }
+    for (int round = 0; round < rounds; ++round) {
+      __syncthreads();
+      const unsigned n = s_n;
+      if (n == 0 || n > QCAP - STAGE) break;
+      const unsigned take = n < WT ? n : WT;
+      const uint32_t my = threadIdx.x < take ? s_ids[n - take + threadIdx.x] : 0xFFFFFFFFu;
+      __syncthreads();
+      if (threadIdx.x == 0) s_n = n - take;
+      __syncthreads();
+      if (my != 0xFFFFFFFFu) visit(A, d, K, st, my);
+    }
+    stage_flush(st, A.order, end, next_counter);
     grid.sync();
     begin = end;
     end = begin + *reinterpret_cast<volatile unsigned*>(next_counter);
@@ -485,6 +483,16 @@ int run_weti(litap_grid* g, double grid_m) {
   KERNEL("k_weti_rank", k_weti_rank<<<nblk(nd), 256, 0, st>>>(sorted, nd, A.rank));
   KERNEL("k_weti_donors", k_weti_donors<<<cgrid, WT, 0, st>>>(A, d, counters));
 
+  // LITAP_WETI_WAVELOG=1: print the wave-size histogram of the dependency DAG (tuning aid)
+  unsigned* wavelog = nullptr;
+  unsigned wavelog_cap = 0;
+  if (getenv("LITAP_WETI_WAVELOG")) {
+    wavelog_cap = 1u << 20;
+    wavelog = S.get<unsigned>(wavelog_cap);
+    if (wavelog) CUDA_TRY(cudaMemsetAsync(wavelog, 0, wavelog_cap * sizeof(unsigned), st));
+  }
+  int local_rounds = 16;
+  if (const char* e = getenv("LITAP_WETI_ROUNDS")) local_rounds = atoi(e);  // tuning aid
   static int coop_blocks = 0;
   if (!coop_blocks) {
     int per_sm = 0;
@@ -494,7 +502,7 @@ int run_weti(litap_grid* g, double grid_m) {
   }
   {
     GridDims dd = d;
-    void* args[] = {(void*)&A, (void*)&dd, (void*)&K, (void*)&counters};
+    void* args[] = {(void*)&A, (void*)&dd, (void*)&K, (void*)&counters, (void*)&wavelog, (void*)&wavelog_cap, (void*)&local_rounds};
     ProfScope prof("k_weti_waves");
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_weti_waves, dim3(coop_blocks), dim3(WT), args, 0, st));
     c.launches++;
@@ -513,5 +521,22 @@ int run_weti(litap_grid* g, double grid_m) {
   CUDA_TRY(cudaMemcpyAsync(hc, counters, sizeof(hc), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));  // scratch goes back to the pool
   c.tm.weti_waves = (int)hc[3];
+  if (wavelog) {
+    std::vector<unsigned> h(std::min<unsigned>(hc[3], wavelog_cap));
+    cudaMemcpy(h.data(), wavelog, h.size() * sizeof(unsigned), cudaMemcpyDeviceToHost);
+    unsigned long long cnt[2][33] = {}, cells[2][33] = {};
+    for (unsigned v : h) {
+      int tail = 0;
+      unsigned n = v & 0x7FFFFFFFu;
+      int b = 0;
+      while ((1u << b) < n) ++b;
+      cnt[tail][b]++;
+      cells[tail][b] += n;
+    }
+    fprintf(stderr, "weti wave-size histogram (%zu waves): bucket <=2^b : grid-mode waves/cells | tail-mode waves/cells\n", h.size());
+    for (int b = 0; b <= 32; ++b)
+      if (cnt[0][b] || cnt[1][b])
+        fprintf(stderr, "  2^%-2d : %8llu %12llu | %8llu %12llu\n", b, cnt[0][b], cells[0][b], cnt[1][b], cells[1][b]);
+  }
   return LITAP_OK;
 }
