@@ -134,6 +134,8 @@ int litap_band_create(int64_t gnr, int64_t nc, int band, int nbands, litap_grid*
 int litap_band_synth(litap_grid* band, uint32_t seed, double quant, int na_permille);
 /* elev_full: the whole buffered DEM, (gnr+2) x (nc+2) dense; the band copies its rows and halos */
 int litap_band_upload_elev(litap_grid* band, const double* elev_full);
+/* rows: only this band's rows of the buffered DEM, halo rows included: (own rows + 2) x (nc+2) dense */
+int litap_band_upload_rows(litap_grid* band, const double* rows);
 int litap_bands_ddir(litap_grid** bands, int n, int invert);
 int litap_bands_shed(litap_grid** bands, int n);
 int litap_bands_form(litap_grid** bands, int n, double grid_m);

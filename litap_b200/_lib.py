@@ -16,7 +16,7 @@ SYMBOLS = [
     "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
-    "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_bands_ddir", "litap_bands_shed",
+    "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
     "litap_bands_form", "litap_band_rows", "litap_band_download",
 ]
 
@@ -78,6 +78,7 @@ def load():
     L.litap_band_create.argtypes = [i64, i64, ci, ci, C.POINTER(vp)]
     L.litap_band_synth.argtypes = [vp, C.c_uint32, dbl, ci]
     L.litap_band_upload_elev.argtypes = [vp, vp]
+    L.litap_band_upload_rows.argtypes = [vp, vp]
     L.litap_bands_ddir.argtypes = [C.POINTER(vp), ci, ci]
     L.litap_bands_shed.argtypes = [C.POINTER(vp), ci]
     L.litap_bands_form.argtypes = [C.POINTER(vp), ci, dbl]

@@ -76,6 +76,16 @@ class BandedDEM:
         for h in self._h:
             check(lib().litap_band_upload_elev(h, e.ctypes.data))
 
+    def upload_rows(self, rows, i=0):
+        """Local band i from its own rows of the buffered DEM (halo rows included): (own + 2, nc + 2)."""
+        e = np.ascontiguousarray(rows, dtype=np.float64)
+        check(lib().litap_band_upload_rows(self._h[i], e.ctypes.data))
+
+    def halo_rows(self, i=0):
+        """(first row, row count) in the buffered DEM of the rows band i holds, halo rows included."""
+        r0, n = band_rows(self.gnr, self.bands[i], self.nbands)
+        return r0, n - r0 + 2
+
     def ddir(self, invert=False):
         check(lib().litap_bands_ddir(self._arr, len(self._h), int(bool(invert))))
 
@@ -90,6 +100,11 @@ class BandedDEM:
         r0, n = C.c_int64(0), C.c_int64(0)
         check(lib().litap_band_rows(self._h[i], C.byref(r0), C.byref(n)))
         return r0.value, n.value
+
+    def download_into(self, name, out, i=0):
+        """Like download(name, i) into a preallocated (e.g. pinned) array."""
+        check(lib().litap_band_download(self._h[i], name.encode(), out.ctypes.data))
+        return out
 
     def download(self, name, i=None):
         """Rows of result `name` held by local band i, or (i=None) by all local bands stacked in band

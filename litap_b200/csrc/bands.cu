@@ -261,6 +261,18 @@ extern "C" int litap_band_synth(litap_grid* g, uint32_t seed, double quant, int 
   return LITAP_OK;
 }
 
+// the band's own copy of its rows: local rows 1 .. NR-1 (halo rows included), NC wide, dense
+extern "C" int litap_band_upload_rows(litap_grid* g, const double* rows) {
+  if (!g || g->nbands < 1 || !rows) return set_error(LITAP_EARG, "litap_band_upload_rows: bad arguments");
+  const GridDims d = g->d;
+  CUDA_TRY(cudaMemcpy2DAsync(g->elev + d.pitch, (size_t)d.pitch * 8, rows, (size_t)d.NC * 8, (size_t)d.NC * 8, d.NR - 1,
+                             cudaMemcpyHostToDevice, ctx().stream));
+  CUDA_TRY(cudaMemsetAsync(g->elev, 0xFF, (size_t)d.pitch * sizeof(double), ctx().stream));
+  g->have_ddir = g->have_shed = false;
+  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  return LITAP_OK;
+}
+
 // rows of the full buffered DEM (gnr+2 rows, NC wide) that belong to this band, halo rows included
 extern "C" int litap_band_upload_elev(litap_grid* g, const double* elev_full) {
   if (!g || g->nbands < 1 || !elev_full) return set_error(LITAP_EARG, "litap_band_upload_elev: bad arguments");

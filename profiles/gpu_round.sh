@@ -9,7 +9,7 @@ tail -5 gpurun_out/pytest_$tag.log
 python bench.py > gpurun_out/bench_$tag.json 2> gpurun_out/bench_$tag.err; echo "bench exit $?"
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_$tag.json 2>> gpurun_out/bench_$tag.err; echo "ref exit $?"
 python profiles/stage_times.py 8192 3 > gpurun_out/stages_$tag.log 2>&1
-B="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu"
+B="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu --no-weti"
 $B > gpurun_out/plain_$tag.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$tag.csv $B > gpurun_out/ncu1_$tag.log 2>&1
 echo "ncu launches exit $?"
