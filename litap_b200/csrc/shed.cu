@@ -34,122 +34,138 @@ __global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsig
 }
 
 // ------------------------------------------------------------------------------------------------
-constexpr size_t SMEM_A = (size_t)LC * (8 + 4 + 2 + 1) + 64;  // key, idx|cnt, ptr, dir
+// shared memory of k_shed_local: ptr, dir, cnt, key hi / lo / idx (no aliasing: fewer barriers)
+constexpr size_t SMEM_A = (size_t)LC * (2 + 1 + 4 + 4 + 4 + 4) + 64;
 
-__global__ void __launch_bounds__(NT, 1024 / NT) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
-                                                   const double* __restrict__ elev, uint32_t* __restrict__ lab,
-                                                   L2 l2, Pits pits, unsigned long long* pit_cursor) {
+__global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
+                                                      const double* __restrict__ elev, uint32_t* __restrict__ lab,
+                                                      L2 l2, Pits pits, unsigned long long* pit_cursor) {
   extern __shared__ __align__(16) unsigned char smem[];
-  unsigned long long* s_key = reinterpret_cast<unsigned long long*>(smem);       // LC x 8
-  uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);           // LC x 4
-  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 12);          // LC x 2
-  uint8_t* s_dir = smem + (size_t)LC * 14;                                        // LC x 1
-  unsigned* s_cnt = s_idx;                                                        // dead before s_idx is first used
+  unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                               // LC x 4
+  uint32_t* s_khi = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);              // LC x 4: key, high word
+  uint32_t* s_klo = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);              // LC x 4: key, low word
+  uint32_t* s_kid = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 12);             // LC x 4: lowest cell id / pid
+  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 16);             // LC x 2
+  uint8_t* s_dir = smem + (size_t)LC * 18;                                           // LC x 1
   __shared__ unsigned s_npit;
   __shared__ unsigned long long s_pitbase;
 
   const TileCtx t = tile_ctx();
   const int lx = owned_lx(), c = t.c_base + lx;
+  const int base = owned_local(0);
   const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
+  const size_t cell0 = (size_t)(t.r_base + owned_ly(0)) * g.d.pitch + c;  // k-th owned cell: cell0 + k*pitch
   if (threadIdx.x == 0) s_npit = 0;
-  tile_load_dir(g, t, ddir, s_dir);
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) s_key[owned_local(k)] = 0ull;
-  __syncthreads();
-  // ---- local terminals + local flow counts; exits hand their count to the entry cell's slot
-  // (base of the level-2 sum)
-  {
-    unsigned w[CPT];
-#pragma unroll
-    for (int k = 0; k < CPT; ++k) w[k] = s_dir[owned_local(k)] != 0 ? 1u : 0u;  // out-of-grid cells have ddir 0
-    tile_jump_accumulate(s_dir, s_ptr, s_cnt, w);
-  }
-  unsigned pcnt[CPT];  // pits: cells draining into them inside this tile
+  int p[CPT];
+  const unsigned dvp = tile_setup(g, t, ddir, s_ptr, s_dir, p);
+  // elevations of the owned cells: issued now, consumed after the pointer-doubling loop
+  double ev[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int ly = owned_ly(k), i = ly * LW + lx;
-    int dv = s_dir[i];
+    const bool valid = ((dvp >> (4 * k)) & 15u) != 0;
+    ev[k] = valid ? elev[cell0 + (size_t)k * g.d.pitch] : 0.0;
+    const int i = base + k * LW;
+    s_cnt[i] = valid ? 1u : 0u;  // out-of-grid and NA cells carry no weight
+    s_khi[i] = 0u;
+    s_klo[i] = 0u;
+    s_kid[i] = 0xFFFFFFFFu;
+  }
+  __syncthreads();
+  const unsigned pit_mask_src = dvp;  // dv == 5 <-> pit
+  tile_jump_accumulate(s_ptr, s_cnt, p);
+  // here: all REDs into s_cnt are complete (the loop ends with a barrier or with the all-done vote)
+
+  // ---- exits hand their count to the entry cell's slot (base of the level-2 sum); pits keep theirs
+  unsigned pcnt[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    const int dv = (dvp >> (4 * k)) & 15u;
+    const int i = base + k * LW;
     pcnt[k] = s_cnt[i];
-    if (s_ptr[i] == i && dv != 5) {  // valid exit: entry cell on the local ring
-      long long es = slot_of_rc(t.r_base + ly + nb_dr(dv), c + nb_dc(dv), g.tilesX);
+    // own initial pointer word had T_EXIT <=> the final one has it and points at the cell itself
+    if ((p[k] & (OVER | T_EXIT)) == (OVER | T_EXIT) && (p[k] & PIDX) == i) {
+      const long long es = slot_of_rc(t.r_base + owned_ly(k) + nb_dr(dv), c + nb_dc(dv), g.tilesX);
       if (es >= 0) atomicAdd(&l2.ext[es], pcnt[k]);
     }
   }
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) s_idx[owned_local(k)] = 0xFFFFFFFFu;  // s_cnt is dead: same memory
-  __syncthreads();
 
-  // ---- per-terminal key: max elevation, then lowest cell id attaining it
+  // ---- per-terminal key: max elevation, then lowest cell id attaining it; three rounds of native
+  // 32-bit shared REDs (high word, low word among the high-word winners, id among the winners)
+  uint32_t khi[CPT], klo[CPT];
   int term[CPT];
-  unsigned long long key[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(k);
-    term[k] = s_ptr[i];  // 0 = NA
-    key[k] = 0;
-    if (term[k]) {
-      key[k] = f64_orderable(elev[(size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c]);
-      atomicMax(&s_key[term[k]], key[k]);
-    }
+    const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
+    term[k] = ok ? (p[k] & PIDX) : 0;  // 0 = NA (the ring corner is never a terminal)
+    const unsigned long long key = f64_orderable(ev[k]);
+    khi[k] = (uint32_t)(key >> 32);
+    klo[k] = (uint32_t)key;
+    if (term[k]) atomicMax(&s_khi[term[k]], khi[k]);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    if (term[k] && khi[k] == s_khi[term[k]]) atomicMax(&s_klo[term[k]], klo[k]);
+    else term[k] = -term[k];  // out of the race (sign keeps the terminal for nothing: not used again)
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if (term[k] && key[k] == s_key[term[k]])
-      atomicMin(&s_idx[term[k]], (uint32_t)((size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c));
-  __syncthreads();
+    if (term[k] > 0 && klo[k] == s_klo[term[k]]) atomicMin(&s_kid[term[k]], (uint32_t)(cell0 + (size_t)k * g.d.pitch));
 
   // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
   unsigned rk[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     rk[k] = 0xFFFFFFFFu;
-    if (s_dir[owned_local(k)] == 5) rk[k] = atomicAdd(&s_npit, 1u);
+    if (((pit_mask_src >> (4 * k)) & 15u) == 5u) rk[k] = atomicAdd(&s_npit, 1u);
   }
-  __syncthreads();
+  __syncthreads();  // keys complete, s_npit complete
   if (threadIdx.x == 0 && s_npit) s_pitbase = atomicAdd(pit_cursor, (unsigned long long)s_npit);
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     if (rk[k] == 0xFFFFFFFFu) continue;
-    int i = owned_local(k);
-    uint32_t pid = (uint32_t)(s_pitbase + rk[k]);
-    pits.rootmax[pid] = s_key[i];
-    pits.pitkmax[pid] = s_key[i];
-    pits.pitkidx[pid] = s_idx[i];
+    const int i = base + k * LW;
+    const uint32_t pid = (uint32_t)(s_pitbase + rk[k]);
+    const unsigned long long key = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
+    pits.rootmax[pid] = key;
+    pits.pitkmax[pid] = key;
+    pits.pitkidx[pid] = s_kid[i];
     pits.rootidx[pid] = 0xFFFFFFFFu;
-    pits.cell[pid] = (uint32_t)((size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c);
+    pits.cell[pid] = (uint32_t)(cell0 + (size_t)k * g.d.pitch);
     pits.cnt[pid] = pcnt[k];
-    lab[(size_t)(t.r_base + owned_ly(k)) * g.d.pitch + c] = pid;  // read back by k_shed_final of this tile
-    s_idx[i] = pid;                                                // from here on s_idx[pit] is its pid
+    lab[cell0 + (size_t)k * g.d.pitch] = pid;  // read back by k_shed_final of this tile
+    s_cnt[i] = pid;                            // from here on s_cnt[pit] is its pid (counts are consumed)
   }
   __syncthreads();
 
-  // ---- level-2 edges and key partials of the border cells
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int ly = owned_ly(k);
-    int bs = border_slot_local(lx, ly);
-    if (bs < 0) continue;
-    int i = ly * LW + lx;
+  // ---- level-2 edges and key partials: one thread per border slot
+  if (threadIdx.x < BUSED) {
+    int bx, by;
+    slot_to_local((int)threadIdx.x, bx, by);
+    const int i = by * LW + bx;
+    const int pw = s_ptr[i];
     uint32_t edge = ID_NA;
     unsigned long long pk = 0;
     uint32_t pi = 0xFFFFFFFFu;
-    int tt = term[k];
-    if (tt) {
-      int dv = s_dir[tt];
-      if (dv == 5) edge = ID_ROOT | s_idx[tt];
+    if ((pw & OVER) && (pw & (T_PIT | T_EXIT))) {
+      const int tt = pw & PIDX;
+      if (pw & T_PIT) edge = ID_ROOT | s_cnt[tt];
       else {  // exit: continue at the entry cell of the neighbouring tile
-        int ty_ = tt / LW, tx_ = tt - ty_ * LW;
+        const int dv = s_dir[tt];
+        const int ty_ = tt / LW, tx_ = tt - ty_ * LW;
         edge = (uint32_t)((size_t)(t.r_base + ty_ + nb_dr(dv)) * g.d.pitch + (t.c_base + tx_ + nb_dc(dv)));
-        if (tt == i) { pk = s_key[i]; pi = s_idx[i]; }  // this border cell is the exit itself
+        if (tt == i) {  // this border cell is the exit itself
+          pk = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
+          pi = s_kid[i];
+        }
       }
     }
-    l2.jump0[tile_slot0 + bs] = edge;
-    l2.jres[tile_slot0 + bs] = edge;
-    l2.pkmax[tile_slot0 + bs] = pk;
-    l2.pkidx[tile_slot0 + bs] = pi;
+    l2.jump0[tile_slot0 + threadIdx.x] = edge;
+    l2.jres[tile_slot0 + threadIdx.x] = edge;
+    l2.pkmax[tile_slot0 + threadIdx.x] = pk;
+    l2.pkidx[tile_slot0 + threadIdx.x] = pi;
   }
 }
 
@@ -241,44 +257,63 @@ __global__ void k_scatter_rank(const uint32_t* __restrict__ order, uint32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------
-constexpr size_t SMEM_B = (size_t)LC * (4 + 4 + 2 + 1) + 64;  // cnt, lab, ptr, dir
+// shared memory of k_shed_final: cnt, terminal labels, cell labels, ptr, dir
+constexpr size_t SMEM_B = (size_t)LC * (4 + 4 + 4 + 2 + 1) + 64;
 
-__global__ void __launch_bounds__(NT, 1024 / NT) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
-                                                   const uint32_t* __restrict__ rank, int32_t* shed_out,
-                                                   uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge,
-                                                   BandSeeds seeds) {
+__device__ __forceinline__ uint32_t rank_of_edge(uint32_t v, const uint32_t* __restrict__ rank) {
+  return (v != ID_NA && (v & ID_ROOT)) ? rank[v & ~ID_ROOT] : 0u;
+}
+
+__global__ void __launch_bounds__(NT, 6) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
+                                                      const uint32_t* __restrict__ rank, int32_t* shed_out,
+                                                      uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge,
+                                                      BandSeeds seeds) {
   extern __shared__ __align__(16) unsigned char smem[];
   unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                      // LC x 4
-  uint32_t* s_lab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);     // LC x 4
-  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 8);     // LC x 2
-  uint8_t* s_dir = smem + (size_t)LC * 10;                                  // LC x 1
+  uint32_t* s_tlab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);    // LC x 4: label of a terminal
+  uint32_t* s_lab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);     // LC x 4: label of every local cell
+  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 12);    // LC x 2
+  uint8_t* s_dir = smem + (size_t)LC * 14;                                  // LC x 1
   const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
 
   const TileCtx t = tile_ctx();
   const int lx = owned_lx(), c = t.c_base + lx;
+  const int base = owned_local(0);
   const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
-  tile_load_dir(g, t, ddir, s_dir);
-  __syncthreads();
-  // ---- local terminals + upslope: in-tile accumulation seeded with the external inflow of the
-  // border cells (level-2 result)
-  {
-    unsigned w[CPT];
+  const size_t cell0 = (size_t)(t.r_base + owned_ly(0)) * g.d.pitch + c;
+  int p[CPT];
+  const unsigned dvp = tile_setup(g, t, ddir, s_ptr, s_dir, p);
+  // weights: 1 per valid cell (+ flow entering a row band at its first / last own row)
 #pragma unroll
-    for (int k = 0; k < CPT; ++k) {
-      int ly = owned_ly(k);
-      w[k] = 0;
-      if (s_dir[ly * LW + lx] != 0) {
-        w[k] = 1;
-        int bs = border_slot_local(lx, ly);
-        if (bs >= 0) w[k] += l2.ext[tile_slot0 + bs];
-        // row band: flow entering from the neighbouring bands at the first / last own row
-        if (seeds.x_top && t.r_base + ly == seeds.row_top) w[k] += seeds.x_top[c];
-        if (seeds.x_bot && t.r_base + ly == seeds.row_bot) w[k] += seeds.x_bot[c];
-      }
-    }
-    tile_jump_accumulate(s_dir, s_ptr, s_cnt, w);
+  for (int k = 0; k < CPT; ++k) {
+    unsigned w = ((dvp >> (4 * k)) & 15u) != 0 ? 1u : 0u;
+    if (w && seeds.x_top && t.r_base + owned_ly(k) == seeds.row_top) w += seeds.x_top[c];
+    if (w && seeds.x_bot && t.r_base + owned_ly(k) == seeds.row_bot) w += seeds.x_bot[c];
+    s_cnt[base + k * LW] = w;
   }
+  __syncthreads();
+  // + the external inflow of the border cells (level-2 result): one thread per border slot
+  if (threadIdx.x < BUSED) {
+    int bx, by;
+    slot_to_local((int)threadIdx.x, bx, by);
+    const int i = by * LW + bx;
+    if (s_dir[i] != 0) s_cnt[i] += l2.ext[tile_slot0 + threadIdx.x];
+  }
+  __syncthreads();
+  tile_jump_accumulate(s_ptr, s_cnt, p);
 
+  // ---- labels of the terminals: pits look up their own rank, exits the rank of their resolved root
+#pragma unroll
+  for (int k = 0; k < CPT; ++k)
+    if (((dvp >> (4 * k)) & 15u) == 5u) s_tlab[base + k * LW] = rank[lab_in[cell0 + (size_t)k * g.d.pitch]];
+  if (threadIdx.x < BUSED) {
+    int bx, by;
+    slot_to_local((int)threadIdx.x, bx, by);
+    const int i = by * LW + bx;
+    const int pw = s_ptr[i];
+    if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == i)
+      s_tlab[i] = rank_of_edge(l2.jres[tile_slot0 + threadIdx.x], rank);
+  }
   // ---- labels of the ring cells (for the ridge test): border cells of the neighbouring tiles
   for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
     int ry, rx;
@@ -286,65 +321,62 @@ __global__ void __launch_bounds__(NT, 1024 / NT) k_shed_final(TileGeom g, const 
     else if (q < 2 * LW) { ry = LH - 1; rx = q - LW; }
     else if (q < 2 * LW + TH) { ry = q - 2 * LW + 1; rx = 0; }
     else { ry = q - 2 * LW - TH + 1; rx = LW - 1; }
-    int r = t.r_base + ry, cc = t.c_base + rx;
+    const int r = t.r_base + ry, cc = t.c_base + rx;
     uint32_t lb = 0;
     if (r >= 1 && cc >= 1 && in_grid(g, r, cc)) {
-      long long s = slot_of_rc(r, cc, g.tilesX);
-      uint32_t v = s >= 0 ? l2.jres[s] : ID_NA;
-      if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
+      const long long s = slot_of_rc(r, cc, g.tilesX);
+      if (s >= 0) lb = rank_of_edge(l2.jres[s], rank);
     }
     s_lab[ry * LW + rx] = lb;
-  }
-  // ---- labels of the terminals: pits look up their own rank, exits the rank of their resolved root
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int ly = owned_ly(k), i = ly * LW + lx;
-    if (s_ptr[i] != i) continue;
-    uint32_t lb = 0;
-    if (s_dir[i] == 5) lb = rank[lab_in[(size_t)(t.r_base + ly) * g.d.pitch + c]];
-    else {
-      uint32_t v = l2.jres[tile_slot0 + border_slot_local(lx, ly)];
-      if (v != ID_NA && (v & ID_ROOT)) lb = rank[v & ~ID_ROOT];
-    }
-    s_lab[i] = lb;
   }
   __syncthreads();
   uint32_t mylab[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int tt = s_ptr[owned_local(k)];
-    mylab[k] = tt ? s_lab[tt] : 0u;
+    const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
+    mylab[k] = ok ? s_tlab[p[k] & PIDX] : 0u;
+    s_lab[base + k * LW] = mylab[k];
   }
   __syncthreads();
+
+  // ---- outputs; the ridge window slides down the thread's column (3 new labels per cell)
+  uint32_t w0[3], w1[3], w2[3];  // rows above / at / below the current cell, columns lx-1 .. lx+1
 #pragma unroll
-  for (int k = 0; k < CPT; ++k) s_lab[owned_local(k)] = mylab[k];
-
-  __syncthreads();
-
-  // ---- outputs
+  for (int j = 0; j < 3; ++j) {
+    w0[j] = s_lab[base - LW + j - 1];
+    w1[j] = s_lab[base + j - 1];
+  }
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int ly = owned_ly(k), i = ly * LW + lx;
-    int r = t.r_base + ly;
-    if (!in_grid(g, r, c)) continue;
-    size_t o = (size_t)r * g.d.pitch + c;
-    uint32_t lb = mylab[k];
-    uint8_t rg = 2;  // NA on the ring
-    if (r < g.d.NR - 1 && c < g.d.NC - 1) {
-      uint32_t first = 0;
-      bool multi = false;
+    const int i = base + k * LW;
 #pragma unroll
-      for (int n = 1; n <= 9; ++n) {
-        uint32_t s = s_lab[i + nb_dr(n) * LW + nb_dc(n)];
-        if (!s) continue;
-        if (!first) first = s;
-        else if (s != first) multi = true;
+    for (int j = 0; j < 3; ++j) w2[j] = s_lab[i + LW + j - 1];
+    const int r = t.r_base + owned_ly(k);
+    if (in_grid(g, r, c)) {
+      const size_t o = cell0 + (size_t)k * g.d.pitch;
+      const uint32_t lb = mylab[k];
+      uint8_t rg = 2;  // NA on the ring
+      if (r < g.d.NR - 1 && c < g.d.NC - 1) {
+        // more than one distinct non-NA label in the 3 x 3 window (R/flow_02_calc_shed.R:48-57)
+        uint32_t first = lb;
+        bool multi = false;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const uint32_t v[3] = {w0[j], w1[j], w2[j]};
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            if (!first) first = v[q];
+            multi |= (v[q] != 0u) & (v[q] != first) & (first != 0u);
+          }
+        }
+        rg = multi;
       }
-      rg = multi;
+      shed_out[o] = (int32_t)lb;
+      upslope[o] = lb ? s_cnt[i] : 0u;
+      ridge[o] = rg;
     }
-    shed_out[o] = (int32_t)lb;
-    upslope[o] = lb ? s_cnt[i] : 0u;
-    ridge[o] = rg;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) { w0[j] = w1[j]; w1[j] = w2[j]; }
   }
 }
 

@@ -15,10 +15,14 @@
 namespace shed {
 
 constexpr int NT = TW * TH / 8;    // threads per tile CTA: 8 interior cells per thread
-constexpr int CPT = TW * TH / NT;  // interior cells per thread (8)
-constexpr int RPK = NT / TW;       // tile rows covered by one pass of the CTA
-static_assert(NT % TW == 0 && (TW & (TW - 1)) == 0, "row-wise ownership needs a power-of-two tile width");
-constexpr uint8_t RING = 0x80;     // s_dir flag of the local ring cells
+constexpr int CPT = TW * TH / NT;  // interior cells per thread (8): consecutive rows of one column
+constexpr int RG = NT / TW;        // row groups of the CTA
+static_assert(NT % TW == 0 && RG * CPT == TH, "a thread owns CPT consecutive rows of one tile column");
+static_assert(CPT <= 8, "direction codes of the owned cells are packed 4 bits each in one register");
+// local pointer word (16 bit): low 11 bits = local index, OVER = the walk has reached / passed the
+// terminal whose index is in the low bits, T_PIT / T_EXIT = kind of that terminal (neither = NA)
+constexpr int OVER = 0x8000, T_PIT = 0x4000, T_EXIT = 0x2000, PIDX = 0x07FF;
+static_assert(LC <= PIDX + 1, "local indices must fit 11 bits");
 
 struct TileGeom {
   GridDims d;
@@ -31,11 +35,19 @@ __device__ __forceinline__ int loc_off(int dir) {
   int dc = (int)((0x92490u >> (2 * dir)) & 3u) - 1;  // 2-bit table of (dir-1)%3 for dir 0..9 (dir 0 -> unused)
   return dr * LW + dc;
 }
-// k-th interior cell owned by this thread: consecutive threads take consecutive columns of a row
-__device__ __forceinline__ int owned_ly(int k) { return k * RPK + (int)(threadIdx.x / TW) + 1; }
+// k-th interior cell owned by this thread: a warp covers 32 consecutive columns of one row (coalesced
+// global accesses); a thread walks down CPT consecutive rows (vertical reuse in the ridge window)
+__device__ __forceinline__ int owned_ly(int k) { return (int)(threadIdx.x / TW) * CPT + k + 1; }
 __device__ __forceinline__ int owned_lx() { return (int)(threadIdx.x % TW) + 1; }
 __device__ __forceinline__ int owned_local(int k) { return owned_ly(k) * LW + owned_lx(); }
 
+// local coordinates of border slot s (0 <= s < BUSED): inverse of border_slot_local
+__device__ __forceinline__ void slot_to_local(int s, int& lx, int& ly) {
+  if (s < TW) { ly = 1; lx = s + 1; }
+  else if (s < 2 * TW) { ly = TH; lx = s - TW + 1; }
+  else if (s < 2 * TW + TH - 2) { lx = 1; ly = s - 2 * TW + 2; }
+  else { lx = TW; ly = s - (2 * TW + TH - 2) + 2; }
+}
 __device__ __forceinline__ int border_slot_local(int lx, int ly) {
   if (ly == 1) return lx - 1;
   if (ly == TH) return TW + lx - 1;
@@ -104,101 +116,81 @@ __device__ __forceinline__ TileCtx tile_ctx() {
 }
 __device__ __forceinline__ bool in_grid(const TileGeom& g, int r, int c) { return r < g.d.NR && c < g.d.NC; }
 
-// Phase 0: stage ddir of the interior (0 outside the grid; buffered row 0 / column 0 belong to no
-// tile: they are the NA ring) and flag the local ring.  A cell whose ddir points outside the grid
-// or onto row 0 / column 0 becomes NA itself (its chain has an NA drec).
-__device__ __forceinline__ void tile_load_dir(const TileGeom& g, const TileCtx& t, const uint8_t* __restrict__ ddir,
-                                              uint8_t* s_dir) {
-  for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
-    int li;
-    if (q < LW) li = q;
-    else if (q < 2 * LW) li = (LH - 1) * LW + (q - LW);
-    else if (q < 2 * LW + TH) li = (q - 2 * LW + 1) * LW;
-    else li = (q - 2 * LW - TH + 1) * LW + LW - 1;
-    s_dir[li] = RING;
-  }
+// Phase 0: stage ddir of the owned cells and their initial pointer words.  Cells outside the grid,
+// with NA ddir, or whose ddir leaves the grid / points onto buffered row 0 or column 0 (which belong
+// to no tile: the NA ring) are NA terminals.  Returns the 8 direction codes packed 4 bits each; p[k]
+// gets the pointer word of the k-th owned cell.
+__device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx& t, const uint8_t* __restrict__ ddir,
+                                               uint16_t* s_ptr, uint8_t* s_dir, int* p) {
   const int lx = owned_lx(), c = t.c_base + lx;
+  const bool atL = lx == 1, atR = lx == TW;
+  unsigned pack = 0;
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    int ly = owned_ly(k), r = t.r_base + ly;
-    uint8_t dv = 0;
+    const int ly = owned_ly(k), r = t.r_base + ly, i = ly * LW + lx;
+    int dv = 0;
     if (in_grid(g, r, c)) {
       dv = ddir[(size_t)r * g.d.pitch + c];
       if (dv > 9) dv = 0;
-      if (dv != 0 && dv != 5) {
-        int rr = r + nb_dr(dv), cc = c + nb_dc(dv);
-        if (rr < 1 || cc < 1 || !in_grid(g, rr, cc)) dv = 0;
+    }
+    int pw = i | OVER;  // NA terminal unless shown otherwise
+    if (dv == 5) pw |= T_PIT;
+    else if (dv != 0) {
+      const int dr = (dv < 4) - (dv > 6);
+      const int dc = (int)((0x92490u >> (2 * dv)) & 3u) - 1;  // (dv-1)%3 - 1
+      const int rr = r + dr, cc = c + dc;
+      if (rr < 1 || cc < 1 || !in_grid(g, rr, cc)) dv = 0;
+      else {
+        const bool ex = (dc < 0 && atL) || (dc > 0 && atR) || (dr < 0 && ly == 1) || (dr > 0 && ly == TH);
+        pw = ex ? (i | OVER | T_EXIT) : (i + dr * LW + dc);
       }
     }
-    s_dir[ly * LW + lx] = dv;
+    s_ptr[i] = (uint16_t)pw;
+    s_dir[i] = (uint8_t)dv;
+    p[k] = pw;
+    pack |= (unsigned)dv << (4 * k);
   }
+  return pack;
 }
 
 // Phase 1: local terminals AND in-tile flow accumulation in one pointer-doubling loop, no
 // divergent walks and no return-value atomics.  p_k(c) is the cell 2^k steps downstream of c inside
-// the tile, flagged OVER once the walk would pass the local terminal; S_k(c) is the weight of all
-// cells at distance < 2^k upstream of c (S_0 = own weight).  One round does
+// the tile, flagged OVER (with the terminal's index and kind) once the walk would pass the local
+// terminal; S_k(c) is the weight of all cells at distance < 2^k upstream of c (S_0 = own weight).
+// One round does
 //     S_{k+1}(p_k(y)) += S_k(y)   for every y whose p_k is not OVER      (32-bit shared RED)
 //     p_{k+1}(y) = p_k(p_k(y))
 // because the cells at distance 2^k .. 2^(k+1)-1 above c are exactly the S_k sets of the cells y
 // sitting 2^k steps above c.  ceil(log2(longest in-tile path)) rounds, two barriers per round.
-// On return, for every interior cell i: s_cnt[i] = weight draining through i inside the tile
-// (itself included) and s_ptr[i] = local index of its valid terminal (a pit or an exit cell), or
-// 0 (the ring corner, never a terminal) when the chain is NA: NA ddir, leaves the grid, or a cycle.
-constexpr int OVER = 0x8000;
+// The caller has stored the weights in s_cnt and synchronised.  On return p[k] is the final pointer
+// word of the k-th owned cell (a cycle never gets OVER: treat as NA) and s_cnt[i] the weight draining
+// through cell i inside the tile, itself included.
 constexpr int MAX_ROUNDS = LC > 2048 ? 14 : 12;  // 2^(MAX_ROUNDS-1) > LC: only cycles are still live after that
 
-__device__ __forceinline__ void tile_jump_accumulate(const uint8_t* s_dir, uint16_t* s_ptr, unsigned* s_cnt,
-                                                     const unsigned* w) {
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int i = owned_local(k);
-    int dv = s_dir[i], p = i | OVER;
-    if (dv != 0 && dv != 5) {
-      int t = i + loc_off(dv);
-      if (!(s_dir[t] & RING)) p = t;  // else: exit cell, a terminal
-    }
-    s_ptr[i] = (uint16_t)p;
-    s_cnt[i] = w[k];
-  }
-  __syncthreads();
+__device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* s_cnt, int* p) {
+  const int base = owned_local(0);
   for (int round = 0; round < MAX_ROUNDS; ++round) {
-    int a[CPT], b[CPT];
+    int b[CPT];
     unsigned sv[CPT];
     bool any = false;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
-      int i = owned_local(k);
-      a[k] = s_ptr[i];
-      if (!(a[k] & OVER)) {
-        b[k] = s_ptr[a[k]];
-        sv[k] = s_cnt[i];
+      if (!(p[k] & OVER)) {
+        b[k] = s_ptr[p[k]];
+        sv[k] = s_cnt[base + k * LW];
         any = true;
       }
     }
     if (!__syncthreads_or(any)) break;  // also separates this round's reads from its writes
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
-      if (a[k] & OVER) continue;
-      s_ptr[owned_local(k)] = (uint16_t)b[k];
-      atomicAdd(&s_cnt[a[k]], sv[k]);
+      if (p[k] & OVER) continue;
+      s_ptr[base + k * LW] = (uint16_t)b[k];
+      atomicAdd(&s_cnt[p[k]], sv[k]);
+      p[k] = b[k];
     }
     __syncthreads();
   }
-  // classify: a valid terminal was reached (OVER) and is a pit or an exit
-  int res[CPT];
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    int pv = s_ptr[owned_local(k)];
-    int tt = pv & (OVER - 1);
-    int dv = s_dir[tt];
-    bool ok = (pv & OVER) && dv != 0 && (dv == 5 || (s_dir[tt + loc_off(dv)] & RING));
-    res[k] = ok ? tt : 0;
-  }
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) s_ptr[owned_local(k)] = (uint16_t)res[k];
-  __syncthreads();
 }
 
 }  // namespace shed
