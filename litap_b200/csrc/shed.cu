@@ -40,13 +40,14 @@ constexpr size_t SMEM_A = (size_t)LC * (2 + 1 + 4 + 4 + 4 + 4) + 64;
 __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
                                                       const double* __restrict__ elev, uint32_t* __restrict__ lab,
                                                       L2 l2, Pits pits, unsigned long long* pit_cursor) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                               // LC x 4
-  uint32_t* s_khi = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);              // LC x 4: key, high word
-  uint32_t* s_klo = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);              // LC x 4: key, low word
-  uint32_t* s_kid = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 12);             // LC x 4: lowest cell id / pid
-  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 16);             // LC x 2
-  uint8_t* s_dir = smem + (size_t)LC * 18;                                           // LC x 1
+  // static shared arrays: the compiler addresses them with immediate offsets (with dynamic shared
+  // memory it rebuilt the shared-window base, 4 instructions, in front of most accesses)
+  __shared__ unsigned s_cnt[LC];
+  __shared__ uint32_t s_khi[LC];   // key, high word
+  __shared__ uint32_t s_klo[LC];   // key, low word
+  __shared__ uint32_t s_kid[LC];   // lowest cell id attaining the key; later the pit id
+  __shared__ uint16_t s_ptr[LC];
+  __shared__ uint8_t s_dir[LC];
   __shared__ unsigned s_npit;
   __shared__ unsigned long long s_pitbase;
 
@@ -92,26 +93,27 @@ __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t*
   // ---- per-terminal key: max elevation, then lowest cell id attaining it; three rounds of native
   // 32-bit shared REDs (high word, low word among the high-word winners, id among the winners)
   uint32_t khi[CPT], klo[CPT];
-  int term[CPT];
+  int term[CPT];  // 4 * local index of the terminal; 0 = NA (the ring corner is never a terminal)
+  const uint32_t a_khi = smem_addr(s_khi), a_klo = smem_addr(s_klo), a_kid = smem_addr(s_kid);
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
-    term[k] = ok ? (p[k] & PIDX) : 0;  // 0 = NA (the ring corner is never a terminal)
+    term[k] = ok ? 4 * (p[k] & PIDX) : 0;
     const unsigned long long key = f64_orderable(ev[k]);
     khi[k] = (uint32_t)(key >> 32);
     klo[k] = (uint32_t)key;
-    if (term[k]) atomicMax(&s_khi[term[k]], khi[k]);
+    if (term[k]) red_max_u32(a_khi + term[k], khi[k]);
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    if (term[k] && khi[k] == s_khi[term[k]]) atomicMax(&s_klo[term[k]], klo[k]);
-    else term[k] = -term[k];  // out of the race (sign keeps the terminal for nothing: not used again)
+    if (term[k] && khi[k] == lds_u32(a_khi + term[k])) red_max_u32(a_klo + term[k], klo[k]);
+    else term[k] = 0;  // out of the race
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if (term[k] > 0 && klo[k] == s_klo[term[k]]) atomicMin(&s_kid[term[k]], (uint32_t)(cell0 + (size_t)k * g.d.pitch));
+    if (term[k] && klo[k] == lds_u32(a_klo + term[k])) red_min_u32(a_kid + term[k], (uint32_t)(cell0 + (size_t)k * g.d.pitch));
 
   // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
   unsigned rk[CPT];
@@ -268,12 +270,11 @@ __global__ void __launch_bounds__(NT, 6) k_shed_final(TileGeom g, const uint8_t*
                                                       const uint32_t* __restrict__ rank, int32_t* shed_out,
                                                       uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge,
                                                       BandSeeds seeds) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  unsigned* s_cnt = reinterpret_cast<unsigned*>(smem);                      // LC x 4
-  uint32_t* s_tlab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 4);    // LC x 4: label of a terminal
-  uint32_t* s_lab = reinterpret_cast<uint32_t*>(smem + (size_t)LC * 8);     // LC x 4: label of every local cell
-  uint16_t* s_ptr = reinterpret_cast<uint16_t*>(smem + (size_t)LC * 12);    // LC x 2
-  uint8_t* s_dir = smem + (size_t)LC * 14;                                  // LC x 1
+  __shared__ unsigned s_cnt[LC];
+  __shared__ uint32_t s_tlab[LC];  // label of a terminal
+  __shared__ uint32_t s_lab[LC];   // label of every local cell
+  __shared__ uint16_t s_ptr[LC];
+  __shared__ uint8_t s_dir[LC];
   const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
 
   const TileCtx t = tile_ctx();
@@ -331,10 +332,11 @@ __global__ void __launch_bounds__(NT, 6) k_shed_final(TileGeom g, const uint8_t*
   }
   __syncthreads();
   uint32_t mylab[CPT];
+  const uint32_t a_tlab = smem_addr(s_tlab);
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
-    mylab[k] = ok ? s_tlab[p[k] & PIDX] : 0u;
+    mylab[k] = ok ? lds_u32(a_tlab + 4 * (p[k] & PIDX)) : 0u;
     s_lab[base + k * LW] = mylab[k];
   }
   __syncthreads();
@@ -416,12 +418,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   if (!g->ridge) g->ridge = grid_alloc_array<uint8_t>(d, -1);
   if (!g->shed || !g->upslope || !g->ridge) return set_error(LITAP_ENOMEM, "device allocation failed (shed outputs)");
 
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(k_shed_local, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_A));
-    CUDA_TRY(cudaFuncSetAttribute(k_shed_final, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_B));
-    attr_set = true;
-  }
+  static_assert(SMEM_A <= 48 * 1024 && SMEM_B <= 48 * 1024, "tile arrays are static shared memory");
   TileGeom& tg = W.tg;
   tg.d = d;
   tg.tilesX = (d.NC - 1 + TW - 1) / TW;
@@ -469,7 +466,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
 
   dim3 tgrid(tg.tilesX, tg.tilesY);
-  KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, SMEM_A, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), l2, pits,
+  KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, 0, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), l2, pits,
                                          counters + 1));
 
   const unsigned sblk = (unsigned)((nslots + 255) / 256);
@@ -543,7 +540,7 @@ int shed_phase_final(litap_grid* g, shed::ShedWork& W, const shed::BandSeeds& se
     KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge, g->halo_bot ? 1 : 0));
   }
   dim3 tgrid(W.tg.tilesX, W.tg.tilesY);
-  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, SMEM_B, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, g->shed, g->upslope,
+  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, 0, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, g->shed, g->upslope,
                                                                 g->ridge, seeds));
   return LITAP_OK;
 }

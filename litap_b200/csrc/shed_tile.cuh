@@ -167,17 +167,50 @@ __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx&
 // through cell i inside the tile, itself included.
 constexpr int MAX_ROUNDS = LC > 2048 ? 14 : 12;  // 2^(MAX_ROUNDS-1) > LC: only cycles are still live after that
 
+// 32-bit shared-window addresses + explicit ld/st/red.shared: with ordinary pointers the compiler
+// rebuilt the window base (S2R CgaCtaId, MOV, VIADD, LEA) in front of every data-dependent access of
+// the hot loop — 4 extra instructions per access.  The empty asm makes the base opaque, so it stays
+// in a register.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("" : "+r"(a));
+  return a;
+}
+__device__ __forceinline__ unsigned lds_u16(uint32_t a) {
+  unsigned v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned lds_u32(uint32_t a) {
+  unsigned v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, unsigned v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_u32(uint32_t a, unsigned v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_max_u32(uint32_t a, unsigned v) {
+  asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_min_u32(uint32_t a, unsigned v) {
+  asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* s_cnt, int* p) {
   const int base = owned_local(0);
+  const uint32_t a_ptr = smem_addr(s_ptr), a_cnt = smem_addr(s_cnt);
+  const uint32_t own_ptr = a_ptr + 2 * base, own_cnt = a_cnt + 4 * base;
   for (int round = 0; round < MAX_ROUNDS; ++round) {
-    int b[CPT];
-    unsigned sv[CPT];
+    unsigned b[CPT], sv[CPT];
     bool any = false;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
       if (!(p[k] & OVER)) {
-        b[k] = s_ptr[p[k]];
-        sv[k] = s_cnt[base + k * LW];
+        b[k] = lds_u16(a_ptr + 2 * p[k]);
+        sv[k] = lds_u32(own_cnt + 4 * k * LW);
         any = true;
       }
     }
@@ -185,9 +218,9 @@ __device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* 
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
       if (p[k] & OVER) continue;
-      s_ptr[base + k * LW] = (uint16_t)b[k];
-      atomicAdd(&s_cnt[p[k]], sv[k]);
-      p[k] = b[k];
+      sts_u16(own_ptr + 2 * k * LW, b[k]);
+      red_add_u32(a_cnt + 4 * p[k], sv[k]);
+      p[k] = (int)b[k];
     }
     __syncthreads();
   }
