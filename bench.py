@@ -150,13 +150,14 @@ def run_ours(a):
     _lib.set_stream(stream.cuda_stream)
 
     n = a.size
-    NR = NC = n + 2
+    ncols = a.cols or n          # --cols: wider bands (e.g. 8 x 8192 rows x 65536 cols = 65536^2 on 8 GPUs)
+    NR, NC = n + 2, ncols + 2
     if world > 1:
         # one DEM of (world * n) x n cells cut into row bands, one band per GPU (weak scaling); halo rows
         # and boundary tables travel over NCCL inside the library (litap_b200/csrc/bands.cu)
         from litap_b200.bands import BandedDEM, init_comm
         init_comm(rank, world)
-        g = BandedDEM(n * world, n, world, band=rank)
+        g = BandedDEM(n * world, ncols, world, band=rank)
         g.synth(seed=SEED, quant=QUANT)
     else:
         g = lb.DeviceGrid(NR, NC)
@@ -196,7 +197,7 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    cells_job = n * n * world
+    cells_job = n * ncols * world
     value = cells_job * a.steps / (ms * 1e-3) / 1e6
     stage = lb.timings()
 
@@ -214,13 +215,13 @@ def run_ours(a):
             "traffic": None, "peak_source": peak_src}
     if dom in ALG_BYTES:
         avg_ms = prof[dom][1] / prof[dom][0]
-        ach = ALG_BYTES[dom] * n * n / (avg_ms * 1e-3) / 1e9
+        ach = ALG_BYTES[dom] * n * ncols / (avg_ms * 1e-3) / 1e9
         roof.update(achieved=ach, frac=ach / peak, alg_bytes_per_cell=ALG_BYTES[dom], avg_launch_ms=avg_ms)
     rf_all = {}
     for k, b in ALG_BYTES.items():
         if k in prof:
             avg = prof[k][1] / prof[k][0]
-            rf_all[k] = round(b * n * n / (avg * 1e-3) / 1e9 / peak, 4)
+            rf_all[k] = round(b * n * ncols / (avg * 1e-3) / 1e9 / peak, 4)
 
     # ---- calc_weti2 (not part of the composite metric; single-device stage), reported beside it
     weti = None
@@ -312,9 +313,9 @@ def run_ours(a):
             "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": (f"hash-fBm DEM {n}x{n}" if world == 1 else
-                                    f"hash-fBm DEM {n * world}x{n} in {world} row bands of {n} rows")
+                                    f"hash-fBm DEM {n * world}x{ncols} in {world} row bands of {n} rows")
                        + f", quant 0.001 m, grid 5 m, seed {SEED}",
-                       "cells_per_gpu": n * n, "l2": "inputs (537 MB elev per GPU) larger than L2; no flush needed",
+                       "cells_per_gpu": n * ncols, "l2": "inputs (537 MB elev per GPU) larger than L2; no flush needed",
                        "parallelism": "1 GPU" if world == 1 else
                        f"row bands, one per GPU; NCCL halo rows + boundary-graph tables (DESIGN.md section 4)",
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
@@ -333,7 +334,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--size", type=int, default=8192)
+    ap.add_argument("--size", type=int, default=8192, help="DEM rows per GPU (and columns unless --cols)")
+    ap.add_argument("--cols", type=int, default=0, help="DEM columns (multi-GPU band mode), default = --size")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-rows", type=int, default=2048, help="rows of the DEM in the CPU sample")
     ap.add_argument("--e2e-steps", type=int, default=5)
