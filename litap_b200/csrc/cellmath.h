@@ -348,6 +348,159 @@ LITAP_HD bool form_cell_fast(const double* e, const FormK& K, const double* sin_
 }
 
 // ---------------------------------------------------------------------------------------------
+// Quick path of calc_form (the one k_form runs on every cell; form_cell_fast / form_cell take the
+// cells it leaves in doubt).  Same contract as form_cell_fast: when it returns true the five outputs
+// are bit-identical with form_cell(); it differs in HOW the integer k = round(1000 v) is found:
+//   * slope_pct: fp64 sqrt from an f32 rsqrt seed and one Newton step (relative error < 2e-13);
+//   * the three arctangents (slope_deg, prof, plan) come out directly in units of 0.001 degree as
+//     T[i] + corr (after a -> 1/a for a > 1): T[i] = 1000*deg(atan(i/512)) from a 513-entry fp64
+//     table, corr = the f32 evaluation of atan((x - i/512) / (1 + x*i/512)), |argument| <= 1/1024,
+//     so that the ABSOLUTE error of an f32 chain (9 roundings, ~5.4e-7 relative) is < 4e-5 units;
+//   * curvature numerators use the identity (R/form_01_calc_form.R:87-106, both branches)
+//       2*z5 - z1 - z2 = -( |c| s D_diag + |c| (1-s) D_82 + (1-|c|) s D_64 ),  s = sin A, c = cos A,
+//       D_ab = z_a + z_b - 2 z5,  D_diag = D_91 for A <= 90 and D_37 for A > 90,
+//     with the three weights (times -1/grid^2) tabulated per integer aspect A = 0..180;
+//   * aspect is rounded to a whole degree, so its arctangent is a plain f32 polynomial.
+// Guards (in units of 0.001 of the output): QK_GUARD_T = 2e-4 for the table arctangents (5x the
+// bound above), plus |z5| * gz for the rounding noise of z = elev*100 in second differences
+// (both this path's and the reference's: <= 4.5 * 2^-51 |z| / grid^2 radians); 3e-4 degree for
+// aspect (error budget 5e-5).  Values that round to k = 0 must also have a certain sign (-0.0).
+struct FormQ {
+  double inv2g;   // 1 / (2 grid)
+  double gz;      // guard per unit |z5|: 8 * 2^-51 * 57295.78 / grid^2
+};
+#define QK_ATAN_N 513          // x in [0, 1]: i = rint(512 x) <= 512
+#define QK_GUARD_T 2.0e-4
+
+// tables for form_cell_quick, filled by the host (libm in long double):
+//   w[3*A + {0,1,2}] = -{ |c| s, |c| (1-s), (1-|c|) s } / grid^2 ; at[i] = 1000 * deg(atan(i/512))
+inline void form_fill_quick_tables(double grid, const double* sin_t, const double* cos_t, double* w, double* at) {
+  const double invg2 = 1.0 / (grid * grid);
+  for (int A = 0; A <= 180; ++A) {
+    double s = sin_t[A], c = fabs(cos_t[A]);
+    w[3 * A + 0] = -(c * s) * invg2;
+    w[3 * A + 1] = -(c * (1 - s)) * invg2;
+    w[3 * A + 2] = -((1 - c) * s) * invg2;
+  }
+  for (int i = 0; i < QK_ATAN_N; ++i)
+    at[i] = (double)(atanl((long double)i / 512.0L) * (180000.0L / 3.14159265358979323846264338327950288L));
+}
+
+LITAP_HD float qk_rcp(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / x;
+#endif
+}
+LITAP_HD float qk_rsqrt(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / sqrtf(x);
+#endif
+}
+// t = 1000 * deg(atan(a)) for 0 <= a < 1e30, absolute error < 4e-5; *ok cleared outside the range.
+// a > 1 goes through 1/a (f32 seed + one Newton step, relative error ~1e-14) and 90 deg - atan(1/a).
+LITAP_HD double qk_atan_t(double a, const double* at, bool* ok) {
+  if (!(a < 1e30)) { *ok = false; a = 0.0; }   // also NaN
+  const bool big = a > 1.0;
+  double x;
+  {
+    const double r = (double)qk_rcp((float)a);
+    x = big ? fma(fma(-a, r, 1.0), r, r) : a;
+  }
+  const float xf = (float)x;
+  const float fi = rintf(xf * 512.0f);
+  const double dd = fma((double)fi, -0.001953125, x);          // x - i/512, exact to ~1e-16
+  const float den = fmaf(xf, fi * 0.001953125f, 1.0f);
+  const float dl = (float)dd * qk_rcp(den);
+  const float corr = dl * fmaf(dl * dl, -0.33333334f, 1.0f);  // atan(dl), |dl| < 0.001: next term < 2e-16
+  const double t = at[(int)fi] + (double)(corr * 57295.78f);
+  return big ? 90000.0 - t : t;
+}
+// decide round(v, 3) from t = 1000 |v| with an absolute guard; sign of the result from sgn
+LITAP_HD bool qk_round_t(double t, double guard, double sgn, double* out) {
+  const double k = rint(t);
+  const double dist = fabs(t - k);
+  *out = copysign(div1000(k), sgn);
+  return dist <= 0.5 - guard && t > guard;  // away from a half, and a certain sign when k == 0
+}
+
+// z[n] = elev_n * 100 (n = 1..9, the reference's z values); qw / qat: the tables above
+LITAP_HD bool form_cell_quick(const double* z, const FormQ& Q, const double* qw, const double* qat, FormOut* o) {
+  bool ok = true;
+  const double dx = z[6] - z[4], dy = z[2] - z[8];
+  const double sx = dx * Q.inv2g, sy = dy * Q.inv2g;
+  const double ax = fabs(sx), ay = fabs(sy);
+  const double mx = ax < ay ? ay : ax;
+  ok = mx > 1e-15 && mx < 1e15;            // flat window, absurd values or NaN: not decided here
+  const double s2 = fma(sx, sx, sy * sy);
+  double sp;
+  {
+    const double y = (double)qk_rsqrt((float)s2);
+    const double g = s2 * y;
+    sp = fma(fma(-g, g, s2), 0.5 * y, g);   // one Newton step: relative error < 2e-13
+  }
+  ok &= fast_round3(sp, &o->slope_pct);
+  // second differences through the centre; the sum is NaN iff a corner or the centre is
+  const double tz5 = z[5] + z[5];
+  const double d91 = (z[9] + z[1]) - tz5, d37 = (z[3] + z[7]) - tz5;
+  const double d82 = (z[8] + z[2]) - tz5, d64 = (z[6] + z[4]) - tz5;
+  const double dsum = d91 + d37;
+  ok &= dsum == dsum;
+  const double guard = fma(fabs(z[5]), Q.gz, QK_GUARD_T);
+  {
+    const double t = qk_atan_t(sp * 0.01, qat, &ok);
+    ok &= qk_round_t(t, guard, 1.0, &o->slope_deg);
+  }
+  // aspect (R/form_01_calc_form.R:71-80): la = acos(|sx|/sp) = atan(|sy|/|sx|) in f32
+  int A;
+  {
+    const float fx = (float)ax, fy = (float)ay;
+    const float q = fminf(fx, fy) * qk_rcp(fmaxf(fx, fy));
+    const float t = q * q;
+    float p = 0.00680924067273736f;
+    p = fmaf(p, t, -0.03359666094183922f);
+    p = fmaf(p, t, 0.07961514592170715f);
+    p = fmaf(p, t, -0.1323288530111313f);
+    p = fmaf(p, t, 0.198076993227005f);
+    p = fmaf(p, t, -0.333173543214798f);
+    p = fmaf(p, t, 0.9999961256980896f);
+    float la = q * p;                           // |error| < 4e-7 rad
+    if (fy > fx) la = 1.5707964f - la;
+    la *= 57.29578f;
+    float ah = dx > 0 ? (dy > 0 ? 270.0f + la : 270.0f - la) : (dy > 0 ? 90.0f - la : 90.0f + la);
+    if (dx == 0) ah = dy < 0 ? 180.0f : 360.0f;
+    if (dy == 0) ah = dx < 0 ? 90.0f : 270.0f;
+    const float as = rintf(ah);
+    ok &= fabsf(ah - as) < 0.5f - 3e-4f;
+    A = (int)as;
+    if (!(A >= 0 && A <= 360)) A = 0;           // NaN window: keeps the table index legal
+    o->aspect = (double)A;
+  }
+  const int pa = A > 180 ? A - 180 : A;
+  const int pl = pa + 90 > 180 ? pa - 90 : pa + 90;
+  {
+    const double* w = qw + 3 * pa;
+    const double c = fma(w[0], pa <= 90 ? d91 : d37, fma(w[1], d82, w[2] * d64));
+    const double t = qk_atan_t(fabs(c), qat, &ok);
+    ok &= qk_round_t(t, guard, c, &o->prof);
+  }
+  {
+    const double* w = qw + 3 * pl;
+    const double c = fma(w[0], pl <= 90 ? d91 : d37, fma(w[1], d82, w[2] * d64));
+    const double t = qk_atan_t(fabs(c), qat, &ok);
+    ok &= qk_round_t(t, guard, c, &o->plan);
+  }
+  return ok;
+}
+
+// ---------------------------------------------------------------------------------------------
 // R's sum() accumulates in long double (x87 80-bit extended, 64-bit significand) and rounds the
 // result to double once (src/main/summary.c rsum; call site R/form_02b_calc_weti.R:67).  The terms
 // summed on this path are all >= 0, so the emulation only needs the addition of non-negative

@@ -73,6 +73,40 @@ void host_form_fast_check(const double* elev, long long NR, long long NC, double
   out[0] = nfast;
   out[1] = nbad;
 }
+// quick path (the one k_form runs first) vs reference tree: out[0] = windows it decided, out[1] = of
+// those, windows that differ in any bit from form_cell(), out[2] = windows (with 9 valid cells and a
+// slope) it left in doubt
+void host_form_quick_check(const double* elev, long long NR, long long NC, double grid, long long* out) {
+  double st[181], ct[181], qw[181 * 3], qat[QK_ATAN_N];
+  host_fill_trig(st, ct);
+  form_fill_quick_tables(grid, st, ct, qw, qat);
+  FormQ Q;
+  Q.inv2g = 1.0 / (2 * grid);
+  Q.gz = 8.0 * 4.440892098500626e-16 * 57295.78 / (grid * grid);
+  long long nq = 0, nbad = 0, ndoubt = 0;
+  for (long long r = 0; r < NR; ++r)
+    for (long long c = 0; c < NC; ++c) {
+      double e[10], z[10];
+      bool na = false;
+      for (int n = 1; n <= 9; ++n) {
+        long long rr = r + nb_dr(n), cc = c + nb_dc(n);
+        e[n] = (rr < 0 || cc < 0 || rr >= NR || cc >= NC) ? NAN : elev[rr * NC + cc];
+        z[n] = e[n] * 100;
+        na |= is_nan(e[n]);
+      }
+      FormOut a, b = form_cell(e, grid, st, ct);
+      if (!form_cell_quick(z, Q, qw, qat, &a)) { ndoubt += (!na && b.slope_pct > 0); continue; }
+      ++nq;
+      const double av[5] = {a.slope_pct, a.slope_deg, a.aspect, a.prof, a.plan};
+      const double bv[5] = {b.slope_pct, b.slope_deg, b.aspect, b.prof, b.plan};
+      bool same = true;
+      for (int k = 0; k < 5; ++k) same &= __builtin_memcmp(&av[k], &bv[k], 8) == 0;
+      nbad += !same;
+    }
+  out[0] = nq;
+  out[1] = nbad;
+  out[2] = ndoubt;
+}
 }
 
 // emulated long-double accumulation vs the host's real long double (x86-64: x87 extended)

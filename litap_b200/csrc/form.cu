@@ -10,7 +10,7 @@
 namespace {
 
 constexpr int FORM_CPT = 2;       // columns per thread: 16-byte loads and stores
-constexpr int FORM_ROWS = 16;
+constexpr int FORM_ROWS = 32;
 constexpr int FORM_THREADS = 128;  // 256 columns per block
 
 struct FormPtrs { double* o[5]; };
@@ -36,17 +36,47 @@ __device__ __forceinline__ void store_final(const FormPtrs& P, size_t i, FormOut
   P.o[4][i] = o.plan;
 }
 
-__global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict__ elev, GridDims d, FormK K,
-                                                       const double* __restrict__ trig, FormPtrs P) {
-  __shared__ double s_sin[181], s_cos[181];
-  for (int i = threadIdx.x; i < 181; i += FORM_THREADS) { s_sin[i] = trig[i]; s_cos[i] = trig[181 + i]; }
+// One block = FORM_ROWS rows x 256 columns.  Every cell first takes form_cell_quick (cellmath.h);
+// the few it leaves in doubt (~0.2 % on terrain; every cell next to an NA) are queued in shared memory
+// and resolved densely at the end of the block by form_cell_fast / form_cell, so the exact paths
+// never run inside a divergent warp.
+constexpr int FORM_QCAP = 2048;
+#ifndef FORM_MINB
+#define FORM_MINB 5
+#endif
+
+__device__ __noinline__ void form_exact_cell(const double* __restrict__ elev, const GridDims& d, const FormK& K,
+                                                const double* __restrict__ trig, const FormPtrs& P, int r, int c) {
+  double e[10];
+#pragma unroll
+  for (int n = 1; n <= 9; ++n) {
+    const int rr = r + nb_dr(n), cc = c + nb_dc(n);  // cc >= 0: column 0 is never queued; pad columns are NaN
+    e[n] = (rr < 0 || rr >= d.NR) ? sw_nan() : __ldg(elev + (size_t)rr * d.pitch + cc);
+  }
+  FormOut o;
+  if (!form_cell_fast(e, K, trig, trig + 181, &o)) o = form_cell(e, K.grid, trig, trig + 181);
+  store_final(P, (size_t)r * d.pitch + c, o, !is_nan(e[5]));
+}
+
+__global__ void __launch_bounds__(FORM_THREADS, FORM_MINB) k_form(const double* __restrict__ elev, GridDims d, FormK K, FormQ Q,
+                                                       const double* __restrict__ trig,
+                                                       const double* __restrict__ qtab, FormPtrs P) {
+  __shared__ double s_qw[181 * 3], s_qat[QK_ATAN_N];
+  __shared__ unsigned short s_queue[FORM_QCAP];
+  __shared__ unsigned s_qn;
+  for (int i = threadIdx.x; i < 181 * 3 + QK_ATAN_N; i += FORM_THREADS) {
+    const double v = __ldg(qtab + i);
+    if (i < 181 * 3) s_qw[i] = v; else s_qat[i - 181 * 3] = v;
+  }
+  if (threadIdx.x == 0) s_qn = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31;
-  const int c0 = (blockIdx.x * FORM_THREADS + threadIdx.x) * FORM_CPT + 1;  // column 1 is the aligned one
+  const int cb = blockIdx.x * FORM_THREADS * FORM_CPT + 1;  // first column of the block (column 1 is the aligned one)
+  const int c0 = cb + threadIdx.x * FORM_CPT;
   const int r0 = blockIdx.y * FORM_ROWS;
   const int rend = min(r0 + FORM_ROWS, d.NR);
   const bool live = c0 < d.pitch - LITAP_XOFF;
-  RowWin<FORM_CPT> p, q, n, f;
+  RowWin<FORM_CPT> p, q, n, f;  // rows r-1, r, r+1, r+2 as z = elev * 100
   if (live) {
     sw_issue(p, elev, d, r0 - 1, c0, lane);
     sw_issue(q, elev, d, r0, c0, lane);
@@ -55,6 +85,11 @@ __global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict_
 #pragma unroll
     for (int k = 0; k < FORM_CPT + 2; ++k) p.v[k] = q.v[k] = n.v[k] = sw_nan();
   }
+#pragma unroll
+  for (int k = 1; k <= FORM_CPT; ++k) { p.v[k] *= 100; q.v[k] *= 100; n.v[k] *= 100; }
+  p.v[0] *= 100; p.v[FORM_CPT + 1] *= 100;
+  q.v[0] *= 100; q.v[FORM_CPT + 1] *= 100;
+  n.v[0] *= 100; n.v[FORM_CPT + 1] *= 100;
   sw_finish(p, lane);
   sw_finish(q, lane);
   sw_finish(n, lane);
@@ -65,14 +100,14 @@ __global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict_
       for (int k = 0; k < FORM_CPT + 2; ++k) f.v[k] = sw_nan();
     }
     FormOut o[FORM_CPT];
+    bool okj[FORM_CPT];
 #pragma unroll
     for (int j = 0; j < FORM_CPT; ++j) {
-      double e[10];
-      e[7] = p.v[j]; e[8] = p.v[j + 1]; e[9] = p.v[j + 2];
-      e[4] = q.v[j]; e[5] = q.v[j + 1]; e[6] = q.v[j + 2];
-      e[1] = n.v[j]; e[2] = n.v[j + 1]; e[3] = n.v[j + 2];
-      if (!form_cell_fast(e, K, s_sin, s_cos, &o[j])) o[j] = form_cell(e, K.grid, s_sin, s_cos);
-      finalise(o[j], !is_nan(e[5]));
+      double z[10];
+      z[7] = p.v[j]; z[8] = p.v[j + 1]; z[9] = p.v[j + 2];
+      z[4] = q.v[j]; z[5] = q.v[j + 1]; z[6] = q.v[j + 2];
+      z[1] = n.v[j]; z[2] = n.v[j + 1]; z[3] = n.v[j + 2];
+      okj[j] = form_cell_quick(z, Q, s_qw, s_qat, &o[j]);
     }
     if (live) {
       const size_t i = (size_t)r * d.pitch + c0;
@@ -85,11 +120,31 @@ __global__ void __launch_bounds__(FORM_THREADS) k_form(const double* __restrict_
 #pragma unroll
         for (int k = 0; k < 5; ++k) P.o[k][i - 1] = sw_nan();
       }
+#pragma unroll
+      for (int j = 0; j < FORM_CPT; ++j) {
+        if (c0 + j >= d.NC) {  // pad columns: NA
+#pragma unroll
+          for (int k = 0; k < 5; ++k) P.o[k][i + j] = sw_nan();
+        } else if (!okj[j]) {
+          const unsigned slot = atomicAdd(&s_qn, 1u);
+          if (slot < FORM_QCAP) s_queue[slot] = (unsigned short)(((r - r0) << 8) | (threadIdx.x * FORM_CPT + j));
+          else form_exact_cell(elev, d, K, trig, P, r, c0 + j);  // queue full (NA-heavy block): resolve in place
+        }
+      }
     }
     p = q;
     q = n;
-    n = f;
+#pragma unroll
+    for (int k = 1; k <= FORM_CPT; ++k) n.v[k] = f.v[k] * 100;
+    n.v[0] = f.v[0] * 100;
+    n.v[FORM_CPT + 1] = f.v[FORM_CPT + 1] * 100;
     sw_finish(n, lane);
+  }
+  __syncthreads();  // queued cells overwrite what the quick path stored for them
+  const unsigned nq = min(s_qn, (unsigned)FORM_QCAP);
+  for (unsigned i = threadIdx.x; i < nq; i += FORM_THREADS) {
+    const unsigned w = s_queue[i];
+    form_exact_cell(elev, d, K, trig, P, r0 + (int)(w >> 8), cb + (int)(w & 255u));
   }
 }
 
@@ -122,6 +177,9 @@ __global__ void k_form_edges(const double* __restrict__ elev, GridDims d, double
 }
 
 double* g_trig = nullptr;  // sin((A*pi)/180), cos((A*pi)/180), A = 0..180, from the host libm
+double* g_qtab = nullptr;  // form_fill_quick_tables(): 543 curvature weights + 513 arctangents
+double g_qtab_grid = 0.0;  // the grid size the weights were built for
+double g_trig_host[362];
 }  // namespace
 
 int run_form(litap_grid* g, double grid_m) {
@@ -139,6 +197,16 @@ int run_form(litap_grid* g, double grid_m) {
     if (!g_trig) return set_error(LITAP_ENOMEM, "device allocation failed (trig table)");
     CUDA_TRY(cudaMemcpyAsync(g_trig, h, sizeof(h), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    for (int i = 0; i < 362; ++i) g_trig_host[i] = h[i];
+  }
+  if (!g_qtab || g_qtab_grid != grid_m) {
+    double h[181 * 3 + QK_ATAN_N];
+    form_fill_quick_tables(grid_m, g_trig_host, g_trig_host + 181, h, h + 181 * 3);
+    if (!g_qtab) g_qtab = (double*)pool_alloc(sizeof(h));
+    if (!g_qtab) return set_error(LITAP_ENOMEM, "device allocation failed (form tables)");
+    CUDA_TRY(cudaMemcpyAsync(g_qtab, h, sizeof(h), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));  // h is a stack array; also orders the update after earlier launches
+    g_qtab_grid = grid_m;
   }
   FormPtrs P;
   for (int k = 0; k < 5; ++k) {
@@ -153,7 +221,10 @@ int run_form(litap_grid* g, double grid_m) {
     K.grid = grid_m;
     K.inv2g = 1.0 / (2 * grid_m);
     K.invg2 = 1.0 / (grid_m * grid_m);
-    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, K, g_trig, P));
+    FormQ Q;
+    Q.inv2g = K.inv2g;
+    Q.gz = 8.0 * 4.440892098500626e-16 * 57295.78 / (grid_m * grid_m);
+    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, K, Q, g_trig, g_qtab, P));
   }
   // R/form_01_calc_form.R:54-57 in buffered 0-based coordinates, in this order:
   //   col 1 <- col 2 ; col NC-2 <- col NC-3 ; row 1 <- row 2 ; row NR-2 <- row NR-3
@@ -172,4 +243,4 @@ int run_form(litap_grid* g, double grid_m) {
 }
 
 // called by litap_shutdown through pool_release_all(): the table is pool-owned
-void form_forget_trig() { g_trig = nullptr; }
+void form_forget_trig() { g_trig = nullptr; g_qtab = nullptr; g_qtab_grid = 0.0; }
