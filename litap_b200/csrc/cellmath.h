@@ -370,7 +370,7 @@ struct FormQ {
   double gz;      // guard per unit |z5|: 8 * 2^-51 * 57295.78 / grid^2
 };
 #define QK_ATAN_N 513          // x in [0, 1]: i = rint(512 x) <= 512
-#define QK_GUARD_T 2.0e-4
+#define QK_GUARD_T 2.0e-5
 
 // tables for form_cell_quick, filled by the host (libm in long double):
 //   w[3*A + {0,1,2}] = -{ |c| s, |c| (1-s), (1-|c|) s } / grid^2 ; at[i] = 1000 * deg(atan(i/512))
@@ -395,37 +395,73 @@ LITAP_HD float qk_rcp(float x) {
   return 1.0f / x;
 #endif
 }
-LITAP_HD float qk_rsqrt(float x) {
+// Seeds with >= 20 good bits (MUFU.RCP64H / MUFU.RSQ64H work on the high word of the double: one
+// conversion-pipe instruction instead of f64 -> f32 -> MUFU -> f64).  The host build keeps 20 bits
+// of the exact value so that the CPU test exercises the same refinement steps.
+LITAP_HD double qk_seed20(double v) {
 #if defined(__CUDA_ARCH__)
-  float r;
-  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
+  return v;
 #else
-  return 1.0f / sqrtf(x);
+  unsigned long long b;
+  __builtin_memcpy(&b, &v, 8);
+  b &= 0xFFFFFFFF00000000ull;
+  __builtin_memcpy(&v, &b, 8);
+  return v;
 #endif
 }
-// t = 1000 * deg(atan(a)) for 0 <= a < 1e30, absolute error < 4e-5; *ok cleared outside the range.
-// a > 1 goes through 1/a (f32 seed + one Newton step, relative error ~1e-14) and 90 deg - atan(1/a).
+LITAP_HD double qk_rcp64(double x) {
+#if defined(__CUDA_ARCH__)
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  return r;
+#else
+  return qk_seed20(1.0 / x);
+#endif
+}
+LITAP_HD double qk_rsqrt64(double x) {
+#if defined(__CUDA_ARCH__)
+  double r;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  return r;
+#else
+  return qk_seed20(1.0 / sqrt(x));
+#endif
+}
+LITAP_HD int qk_lo32(double u) {
+#if defined(__CUDA_ARCH__)
+  return __double2loint(u);
+#else
+  unsigned long long b;
+  __builtin_memcpy(&b, &u, 8);
+  return (int)(unsigned)(b & 0xFFFFFFFFull);
+#endif
+}
+#define QK_MAGIC 6755399441055744.0   // 2^52 + 2^51: (v + M) - M = rint(v) for |v| < 2^51, low word of v + M = the integer
+// t = 1000 * deg(atan(a)) for 0 <= a < 1e30, absolute error < 1e-7; *ok cleared outside the range.
+// a > 1 goes through x = 1/a and 90 deg - atan(x).  With i = rint(512 x), c0 = i/512:
+// atan(x) = atan(c0) + atan(dl), dl = (x - c0) / (1 + x c0), |dl| <= 1/1024, atan(dl) = dl (1 - dl^2/3)
+// up to 2e-16.  Both reciprocals: 20-bit seed + one Newton step (relative error < 1e-12).
 LITAP_HD double qk_atan_t(double a, const double* at, bool* ok) {
   if (!(a < 1e30)) { *ok = false; a = 0.0; }   // also NaN
   const bool big = a > 1.0;
-  double x;
-  {
-    const double r = (double)qk_rcp((float)a);
-    x = big ? fma(fma(-a, r, 1.0), r, r) : a;
-  }
-  const float xf = (float)x;
-  const float fi = rintf(xf * 512.0f);
-  const double dd = fma((double)fi, -0.001953125, x);          // x - i/512, exact to ~1e-16
-  const float den = fmaf(xf, fi * 0.001953125f, 1.0f);
-  const float dl = (float)dd * qk_rcp(den);
-  const float corr = dl * fmaf(dl * dl, -0.33333334f, 1.0f);  // atan(dl), |dl| < 0.001: next term < 2e-16
-  const double t = at[(int)fi] + (double)(corr * 57295.78f);
+  double r = qk_rcp64(a);
+  r = fma(fma(-a, r, 1.0), r, r);
+  const double x = big ? r : a;
+  const double u = fma(x, 512.0, QK_MAGIC);
+  const int i = qk_lo32(u);
+  const double c0 = (u - QK_MAGIC) * 0.001953125;
+  const double dd = x - c0;
+  const double den = fma(x, c0, 1.0);
+  double r2 = qk_rcp64(den);
+  r2 = fma(fma(-den, r2, 1.0), r2, r2);
+  const double dl = dd * r2;
+  const double corr = dl * fma(dl * dl, -0.33333333333333331, 1.0);
+  const double t = fma(corr, 57295.779513082323, at[i]);
   return big ? 90000.0 - t : t;
 }
 // decide round(v, 3) from t = 1000 |v| with an absolute guard; sign of the result from sgn
 LITAP_HD bool qk_round_t(double t, double guard, double sgn, double* out) {
-  const double k = rint(t);
+  const double k = (t + QK_MAGIC) - QK_MAGIC;   // rint(t), t < 2^51
   const double dist = fabs(t - k);
   *out = copysign(div1000(k), sgn);
   return dist <= 0.5 - guard && t > guard;  // away from a half, and a certain sign when k == 0
@@ -442,11 +478,14 @@ LITAP_HD bool form_cell_quick(const double* z, const FormQ& Q, const double* qw,
   const double s2 = fma(sx, sx, sy * sy);
   double sp;
   {
-    const double y = (double)qk_rsqrt((float)s2);
+    const double y = qk_rsqrt64(s2);
     const double g = s2 * y;
-    sp = fma(fma(-g, g, s2), 0.5 * y, g);   // one Newton step: relative error < 2e-13
+    sp = fma(fma(-g, g, s2), 0.5 * y, g);   // one Newton step: relative error 1.5 seed^2 < 2e-12
   }
-  ok &= fast_round3(sp, &o->slope_pct);
+  {
+    const double t = sp * 1000.0;
+    ok &= qk_round_t(t, fma(t, 4e-11, 1e-9), 1.0, &o->slope_pct) && t < 4.0e9;
+  }
   // second differences through the centre; the sum is NaN iff a corner or the centre is
   const double tz5 = z[5] + z[5];
   const double d91 = (z[9] + z[1]) - tz5, d37 = (z[3] + z[7]) - tz5;
@@ -477,23 +516,30 @@ LITAP_HD bool form_cell_quick(const double* z, const FormQ& Q, const double* qw,
     float ah = dx > 0 ? (dy > 0 ? 270.0f + la : 270.0f - la) : (dy > 0 ? 90.0f - la : 90.0f + la);
     if (dx == 0) ah = dy < 0 ? 180.0f : 360.0f;
     if (dy == 0) ah = dx < 0 ? 90.0f : 270.0f;
-    const float as = rintf(ah);
+    const float am = ah + 12582912.0f;          // 1.5 * 2^23: rounds to a whole number, ties to even
+    const float as = am - 12582912.0f;
     ok &= fabsf(ah - as) < 0.5f - 3e-4f;
-    A = (int)as;
+#if defined(__CUDA_ARCH__)
+    A = __float_as_int(am) - 0x4B400000;
     if (!(A >= 0 && A <= 360)) A = 0;           // NaN window: keeps the table index legal
+    o->aspect = __hiloint2double(0x43300000, A) - 4503599627370496.0;  // (double)A without a conversion
+#else
+    A = (as >= 0 && as <= 360) ? (int)as : 0;
     o->aspect = (double)A;
+#endif
   }
   const int pa = A > 180 ? A - 180 : A;
   const int pl = pa + 90 > 180 ? pa - 90 : pa + 90;
+  // weights of pl = pa +- 90: sin and |cos| swap, so {w0, w1, w2}(pl) = {w0, w2, w1}(pa)
+  const double* w = qw + 3 * pa;
+  const double w0 = w[0], w1 = w[1], w2 = w[2];
   {
-    const double* w = qw + 3 * pa;
-    const double c = fma(w[0], pa <= 90 ? d91 : d37, fma(w[1], d82, w[2] * d64));
+    const double c = fma(w0, pa <= 90 ? d91 : d37, fma(w1, d82, w2 * d64));
     const double t = qk_atan_t(fabs(c), qat, &ok);
     ok &= qk_round_t(t, guard, c, &o->prof);
   }
   {
-    const double* w = qw + 3 * pl;
-    const double c = fma(w[0], pl <= 90 ? d91 : d37, fma(w[1], d82, w[2] * d64));
+    const double c = fma(w0, pl <= 90 ? d91 : d37, fma(w2, d82, w1 * d64));
     const double t = qk_atan_t(fabs(c), qat, &ok);
     ok &= qk_round_t(t, guard, c, &o->plan);
   }

@@ -5,6 +5,7 @@
 #include <cmath>
 #include "cellmath.h"
 #include "litap_internal.h"
+#include "rowring.cuh"
 #include "stencil.cuh"
 
 namespace {
@@ -58,56 +59,89 @@ __device__ __noinline__ void form_exact_cell(const double* __restrict__ elev, co
   store_final(P, (size_t)r * d.pitch + c, o, !is_nan(e[5]));
 }
 
+constexpr int FORM_STAGES = 12;  // ring slots (rows in flight: 8..12)
+constexpr int FORM_GROUP = 4;    // slots recycled per block barrier
+using FormRing = RowRing<double, FORM_THREADS * FORM_CPT, FORM_STAGES>;
+
+// z = elev * 100 of the thread's window columns in ring slot `row`: own columns 2+2t, 3+2t, the
+// neighbours either side; an invalid row (outside the grid) is NA
+__device__ __forceinline__ void form_take_row(RowWin<FORM_CPT>& w, FormRing& ring, int k, bool valid) {
+  if (valid) {
+    const int s = k % FORM_STAGES;
+    rr_wait(&ring.bar[s], (unsigned)(k / FORM_STAGES) & 1u);
+    const double* row = ring.row[s] + 2 * threadIdx.x;
+    const double2 own = *reinterpret_cast<const double2*>(row + 2);
+    w.v[0] = row[1] * 100;
+    w.v[1] = own.x * 100;
+    w.v[2] = own.y * 100;
+    w.v[3] = row[4] * 100;
+  } else {
+#pragma unroll
+    for (int j = 0; j < FORM_CPT + 2; ++j) w.v[j] = sw_nan();
+  }
+}
+
 __global__ void __launch_bounds__(FORM_THREADS, FORM_MINB) k_form(const double* __restrict__ elev, GridDims d, FormK K, FormQ Q,
                                                        const double* __restrict__ trig,
                                                        const double* __restrict__ qtab, FormPtrs P) {
+  static_assert(FORM_CPT == 2, "window layout of form_take_row");
+  __shared__ FormRing ring;
   __shared__ double s_qw[181 * 3], s_qat[QK_ATAN_N];
   __shared__ unsigned short s_queue[FORM_QCAP];
   __shared__ unsigned s_qn;
-  for (int i = threadIdx.x; i < 181 * 3 + QK_ATAN_N; i += FORM_THREADS) {
-    const double v = __ldg(qtab + i);
-    if (i < 181 * 3) s_qw[i] = v; else s_qat[i - 181 * 3] = v;
-  }
-  if (threadIdx.x == 0) s_qn = 0;
-  __syncthreads();
-  const int lane = threadIdx.x & 31;
   const int cb = blockIdx.x * FORM_THREADS * FORM_CPT + 1;  // first column of the block (column 1 is the aligned one)
   const int c0 = cb + threadIdx.x * FORM_CPT;
   const int r0 = blockIdx.y * FORM_ROWS;
   const int rend = min(r0 + FORM_ROWS, d.NR);
   const bool live = c0 < d.pitch - LITAP_XOFF;
-  RowWin<FORM_CPT> p, q, n, f;  // rows r-1, r, r+1, r+2 as z = elev * 100
-  if (live) {
-    sw_issue(p, elev, d, r0 - 1, c0, lane);
-    sw_issue(q, elev, d, r0, c0, lane);
-    sw_issue(n, elev, d, r0 + 1, c0, lane);
-  } else {
-#pragma unroll
-    for (int k = 0; k < FORM_CPT + 2; ++k) p.v[k] = q.v[k] = n.v[k] = sw_nan();
-  }
-#pragma unroll
-  for (int k = 1; k <= FORM_CPT; ++k) { p.v[k] *= 100; q.v[k] *= 100; n.v[k] *= 100; }
-  p.v[0] *= 100; p.v[FORM_CPT + 1] *= 100;
-  q.v[0] *= 100; q.v[FORM_CPT + 1] *= 100;
-  n.v[0] *= 100; n.v[FORM_CPT + 1] *= 100;
-  sw_finish(p, lane);
-  sw_finish(q, lane);
-  sw_finish(n, lane);
-  for (int r = r0; r < rend; ++r) {
-    if (live && r + 1 < rend) sw_issue(f, elev, d, r + 2, c0, lane);
-    else {
-#pragma unroll
-      for (int k = 0; k < FORM_CPT + 2; ++k) f.v[k] = sw_nan();
+  // ring row k = grid row r0 - 1 + k, k = 0 .. kmax
+  const int kmax = rend - r0 + 1;
+  // the segment starts at column cb - 2 and must stay inside pitch + 32 elements of its row
+  const unsigned seg_bytes = (unsigned)min(FormRing::SEG, ((d.pitch + 32 - (cb - 2)) / 2) * 2) * sizeof(double);
+  int next_k = 0;  // thread 0: first ring row not yet requested
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < FORM_STAGES; ++s) rr_bar_init(&ring.bar[s]);
+    rr_fence_init();
+    s_qn = 0;
+    for (; next_k < FORM_STAGES && next_k <= kmax; ++next_k) {
+      const int rr = r0 - 1 + next_k;
+      if (rr >= 0 && rr < d.NR)
+        rr_issue(ring.row[next_k % FORM_STAGES], elev + (size_t)rr * d.pitch + (cb - 2), seg_bytes, &ring.bar[next_k % FORM_STAGES]);
+      else rr_skip(&ring.bar[next_k % FORM_STAGES]);
     }
+  }
+  for (int i = threadIdx.x; i < 181 * 3 + QK_ATAN_N; i += FORM_THREADS) {
+    const double v = __ldg(qtab + i);
+    if (i < 181 * 3) s_qw[i] = v; else s_qat[i - 181 * 3] = v;
+  }
+  __syncthreads();
+  RowWin<FORM_CPT> p, q, n;  // rows r-1, r, r+1 as z = elev * 100
+  form_take_row(p, ring, 0, r0 - 1 >= 0);
+  form_take_row(q, ring, 1, true);
+  for (int r = r0; r < rend; ++r) {
+    const int j = r - r0;
+    if (j > 0 && (j % FORM_GROUP) == 0) {
+      __syncthreads();  // every thread has taken ring rows <= j + 1: their slots are free
+      if (threadIdx.x == 0) {
+        for (; next_k <= kmax && next_k - FORM_STAGES <= j + 1; ++next_k) {
+          const int rr = r0 - 1 + next_k;
+          if (rr < d.NR)
+            rr_issue(ring.row[next_k % FORM_STAGES], elev + (size_t)rr * d.pitch + (cb - 2), seg_bytes,
+                     &ring.bar[next_k % FORM_STAGES]);
+          else rr_skip(&ring.bar[next_k % FORM_STAGES]);
+        }
+      }
+    }
+    form_take_row(n, ring, j + 2, r + 1 < d.NR);
     FormOut o[FORM_CPT];
     bool okj[FORM_CPT];
 #pragma unroll
-    for (int j = 0; j < FORM_CPT; ++j) {
+    for (int jj = 0; jj < FORM_CPT; ++jj) {
       double z[10];
-      z[7] = p.v[j]; z[8] = p.v[j + 1]; z[9] = p.v[j + 2];
-      z[4] = q.v[j]; z[5] = q.v[j + 1]; z[6] = q.v[j + 2];
-      z[1] = n.v[j]; z[2] = n.v[j + 1]; z[3] = n.v[j + 2];
-      okj[j] = form_cell_quick(z, Q, s_qw, s_qat, &o[j]);
+      z[7] = p.v[jj]; z[8] = p.v[jj + 1]; z[9] = p.v[jj + 2];
+      z[4] = q.v[jj]; z[5] = q.v[jj + 1]; z[6] = q.v[jj + 2];
+      z[1] = n.v[jj]; z[2] = n.v[jj + 1]; z[3] = n.v[jj + 2];
+      okj[jj] = form_cell_quick(z, Q, s_qw, s_qat, &o[jj]);
     }
     if (live) {
       const size_t i = (size_t)r * d.pitch + c0;
@@ -121,24 +155,19 @@ __global__ void __launch_bounds__(FORM_THREADS, FORM_MINB) k_form(const double* 
         for (int k = 0; k < 5; ++k) P.o[k][i - 1] = sw_nan();
       }
 #pragma unroll
-      for (int j = 0; j < FORM_CPT; ++j) {
-        if (c0 + j >= d.NC) {  // pad columns: NA
+      for (int jj = 0; jj < FORM_CPT; ++jj) {
+        if (c0 + jj >= d.NC) {  // pad columns: NA
 #pragma unroll
-          for (int k = 0; k < 5; ++k) P.o[k][i + j] = sw_nan();
-        } else if (!okj[j]) {
+          for (int k = 0; k < 5; ++k) P.o[k][i + jj] = sw_nan();
+        } else if (!okj[jj]) {
           const unsigned slot = atomicAdd(&s_qn, 1u);
-          if (slot < FORM_QCAP) s_queue[slot] = (unsigned short)(((r - r0) << 8) | (threadIdx.x * FORM_CPT + j));
-          else form_exact_cell(elev, d, K, trig, P, r, c0 + j);  // queue full (NA-heavy block): resolve in place
+          if (slot < FORM_QCAP) s_queue[slot] = (unsigned short)((j << 8) | (threadIdx.x * FORM_CPT + jj));
+          else form_exact_cell(elev, d, K, trig, P, r, c0 + jj);  // queue full (NA-heavy block): resolve in place
         }
       }
     }
     p = q;
     q = n;
-#pragma unroll
-    for (int k = 1; k <= FORM_CPT; ++k) n.v[k] = f.v[k] * 100;
-    n.v[0] = f.v[0] * 100;
-    n.v[FORM_CPT + 1] = f.v[FORM_CPT + 1] * 100;
-    sw_finish(n, lane);
   }
   __syncthreads();  // queued cells overwrite what the quick path stored for them
   const unsigned nq = min(s_qn, (unsigned)FORM_QCAP);
