@@ -39,6 +39,7 @@ constexpr size_t SMEM_A = (size_t)LC * (2 + 1 + 4 + 4 + 4 + 4) + 64;
 
 __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
                                                       const double* __restrict__ elev, uint32_t* __restrict__ lab,
+                                                      uint16_t* __restrict__ tword, uint32_t* __restrict__ lcnt,
                                                       L2 l2, Pits pits, unsigned long long* pit_cursor) {
   // static shared arrays: the compiler addresses them with immediate offsets (with dynamic shared
   // memory it rebuilt the shared-window base, 4 instructions, in front of most accesses)
@@ -83,6 +84,10 @@ __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t*
     const int dv = (dvp >> (4 * k)) & 15u;
     const int i = base + k * LW;
     pcnt[k] = s_cnt[i];
+    if (in_grid(g, t.r_base + owned_ly(k), c)) {  // kept for k_shed_final: local terminal and in-tile flow count
+      tword[cell0 + (size_t)k * g.d.pitch] = (uint16_t)p[k];
+      lcnt[cell0 + (size_t)k * g.d.pitch] = pcnt[k];
+    }
     // own initial pointer word had T_EXIT <=> the final one has it and points at the cell itself
     if ((p[k] & (OVER | T_EXIT)) == (OVER | T_EXIT) && (p[k] & PIDX) == i) {
       const long long es = slot_of_rc(t.r_base + owned_ly(k) + nb_dr(dv), c + nb_dc(dv), g.tilesX);
@@ -259,21 +264,36 @@ __global__ void k_scatter_rank(const uint32_t* __restrict__ order, uint32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------
-// shared memory of k_shed_final: cnt, terminal labels, cell labels, ptr, dir
-constexpr size_t SMEM_B = (size_t)LC * (4 + 4 + 4 + 2 + 1) + 64;
-
+// k_shed_final: labels, upslope and ridge of one tile from what k_shed_local left behind — the
+// local terminal of every cell (tword) and its in-tile flow count (upslope array) — plus the level-2
+// results.  Flow entering the tile (external inflow of a border cell; flow entering a row band at its
+// first / last own row) is walked down its in-tile path to the local terminal: at most BUSED + 2 TW
+// short serial walks per tile instead of a second pointer-doubling pass over all its cells.
 __device__ __forceinline__ uint32_t rank_of_edge(uint32_t v, const uint32_t* __restrict__ rank) {
   return (v != ID_NA && (v & ID_ROOT)) ? rank[v & ~ID_ROOT] : 0u;
 }
+__device__ __forceinline__ bool tw_labelled(unsigned w) { return (w & OVER) && (w & (T_PIT | T_EXIT)); }
 
-__global__ void __launch_bounds__(NT, 6) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
-                                                      const uint32_t* __restrict__ rank, int32_t* shed_out,
-                                                      uint32_t* __restrict__ upslope, uint8_t* __restrict__ ridge,
-                                                      BandSeeds seeds) {
+// add x to every cell from local cell i down to its local terminal (inclusive)
+__device__ __forceinline__ void tile_walk_add(uint32_t a_cnt, const uint8_t* s_dir, const uint16_t* s_tw, int i, unsigned x) {
+  const unsigned w = s_tw[i];
+  if (!x || !tw_labelled(w)) return;  // NA chains and cycles carry no upslope
+  const int term = w & PIDX;
+  for (int step = 0; step < LC; ++step) {
+    red_add_u32(a_cnt + 4 * i, x);
+    if (i == term) break;
+    i += loc_off(s_dir[i]);
+  }
+}
+
+__global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
+                                                      const uint32_t* __restrict__ rank,
+                                                      const uint16_t* __restrict__ tword, int32_t* shed_out,
+                                                      uint32_t* upslope, uint8_t* __restrict__ ridge, BandSeeds seeds) {
   __shared__ unsigned s_cnt[LC];
   __shared__ uint32_t s_tlab[LC];  // label of a terminal
   __shared__ uint32_t s_lab[LC];   // label of every local cell
-  __shared__ uint16_t s_ptr[LC];
+  __shared__ uint16_t s_tw[LC];
   __shared__ uint8_t s_dir[LC];
   const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
 
@@ -282,36 +302,48 @@ __global__ void __launch_bounds__(NT, 6) k_shed_final(TileGeom g, const uint8_t*
   const int base = owned_local(0);
   const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
   const size_t cell0 = (size_t)(t.r_base + owned_ly(0)) * g.d.pitch + c;
-  int p[CPT];
-  const unsigned dvp = tile_setup(g, t, ddir, s_ptr, s_dir, p);
-  // weights: 1 per valid cell (+ flow entering a row band at its first / last own row)
+  unsigned tw[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    unsigned w = ((dvp >> (4 * k)) & 15u) != 0 ? 1u : 0u;
-    if (w && seeds.x_top && t.r_base + owned_ly(k) == seeds.row_top) w += seeds.x_top[c];
-    if (w && seeds.x_bot && t.r_base + owned_ly(k) == seeds.row_bot) w += seeds.x_bot[c];
-    s_cnt[base + k * LW] = w;
+    const int i = base + k * LW;
+    unsigned dv = 0, w = 0, n = 0;
+    if (in_grid(g, t.r_base + owned_ly(k), c)) {
+      const size_t o = cell0 + (size_t)k * g.d.pitch;
+      dv = ddir[o];
+      w = tword[o];
+      n = upslope[o];
+    }
+    tw[k] = w;
+    s_dir[i] = (uint8_t)dv;
+    s_tw[i] = (uint16_t)w;
+    s_cnt[i] = n;
   }
   __syncthreads();
-  // + the external inflow of the border cells (level-2 result): one thread per border slot
+  const uint32_t a_cnt = smem_addr(s_cnt);
+  // ---- flow entering the tile, walked down to the local terminal
   if (threadIdx.x < BUSED) {
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
-    const int i = by * LW + bx;
-    if (s_dir[i] != 0) s_cnt[i] += l2.ext[tile_slot0 + threadIdx.x];
+    tile_walk_add(a_cnt, s_dir, s_tw, by * LW + bx, l2.ext[tile_slot0 + threadIdx.x]);
   }
-  __syncthreads();
-  tile_jump_accumulate(s_ptr, s_cnt, p);
-
+  if (seeds.x_top || seeds.x_bot) {
+    const int lt = seeds.row_top - t.r_base, lb = seeds.row_bot - t.r_base;
+    if (threadIdx.x < TW && t.c_base + (int)threadIdx.x + 1 < g.d.NC) {
+      const int cc = t.c_base + (int)threadIdx.x + 1;
+      if (seeds.x_top && lt >= 1 && lt <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lt * LW + (int)threadIdx.x + 1, seeds.x_top[cc]);
+      if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lb * LW + (int)threadIdx.x + 1, seeds.x_bot[cc]);
+    }
+  }
   // ---- labels of the terminals: pits look up their own rank, exits the rank of their resolved root
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if (((dvp >> (4 * k)) & 15u) == 5u) s_tlab[base + k * LW] = rank[lab_in[cell0 + (size_t)k * g.d.pitch]];
+    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k * LW)
+      s_tlab[base + k * LW] = rank[lab_in[cell0 + (size_t)k * g.d.pitch]];
   if (threadIdx.x < BUSED) {
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
     const int i = by * LW + bx;
-    const int pw = s_ptr[i];
+    const int pw = s_tw[i];
     if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == i)
       s_tlab[i] = rank_of_edge(l2.jres[tile_slot0 + threadIdx.x], rank);
   }
@@ -335,8 +367,7 @@ __global__ void __launch_bounds__(NT, 6) k_shed_final(TileGeom g, const uint8_t*
   const uint32_t a_tlab = smem_addr(s_tlab);
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
-    mylab[k] = ok ? lds_u32(a_tlab + 4 * (p[k] & PIDX)) : 0u;
+    mylab[k] = tw_labelled(tw[k]) ? lds_u32(a_tlab + 4 * (tw[k] & PIDX)) : 0u;
     s_lab[base + k * LW] = mylab[k];
   }
   __syncthreads();
@@ -418,7 +449,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   if (!g->ridge) g->ridge = grid_alloc_array<uint8_t>(d, -1);
   if (!g->shed || !g->upslope || !g->ridge) return set_error(LITAP_ENOMEM, "device allocation failed (shed outputs)");
 
-  static_assert(SMEM_A <= 48 * 1024 && SMEM_B <= 48 * 1024, "tile arrays are static shared memory");
+  static_assert(SMEM_A <= 48 * 1024, "tile arrays are static shared memory");
   TileGeom& tg = W.tg;
   tg.d = d;
   tg.tilesX = (d.NC - 1 + TW - 1) / TW;
@@ -466,8 +497,10 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
 
   dim3 tgrid(tg.tilesX, tg.tilesY);
-  KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, 0, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), l2, pits,
-                                         counters + 1));
+  W.tword = S.get<uint16_t>((size_t)d.cells);  // pitched like the grid arrays, indexed by cell id
+  if (!W.tword) return set_error(LITAP_ENOMEM, "device allocation failed (shed terminal words)");
+  KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, 0, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), W.tword,
+                                         g->upslope, l2, pits, counters + 1));
 
   const unsigned sblk = (unsigned)((nslots + 255) / 256);
   // ---- resolve border cells to pits; a drec cycle across tiles never resolves -> NA after the cap
@@ -540,7 +573,7 @@ int shed_phase_final(litap_grid* g, shed::ShedWork& W, const shed::BandSeeds& se
     KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge, g->halo_bot ? 1 : 0));
   }
   dim3 tgrid(W.tg.tilesX, W.tg.tilesY);
-  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, 0, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, g->shed, g->upslope,
+  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, 0, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, W.tword, g->shed, g->upslope,
                                                                 g->ridge, seeds));
   return LITAP_OK;
 }

@@ -101,6 +101,7 @@ struct ShedWork {
   L2 l2 = {};
   Pits pits = {};
   unsigned long long* counters = nullptr;  // [0] npits, [1] pit cursor, [2] flags (2 x u32)
+  uint16_t* tword = nullptr;               // per cell: final local pointer word of k_shed_local (terminal + kind)
 };
 
 struct TileCtx {
