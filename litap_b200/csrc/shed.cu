@@ -318,14 +318,28 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
     s_tw[i] = (uint16_t)w;
     s_cnt[i] = n;
   }
-  __syncthreads();
-  const uint32_t a_cnt = smem_addr(s_cnt);
-  // ---- flow entering the tile, walked down to the local terminal
+  // ---- labels of the terminals, gathered now (two dependent global loads each) and stored after the
+  // walks: pits look up their own rank, exits the rank of their resolved root
+  uint32_t pitlab[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    pitlab[k] = 0xFFFFFFFFu;
+    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k * LW)
+      pitlab[k] = rank[lab_in[cell0 + (size_t)k * g.d.pitch]];
+  }
+  int bi = -1;  // this thread's border slot as a local index
+  uint32_t bext = 0, blab = 0;
   if (threadIdx.x < BUSED) {
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
-    tile_walk_add(a_cnt, s_dir, s_tw, by * LW + bx, l2.ext[tile_slot0 + threadIdx.x]);
+    bi = by * LW + bx;
+    bext = l2.ext[tile_slot0 + threadIdx.x];
+    blab = rank_of_edge(l2.jres[tile_slot0 + threadIdx.x], rank);
   }
+  __syncthreads();
+  const uint32_t a_cnt = smem_addr(s_cnt);
+  // ---- flow entering the tile, walked down to the local terminal
+  if (bi >= 0) tile_walk_add(a_cnt, s_dir, s_tw, bi, bext);
   if (seeds.x_top || seeds.x_bot) {
     const int lt = seeds.row_top - t.r_base, lb = seeds.row_bot - t.r_base;
     if (threadIdx.x < TW && t.c_base + (int)threadIdx.x + 1 < g.d.NC) {
@@ -334,18 +348,12 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
       if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lb * LW + (int)threadIdx.x + 1, seeds.x_bot[cc]);
     }
   }
-  // ---- labels of the terminals: pits look up their own rank, exits the rank of their resolved root
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k * LW)
-      s_tlab[base + k * LW] = rank[lab_in[cell0 + (size_t)k * g.d.pitch]];
-  if (threadIdx.x < BUSED) {
-    int bx, by;
-    slot_to_local((int)threadIdx.x, bx, by);
-    const int i = by * LW + bx;
-    const int pw = s_tw[i];
-    if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == i)
-      s_tlab[i] = rank_of_edge(l2.jres[tile_slot0 + threadIdx.x], rank);
+    if (pitlab[k] != 0xFFFFFFFFu) s_tlab[base + k * LW] = pitlab[k];
+  if (bi >= 0) {
+    const int pw = s_tw[bi];
+    if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == bi) s_tlab[bi] = blab;
   }
   // ---- labels of the ring cells (for the ridge test): border cells of the neighbouring tiles
   for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
@@ -372,44 +380,38 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   }
   __syncthreads();
 
-  // ---- outputs; the ridge window slides down the thread's column (3 new labels per cell)
-  uint32_t w0[3], w1[3], w2[3];  // rows above / at / below the current cell, columns lx-1 .. lx+1
-#pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    w0[j] = s_lab[base - LW + j - 1];
-    w1[j] = s_lab[base + j - 1];
+  // ---- outputs.  ridge = more than one distinct non-NA label in the 3 x 3 window
+  // (R/flow_02_calc_shed.R:48-57) <=> max label != min non-zero label; with 0 -> 0xFFFFFFFF by
+  // "label - 1" the minimum skips NA cells.  Row triples slide down the thread's column.
+  uint32_t mx0, mx1, mn0, mn1;  // rows above / at the current cell
+  {
+    const uint32_t a = s_lab[base - LW - 1], b = s_lab[base - LW], cc = s_lab[base - LW + 1];
+    mx0 = __vimax3_u32(a, b, cc);
+    mn0 = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
+    const uint32_t d0 = s_lab[base - 1], d1 = s_lab[base], d2 = s_lab[base + 1];
+    mx1 = __vimax3_u32(d0, d1, d2);
+    mn1 = __vimin3_u32(d0 - 1u, d1 - 1u, d2 - 1u);
   }
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const int i = base + k * LW;
-#pragma unroll
-    for (int j = 0; j < 3; ++j) w2[j] = s_lab[i + LW + j - 1];
+    const uint32_t a = s_lab[i + LW - 1], b = s_lab[i + LW], cc = s_lab[i + LW + 1];
+    const uint32_t mx2 = __vimax3_u32(a, b, cc), mn2 = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
     const int r = t.r_base + owned_ly(k);
     if (in_grid(g, r, c)) {
       const size_t o = cell0 + (size_t)k * g.d.pitch;
       const uint32_t lb = mylab[k];
       uint8_t rg = 2;  // NA on the ring
       if (r < g.d.NR - 1 && c < g.d.NC - 1) {
-        // more than one distinct non-NA label in the 3 x 3 window (R/flow_02_calc_shed.R:48-57)
-        uint32_t first = lb;
-        bool multi = false;
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-          const uint32_t v[3] = {w0[j], w1[j], w2[j]};
-#pragma unroll
-          for (int q = 0; q < 3; ++q) {
-            if (!first) first = v[q];
-            multi |= (v[q] != 0u) & (v[q] != first) & (first != 0u);
-          }
-        }
-        rg = multi;
+        const uint32_t mx = __vimax3_u32(mx0, mx1, mx2), mn = __vimin3_u32(mn0, mn1, mn2);
+        rg = (mx != 0u) & (mn + 1u != mx);
       }
       shed_out[o] = (int32_t)lb;
       upslope[o] = lb ? s_cnt[i] : 0u;
       ridge[o] = rg;
     }
-#pragma unroll
-    for (int j = 0; j < 3; ++j) { w0[j] = w1[j]; w1[j] = w2[j]; }
+    mx0 = mx1; mn0 = mn1;
+    mx1 = mx2; mn1 = mn2;
   }
 }
 
