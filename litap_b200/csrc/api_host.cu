@@ -2,6 +2,7 @@
 // Each call uploads its inputs, runs the stage(s) on the device and downloads the requested
 // outputs.  No result is ever computed on the host.
 #include <chrono>
+#include <vector>
 #include "litap_internal.h"
 
 namespace {
@@ -38,6 +39,28 @@ int timed_sync(float* slot, cudaEvent_t a, cudaEvent_t b) {
 }
 #define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
 
+// second stream + event list of one pipelined call (destroyed with it; a failed call leaves nothing queued
+// that refers to caller memory because the destructor drains the stream first)
+struct Pipe {
+  cudaStream_t copy = nullptr;
+  std::vector<cudaEvent_t> ev;
+  int init() {
+    CUDA_TRY(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
+    return LITAP_OK;
+  }
+  int mark(cudaStream_t st) {
+    cudaEvent_t e;
+    CUDA_TRY(cudaEventCreate(&e));
+    ev.push_back(e);
+    CUDA_TRY(cudaEventRecord(e, st));
+    return LITAP_OK;
+  }
+  ~Pipe() {
+    if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
+    for (cudaEvent_t e : ev) cudaEventDestroy(e);
+  }
+};
+
 int begin_call(int64_t NR, int64_t NC, const void* must, GridGuard& gg) {
   if (!must) return set_error(LITAP_EARG, "NULL input array");
   RC(ensure_init());
@@ -66,11 +89,41 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   const bool want_shed = shed || upslope || ridge || npits;
   const bool want_form = slope_pct || slope_deg || aspect || prof || plan;
   if (want_form && !(grid > 0)) return set_error(LITAP_EARG, "grid must be > 0");
+  // The DEM goes up in row chunks; calc_form runs on each chunk as soon as its rows (and the row
+  // below) are resident, and its five outputs go back on a second stream while the next chunk is
+  // still uploading and while calc_ddir2 / calc_shed4 run: both PCIe directions stay busy.
+  // form is computed on the elevations as given (form_mapper never sees the inverted DEM).
+  const GridDims d = g->d;
+  double* fouts[5] = {slope_pct, slope_deg, aspect, prof, plan};
+  Pipe P;
+  RC(P.init());
+  const int nchunk = d.NR >= 8 * 256 ? 8 : 1;
+  const int crows = ((d.NR + nchunk - 1) / nchunk + 31) / 32 * 32;
   CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
-  RC(up(g->elev, g->d, elev));
-  RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));
-  // form is computed on the elevations as given (form_mapper never sees the inverted DEM)
-  if (want_form) { RC(litap_grid_form(g, grid)); }
+  int form_done = 0;  // rows [0, form_done) of the form outputs are computed
+  for (int a = 0; a < d.NR; a += crows) {
+    const int b = a + crows < d.NR ? a + crows : d.NR;
+    CUDA_TRY(cudaMemcpy2DAsync(g->elev + (size_t)a * d.pitch, (size_t)d.pitch * 8, elev + (size_t)a * d.NC, (size_t)d.NC * 8,
+                               (size_t)d.NC * 8, b - a, cudaMemcpyHostToDevice, c.stream));
+    if (!want_form) continue;
+    const int hi = b == d.NR ? d.NR : b - 1;  // row hi is needed as the window row below hi - 1
+    if (hi <= form_done) continue;
+    RC(P.mark(c.stream));
+    RC(run_form_rows(g, grid, form_done, hi));
+    RC(P.mark(c.stream));
+    CUDA_TRY(cudaStreamWaitEvent(P.copy, P.ev.back(), 0));
+    for (int i = 0; i < 5; ++i)
+      if (fouts[i])
+        CUDA_TRY(cudaMemcpy2DAsync(fouts[i] + (size_t)form_done * d.NC, (size_t)d.NC * 8, g->form[i] + (size_t)form_done * d.pitch,
+                                   (size_t)d.pitch * 8, (size_t)d.NC * 8, hi - form_done, cudaMemcpyDeviceToHost, P.copy));
+    form_done = hi;
+  }
+  RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));  // uploads + the form kernels between them
+  for (size_t i = 0; i + 1 < P.ev.size(); i += 2) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, P.ev[i], P.ev[i + 1]);
+    c.tm.form_ms += ms;
+  }
   RC(litap_grid_ddir(g, invert));
   if (want_shed) RC(litap_grid_shed(g));
   CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
@@ -82,11 +135,8 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
     RC(down(ridge, g->d, g->ridge));
     if (npits) *npits = g->npits;
   }
-  if (want_form) {
-    double* outs[5] = {slope_pct, slope_deg, aspect, prof, plan};
-    for (int i = 0; i < 5; ++i) RC(down(outs[i], g->d, g->form[i]));
-  }
-  RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));
+  CUDA_TRY(cudaStreamSynchronize(P.copy));
+  RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));  // what is left of the downloads after the last stage
   c.tm.kernel_launches = c.launches - l0;
   c.tm.total_ms = w.ms();
   return LITAP_OK;

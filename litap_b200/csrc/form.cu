@@ -83,7 +83,7 @@ __device__ __forceinline__ void form_take_row(RowWin<FORM_CPT>& w, FormRing& rin
 
 __global__ void __launch_bounds__(FORM_THREADS, FORM_MINB) k_form(const double* __restrict__ elev, GridDims d, FormK K, FormQ Q,
                                                        const double* __restrict__ trig,
-                                                       const double* __restrict__ qtab, FormPtrs P) {
+                                                       const double* __restrict__ qtab, FormPtrs P, int row_lo, int row_hi) {
   static_assert(FORM_CPT == 2, "window layout of form_take_row");
   __shared__ FormRing ring;
   __shared__ double s_qw[181 * 3], s_qat[QK_ATAN_N];
@@ -91,8 +91,8 @@ __global__ void __launch_bounds__(FORM_THREADS, FORM_MINB) k_form(const double* 
   __shared__ unsigned s_qn;
   const int cb = blockIdx.x * FORM_THREADS * FORM_CPT + 1;  // first column of the block (column 1 is the aligned one)
   const int c0 = cb + threadIdx.x * FORM_CPT;
-  const int r0 = blockIdx.y * FORM_ROWS;
-  const int rend = min(r0 + FORM_ROWS, d.NR);
+  const int r0 = row_lo + blockIdx.y * FORM_ROWS;  // rows [row_lo, row_hi) of the grid; row row_hi must be resident
+  const int rend = min(r0 + FORM_ROWS, row_hi);
   const bool live = c0 < d.pitch - LITAP_XOFF;
   // ring row k = grid row r0 - 1 + k, k = 0 .. kmax
   const int kmax = rend - r0 + 1;
@@ -185,13 +185,13 @@ __device__ __forceinline__ int map1(int x, const int* dst, const int* src) {
 }
 
 __global__ void k_form_edges(const double* __restrict__ elev, GridDims d, double grid,
-                             const double* __restrict__ trig, FormPtrs P, EdgeMap em) {
+                             const double* __restrict__ trig, FormPtrs P, EdgeMap em, int row_lo, int row_hi) {
   // line 0,1: destination columns (all rows); line 2,3: destination rows (all columns)
   const int line = blockIdx.y;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   int r, c;
-  if (line < 2) { c = em.dst_c[line]; r = t; if (c < 0 || r >= d.NR) return; }
-  else { r = em.dst_r[line - 2]; c = t; if (r < 0 || c >= d.NC) return; }
+  if (line < 2) { c = em.dst_c[line]; r = row_lo + t; if (c < 0 || r >= row_hi) return; }
+  else { r = em.dst_r[line - 2]; c = t; if (r < row_lo || r >= row_hi || c >= d.NC) return; }
   const int sr = map1(r, em.dst_r, em.src_r), sc = map1(c, em.dst_c, em.src_c);
   const double NA = __longlong_as_double(0x7ff8000000000000LL);
   double e[10];
@@ -211,10 +211,14 @@ double g_qtab_grid = 0.0;  // the grid size the weights were built for
 double g_trig_host[362];
 }  // namespace
 
-int run_form(litap_grid* g, double grid_m) {
+int run_form(litap_grid* g, double grid_m) { return run_form_rows(g, grid_m, 0, g->d.NR); }
+
+// rows [row_lo, row_hi) of every output (row_hi < NR: row row_hi of elev must already be on the device)
+int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi) {
   Ctx& c = ctx();
   const GridDims d = g->d;
   cudaStream_t st = c.stream;
+  if (row_lo >= row_hi) return LITAP_OK;
   if (!g_trig) {
     double h[362];
     for (int A = 0; A <= 180; ++A) {
@@ -245,7 +249,7 @@ int run_form(litap_grid* g, double grid_m) {
   }
   {
     const int cols = (d.pitch - LITAP_XOFF + FORM_CPT - 1) / FORM_CPT;  // threads across a row
-    dim3 grid((cols + FORM_THREADS - 1) / FORM_THREADS, (d.NR + FORM_ROWS - 1) / FORM_ROWS);
+    dim3 grid((cols + FORM_THREADS - 1) / FORM_THREADS, (row_hi - row_lo + FORM_ROWS - 1) / FORM_ROWS);
     FormK K;
     K.grid = grid_m;
     K.inv2g = 1.0 / (2 * grid_m);
@@ -253,7 +257,7 @@ int run_form(litap_grid* g, double grid_m) {
     FormQ Q;
     Q.inv2g = K.inv2g;
     Q.gz = 8.0 * 4.440892098500626e-16 * 57295.78 / (grid_m * grid_m);
-    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, K, Q, g_trig, g_qtab, P));
+    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, K, Q, g_trig, g_qtab, P, row_lo, row_hi));
   }
   // R/form_01_calc_form.R:54-57 in buffered 0-based coordinates, in this order:
   //   col 1 <- col 2 ; col NC-2 <- col NC-3 ; row 1 <- row 2 ; row NR-2 <- row NR-3
@@ -264,9 +268,9 @@ int run_form(litap_grid* g, double grid_m) {
   em.dst_r[0] = g->edge_top_row; em.src_r[0] = g->edge_top_row + 1 < d.NR ? g->edge_top_row + 1 : -1;
   em.dst_r[1] = g->edge_bot_row; em.src_r[1] = g->edge_bot_row - 1;
   {
-    int m = d.NR > d.NC ? d.NR : d.NC;
+    int m = (row_hi - row_lo) > d.NC ? (row_hi - row_lo) : d.NC;
     dim3 grid((m + 127) / 128, 4);
-    KERNEL("k_form_edges", k_form_edges<<<grid, 128, 0, st>>>(g->elev, d, grid_m, g_trig, P, em));
+    KERNEL("k_form_edges", k_form_edges<<<grid, 128, 0, st>>>(g->elev, d, grid_m, g_trig, P, em, row_lo, row_hi));
   }
   return LITAP_OK;
 }

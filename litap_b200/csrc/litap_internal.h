@@ -149,6 +149,7 @@ struct ProfScope {
 int run_ddir(litap_grid* g, int invert);               // ddir.cu
 int run_shed(litap_grid* g);                           // shed.cu
 int run_form(litap_grid* g, double grid_m);            // form.cu
+int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi);  // form.cu: a row range (pipelined upload)
 void form_forget_trig();                               // form.cu (pool-owned table dropped at shutdown)
 int run_weti(litap_grid* g, double grid_m);            // weti.cu
 int run_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille);  // synth.cu
