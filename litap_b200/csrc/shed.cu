@@ -37,7 +37,10 @@ __global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsig
 // shared memory of k_shed_local: ptr, dir, cnt, key hi / lo / idx (no aliasing: fewer barriers)
 constexpr size_t SMEM_A = (size_t)LC * (2 + 1 + 4 + 4 + 4 + 4) + 64;
 
-__global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
+#ifndef SHED_MINB
+#define SHED_MINB 6
+#endif
+__global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
                                                       const double* __restrict__ elev, uint32_t* __restrict__ lab,
                                                       uint16_t* __restrict__ tword, uint32_t* __restrict__ lcnt,
                                                       L2 l2, Pits pits, unsigned long long* pit_cursor) {
@@ -53,20 +56,29 @@ __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t*
   __shared__ unsigned long long s_pitbase;
 
   const TileCtx t = tile_ctx();
-  const int lx = owned_lx(), c = t.c_base + lx;
+  const int r = t.r_base + owned_ly(), c0 = t.c_base + owned_lx0();
+  const bool row_ok = r < g.d.NR;
   const int base = owned_local(0);
   const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
-  const size_t cell0 = (size_t)(t.r_base + owned_ly(0)) * g.d.pitch + c;  // k-th owned cell: cell0 + k*pitch
+  const size_t cell0 = (size_t)r * g.d.pitch + c0;  // k-th owned cell: cell0 + k (an 8-element boundary)
   if (threadIdx.x == 0) s_npit = 0;
   int p[CPT];
   const unsigned dvp = tile_setup(g, t, ddir, s_ptr, s_dir, p);
-  // elevations of the owned cells: issued now, consumed after the pointer-doubling loop
+  // elevations of the owned cells (64 contiguous bytes): issued now, consumed after the pointer-doubling loop
   double ev[CPT];
+  if (row_ok) {
+#pragma unroll
+    for (int k = 0; k < CPT; k += 2) {
+      const double2 v = __ldg(reinterpret_cast<const double2*>(elev + cell0 + k));
+      ev[k] = v.x;
+      ev[k + 1] = v.y;
+    }
+  }
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const bool valid = ((dvp >> (4 * k)) & 15u) != 0;
-    ev[k] = valid ? elev[cell0 + (size_t)k * g.d.pitch] : 0.0;
-    const int i = base + k * LW;
+    if (!valid) ev[k] = 0.0;
+    const int i = base + k;
     s_cnt[i] = valid ? 1u : 0u;  // out-of-grid and NA cells carry no weight
     s_khi[i] = 0u;
     s_klo[i] = 0u;
@@ -82,17 +94,23 @@ __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t*
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const int dv = (dvp >> (4 * k)) & 15u;
-    const int i = base + k * LW;
+    const int i = base + k;
     pcnt[k] = s_cnt[i];
-    if (in_grid(g, t.r_base + owned_ly(k), c)) {  // kept for k_shed_final: local terminal and in-tile flow count
-      tword[cell0 + (size_t)k * g.d.pitch] = (uint16_t)p[k];
-      lcnt[cell0 + (size_t)k * g.d.pitch] = pcnt[k];
-    }
     // own initial pointer word had T_EXIT <=> the final one has it and points at the cell itself
     if ((p[k] & (OVER | T_EXIT)) == (OVER | T_EXIT) && (p[k] & PIDX) == i) {
-      const long long es = slot_of_rc(t.r_base + owned_ly(k) + nb_dr(dv), c + nb_dc(dv), g.tilesX);
+      const long long es = slot_of_rc(r + nb_dr(dv), c0 + k + nb_dc(dv), g.tilesX);
       if (es >= 0) atomicAdd(&l2.ext[es], pcnt[k]);
     }
+  }
+  if (row_ok) {  // kept for k_shed_final: local terminal word and in-tile flow count of every cell (pads included)
+    uint4 w;
+    w.x = (unsigned)p[0] & 0xFFFFu | (unsigned)p[1] << 16;
+    w.y = (unsigned)p[2] & 0xFFFFu | (unsigned)p[3] << 16;
+    w.z = (unsigned)p[4] & 0xFFFFu | (unsigned)p[5] << 16;
+    w.w = (unsigned)p[6] & 0xFFFFu | (unsigned)p[7] << 16;
+    *reinterpret_cast<uint4*>(tword + cell0) = w;
+    *reinterpret_cast<uint4*>(lcnt + cell0) = make_uint4(pcnt[0], pcnt[1], pcnt[2], pcnt[3]);
+    *reinterpret_cast<uint4*>(lcnt + cell0 + 4) = make_uint4(pcnt[4], pcnt[5], pcnt[6], pcnt[7]);
   }
 
   // ---- per-terminal key: max elevation, then lowest cell id attaining it; three rounds of native
@@ -118,7 +136,7 @@ __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t*
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if (term[k] && klo[k] == lds_u32(a_klo + term[k])) red_min_u32(a_kid + term[k], (uint32_t)(cell0 + (size_t)k * g.d.pitch));
+    if (term[k] && klo[k] == lds_u32(a_klo + term[k])) red_min_u32(a_kid + term[k], (uint32_t)(cell0 + k));
 
   // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
   unsigned rk[CPT];
@@ -133,17 +151,17 @@ __global__ void __launch_bounds__(NT, 6) k_shed_local(TileGeom g, const uint8_t*
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     if (rk[k] == 0xFFFFFFFFu) continue;
-    const int i = base + k * LW;
+    const int i = base + k;
     const uint32_t pid = (uint32_t)(s_pitbase + rk[k]);
     const unsigned long long key = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
     pits.rootmax[pid] = key;
     pits.pitkmax[pid] = key;
     pits.pitkidx[pid] = s_kid[i];
     pits.rootidx[pid] = 0xFFFFFFFFu;
-    pits.cell[pid] = (uint32_t)(cell0 + (size_t)k * g.d.pitch);
+    pits.cell[pid] = (uint32_t)(cell0 + k);
     pits.cnt[pid] = pcnt[k];
-    lab[cell0 + (size_t)k * g.d.pitch] = pid;  // read back by k_shed_final of this tile
-    s_cnt[i] = pid;                            // from here on s_cnt[pit] is its pid (counts are consumed)
+    lab[cell0 + k] = pid;  // read back by k_shed_final of this tile
+    s_cnt[i] = pid;        // from here on s_cnt[pit] is its pid (counts are consumed)
   }
   __syncthreads();
 
@@ -298,25 +316,33 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
 
   const TileCtx t = tile_ctx();
-  const int lx = owned_lx(), c = t.c_base + lx;
+  const int r = t.r_base + owned_ly(), c0 = t.c_base + owned_lx0();
+  const bool row_ok = r < g.d.NR;
   const int base = owned_local(0);
   const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
-  const size_t cell0 = (size_t)(t.r_base + owned_ly(0)) * g.d.pitch + c;
+  const size_t cell0 = (size_t)r * g.d.pitch + c0;  // k-th owned cell: cell0 + k (an 8-element boundary)
   unsigned tw[CPT];
-#pragma unroll
-  for (int k = 0; k < CPT; ++k) {
-    const int i = base + k * LW;
-    unsigned dv = 0, w = 0, n = 0;
-    if (in_grid(g, t.r_base + owned_ly(k), c)) {
-      const size_t o = cell0 + (size_t)k * g.d.pitch;
-      dv = ddir[o];
-      w = tword[o];
-      n = upslope[o];
+  {
+    unsigned long long draw = 0;
+    uint4 wraw = make_uint4(0, 0, 0, 0), n0 = wraw, n1 = wraw;
+    if (row_ok) {
+      draw = __ldg(reinterpret_cast<const unsigned long long*>(ddir + cell0));
+      wraw = __ldg(reinterpret_cast<const uint4*>(tword + cell0));
+      n0 = *reinterpret_cast<const uint4*>(upslope + cell0);
+      n1 = *reinterpret_cast<const uint4*>(upslope + cell0 + 4);
     }
-    tw[k] = w;
-    s_dir[i] = (uint8_t)dv;
-    s_tw[i] = (uint16_t)w;
-    s_cnt[i] = n;
+    const unsigned wv[4] = {wraw.x, wraw.y, wraw.z, wraw.w};
+    const unsigned nv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+      const int i = base + k;
+      const bool in = c0 + k < g.d.NC;  // (row_ok is folded into the zero loads)
+      const unsigned w = in ? (wv[k >> 1] >> (16 * (k & 1))) & 0xFFFFu : 0u;
+      tw[k] = w;
+      s_dir[i] = in ? (uint8_t)(draw >> (8 * k)) : (uint8_t)0;
+      s_tw[i] = (uint16_t)w;
+      s_cnt[i] = in ? nv[k] : 0u;
+    }
   }
   // ---- labels of the terminals, gathered now (two dependent global loads each) and stored after the
   // walks: pits look up their own rank, exits the rank of their resolved root
@@ -324,8 +350,8 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     pitlab[k] = 0xFFFFFFFFu;
-    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k * LW)
-      pitlab[k] = rank[lab_in[cell0 + (size_t)k * g.d.pitch]];
+    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k)
+      pitlab[k] = rank[lab_in[cell0 + k]];
   }
   int bi = -1;  // this thread's border slot as a local index
   uint32_t bext = 0, blab = 0;
@@ -350,7 +376,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   }
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
-    if (pitlab[k] != 0xFFFFFFFFu) s_tlab[base + k * LW] = pitlab[k];
+    if (pitlab[k] != 0xFFFFFFFFu) s_tlab[base + k] = pitlab[k];
   if (bi >= 0) {
     const int pw = s_tw[bi];
     if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == bi) s_tlab[bi] = blab;
@@ -376,43 +402,42 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     mylab[k] = tw_labelled(tw[k]) ? lds_u32(a_tlab + 4 * (tw[k] & PIDX)) : 0u;
-    s_lab[base + k * LW] = mylab[k];
+    s_lab[base + k] = mylab[k];
   }
   __syncthreads();
 
   // ---- outputs.  ridge = more than one distinct non-NA label in the 3 x 3 window
   // (R/flow_02_calc_shed.R:48-57) <=> max label != min non-zero label; with 0 -> 0xFFFFFFFF by
-  // "label - 1" the minimum skips NA cells.  Row triples slide down the thread's column.
-  uint32_t mx0, mx1, mn0, mn1;  // rows above / at the current cell
-  {
-    const uint32_t a = s_lab[base - LW - 1], b = s_lab[base - LW], cc = s_lab[base - LW + 1];
-    mx0 = __vimax3_u32(a, b, cc);
-    mn0 = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
-    const uint32_t d0 = s_lab[base - 1], d1 = s_lab[base], d2 = s_lab[base + 1];
-    mx1 = __vimax3_u32(d0, d1, d2);
-    mn1 = __vimin3_u32(d0 - 1u, d1 - 1u, d2 - 1u);
+  // "label - 1" the minimum skips NA cells.  Column triples (rows above / at / below) of the 10
+  // window columns of the thread's 8 cells, then 3 adjacent columns per cell.
+  if (!row_ok) return;
+  uint32_t cmx[CPT + 2], cmn[CPT + 2];
+#pragma unroll
+  for (int j = 0; j < CPT + 2; ++j) {
+    const uint32_t a = s_lab[base - LW - 1 + j], b = s_lab[base - 1 + j], cc = s_lab[base + LW - 1 + j];
+    cmx[j] = __vimax3_u32(a, b, cc);
+    cmn[j] = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
   }
+  uint32_t up[CPT];
+  unsigned long long rg8 = 0;
+  const bool row_in = r < g.d.NR - 1;
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    const int i = base + k * LW;
-    const uint32_t a = s_lab[i + LW - 1], b = s_lab[i + LW], cc = s_lab[i + LW + 1];
-    const uint32_t mx2 = __vimax3_u32(a, b, cc), mn2 = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
-    const int r = t.r_base + owned_ly(k);
-    if (in_grid(g, r, c)) {
-      const size_t o = cell0 + (size_t)k * g.d.pitch;
-      const uint32_t lb = mylab[k];
-      uint8_t rg = 2;  // NA on the ring
-      if (r < g.d.NR - 1 && c < g.d.NC - 1) {
-        const uint32_t mx = __vimax3_u32(mx0, mx1, mx2), mn = __vimin3_u32(mn0, mn1, mn2);
-        rg = (mx != 0u) & (mn + 1u != mx);
-      }
-      shed_out[o] = (int32_t)lb;
-      upslope[o] = lb ? s_cnt[i] : 0u;
-      ridge[o] = rg;
+    const uint32_t lb = mylab[k];
+    unsigned rg = 2;  // NA on the ring
+    if (row_in && c0 + k < g.d.NC - 1) {
+      const uint32_t mx = __vimax3_u32(cmx[k], cmx[k + 1], cmx[k + 2]), mn = __vimin3_u32(cmn[k], cmn[k + 1], cmn[k + 2]);
+      rg = (mx != 0u) & (mn + 1u != mx);
     }
-    mx0 = mx1; mn0 = mn1;
-    mx1 = mx2; mn1 = mn2;
+    up[k] = lb ? s_cnt[base + k] : 0u;
+    rg8 |= (unsigned long long)rg << (8 * k);
   }
+  // pad columns (>= NC) get label 0 / upslope 0 / ridge NA: one aligned vector per array
+  *reinterpret_cast<uint4*>(shed_out + cell0) = make_uint4(mylab[0], mylab[1], mylab[2], mylab[3]);
+  *reinterpret_cast<uint4*>(shed_out + cell0 + 4) = make_uint4(mylab[4], mylab[5], mylab[6], mylab[7]);
+  *reinterpret_cast<uint4*>(upslope + cell0) = make_uint4(up[0], up[1], up[2], up[3]);
+  *reinterpret_cast<uint4*>(upslope + cell0 + 4) = make_uint4(up[4], up[5], up[6], up[7]);
+  *reinterpret_cast<unsigned long long*>(ridge + cell0) = rg8;
 }
 
 // ring row 0 / column 0 (never inside a tile) and, for uniformity, the other two ring lines
@@ -499,8 +524,9 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
 
   dim3 tgrid(tg.tilesX, tg.tilesY);
-  W.tword = S.get<uint16_t>((size_t)d.cells);  // pitched like the grid arrays, indexed by cell id
+  W.tword = S.get<uint16_t>((size_t)d.cells + 64);  // pitched and offset like the grid arrays (aligned 16-byte vectors)
   if (!W.tword) return set_error(LITAP_ENOMEM, "device allocation failed (shed terminal words)");
+  W.tword += LITAP_XOFF;
   KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, 0, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), W.tword,
                                          g->upslope, l2, pits, counters + 1));
 

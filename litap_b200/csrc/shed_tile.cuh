@@ -15,10 +15,10 @@
 namespace shed {
 
 constexpr int NT = TW * TH / 8;    // threads per tile CTA: 8 interior cells per thread
-constexpr int CPT = TW * TH / NT;  // interior cells per thread (8): consecutive rows of one column
-constexpr int RG = NT / TW;        // row groups of the CTA
-static_assert(NT % TW == 0 && RG * CPT == TH, "a thread owns CPT consecutive rows of one tile column");
-static_assert(CPT <= 8, "direction codes of the owned cells are packed 4 bits each in one register");
+constexpr int CPT = 8;             // interior cells per thread: 8 consecutive columns of one tile row, so that
+                                   // every global access of a thread is one aligned vector (8 B of ddir ... 64 B of elev)
+constexpr int GX = TW / CPT;       // threads per tile row
+static_assert(TW % CPT == 0 && NT == GX * TH, "a thread owns CPT consecutive columns of one tile row");
 // local pointer word (16 bit): low 11 bits = local index, OVER = the walk has reached / passed the
 // terminal whose index is in the low bits, T_PIT / T_EXIT = kind of that terminal (neither = NA)
 constexpr int OVER = 0x8000, T_PIT = 0x4000, T_EXIT = 0x2000, PIDX = 0x07FF;
@@ -35,11 +35,12 @@ __device__ __forceinline__ int loc_off(int dir) {
   int dc = (int)((0x92490u >> (2 * dir)) & 3u) - 1;  // 2-bit table of (dir-1)%3 for dir 0..9 (dir 0 -> unused)
   return dr * LW + dc;
 }
-// k-th interior cell owned by this thread: a warp covers 32 consecutive columns of one row (coalesced
-// global accesses); a thread walks down CPT consecutive rows (vertical reuse in the ridge window)
-__device__ __forceinline__ int owned_ly(int k) { return (int)(threadIdx.x / TW) * CPT + k + 1; }
-__device__ __forceinline__ int owned_lx() { return (int)(threadIdx.x % TW) + 1; }
-__device__ __forceinline__ int owned_local(int k) { return owned_ly(k) * LW + owned_lx(); }
+// k-th interior cell owned by this thread: local row owned_ly(), local column owned_lx0() + k.  Column 1
+// of every grid row is 32-element aligned (LITAP_XOFF) and tiles are 32 columns wide, so the thread's
+// 8 cells start at an 8-element boundary of every per-cell array.
+__device__ __forceinline__ int owned_ly() { return (int)(threadIdx.x / GX) + 1; }
+__device__ __forceinline__ int owned_lx0() { return (int)(threadIdx.x % GX) * CPT + 1; }
+__device__ __forceinline__ int owned_local(int k) { return owned_ly() * LW + owned_lx0() + k; }
 
 // local coordinates of border slot s (0 <= s < BUSED): inverse of border_slot_local
 __device__ __forceinline__ void slot_to_local(int s, int& lx, int& ly) {
@@ -117,23 +118,26 @@ __device__ __forceinline__ TileCtx tile_ctx() {
 }
 __device__ __forceinline__ bool in_grid(const TileGeom& g, int r, int c) { return r < g.d.NR && c < g.d.NC; }
 
+// 8 bytes of a u8 array at the thread's owned cells (0 outside the grid rows)
+__device__ __forceinline__ unsigned long long load_owned_u8(const TileGeom& g, const TileCtx& t, const uint8_t* __restrict__ a) {
+  const int r = t.r_base + owned_ly();
+  if (r >= g.d.NR) return 0ull;
+  return __ldg(reinterpret_cast<const unsigned long long*>(a + (size_t)r * g.d.pitch + t.c_base + owned_lx0()));
+}
 // Phase 0: stage ddir of the owned cells and their initial pointer words.  Cells outside the grid,
 // with NA ddir, or whose ddir leaves the grid / points onto buffered row 0 or column 0 (which belong
 // to no tile: the NA ring) are NA terminals.  Returns the 8 direction codes packed 4 bits each; p[k]
 // gets the pointer word of the k-th owned cell.
 __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx& t, const uint8_t* __restrict__ ddir,
                                                uint16_t* s_ptr, uint8_t* s_dir, int* p) {
-  const int lx = owned_lx(), c = t.c_base + lx;
-  const bool atL = lx == 1, atR = lx == TW;
+  const int ly = owned_ly(), r = t.r_base + ly, lx0 = owned_lx0();
+  const unsigned long long raw = load_owned_u8(g, t, ddir);
   unsigned pack = 0;
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    const int ly = owned_ly(k), r = t.r_base + ly, i = ly * LW + lx;
-    int dv = 0;
-    if (in_grid(g, r, c)) {
-      dv = ddir[(size_t)r * g.d.pitch + c];
-      if (dv > 9) dv = 0;
-    }
+    const int lx = lx0 + k, c = t.c_base + lx, i = ly * LW + lx;
+    int dv = (int)((raw >> (8 * k)) & 0xFFull);
+    if (c >= g.d.NC || dv > 9) dv = 0;
     int pw = i | OVER;  // NA terminal unless shown otherwise
     if (dv == 5) pw |= T_PIT;
     else if (dv != 0) {
@@ -142,7 +146,7 @@ __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx&
       const int rr = r + dr, cc = c + dc;
       if (rr < 1 || cc < 1 || !in_grid(g, rr, cc)) dv = 0;
       else {
-        const bool ex = (dc < 0 && atL) || (dc > 0 && atR) || (dr < 0 && ly == 1) || (dr > 0 && ly == TH);
+        const bool ex = (dc < 0 && lx == 1) || (dc > 0 && lx == TW) || (dr < 0 && ly == 1) || (dr > 0 && ly == TH);
         pw = ex ? (i | OVER | T_EXIT) : (i + dr * LW + dc);
       }
     }
@@ -211,7 +215,7 @@ __device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* 
     for (int k = 0; k < CPT; ++k) {
       if (!(p[k] & OVER)) {
         b[k] = lds_u16(a_ptr + 2 * p[k]);
-        sv[k] = lds_u32(own_cnt + 4 * k * LW);
+        sv[k] = lds_u32(own_cnt + 4 * k);
         any = true;
       }
     }
@@ -219,7 +223,7 @@ __device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* 
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
       if (p[k] & OVER) continue;
-      sts_u16(own_ptr + 2 * k * LW, b[k]);
+      sts_u16(own_ptr + 2 * k, b[k]);
       red_add_u32(a_cnt + 4 * p[k], sv[k]);
       p[k] = (int)b[k];
     }
