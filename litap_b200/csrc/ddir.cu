@@ -471,6 +471,7 @@ int run_ddir(litap_grid* g, int invert) {
     if (rc) return rc;
   }
   c.tm.flat_cells = (int64_t)h.nflat;
+  g->pit_bound = (int64_t)h.nflat;  // pits are cells that stay flat: calc_shed4 sizes its pit arrays from this
   c.tm.plateau_rounds = (int)h.rounds;
   c.tm.patch_cells = h.npatch;
   if (h.npatch) {

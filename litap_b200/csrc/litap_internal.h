@@ -62,6 +62,7 @@ struct litap_grid {
   // row band of a larger DEM (bands.cu): nbands == 0 for a whole DEM
   int band = 0, nbands = 0;
   long long gnr = 0;                        // rows of the whole DEM
+  int64_t pit_bound = -1;                   // >= number of pits of the ddir on the grid (flat cells of the D8 stencil), -1 unknown
   int edge_top_row = -1, edge_bot_row = -1; // local row holding the first / last DEM row, -1 if not in this grid
   // calc_ddir2 worklists (ddir.cu)
   uint32_t* dd_list = nullptr;

@@ -487,15 +487,18 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   unsigned long long* counters = W.counters = S.get<unsigned long long>(4);
   if (!counters) return set_error(LITAP_ENOMEM, "device allocation failed (shed scratch)");
   CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), st));
-  {
+  // capacity of the pit arrays: the flat-cell count of the D8 stencil when calc_ddir2 ran on this grid
+  // (pits are a subset), else an exact count (one more pass over ddir and a host sync)
+  size_t np = 1;
+  if (g->pit_bound >= 0 && g->nbands == 0) np = g->pit_bound ? (size_t)g->pit_bound : 1;
+  else {
     dim3 grid((d.NC - 1 + 255) / 256, d.NR - 1 < 256 ? d.NR - 1 : 256);
     KERNEL("k_count_pits", k_count_pits<<<grid, 256, 0, st>>>(g->ddir, d, counters));
+    unsigned long long npits64 = 0;
+    CUDA_TRY(cudaMemcpyAsync(&npits64, counters, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    np = npits64 ? (size_t)npits64 : 1;
   }
-  unsigned long long npits64 = 0;
-  CUDA_TRY(cudaMemcpyAsync(&npits64, counters, 8, cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  const unsigned npits = W.npits = (unsigned)npits64;
-  const size_t np = npits ? npits : 1;
 
   L2& l2 = W.l2;
   l2.jump0 = S.get<uint32_t>(nslots);
@@ -532,16 +535,20 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
 
   const unsigned sblk = (unsigned)((nslots + 255) / 256);
   // ---- resolve border cells to pits; a drec cycle across tiles never resolves -> NA after the cap
+  // (two rounds per host check; the same read-back brings the pit count = the pit cursor of k_shed_local)
   unsigned* flag = reinterpret_cast<unsigned*>(counters + 2);
   bool open = true;
-  for (int round = 0; round < 64 && open; ++round) {
-    CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
-    KERNEL("k_l2_resolve", k_l2_resolve<<<sblk, 256, 0, st>>>(tg, l2.jres, nslots, flag));
-    unsigned h = 0;
-    CUDA_TRY(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, st));
+  unsigned long long hb[2] = {0, 0};
+  for (int round = 0; round < 64 && open; round += 2) {
+    for (int k = 0; k < 2; ++k) {
+      CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+      KERNEL("k_l2_resolve", k_l2_resolve<<<sblk, 256, 0, st>>>(tg, l2.jres, nslots, flag));
+    }
+    CUDA_TRY(cudaMemcpyAsync(hb, counters + 1, 16, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    open = h != 0;
+    open = (unsigned)(hb[1] & 0xFFFFFFFFull) != 0;
   }
+  const unsigned npits = W.npits = (unsigned)hb[0];
   if (open) {
     KERNEL("k_l2_close_cycles", k_l2_close_cycles<<<sblk, 256, 0, st>>>(l2.jres, nslots));
   }
