@@ -410,12 +410,15 @@ int ddir_patch_resolve(const unsigned long long* keys, unsigned np, PoolScratch&
   if (!K || !kc || !kr || !kc2 || !kr2 || !bestd || !parent || !bestid || !medc || !medr || !opts || !newdir || !tmp)
     return set_error(LITAP_ENOMEM, "device allocation failed (patch scratch)");
   const unsigned nb = nblk(np);
-  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, keys, K, (int)np, 0, 64, st));
+  // key = (global row << 32 | col), rows < 2^24; (component < np) << 32 | row or col below: skip the empty top digits
+  int cbits = 1;
+  while ((1ull << cbits) < (unsigned long long)np) ++cbits;
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, keys, K, (int)np, 0, 56, st));
   KERNEL("k_patch_init", k_patch_init<<<nb, 256, 0, st>>>(np, parent, bestd, bestid));
   KERNEL("k_patch_union", k_patch_union<<<nb, 256, 0, st>>>(K, np, parent, opts));
   KERNEL("k_patch_flatten", k_patch_flatten<<<nb, 256, 0, st>>>(K, np, parent, kc, kr));
-  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, kc, kc2, (int)np, 0, 64, st));
-  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, kr, kr2, (int)np, 0, 64, st));
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, kc, kc2, (int)np, 0, 32 + cbits, st));
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(tmp, tmpn, kr, kr2, (int)np, 0, 32 + cbits, st));
   KERNEL("k_patch_median", k_patch_median<<<nb, 256, 0, st>>>(kc2, kr2, np, medc, medr));
   KERNEL("k_patch_best", k_patch_best<<<nb, 256, 0, st>>>(K, np, parent, medc, medr, bestd, bestid, 0));
   KERNEL("k_patch_best", k_patch_best<<<nb, 256, 0, st>>>(K, np, parent, medc, medr, bestd, bestid, 1));

@@ -39,6 +39,7 @@ def lib():
         L.oracle_shed.argtypes = [_f64p, _u8p, C.c_int64, C.c_int64, _i32p, _i64p, _u8p, C.POINTER(C.c_int64)]
         L.oracle_form.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 5 + [C.c_int]
         L.oracle_weti.argtypes = [_f64p, _u8p, _f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 4
+        L.oracle_slope_gc.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 6 + [_u8p] * 2 + [_i32p] * 4
         L.oracle_r_round.argtypes = [C.c_double, C.c_int]
         L.oracle_r_round.restype = C.c_double
         L.oracle_synth_dem.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_uint32,
@@ -110,6 +111,21 @@ def weti(elev_b, ddir_b, upslope_b, grid):
     outs = [np.empty((NR, NC)) for _ in range(4)]
     lib().oracle_weti(e, d, u, NR, NC, float(grid), *outs)
     return dict(zip(("qarea1", "qarea2", "qweti1", "qweti2"), outs))
+
+
+GC_F64 = ("sgre", "sgr", "sgcn", "sgc", "scr", "scc")
+GC_U8 = ("hill_r_dir", "hill_c_dir")
+GC_I32 = ("hill_r_n", "hill_r_cell", "hill_c_n", "hill_c_cell")
+
+
+def slope_gc(elev_b, grid):
+    """slope_gc on a buffered grid (R/flow_05_slope_gc.R:73-164). f64 outputs NaN = NA; u8 / i32 outputs 0 = NA."""
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    out = {k: np.empty(e.shape) for k in GC_F64}
+    out.update({k: np.empty(e.shape, np.uint8) for k in GC_U8})
+    out.update({k: np.empty(e.shape, np.int32) for k in GC_I32})
+    lib().oracle_slope_gc(e, e.shape[0], e.shape[1], float(grid), *[out[k] for k in GC_F64 + GC_U8 + GC_I32])
+    return out
 
 
 def r_round(x, digits):

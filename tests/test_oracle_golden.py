@@ -140,3 +140,49 @@ def test_synth_dem_bands_bit_identical():
     assert (np.round(full[1:-1, 1:-1] * 1000) / 1000 == full[1:-1, 1:-1]).all()
     na = oracle.synth_dem(64, 64, seed=7, na_permille=10)
     assert 5 < np.isnan(na[1:-1, 1:-1]).sum() < 100
+
+
+# ---- slope_gc: R/flow_05_slope_gc.R:73-164 -------------------------------------
+def test_slope_gc_fullgrid_golden(golden):
+    """flow_mapper calls slope_gc(db_fill, grid = 1) (R/flow_mapper.R:307); flow/dem_fill.rds holds all
+    twelve columns for the 8 100 cells of testELEV."""
+    z = golden["dem_fill"]
+    e = oracle.add_buffer(z["elev"].reshape(90, 90))
+    o = oracle.slope_gc(e, 1.0)
+    for k in oracle.GC_F64:
+        a = o[k][1:-1, 1:-1].ravel()
+        assert (a.view(np.uint64) == z[k].view(np.uint64)).all(), k  # bit-identical doubles (no NA inside testELEV)
+    for k in oracle.GC_U8 + oracle.GC_I32:
+        a = o[k][1:-1, 1:-1].ravel().astype(np.float64)
+        a[a == 0] = np.nan
+        assert eq_na(a, z[k]).all(), k
+
+
+def test_slope_gc_test_dem_kats(golden):
+    """tests/testthat/test_00_utility.R:73-126 on data/test_dem.rda (already buffered, grid = 5)."""
+    td = golden["dems"]
+    NR, NC = int(td["test_dem_row"].max()), int(td["test_dem_col"].max())
+    e = td["test_dem_elev"].reshape(NR, NC).copy()
+    o = oracle.slope_gc(e, 5.0)
+    s = {k: v[1:-1, 1:-1].ravel() for k, v in o.items()}   # remove_buffer()
+    el = e[1:-1, 1:-1].ravel()
+    mc = NC - 2
+    for k in ("sgc", "sgr", "sgcn", "sgre"):
+        assert (s[k] != 0).all()
+    assert np.allclose(s["sgc"], np.abs(s["sgcn"]), atol=1e-5) and np.allclose(s["sgr"], np.abs(s["sgre"]), atol=1e-5)
+    for i in (500, 1000, 5000, 10000, 16000, 20000, 24000, 26000, 30000, 32000, 34000):
+        j = i - 1  # R is 1-based
+        assert s["sgre"][j] == pytest.approx((el[j - 1] - el[j + 1]) / (2 * 5))
+        assert s["sgcn"][j] == pytest.approx((el[j + mc] - el[j - mc]) / (2 * 5))
+        assert s["scr"][j] == pytest.approx((2 * el[j] - el[j - 1] - el[j + 1]) / 25)
+        assert s["scc"][j] == pytest.approx((2 * el[j] - el[j + mc] - el[j - mc]) / 25)
+    assert set(np.unique(s["hill_r_dir"])) <= {2, 4} and set(np.unique(s["hill_c_dir"])) <= {1, 3}
+    assert (s["hill_r_dir"][s["sgre"] < 0] == 4).all() and (s["hill_r_dir"][s["sgre"] > 0] == 2).all()
+    assert (s["hill_c_dir"][s["sgcn"] < 0] == 3).all() and (s["hill_c_dir"][s["sgcn"] > 0] == 1).all()
+    assert s["hill_r_n"].max() <= mc and s["hill_c_n"].max() <= NR - 2
+    assert (s["hill_r_n"][409:416] == 1).all() and (s["hill_r_cell"][409:416] == np.arange(36, 43)).all()
+    assert (s["hill_r_n"][416:425] == 2).all() and (s["hill_r_cell"][416:425] == np.arange(1, 10)).all()
+    col = o["hill_c_n"][1:-1, 1:-1][:, 121]
+    cell = o["hill_c_cell"][1:-1, 1:-1][:, 121]
+    assert (col[0:10] == 1).all() and (cell[0:10] == np.arange(1, 11)).all()
+    assert (col[58:68] == 5).all() and (cell[58:68] == np.arange(1, 11)).all()
