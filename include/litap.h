@@ -12,6 +12,7 @@
  *   litap_form   <- calc_form()    R/form_01_calc_form.R:4-67    (called R/form_mapper.R:103)
  *   litap_weti   <- calc_weti2()   R/form_02b_calc_weti.R:3-110  (called R/form_mapper.R:127)
  *   invert flag  <- invert()       R/flow_06_invert.R:1-5        (called R/flow_mapper.R:343-346)
+ *   litap_slope_gc <- slope_gc()   R/flow_05_slope_gc.R:73-164   (called R/flow_mapper.R:307)
  *
  * Grid convention (R/LITAP_load.R:273-332 add_buffer; R/LITAP_functions.R:207-235 nb_values):
  * every array is the BUFFERED grid, NR = nrow+2 by NC = ncol+2, dense row-major, row 0 = north,
@@ -52,6 +53,7 @@ typedef struct litap_timings {
   int weti_waves;   /* dependency waves of the last calc_weti2 (depth of the flow DAG) */
   int64_t flat_cells, patch_cells, npits;
   int64_t kernel_launches; /* kernels of this library launched by the call */
+  float gc_ms;      /* slope_gc */
 } litap_timings;
 
 int litap_init(int device);        /* selects the device and creates the stream; idempotent */
@@ -89,6 +91,15 @@ int litap_weti(const double* elev, const uint8_t* ddir, const uint32_t* upslope,
                int64_t NR, int64_t NC, double grid,
                double* qarea1, double* qarea2, double* qweti1, double* qweti2);
 
+/* slope_gc: gradients towards east / north with their zero signs settled, magnitudes (0 -> 0.00001),
+ * row / column curvatures, hillslope run labels per row and per column.  f64 outputs NaN = NA;
+ * hill_*_dir (2 = east, 4 = west; 1 = north, 3 = south) and hill_*_n / hill_*_cell: 0 = NA.
+ * The grid must carry the NA ring of add_buffer().  Any output may be NULL. */
+int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double grid,
+                   double* sgre, double* sgr, double* sgcn, double* sgc, double* scr, double* scc,
+                   uint8_t* hill_r_dir, uint8_t* hill_c_dir, int32_t* hill_r_n, int32_t* hill_r_cell,
+                   int32_t* hill_c_n, int32_t* hill_c_cell);
+
 /* Fused composite (ddir -> shed/upslope/ridge -> form) with one upload of elev; the
  * intermediate ddir never leaves the device.  Any output may be NULL (then not downloaded). */
 int litap_flow_form(const double* elev, int64_t NR, int64_t NC, double grid, int invert,
@@ -110,8 +121,10 @@ int litap_grid_ddir(litap_grid* g, int invert);
 int litap_grid_shed(litap_grid* g);
 int litap_grid_form(litap_grid* g, double grid_m);
 int litap_grid_weti(litap_grid* g, double grid_m);
+int litap_grid_slope_gc(litap_grid* g, double grid_m);
 /* copy results out (dense NR*NC); name is one of: elev ddir flatcell shed upslope ridge
- * slope_pct slope_deg aspect prof plan qarea1 qarea2 qweti1 qweti2 */
+ * slope_pct slope_deg aspect prof plan qarea1 qarea2 qweti1 qweti2
+ * sgre sgr sgcn sgc scr scc hill_r_dir hill_c_dir hill_r_n hill_r_cell hill_c_n hill_c_cell */
 int litap_grid_download(litap_grid* g, const char* name, void* dst);
 int64_t litap_grid_npits(const litap_grid* g);
 /* order-independent checksum (sum of value*index hashes) of a result array, computed on the device */

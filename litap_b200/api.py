@@ -129,6 +129,31 @@ def calc_form(db, grid, verbose=False):
     return res
 
 
+GC_F64 = ("sgre", "sgr", "sgcn", "sgc", "scr", "scc")
+GC_U8 = ("hill_r_dir", "hill_c_dir")
+GC_I32 = ("hill_r_n", "hill_r_cell", "hill_c_n", "hill_c_cell")
+
+
+def slope_gc(db, grid=1):
+    """R/flow_05_slope_gc.R:73-164.  Needs the buffered elev; returns db + sgre, sgr, sgcn, sgc, scr, scc,
+    hill_r_dir, hill_c_dir, hill_r_n, hill_r_cell, hill_c_n, hill_c_cell (doubles, NaN = NA, like the R columns;
+    the raw uint8 / int32 encodings of the C ABI, 0 = NA, are kept under '<name>_raw')."""
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    f = [np.empty(NR * NC) for _ in GC_F64]
+    u = [np.empty(NR * NC, np.uint8) for _ in GC_U8]
+    n = [np.empty(NR * NC, np.int32) for _ in GC_I32]
+    check(lib().litap_slope_gc(e.ctypes.data, NR, NC, float(grid), *[a.ctypes.data for a in f + u + n]))
+    out = dict(db)
+    out.update(zip(GC_F64, f))
+    for k, a in zip(GC_U8 + GC_I32, u + n):
+        out[k + "_raw"] = a
+        v = a.astype(np.float64)
+        v[a == 0] = np.nan
+        out[k] = v
+    return out
+
+
 def calc_weti2(db, grid, verbose=False):
     """R/form_02b_calc_weti.R:3-110.  Needs elev, ddir, upslope; returns db + qarea1/2, qweti1/2."""
     NR, NC = _dims(db)
@@ -180,7 +205,8 @@ class DeviceGrid:
     """A DEM (or row band) resident in HBM: litap_grid_* of include/litap.h."""
 
     _DT = {"elev": np.float64, "ddir": np.uint8, "flatcell": np.uint8, "shed": np.int32, "upslope": np.uint32,
-           "ridge": np.uint8}
+           "ridge": np.uint8, "hill_r_dir": np.uint8, "hill_c_dir": np.uint8, "hill_r_n": np.int32,
+           "hill_r_cell": np.int32, "hill_c_n": np.int32, "hill_c_cell": np.int32}
 
     def __init__(self, NR, NC):
         self.NR, self.NC = int(NR), int(NC)
@@ -215,6 +241,9 @@ class DeviceGrid:
 
     def weti(self, grid):
         check(lib().litap_grid_weti(self._h, float(grid)))
+
+    def slope_gc(self, grid):
+        check(lib().litap_grid_slope_gc(self._h, float(grid)))
 
     def download(self, name):
         a = np.empty((self.NR, self.NC), self._DT.get(name, np.float64))

@@ -134,6 +134,9 @@ extern "C" void litap_grid_destroy(litap_grid* g) {
   grid_free_array(g->ridge);
   for (auto& p : g->form) grid_free_array(p);
   for (auto& p : g->weti) grid_free_array(p);
+  for (auto& p : g->gc_f64) grid_free_array(p);
+  for (auto& p : g->gc_u8) grid_free_array(p);
+  for (auto& p : g->gc_i32) grid_free_array(p);
   if (g->dd_list) pool_free(g->dd_list);
   if (g->dd_cand) pool_free(g->dd_cand);
   if (g->dd_keys) pool_free(g->dd_keys);
@@ -234,6 +237,19 @@ extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
   return rc;
 }
 
+extern "C" int litap_grid_slope_gc(litap_grid* g, double grid_m) {
+  if (!g) return set_error(LITAP_EARG, "litap_grid_slope_gc: NULL");
+  if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_slope_gc: grid must be > 0");
+  if (g->nbands > 0) return set_error(LITAP_EARG, "litap_grid_slope_gc: not available on a row band (columns span all bands)");
+  int64_t l0 = ctx().launches;
+  StageTimer t(&ctx().tm.gc_ms, 4);
+  int rc = run_slope_gc(g, grid_m);
+  if (rc) return rc;
+  rc = t.finish();
+  ctx().tm.kernel_launches = ctx().launches - l0;
+  return rc;
+}
+
 extern "C" int64_t litap_grid_npits(const litap_grid* g) { return g ? g->npits : -1; }
 
 struct ArrRef { const void* p; int esize; };
@@ -248,6 +264,12 @@ static ArrRef find_array(litap_grid* g, const char* name) {
   if (!strcmp(name, "ridge")) return {g->ridge, 1};
   for (int i = 0; i < 5; ++i) if (!strcmp(name, fn[i])) return {g->form[i], 8};
   for (int i = 0; i < 4; ++i) if (!strcmp(name, wn[i])) return {g->weti[i], 8};
+  static const char* gf[6] = {"sgre", "sgr", "sgcn", "sgc", "scr", "scc"};
+  static const char* gu[2] = {"hill_r_dir", "hill_c_dir"};
+  static const char* gi[4] = {"hill_r_n", "hill_r_cell", "hill_c_n", "hill_c_cell"};
+  for (int i = 0; i < 6; ++i) if (!strcmp(name, gf[i])) return {g->gc_f64[i], 8};
+  for (int i = 0; i < 2; ++i) if (!strcmp(name, gu[i])) return {g->gc_u8[i], 1};
+  for (int i = 0; i < 4; ++i) if (!strcmp(name, gi[i])) return {g->gc_i32[i], 4};
   return {nullptr, 0};
 }
 

@@ -218,3 +218,31 @@ extern "C" int litap_weti(const double* elev, const uint8_t* ddir, const uint32_
   c.tm.total_ms = w.ms();
   return LITAP_OK;
 }
+
+extern "C" int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double grid, double* sgre, double* sgr,
+                              double* sgcn, double* sgc, double* scr, double* scc, uint8_t* hill_r_dir,
+                              uint8_t* hill_c_dir, int32_t* hill_r_n, int32_t* hill_r_cell, int32_t* hill_c_n,
+                              int32_t* hill_c_cell) {
+  Wall w;
+  GridGuard gg;
+  if (!(grid > 0)) return set_error(LITAP_EARG, "litap_slope_gc: grid must be > 0");
+  RC(begin_call(NR, NC, elev, gg));
+  litap_grid* g = gg.g;
+  Ctx& c = ctx();
+  int64_t l0 = c.launches;
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  RC(up(g->elev, g->d, elev));
+  RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));
+  RC(litap_grid_slope_gc(g, grid));
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  double* f[6] = {sgre, sgr, sgcn, sgc, scr, scc};
+  uint8_t* u[2] = {hill_r_dir, hill_c_dir};
+  int32_t* n[4] = {hill_r_n, hill_r_cell, hill_c_n, hill_c_cell};
+  for (int i = 0; i < 6; ++i) RC(down(f[i], g->d, g->gc_f64[i]));
+  for (int i = 0; i < 2; ++i) RC(down(u[i], g->d, g->gc_u8[i]));
+  for (int i = 0; i < 4; ++i) RC(down(n[i], g->d, g->gc_i32[i]));
+  RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));
+  c.tm.kernel_launches = c.launches - l0;
+  c.tm.total_ms = w.ms();
+  return LITAP_OK;
+}

@@ -1,0 +1,278 @@
+// gc.cu — slope_gc on the device (R/flow_05_slope_gc.R:73-164): gradients
+// towards east / north (sgre, sgcn), their magnitudes (sgr, sgc, 0 -> 0.00001), row / column
+// curvatures (scr, scc) and the hillslope run labels of every row and every column
+// (hill_r_dir/n/cell, hill_c_dir/n/cell).
+//
+// What the reference does, and how it maps:
+//   * :103-135  zero gradients take 0.00001 x the sign of the previous cell (west for sgre, SOUTH for
+//     sgcn), found by synchronous rounds over the whole grid with a "no progress -> +0.00001" exit.
+//     Its fixed point is a sweep along the line: a run of zeros takes the sign of the non-zero value
+//     before it; a run whose predecessor is NA is never resolved (-> +0.00001) unless it is a single
+//     cell, which then looks at the cell after it (fix_step below; checked against the literal
+//     Jacobi rounds of the oracle).
+//   * :145-160  cumsum / factor / 1:n() per row and per column are a second sweep with a handful of
+//     counters (label_step): NA gradients poison the rest of the line exactly like cumsum(NA).
+// A line is inherently sequential in this formulation; all lines run in parallel:
+//   k_gc_rows   a block owns 16 rows and walks along them in 32-column chunks staged through shared
+//               memory (coalesced loads / stores by the whole block, one lane per row in between)
+//   k_gc_cols_a one thread per column, south -> north: sgcn (signs fixed), sgc, scc
+//   k_gc_cols_b one thread per column, north -> south: hill_c_dir / n / cell
+// The NA ring of add_buffer() is required (like everywhere on this path): it is what makes the
+// reference's linear seqno +- 1 addressing row-local.
+#include "cellmath.h"
+#include "litap_internal.h"
+
+namespace {
+
+constexpr double GC_TINY = 0.00001;
+__device__ __forceinline__ double gc_na() { return __longlong_as_double(0x7ff8000000000000LL); }
+
+struct GcPtrs {
+  double *sgre, *sgr, *sgcn, *sgc, *scr, *scc;
+  uint8_t *rdir, *cdir;
+  int32_t *rn, *rcell, *cn, *ccell;
+};
+
+// ---- the two sweeps ------------------------------------------------------------------------------
+struct FixState {
+  double prev;    // fixed value of the previous cell of the line (NA before the first)
+  double runval;  // what the cells of the current zero run take
+  bool in_run;
+};
+__device__ __forceinline__ void fix_init(FixState& s) { s.prev = gc_na(); s.runval = 0; s.in_run = false; }
+// g: this cell's gradient as computed; nxt: the next cell's (NA past the end).  Returns the fixed value.
+__device__ __forceinline__ double fix_step(FixState& s, double g, double nxt) {
+  double out = g;
+  if (g == 0.0) {
+    if (!s.in_run) {
+      if (s.prev == s.prev) s.runval = s.prev > 0 ? GC_TINY : -GC_TINY;         // 0.00001 * sign(previous)
+      else if (nxt == 0.0) s.runval = GC_TINY;                                  // never resolved: positive
+      else s.runval = nxt != nxt ? gc_na() : (nxt > 0 ? GC_TINY : -GC_TINY);    // single cell: 0.00001 * sign(next)
+      s.in_run = true;
+    }
+    out = s.runval;
+  } else s.in_run = false;
+  s.prev = out;
+  return out;
+}
+
+struct LabelState {
+  int cum, dense, last_val, cnt, na_cnt;
+  bool lag_na, lag_pos, poisoned, have_last;
+};
+__device__ __forceinline__ void label_init(LabelState& s) {
+  s.cum = s.dense = s.last_val = s.cnt = s.na_cnt = 0;
+  s.lag_na = true; s.lag_pos = false; s.poisoned = false; s.have_last = false;
+}
+// v: fixed gradient of the cell (never 0; NaN = NA), elev_na: the cell has no elevation
+__device__ __forceinline__ void label_step(LabelState& s, double v, bool elev_na, int& n_out, int& cell_out) {
+  const bool s_na = v != v, pos = v > 0;
+  if (!s.lag_na && s_na) s.poisoned = true;                       // (NA | FALSE) = NA: cumsum is NA from here on
+  else if (!s.poisoned) s.cum += (s.lag_na || pos != s.lag_pos) ? 1 : 0;
+  if (!elev_na && !s.poisoned) {
+    if (!s.have_last || s.cum != s.last_val) { ++s.dense; s.last_val = s.cum; s.have_last = true; s.cnt = 0; }
+    n_out = s.dense;
+    cell_out = ++s.cnt;
+  } else {
+    ++s.na_cnt;                 // NA is one more group of the line
+    n_out = 0;
+    cell_out = elev_na ? 0 : s.na_cnt;
+  }
+  s.lag_na = s_na;
+  s.lag_pos = pos;
+}
+
+// ---- rows ------------------------------------------------------------------------------------------
+constexpr int GR_ROWS = 16;     // rows per block = lanes of the sweep
+constexpr int GR_CH = 32;       // columns per chunk
+constexpr int GR_THREADS = 128;
+
+// elevation of linear neighbour seqno - 1 / seqno + 1 exactly as nb_values addresses it (no wrap check)
+__device__ __forceinline__ double gc_elev_lin(const double* __restrict__ elev, const GridDims& d, int r, int c) {
+  if (c < 0) { c = d.NC - 1; --r; }
+  else if (c >= d.NC) { c = 0; ++r; }
+  if (r < 0 || r >= d.NR) return gc_na();
+  return __ldg(elev + (size_t)r * d.pitch + c);
+}
+// (sgre, scr) of a cell from its elevation and its west / east neighbours (R/flow_05_slope_gc.R:80-90)
+__device__ __forceinline__ void gc_row_cell(double e5, double n4, double n6, double two_g, double g2, double& ge, double& cr) {
+  if (n4 != n4) n4 = e5;
+  if (n6 != n6) n6 = e5;
+  ge = (n4 - n6) / two_g;
+  cr = (2 * e5 - n4 - n6) / g2;
+}
+
+__global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
+  __shared__ double s_e[GR_ROWS][GR_CH + 5];     // columns cb-1 .. cb+GR_CH+2 of the block's rows
+  __shared__ double s_ge[GR_ROWS][GR_CH + 1], s_gr[GR_ROWS][GR_CH + 1], s_cr[GR_ROWS][GR_CH + 1];
+  __shared__ int s_n[GR_ROWS][GR_CH + 1], s_cell[GR_ROWS][GR_CH + 1];
+  __shared__ uint8_t s_dir[GR_ROWS][GR_CH + 4];
+  const int r0 = blockIdx.x * GR_ROWS;
+  const double two_g = 2 * grid_m, g2 = grid_m * grid_m;
+  FixState fs;
+  LabelState ls;
+  fix_init(fs);
+  label_init(ls);
+  double g_cur = gc_na();  // gradient of the next cell to visit, computed one step ahead
+  for (int cb = 0; cb < d.NC; cb += GR_CH) {
+    __syncthreads();  // the previous chunk's tiles have been stored
+    for (int i = threadIdx.x; i < GR_ROWS * (GR_CH + 3); i += GR_THREADS) {
+      const int rr = i / (GR_CH + 3), k = i - rr * (GR_CH + 3);
+      const int r = r0 + rr;
+      s_e[rr][k] = r < d.NR ? gc_elev_lin(elev, d, r, cb - 1 + k) : gc_na();
+    }
+    __syncthreads();
+    if (threadIdx.x < GR_ROWS && r0 + (int)threadIdx.x < d.NR) {
+      const int rr = threadIdx.x;
+      const double* e = s_e[rr];  // e[k] = column cb - 1 + k
+      if (cb == 0) {
+        double cr;
+        gc_row_cell(e[1], e[0], e[2], two_g, g2, g_cur, cr);
+      }
+      const int nc = min(GR_CH, d.NC - cb);
+      for (int j = 0; j < nc; ++j) {
+        double ge, cr, g_nxt = gc_na(), cr_nxt;
+        gc_row_cell(e[j + 1], e[j], e[j + 2], two_g, g2, ge, cr);  // ge == g_cur: recomputed for scr
+        if (cb + j + 1 < d.NC) gc_row_cell(e[j + 2], e[j + 1], e[j + 3], two_g, g2, g_nxt, cr_nxt);
+        const double v = fix_step(fs, g_cur, g_nxt);
+        double ar = fabs(ge);
+        if (ar == 0) ar = GC_TINY;
+        int hn, hc;
+        label_step(ls, v, e[j + 1] != e[j + 1], hn, hc);
+        s_ge[rr][j] = v;
+        s_gr[rr][j] = ar;
+        s_cr[rr][j] = cr;
+        s_dir[rr][j] = v != v ? 0 : (v > 0 ? 2 : 4);
+        s_n[rr][j] = hn;
+        s_cell[rr][j] = hc;
+        g_cur = g_nxt;
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < GR_ROWS * GR_CH; i += GR_THREADS) {
+      const int rr = i / GR_CH, j = i - rr * GR_CH;
+      const int r = r0 + rr, c = cb + j;
+      if (r >= d.NR || c >= d.NC) continue;
+      const size_t o = (size_t)r * d.pitch + c;
+      P.sgre[o] = s_ge[rr][j];
+      P.sgr[o] = s_gr[rr][j];
+      P.scr[o] = s_cr[rr][j];
+      P.rdir[o] = s_dir[rr][j];
+      P.rn[o] = s_n[rr][j];
+      P.rcell[o] = s_cell[rr][j];
+    }
+  }
+}
+
+// ---- columns ---------------------------------------------------------------------------------------
+constexpr int GC_THREADS = 32;
+constexpr int GC_PF = 8;  // rows fetched ahead of the sweep
+
+__device__ __forceinline__ void gc_col_cell(double e5, double n2, double n8, double two_g, double g2, double& gn, double& cc) {
+  if (n2 != n2) n2 = e5;
+  if (n8 != n8) n8 = e5;
+  gn = (n2 - n8) / two_g;
+  cc = (2 * e5 - n2 - n8) / g2;
+}
+
+// south -> north: the previous cell of the sign rule is n2 (south), the fallback n8 (north)
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_a(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
+  const int c = blockIdx.x * GC_THREADS + threadIdx.x;
+  if (c >= d.NC) return;
+  const double two_g = 2 * grid_m, g2 = grid_m * grid_m;
+  auto E = [&](int r) { return (r < 0 || r >= d.NR) ? gc_na() : __ldg(elev + (size_t)r * d.pitch + c); };
+  FixState fs;
+  fix_init(fs);
+  // window while visiting row r: s = elev(r+1), m = elev(r), n1 = elev(r-1), n2v = elev(r-2)
+  double s = gc_na(), m = E(d.NR - 1), n1 = E(d.NR - 2);
+  double buf[GC_PF];
+#pragma unroll
+  for (int k = 0; k < GC_PF; ++k) buf[k] = E(d.NR - 3 - k);
+  for (int rt = d.NR - 1; rt >= 0; rt -= GC_PF) {
+    double nb[GC_PF];
+#pragma unroll
+    for (int k = 0; k < GC_PF; ++k) nb[k] = E(rt - 2 - GC_PF - k);  // the group after this one
+#pragma unroll
+    for (int k = 0; k < GC_PF; ++k) {
+      const int r = rt - k;
+      if (r < 0) break;
+      const double n2v = buf[k];
+      double gn, cc, g_nxt, cc_nxt;
+      gc_col_cell(m, s, n1, two_g, g2, gn, cc);
+      gc_col_cell(n1, m, n2v, two_g, g2, g_nxt, cc_nxt);
+      if (r == 0) g_nxt = gc_na();
+      const double v = fix_step(fs, gn, g_nxt);
+      double ac = fabs(gn);
+      if (ac == 0) ac = GC_TINY;
+      const size_t o = (size_t)r * d.pitch + c;
+      P.sgcn[o] = v;
+      P.sgc[o] = ac;
+      P.scc[o] = cc;
+      s = m; m = n1; n1 = n2v;
+    }
+#pragma unroll
+    for (int k = 0; k < GC_PF; ++k) buf[k] = nb[k];
+  }
+}
+
+// north -> south (the data order inside group_by(col))
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_b(const double* __restrict__ elev, GridDims d, GcPtrs P) {
+  const int c = blockIdx.x * GC_THREADS + threadIdx.x;
+  if (c >= d.NC) return;
+  LabelState ls;
+  label_init(ls);
+  double ve[GC_PF], vg[GC_PF];
+#pragma unroll
+  for (int k = 0; k < GC_PF; ++k) {
+    const bool ok = k < d.NR;
+    ve[k] = ok ? __ldg(elev + (size_t)k * d.pitch + c) : gc_na();
+    vg[k] = ok ? P.sgcn[(size_t)k * d.pitch + c] : gc_na();
+  }
+  for (int rt = 0; rt < d.NR; rt += GC_PF) {
+    double ne[GC_PF], ng[GC_PF];
+#pragma unroll
+    for (int k = 0; k < GC_PF; ++k) {
+      const int r = rt + GC_PF + k;
+      const bool ok = r < d.NR;
+      ne[k] = ok ? __ldg(elev + (size_t)r * d.pitch + c) : gc_na();
+      ng[k] = ok ? P.sgcn[(size_t)r * d.pitch + c] : gc_na();
+    }
+#pragma unroll
+    for (int k = 0; k < GC_PF; ++k) {
+      const int r = rt + k;
+      if (r >= d.NR) break;
+      int hn, hc;
+      label_step(ls, vg[k], ve[k] != ve[k], hn, hc);
+      const size_t o = (size_t)r * d.pitch + c;
+      P.cdir[o] = vg[k] != vg[k] ? 0 : (vg[k] > 0 ? 1 : 3);
+      P.cn[o] = hn;
+      P.ccell[o] = hc;
+    }
+#pragma unroll
+    for (int k = 0; k < GC_PF; ++k) { ve[k] = ne[k]; vg[k] = ng[k]; }
+  }
+}
+
+}  // namespace
+
+int run_slope_gc(litap_grid* g, double grid_m) {
+  Ctx& c = ctx();
+  const GridDims d = g->d;
+  cudaStream_t st = c.stream;
+  for (int k = 0; k < 6; ++k) if (!g->gc_f64[k]) g->gc_f64[k] = grid_alloc_array<double>(d, -1);
+  for (int k = 0; k < 2; ++k) if (!g->gc_u8[k]) g->gc_u8[k] = grid_alloc_array<uint8_t>(d, -1);
+  for (int k = 0; k < 4; ++k) if (!g->gc_i32[k]) g->gc_i32[k] = grid_alloc_array<int32_t>(d, -1);
+  for (int k = 0; k < 6; ++k) if (!g->gc_f64[k]) return set_error(LITAP_ENOMEM, "device allocation failed (slope_gc outputs)");
+  for (int k = 0; k < 2; ++k) if (!g->gc_u8[k]) return set_error(LITAP_ENOMEM, "device allocation failed (slope_gc outputs)");
+  for (int k = 0; k < 4; ++k) if (!g->gc_i32[k]) return set_error(LITAP_ENOMEM, "device allocation failed (slope_gc outputs)");
+  GcPtrs P;
+  P.sgre = g->gc_f64[0]; P.sgr = g->gc_f64[1]; P.sgcn = g->gc_f64[2]; P.sgc = g->gc_f64[3];
+  P.scr = g->gc_f64[4]; P.scc = g->gc_f64[5];
+  P.rdir = g->gc_u8[0]; P.cdir = g->gc_u8[1];
+  P.rn = g->gc_i32[0]; P.rcell = g->gc_i32[1]; P.cn = g->gc_i32[2]; P.ccell = g->gc_i32[3];
+  KERNEL("k_gc_rows", k_gc_rows<<<(d.NR + GR_ROWS - 1) / GR_ROWS, GR_THREADS, 0, st>>>(g->elev, d, grid_m, P));
+  const int cblk = (d.NC + GC_THREADS - 1) / GC_THREADS;
+  KERNEL("k_gc_cols_a", k_gc_cols_a<<<cblk, GC_THREADS, 0, st>>>(g->elev, d, grid_m, P));
+  KERNEL("k_gc_cols_b", k_gc_cols_b<<<cblk, GC_THREADS, 0, st>>>(g->elev, d, P));
+  return LITAP_OK;
+}

@@ -52,6 +52,10 @@ struct litap_grid {
   uint8_t* ridge = nullptr;
   double* form[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   double* weti[4] = {nullptr, nullptr, nullptr, nullptr};
+  // slope_gc: sgre, sgr, sgcn, sgc, scr, scc / hill_r_dir, hill_c_dir / hill_r_n, hill_r_cell, hill_c_n, hill_c_cell
+  double* gc_f64[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  uint8_t* gc_u8[2] = {nullptr, nullptr};
+  int32_t* gc_i32[4] = {nullptr, nullptr, nullptr, nullptr};
   int64_t npits = 0;
   bool have_ddir = false, have_shed = false;
   // row-band geometry: rows [own_lo, own_hi) are this grid's own cells; row 0 / NR-1 are the NA ring
@@ -153,5 +157,6 @@ int run_form(litap_grid* g, double grid_m);            // form.cu
 int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi);  // form.cu: a row range (pipelined upload)
 void form_forget_trig();                               // form.cu (pool-owned table dropped at shutdown)
 int run_weti(litap_grid* g, double grid_m);            // weti.cu
+int run_slope_gc(litap_grid* g, double grid_m);        // gc.cu
 int run_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille);  // synth.cu
 int run_checksum(const void* arr, int elem_size, const GridDims& d, uint64_t* out);                     // synth.cu
