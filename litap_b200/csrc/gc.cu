@@ -15,8 +15,8 @@
 // A line is inherently sequential in this formulation; all lines run in parallel:
 //   k_gc_rows   a block owns 16 rows and walks along them in 32-column chunks staged through shared
 //               memory (coalesced loads / stores by the whole block, one lane per row in between)
-//   k_gc_cols_a one thread per column, south -> north: sgcn (signs fixed), sgc, scc
-//   k_gc_cols_b one thread per column, north -> south: hill_c_dir / n / cell
+//   k_gc_cols_stencil / _fix / _label  a plain stencil, then one thread per column south -> north (zero signs)
+//               and north -> south (hill_c_dir / n / cell)
 // The NA ring of add_buffer() is required (like everywhere on this path): it is what makes the
 // reference's linear seqno +- 1 addressing row-local.
 #include "cellmath.h"
@@ -83,9 +83,9 @@ __device__ __forceinline__ void label_step(LabelState& s, double v, bool elev_na
 }
 
 // ---- rows ------------------------------------------------------------------------------------------
-constexpr int GR_ROWS = 16;     // rows per block = lanes of the sweep
+constexpr int GR_ROWS = 32;     // rows per block = lanes of the sweep (one full warp)
 constexpr int GR_CH = 32;       // columns per chunk
-constexpr int GR_THREADS = 128;
+constexpr int GR_THREADS = 256;
 
 // elevation of linear neighbour seqno - 1 / seqno + 1 exactly as nb_values addresses it (no wrap check)
 __device__ __forceinline__ double gc_elev_lin(const double* __restrict__ elev, const GridDims& d, int r, int c) {
@@ -103,46 +103,51 @@ __device__ __forceinline__ void gc_row_cell(double e5, double n4, double n6, dou
 }
 
 __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
-  __shared__ double s_e[GR_ROWS][GR_CH + 5];     // columns cb-1 .. cb+GR_CH+2 of the block's rows
-  __shared__ double s_ge[GR_ROWS][GR_CH + 1], s_gr[GR_ROWS][GR_CH + 1], s_cr[GR_ROWS][GR_CH + 1];
+  __shared__ double s_e[GR_ROWS][GR_CH + 5];     // columns cb-1 .. cb+GR_CH+1 of the block's rows
+  __shared__ double s_ge[GR_ROWS][GR_CH + 3];    // gradient of columns cb .. cb+GR_CH (one ahead); then the fixed values
   __shared__ int s_n[GR_ROWS][GR_CH + 1], s_cell[GR_ROWS][GR_CH + 1];
-  __shared__ uint8_t s_dir[GR_ROWS][GR_CH + 4];
   const int r0 = blockIdx.x * GR_ROWS;
   const double two_g = 2 * grid_m, g2 = grid_m * grid_m;
   FixState fs;
   LabelState ls;
   fix_init(fs);
   label_init(ls);
-  double g_cur = gc_na();  // gradient of the next cell to visit, computed one step ahead
   for (int cb = 0; cb < d.NC; cb += GR_CH) {
-    __syncthreads();  // the previous chunk's tiles have been stored
+    __syncthreads();  // the previous chunk's tiles have been consumed
     for (int i = threadIdx.x; i < GR_ROWS * (GR_CH + 3); i += GR_THREADS) {
       const int rr = i / (GR_CH + 3), k = i - rr * (GR_CH + 3);
       const int r = r0 + rr;
       s_e[rr][k] = r < d.NR ? gc_elev_lin(elev, d, r, cb - 1 + k) : gc_na();
     }
     __syncthreads();
-    if (threadIdx.x < GR_ROWS && r0 + (int)threadIdx.x < d.NR) {
-      const int rr = threadIdx.x;
-      const double* e = s_e[rr];  // e[k] = column cb - 1 + k
-      if (cb == 0) {
-        double cr;
-        gc_row_cell(e[1], e[0], e[2], two_g, g2, g_cur, cr);
-      }
-      const int nc = min(GR_CH, d.NC - cb);
-      for (int j = 0; j < nc; ++j) {
-        double ge, cr, g_nxt = gc_na(), cr_nxt;
-        gc_row_cell(e[j + 1], e[j], e[j + 2], two_g, g2, ge, cr);  // ge == g_cur: recomputed for scr
-        if (cb + j + 1 < d.NC) gc_row_cell(e[j + 2], e[j + 1], e[j + 3], two_g, g2, g_nxt, cr_nxt);
-        const double v = fix_step(fs, g_cur, g_nxt);
+    // data-parallel part, all threads: gradient (one column ahead for the sign rule), magnitude, curvature
+    for (int i = threadIdx.x; i < GR_ROWS * (GR_CH + 1); i += GR_THREADS) {
+      const int rr = i / (GR_CH + 1), j = i - rr * (GR_CH + 1);
+      const int r = r0 + rr, c = cb + j;
+      double ge = gc_na(), cr = gc_na();
+      if (r < d.NR && c < d.NC) gc_row_cell(s_e[rr][j + 1], s_e[rr][j], s_e[rr][j + 2], two_g, g2, ge, cr);
+      s_ge[rr][j] = ge;
+      if (j < GR_CH && r < d.NR && c < d.NC) {
+        const size_t o = (size_t)r * d.pitch + c;
         double ar = fabs(ge);
         if (ar == 0) ar = GC_TINY;
+        P.sgr[o] = ar;
+        P.scr[o] = cr;
+      }
+    }
+    __syncthreads();
+    // sequential part, one lane per row: the two sweeps over the chunk
+    if (threadIdx.x < GR_ROWS && r0 + (int)threadIdx.x < d.NR) {
+      const int rr = threadIdx.x;
+      const int nc = min(GR_CH, d.NC - cb);
+      double g_cur = s_ge[rr][0];
+      for (int j = 0; j < nc; ++j) {
+        const double g_nxt = s_ge[rr][j + 1];   // NA past the last column
+        const double v = fix_step(fs, g_cur, g_nxt);
         int hn, hc;
-        label_step(ls, v, e[j + 1] != e[j + 1], hn, hc);
+        const double e5 = s_e[rr][j + 1];
+        label_step(ls, v, e5 != e5, hn, hc);
         s_ge[rr][j] = v;
-        s_gr[rr][j] = ar;
-        s_cr[rr][j] = cr;
-        s_dir[rr][j] = v != v ? 0 : (v > 0 ? 2 : 4);
         s_n[rr][j] = hn;
         s_cell[rr][j] = hc;
         g_cur = g_nxt;
@@ -154,10 +159,9 @@ __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict
       const int r = r0 + rr, c = cb + j;
       if (r >= d.NR || c >= d.NC) continue;
       const size_t o = (size_t)r * d.pitch + c;
-      P.sgre[o] = s_ge[rr][j];
-      P.sgr[o] = s_gr[rr][j];
-      P.scr[o] = s_cr[rr][j];
-      P.rdir[o] = s_dir[rr][j];
+      const double v = s_ge[rr][j];
+      P.sgre[o] = v;
+      P.rdir[o] = v != v ? 0 : (v > 0 ? 2 : 4);
       P.rn[o] = s_n[rr][j];
       P.rcell[o] = s_cell[rr][j];
     }
@@ -165,8 +169,14 @@ __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict
 }
 
 // ---- columns ---------------------------------------------------------------------------------------
+// k_gc_cols_stencil  data-parallel: sgcn as computed, sgc, scc; hill_c_dir temporarily holds "elev is NA"
+// k_gc_cols_fix      one thread per column, south -> north: zero gradients take their sign (only those cells
+//                    are rewritten)
+// k_gc_cols_label    one thread per column, north -> south: hill_c_dir / n / cell
+// The sweeps read 8-9 bytes per cell and keep GC_PF x 2 rows in flight per thread: with one thread per
+// column there are only NC/32 warps, so latency has to be covered inside the thread.
 constexpr int GC_THREADS = 32;
-constexpr int GC_PF = 8;  // rows fetched ahead of the sweep
+constexpr int GC_PF = 16;  // rows per group; two groups are in flight
 
 __device__ __forceinline__ void gc_col_cell(double e5, double n2, double n8, double two_g, double g2, double& gn, double& cc) {
   if (n2 != n2) n2 = e5;
@@ -175,81 +185,86 @@ __device__ __forceinline__ void gc_col_cell(double e5, double n2, double n8, dou
   cc = (2 * e5 - n2 - n8) / g2;
 }
 
-// south -> north: the previous cell of the sign rule is n2 (south), the fallback n8 (north)
-__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_a(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
+__global__ void __launch_bounds__(256) k_gc_cols_stencil(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  const int r = blockIdx.y;
+  if (c >= d.NC) return;
+  const size_t o = (size_t)r * d.pitch + c;
+  const double e5 = __ldg(elev + o);
+  const double n2 = r + 1 < d.NR ? __ldg(elev + o + d.pitch) : gc_na();   // seqno + max_cols past the end: NA
+  const double n8 = r > 0 ? __ldg(elev + o - d.pitch) : gc_na();
+  double gn, cc;
+  gc_col_cell(e5, n2, n8, 2 * grid_m, grid_m * grid_m, gn, cc);
+  double ac = fabs(gn);
+  if (ac == 0) ac = GC_TINY;
+  P.sgcn[o] = gn;
+  P.sgc[o] = ac;
+  P.scc[o] = cc;
+  P.cdir[o] = e5 != e5 ? 0x80 : 0;
+}
+
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_fix(GridDims d, GcPtrs P) {
   const int c = blockIdx.x * GC_THREADS + threadIdx.x;
   if (c >= d.NC) return;
-  const double two_g = 2 * grid_m, g2 = grid_m * grid_m;
-  auto E = [&](int r) { return (r < 0 || r >= d.NR) ? gc_na() : __ldg(elev + (size_t)r * d.pitch + c); };
+  double* g = P.sgcn + c;
+  auto G = [&](int r) { return (r < 0 || r >= d.NR) ? gc_na() : g[(size_t)r * d.pitch]; };
   FixState fs;
   fix_init(fs);
-  // window while visiting row r: s = elev(r+1), m = elev(r), n1 = elev(r-1), n2v = elev(r-2)
-  double s = gc_na(), m = E(d.NR - 1), n1 = E(d.NR - 2);
-  double buf[GC_PF];
+  // rows are visited from NR-1 down to 0; a[k] = row rt-k, b[k] = row rt-GC_PF-k, then one more group is fetched
+  double a[GC_PF], b[GC_PF];
 #pragma unroll
-  for (int k = 0; k < GC_PF; ++k) buf[k] = E(d.NR - 3 - k);
+  for (int k = 0; k < GC_PF; ++k) { a[k] = G(d.NR - 1 - k); b[k] = G(d.NR - 1 - GC_PF - k); }
   for (int rt = d.NR - 1; rt >= 0; rt -= GC_PF) {
-    double nb[GC_PF];
+    double n[GC_PF];
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) nb[k] = E(rt - 2 - GC_PF - k);  // the group after this one
+    for (int k = 0; k < GC_PF; ++k) n[k] = G(rt - 2 * GC_PF - k);
 #pragma unroll
     for (int k = 0; k < GC_PF; ++k) {
       const int r = rt - k;
-      if (r < 0) break;
-      const double n2v = buf[k];
-      double gn, cc, g_nxt, cc_nxt;
-      gc_col_cell(m, s, n1, two_g, g2, gn, cc);
-      gc_col_cell(n1, m, n2v, two_g, g2, g_nxt, cc_nxt);
-      if (r == 0) g_nxt = gc_na();
-      const double v = fix_step(fs, gn, g_nxt);
-      double ac = fabs(gn);
-      if (ac == 0) ac = GC_TINY;
-      const size_t o = (size_t)r * d.pitch + c;
-      P.sgcn[o] = v;
-      P.sgc[o] = ac;
-      P.scc[o] = cc;
-      s = m; m = n1; n1 = n2v;
+      if (r >= 0) {
+        const double cur = a[k], nxt = k + 1 < GC_PF ? a[k + 1] : b[0];  // (rows below 0 read as NA)
+        const double v = fix_step(fs, cur, nxt);
+        if (cur == 0.0) g[(size_t)r * d.pitch] = v;
+      }
     }
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) buf[k] = nb[k];
+    for (int k = 0; k < GC_PF; ++k) { a[k] = b[k]; b[k] = n[k]; }
   }
 }
 
-// north -> south (the data order inside group_by(col))
-__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_b(const double* __restrict__ elev, GridDims d, GcPtrs P) {
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_label(GridDims d, GcPtrs P) {
   const int c = blockIdx.x * GC_THREADS + threadIdx.x;
   if (c >= d.NC) return;
+  const double* g = P.sgcn + c;
+  uint8_t* dir = P.cdir + c;
+  auto G = [&](int r) { return r < d.NR ? g[(size_t)r * d.pitch] : gc_na(); };
+  auto D = [&](int r) { return r < d.NR ? dir[(size_t)r * d.pitch] : (uint8_t)0; };
   LabelState ls;
   label_init(ls);
-  double ve[GC_PF], vg[GC_PF];
+  double ga[GC_PF], gb[GC_PF];
+  uint8_t da[GC_PF], db[GC_PF];
 #pragma unroll
-  for (int k = 0; k < GC_PF; ++k) {
-    const bool ok = k < d.NR;
-    ve[k] = ok ? __ldg(elev + (size_t)k * d.pitch + c) : gc_na();
-    vg[k] = ok ? P.sgcn[(size_t)k * d.pitch + c] : gc_na();
-  }
+  for (int k = 0; k < GC_PF; ++k) { ga[k] = G(k); da[k] = D(k); gb[k] = G(GC_PF + k); db[k] = D(GC_PF + k); }
   for (int rt = 0; rt < d.NR; rt += GC_PF) {
-    double ne[GC_PF], ng[GC_PF];
+    double gn[GC_PF];
+    uint8_t dn[GC_PF];
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) {
-      const int r = rt + GC_PF + k;
-      const bool ok = r < d.NR;
-      ne[k] = ok ? __ldg(elev + (size_t)r * d.pitch + c) : gc_na();
-      ng[k] = ok ? P.sgcn[(size_t)r * d.pitch + c] : gc_na();
-    }
+    for (int k = 0; k < GC_PF; ++k) { gn[k] = G(rt + 2 * GC_PF + k); dn[k] = D(rt + 2 * GC_PF + k); }
 #pragma unroll
     for (int k = 0; k < GC_PF; ++k) {
       const int r = rt + k;
-      if (r >= d.NR) break;
-      int hn, hc;
-      label_step(ls, vg[k], ve[k] != ve[k], hn, hc);
-      const size_t o = (size_t)r * d.pitch + c;
-      P.cdir[o] = vg[k] != vg[k] ? 0 : (vg[k] > 0 ? 1 : 3);
-      P.cn[o] = hn;
-      P.ccell[o] = hc;
+      if (r < d.NR) {
+        int hn, hc;
+        const double v = ga[k];
+        label_step(ls, v, (da[k] & 0x80) != 0, hn, hc);
+        const size_t o = (size_t)r * d.pitch + c;
+        dir[(size_t)r * d.pitch] = v != v ? 0 : (v > 0 ? 1 : 3);
+        P.cn[o] = hn;
+        P.ccell[o] = hc;
+      }
     }
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) { ve[k] = ne[k]; vg[k] = ng[k]; }
+    for (int k = 0; k < GC_PF; ++k) { ga[k] = gb[k]; gb[k] = gn[k]; da[k] = db[k]; db[k] = dn[k]; }
   }
 }
 
@@ -272,7 +287,8 @@ int run_slope_gc(litap_grid* g, double grid_m) {
   P.rn = g->gc_i32[0]; P.rcell = g->gc_i32[1]; P.cn = g->gc_i32[2]; P.ccell = g->gc_i32[3];
   KERNEL("k_gc_rows", k_gc_rows<<<(d.NR + GR_ROWS - 1) / GR_ROWS, GR_THREADS, 0, st>>>(g->elev, d, grid_m, P));
   const int cblk = (d.NC + GC_THREADS - 1) / GC_THREADS;
-  KERNEL("k_gc_cols_a", k_gc_cols_a<<<cblk, GC_THREADS, 0, st>>>(g->elev, d, grid_m, P));
-  KERNEL("k_gc_cols_b", k_gc_cols_b<<<cblk, GC_THREADS, 0, st>>>(g->elev, d, P));
+  KERNEL("k_gc_cols_stencil", k_gc_cols_stencil<<<dim3((d.NC + 255) / 256, d.NR), 256, 0, st>>>(g->elev, d, grid_m, P));
+  KERNEL("k_gc_cols_fix", k_gc_cols_fix<<<cblk, GC_THREADS, 0, st>>>(d, P));
+  KERNEL("k_gc_cols_label", k_gc_cols_label<<<cblk, GC_THREADS, 0, st>>>(d, P));
   return LITAP_OK;
 }
