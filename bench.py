@@ -297,6 +297,16 @@ def run_ours(a):
                "api": "litap_flow_form (C ABI, pinned host buffers)"}
         del pinned, host_in
 
+    # ---- slope_gc (not part of the composite metric), reported beside it
+    gc = None
+    if world == 1 and not a.no_weti:
+        g.slope_gc(GRID_M)
+        g.slope_gc(GRID_M)
+        tg = lb.timings()
+        # compulsory traffic: elev read once, 6 f64 + 2 u8 + 4 i32 outputs written once = 74 B/cell
+        gc = {"ms": tg["gc_ms"], "Mcells_per_s": n * n / tg["gc_ms"] / 1e3, "alg_bytes_per_cell": 74,
+              "frac_of_hbm_peak": round(74 * n * n / (tg["gc_ms"] * 1e-3) / 1e9 / peak, 4)}
+
     # ---- CPU baseline (rank 0, N = 1): the oracle on a bounded sample, single thread
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
@@ -320,7 +330,7 @@ def run_ours(a):
                        f"row bands, one per GPU; NCCL halo rows + boundary-graph tables (DESIGN.md section 4)",
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
             "clocks": clocks, "e2e": e2e, "gpu_launches": nl,
-            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti,
+            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti, "slope_gc": gc,
             "cpu_baseline": cpu}) + "\n").encode())
     g.close()
     if world > 1:

@@ -5,11 +5,12 @@
 #   calc_shed4(db, verbose)        replaces R/flow_02_calc_shed.R:10-58   (callers R/flow_mapper.R:180,377)
 #   calc_form(db, grid, verbose)   replaces R/form_01_calc_form.R:4-67    (caller  R/form_mapper.R:103)
 #   calc_weti2(db, grid, verbose)  replaces R/form_02b_calc_weti.R:3-110  (caller  R/form_mapper.R:127)
+#   slope_gc(db, grid)             replaces R/flow_05_slope_gc.R:73-164   (caller  R/flow_mapper.R:307)
 #
 # Every function calls the CUDA library through .Call unconditionally: there is no CPU fallback
 # (an error from the library, e.g. "no CUDA device", surfaces as an R error).  flow_mapper() and
 # form_mapper() keep their signatures and their output column layout; pit removal (flow_03/04),
-# slope_gc, relief and the I/O stay the reference's R code.
+# relief and the I/O stay the reference's R code.
 #
 # `db` is the reference's buffered tibble: one row per cell of the (nrow+2) x (ncol+2) grid,
 # sorted by seqno (R/LITAP_load.R:273-332).
@@ -64,6 +65,14 @@ calc_weti2 <- function(db, grid, verbose = FALSE) {
   db$qarea2 <- r$qarea2
   db$qweti1 <- r$qweti1
   db$qweti2 <- r$qweti2
+  db
+}
+
+slope_gc <- function(db, grid = 1) {
+  if (!"buffer" %in% names(db)) db <- add_buffer(db)   # as the reference does (R/flow_05_slope_gc.R:75)
+  d <- litap_dims(db)
+  r <- .Call("litap_R_slope_gc", as.double(db$elev), d[1], d[2], as.double(grid))
+  for (n in names(r)) db[[n]] <- r[[n]]                # same twelve columns, same order as the reference appends them
   db
 }
 

@@ -146,6 +146,39 @@ SEXP litap_R_weti(SEXP elev, SEXP ddir, SEXP upslope, SEXP nrow, SEXP ncol, SEXP
   return out;
 }
 
+/* slope_gc(db, grid): the six gradients / curvatures as doubles, hill_*_dir as doubles (2/4, 1/3),
+ * hill_*_n / hill_*_cell as integers; NA where the library reports 0 / NaN */
+SEXP litap_R_slope_gc(SEXP elev, SEXP nrow, SEXP ncol, SEXP grid) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n) Rf_error("litap_R_slope_gc: elev must be double with nrow*ncol entries");
+  const char* nm[12] = {"sgre", "sgr", "sgcn", "sgc", "scr", "scc", "hill_r_dir", "hill_c_dir",
+                        "hill_r_n", "hill_r_cell", "hill_c_n", "hill_c_cell"};
+  SEXP out = PROTECT(named_list(12, nm));
+  double* f[8];
+  int* iv[4];
+  for (int k = 0; k < 8; ++k) {
+    SEXP v = Rf_allocVector(REALSXP, n);
+    SET_VECTOR_ELT(out, k, v);
+    f[k] = REAL(v);
+  }
+  for (int k = 0; k < 4; ++k) {
+    SEXP v = Rf_allocVector(INTSXP, n);
+    SET_VECTOR_ELT(out, 8 + k, v);
+    iv[k] = INTEGER(v);
+  }
+  uint8_t* rd = (uint8_t*)R_alloc((size_t)n, 1);
+  uint8_t* cd = (uint8_t*)R_alloc((size_t)n, 1);
+  fail_if(litap_slope_gc(REAL(elev), NR, NC, Rf_asReal(grid), f[0], f[1], f[2], f[3], f[4], f[5], rd, cd,
+                         (int32_t*)iv[0], (int32_t*)iv[1], (int32_t*)iv[2], (int32_t*)iv[3]), "slope_gc");
+  for (R_xlen_t i = 0; i < n; ++i) {
+    f[6][i] = rd[i] ? (double)rd[i] : NA_REAL;
+    f[7][i] = cd[i] ? (double)cd[i] : NA_REAL;
+    for (int k = 0; k < 4; ++k) if (iv[k][i] == 0) iv[k][i] = NA_INTEGER;
+  }
+  UNPROTECT(1);
+  return out;
+}
+
 SEXP litap_R_init(SEXP device) {
   fail_if(litap_init(Rf_asInteger(device)), "litap_init");
   return Rf_mkString(litap_version());
@@ -170,6 +203,7 @@ SEXP litap_R_timings(void) {
 static const R_CallMethodDef call_methods[] = {
     {"litap_R_ddir", (DL_FUNC)&litap_R_ddir, 4},     {"litap_R_shed", (DL_FUNC)&litap_R_shed, 4},
     {"litap_R_form", (DL_FUNC)&litap_R_form, 4},     {"litap_R_weti", (DL_FUNC)&litap_R_weti, 6},
+    {"litap_R_slope_gc", (DL_FUNC)&litap_R_slope_gc, 4},
     {"litap_R_init", (DL_FUNC)&litap_R_init, 1},     {"litap_R_shutdown", (DL_FUNC)&litap_R_shutdown, 0},
     {"litap_R_timings", (DL_FUNC)&litap_R_timings, 0}, {NULL, NULL, 0}};
 
