@@ -125,6 +125,41 @@ def test_form_fast_path_is_bit_identical_where_it_decides(cellmath, kw, grid):
     assert out[0] > 0.9 * e.size
 
 
+@pytest.mark.parametrize("kw,grid", [({}, 5.0), ({"quant": 0.0}, 0.5), ({"quant": 100.0, "na_permille": 10}, 1.0),
+                                     ({"seed": 4, "quant": 10.0}, 30.0)])
+def test_form_quick_path_is_bit_identical_where_it_decides(cellmath, kw, grid):
+    """The quick path k_form runs on every cell (cellmath.h form_cell_quick: table arctangents, second
+    differences, 20-bit seeds + Newton) either leaves a window in doubt or returns exactly the bits of the
+    reference expression tree; on terrain it decides all but a fraction of a percent of the valid windows."""
+    i64 = np.ctypeslib.ndpointer(np.int64, flags="C")
+    cellmath.host_form_quick_check.argtypes = [np.ctypeslib.ndpointer(np.float64, flags="C"), C.c_longlong,
+                                               C.c_longlong, C.c_double, i64]
+    e = oracle.synth_dem(700, 700, **kw)
+    out = np.zeros(3, np.int64)
+    cellmath.host_form_quick_check(e, e.shape[0], e.shape[1], grid, out)
+    assert out[1] == 0, f"{out[1]} windows differ from the reference tree"
+    assert out[0] > 0.8 * e.size
+    if not kw.get("quant") == 100.0 and not kw.get("quant") == 10.0:   # coarse quantisation: flat windows are never decided
+        assert out[2] < 0.005 * e.size
+
+
+def test_form_quick_path_adversarial_windows(cellmath):
+    """Steep, huge, tiny and planar windows: whatever the quick path decides must be exact."""
+    i64 = np.ctypeslib.ndpointer(np.int64, flags="C")
+    cellmath.host_form_quick_check.argtypes = [np.ctypeslib.ndpointer(np.float64, flags="C"), C.c_longlong,
+                                               C.c_longlong, C.c_double, i64]
+    rng = np.random.default_rng(7)
+    yy, xx = np.mgrid[0:300, 0:300]
+    cases = [(8000 + np.sin(xx / 7.0) * np.cos(yy / 11.0) * 300, 5.0), (600 + rng.random((300, 300)) * 50, 2.0),
+             (1000 + 0.3 * xx + 0.1 * yy + rng.integers(0, 3, xx.shape) * 0.001, 5.0), (1e-3 * rng.random((300, 300)), 10.0),
+             (9e5 + rng.random((300, 300)), 1.0), (600 + np.cumsum(rng.standard_normal((300, 300)) * 0.01, axis=1), 10.0)]
+    for e, grid in cases:
+        e = np.ascontiguousarray(oracle.add_buffer(e))
+        out = np.zeros(3, np.int64)
+        cellmath.host_form_quick_check(e, e.shape[0], e.shape[1], grid, out)
+        assert out[1] == 0
+
+
 def test_ld80_sum_emulation_equals_x87(cellmath):
     """R's sum() (long double accumulator, R/form_02b_calc_weti.R:67) as emulated for the GPU."""
     f64 = np.ctypeslib.ndpointer(np.float64, flags="C")
