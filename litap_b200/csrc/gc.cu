@@ -83,9 +83,9 @@ __device__ __forceinline__ void label_step(LabelState& s, double v, bool elev_na
 }
 
 // ---- rows ------------------------------------------------------------------------------------------
-constexpr int GR_ROWS = 32;     // rows per block = lanes of the sweep (one full warp)
+constexpr int GR_ROWS = 8;      // rows per block = lanes of the sweep; many small blocks per SM overlap their phases
 constexpr int GR_CH = 32;       // columns per chunk
-constexpr int GR_THREADS = 256;
+constexpr int GR_THREADS = 64;
 
 // elevation of linear neighbour seqno - 1 / seqno + 1 exactly as nb_values addresses it (no wrap check)
 __device__ __forceinline__ double gc_elev_lin(const double* __restrict__ elev, const GridDims& d, int r, int c) {
