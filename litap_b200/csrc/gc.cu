@@ -41,17 +41,16 @@ struct FixState {
 };
 __device__ __forceinline__ void fix_init(FixState& s) { s.prev = gc_na(); s.runval = 0; s.in_run = false; }
 // g: this cell's gradient as computed; nxt: the next cell's (NA past the end).  Returns the fixed value.
+// Written with selects only: the lanes of a warp are in different states all the time, branches would
+// serialise them and sit on the critical path of the sweep.
 __device__ __forceinline__ double fix_step(FixState& s, double g, double nxt) {
-  double out = g;
-  if (g == 0.0) {
-    if (!s.in_run) {
-      if (s.prev == s.prev) s.runval = s.prev > 0 ? GC_TINY : -GC_TINY;         // 0.00001 * sign(previous)
-      else if (nxt == 0.0) s.runval = GC_TINY;                                  // never resolved: positive
-      else s.runval = nxt != nxt ? gc_na() : (nxt > 0 ? GC_TINY : -GC_TINY);    // single cell: 0.00001 * sign(next)
-      s.in_run = true;
-    }
-    out = s.runval;
-  } else s.in_run = false;
+  const bool z = g == 0.0;
+  const double rv_prev = s.prev > 0 ? GC_TINY : -GC_TINY;                        // 0.00001 * sign(previous)
+  const double rv_next = nxt != nxt ? gc_na() : (nxt > 0 ? GC_TINY : -GC_TINY);  // single cell: 0.00001 * sign(next)
+  const double rv_start = s.prev == s.prev ? rv_prev : (nxt == 0.0 ? GC_TINY : rv_next);  // never resolved: positive
+  s.runval = (z && !s.in_run) ? rv_start : s.runval;
+  const double out = z ? s.runval : g;
+  s.in_run = z;
   s.prev = out;
   return out;
 }
@@ -64,20 +63,21 @@ __device__ __forceinline__ void label_init(LabelState& s) {
   s.cum = s.dense = s.last_val = s.cnt = s.na_cnt = 0;
   s.lag_na = true; s.lag_pos = false; s.poisoned = false; s.have_last = false;
 }
-// v: fixed gradient of the cell (never 0; NaN = NA), elev_na: the cell has no elevation
+// v: fixed gradient of the cell (never 0; NaN = NA), elev_na: the cell has no elevation (selects only, see fix_step)
 __device__ __forceinline__ void label_step(LabelState& s, double v, bool elev_na, int& n_out, int& cell_out) {
   const bool s_na = v != v, pos = v > 0;
-  if (!s.lag_na && s_na) s.poisoned = true;                       // (NA | FALSE) = NA: cumsum is NA from here on
-  else if (!s.poisoned) s.cum += (s.lag_na || pos != s.lag_pos) ? 1 : 0;
-  if (!elev_na && !s.poisoned) {
-    if (!s.have_last || s.cum != s.last_val) { ++s.dense; s.last_val = s.cum; s.have_last = true; s.cnt = 0; }
-    n_out = s.dense;
-    cell_out = ++s.cnt;
-  } else {
-    ++s.na_cnt;                 // NA is one more group of the line
-    n_out = 0;
-    cell_out = elev_na ? 0 : s.na_cnt;
-  }
+  s.poisoned = s.poisoned || (!s.lag_na && s_na);                // (NA | FALSE) = NA: cumsum is NA from here on
+  const int inc = (s.lag_na || pos != s.lag_pos) ? 1 : 0;
+  s.cum += s.poisoned ? 0 : inc;
+  const bool valid = !elev_na && !s.poisoned;
+  const bool newlab = valid && (!s.have_last || s.cum != s.last_val);
+  s.dense += newlab ? 1 : 0;
+  s.last_val = newlab ? s.cum : s.last_val;
+  s.have_last = s.have_last || newlab;
+  s.cnt = (newlab ? 0 : s.cnt) + (valid ? 1 : 0);
+  s.na_cnt += valid ? 0 : 1;                                     // NA is one more group of the line
+  n_out = valid ? s.dense : 0;
+  cell_out = valid ? s.cnt : (elev_na ? 0 : s.na_cnt);
   s.lag_na = s_na;
   s.lag_pos = pos;
 }
@@ -102,9 +102,12 @@ __device__ __forceinline__ void gc_row_cell(double e5, double n4, double n6, dou
   cr = (2 * e5 - n4 - n6) / g2;
 }
 
+constexpr int GR_LD = (GR_ROWS * (GR_CH + 3) + GR_THREADS - 1) / GR_THREADS;  // elevations a thread stages per chunk
+
 __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
   __shared__ double s_e[GR_ROWS][GR_CH + 5];     // columns cb-1 .. cb+GR_CH+1 of the block's rows
-  __shared__ double s_ge[GR_ROWS][GR_CH + 3];    // gradient of columns cb .. cb+GR_CH (one ahead); then the fixed values
+  __shared__ double s_ge[GR_ROWS][GR_CH + 3];    // gradient of columns cb .. cb+GR_CH (one ahead of the sign rule)
+  __shared__ double s_v[GR_ROWS][GR_CH + 1];     // gradient with its zero signs settled
   __shared__ int s_n[GR_ROWS][GR_CH + 1], s_cell[GR_ROWS][GR_CH + 1];
   const int r0 = blockIdx.x * GR_ROWS;
   const double two_g = 2 * grid_m, g2 = grid_m * grid_m;
@@ -112,14 +115,28 @@ __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict
   LabelState ls;
   fix_init(fs);
   label_init(ls);
-  for (int cb = 0; cb < d.NC; cb += GR_CH) {
-    __syncthreads();  // the previous chunk's tiles have been consumed
-    for (int i = threadIdx.x; i < GR_ROWS * (GR_CH + 3); i += GR_THREADS) {
+  // the chunk after the current one travels in registers while the current one is worked on
+  double pre[GR_LD];
+  auto fetch = [&](int cb) {
+#pragma unroll
+    for (int q = 0; q < GR_LD; ++q) {
+      const int i = threadIdx.x + q * GR_THREADS;
       const int rr = i / (GR_CH + 3), k = i - rr * (GR_CH + 3);
       const int r = r0 + rr;
-      s_e[rr][k] = r < d.NR ? gc_elev_lin(elev, d, r, cb - 1 + k) : gc_na();
+      pre[q] = (rr < GR_ROWS && r < d.NR && cb < d.NC) ? gc_elev_lin(elev, d, r, cb - 1 + k) : gc_na();
+    }
+  };
+  fetch(0);
+  for (int cb = 0; cb < d.NC; cb += GR_CH) {
+    __syncthreads();  // the previous chunk's tiles have been consumed
+#pragma unroll
+    for (int q = 0; q < GR_LD; ++q) {
+      const int i = threadIdx.x + q * GR_THREADS;
+      const int rr = i / (GR_CH + 3), k = i - rr * (GR_CH + 3);
+      if (rr < GR_ROWS) s_e[rr][k] = pre[q];
     }
     __syncthreads();
+    fetch(cb + GR_CH);
     // data-parallel part, all threads: gradient (one column ahead for the sign rule), magnitude, curvature
     for (int i = threadIdx.x; i < GR_ROWS * (GR_CH + 1); i += GR_THREADS) {
       const int rr = i / (GR_CH + 1), j = i - rr * (GR_CH + 1);
@@ -141,13 +158,14 @@ __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict
       const int rr = threadIdx.x;
       const int nc = min(GR_CH, d.NC - cb);
       double g_cur = s_ge[rr][0];
+#pragma unroll 4
       for (int j = 0; j < nc; ++j) {
         const double g_nxt = s_ge[rr][j + 1];   // NA past the last column
+        const double e5 = s_e[rr][j + 1];
         const double v = fix_step(fs, g_cur, g_nxt);
         int hn, hc;
-        const double e5 = s_e[rr][j + 1];
         label_step(ls, v, e5 != e5, hn, hc);
-        s_ge[rr][j] = v;
+        s_v[rr][j] = v;
         s_n[rr][j] = hn;
         s_cell[rr][j] = hc;
         g_cur = g_nxt;
@@ -159,7 +177,7 @@ __global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict
       const int r = r0 + rr, c = cb + j;
       if (r >= d.NR || c >= d.NC) continue;
       const size_t o = (size_t)r * d.pitch + c;
-      const double v = s_ge[rr][j];
+      const double v = s_v[rr][j];
       P.sgre[o] = v;
       P.rdir[o] = v != v ? 0 : (v > 0 ? 2 : 4);
       P.rn[o] = s_n[rr][j];
