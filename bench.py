@@ -28,6 +28,21 @@ METRIC = "Mcells/s (ddir+shed+upslope+form)"
 ALG_BYTES = {"k_d8": 9, "k_form": 48, "k_shed_local": 9, "k_shed_final": 10}
 
 
+def ncu_traffic(kernel):
+    """(GB, file) of 'traffic = dram read + write' for `kernel` in the latest (by name) profiles/ncu_*.txt (written by
+    profiles/summarize.py from an ncu --set full capture of this bench at 8192 x 8192), else None."""
+    import glob
+    import re
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_*.txt")), reverse=True):  # names sort by round
+        cur = None
+        for line in open(f):
+            if line.startswith("## "):
+                cur = line
+            elif cur and "traffic = dram read + write" in line and re.search(r"\b%s\(" % re.escape(kernel), cur):
+                return float(line.split()[-2]) / 1e3, os.path.relpath(f, ROOT)
+    return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -217,6 +232,11 @@ def run_ours(a):
         avg_ms = prof[dom][1] / prof[dom][0]
         ach = ALG_BYTES[dom] * n * ncols / (avg_ms * 1e-3) / 1e9
         roof.update(achieved=ach, frac=ach / peak, alg_bytes_per_cell=ALG_BYTES[dom], avg_launch_ms=avg_ms)
+    # DRAM bytes of one launch of that kernel from the committed ncu --set full capture (same workload), if any
+    if world == 1 and n == 8192 and ncols == 8192:
+        tr = ncu_traffic(dom)
+        if tr:
+            roof.update(traffic=tr[0], traffic_unit="GB per launch (dram read + write)", traffic_source=tr[1])
     rf_all = {}
     for k, b in ALG_BYTES.items():
         if k in prof:
