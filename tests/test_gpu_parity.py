@@ -147,6 +147,24 @@ def test_synthetic_flow_and_form(nr, nc, kw):
     assert_form_parity(e, 5.0, f"{nr}x{nc}{kw}")
 
 
+@pytest.mark.parametrize("n,kw,grid", [(2048, dict(seed=20261104), 5.0), (1500, dict(seed=1), 1.0),
+                                       (1500, dict(seed=2, quant=100.0), 30.0), (1500, dict(seed=3, na_permille=10), 0.5),
+                                       (1200, dict(seed=5, quant=0.0), 5.0)])
+def test_form_bit_identical_with_oracle(n, kw, grid):
+    """calc_form decides every rounded output exactly (quick path, doubt queue, reference tree): the device
+    result equals the oracle bit for bit, NaN for NaN — stronger than the 1e-5 tolerance of the north star."""
+    e = oracle.synth_dem(n, n, **kw)
+    o = oracle.form(e, grid, nthreads=8)
+    g = lb.DeviceGrid(*e.shape)
+    g.upload_elev(e)
+    g.form(grid)
+    for k in FORM:
+        a = g.download(k)
+        same = (a.view(np.uint64) == o[k].view(np.uint64)) | (np.isnan(a) & np.isnan(o[k]))
+        assert same.all(), f"{k}: {(~same).sum()} values differ, first at {np.argwhere(~same)[:4].tolist()}"
+    g.close()
+
+
 def test_real_terrain_with_na(golden):
     """data/test_dem.rda (184 x 187 buffered, 746 NA cells): no golden outputs, oracle parity."""
     td = golden["dems"]
@@ -189,6 +207,29 @@ def test_fused_composite_matches_separate_calls():
     assert (out["upslope"].astype(np.int64) == o_s["upslope"]).all() and (out["ridge"] == o_s["ridge"]).all()
     t = lb.timings()
     assert t["kernel_launches"] > 5 and t["npits"] == o_s["npits"]
+
+
+@pytest.mark.parametrize("nr,nc,kw", [(2100, 300, dict(seed=6)), (2049, 77, dict(seed=7, na_permille=20)),
+                                      (4133, 129, dict(seed=8, quant=100.0))])
+def test_fused_composite_pipelined_chunks(nr, nc, kw):
+    """litap_flow_form uploads DEMs of >= 2048 buffered rows in 8 row chunks, runs calc_form per chunk (ragged
+    chunk heights, edge replication and the doubt queue across chunk seams) and streams its outputs back on a
+    second stream: every output must equal the oracle / the unchunked device-resident stage bit for bit."""
+    e = oracle.synth_dem(nr, nc, **kw)
+    out = lb.flow_form(e, 5.0)
+    o_d = oracle.ddir(e)
+    o_s = oracle.shed(e, o_d["ddir"])
+    assert (out["ddir"] == o_d["ddir"]).all() and (out["shed"] == o_s["shed"]).all()
+    assert (out["upslope"].astype(np.int64) == o_s["upslope"]).all() and (out["ridge"] == o_s["ridge"]).all()
+    o_f = oracle.form(e, 5.0, nthreads=8)
+    g = lb.DeviceGrid(*e.shape)
+    g.upload_elev(e)
+    g.form(5.0)
+    for k in FORM:
+        a, b, c = out[k], g.download(k), o_f[k]
+        assert eq_na(a.ravel(), b.ravel()).all(), f"{k}: chunked != whole-grid stage"
+        assert eq_na(a.ravel(), c.ravel()).all(), f"{k}: chunked != oracle"
+    g.close()
 
 
 def test_device_resident_synth_and_checksums():
