@@ -178,7 +178,17 @@ def run_ours(a):
         g = lb.DeviceGrid(NR, NC)
         g.synth(seed=SEED, quant=QUANT)
 
+    fused = world == 1 and not a.serial_stages
+
     def step():
+        if fused:
+            g.flow_form(GRID_M)  # one call: calc_form overlaps the flow stages on a second stream
+        else:
+            g.form(GRID_M)
+            g.ddir()
+            g.shed()
+
+    def step_serial():  # the per-kernel profiling pass times every kernel alone on the device
         g.form(GRID_M)
         g.ddir()
         g.shed()
@@ -199,9 +209,12 @@ def run_ours(a):
     nl = 0
     ev0.record(stream)
     for _ in range(a.steps):
-        g.form(GRID_M); nl += lb.timings()["kernel_launches"]
-        g.ddir(); nl += lb.timings()["kernel_launches"]
-        g.shed(); nl += lb.timings()["kernel_launches"]
+        if fused:
+            g.flow_form(GRID_M); nl += lb.timings()["kernel_launches"]
+        else:
+            g.form(GRID_M); nl += lb.timings()["kernel_launches"]
+            g.ddir(); nl += lb.timings()["kernel_launches"]
+            g.shed(); nl += lb.timings()["kernel_launches"]
     ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -220,7 +233,7 @@ def run_ours(a):
     _lib.profile(True)
     PROF_STEPS = 3
     for _ in range(PROF_STEPS):
-        step()
+        step_serial()
     prof = _lib.profile_report()
     _lib.profile(False)
     per_kernel = {k: {"launches_per_step": v[0] / PROF_STEPS, "ms_per_step": v[1] / PROF_STEPS} for k, v in prof.items()}
@@ -348,6 +361,9 @@ def run_ours(a):
                        "cells_per_gpu": n * ncols, "l2": "inputs (537 MB elev per GPU) larger than L2; no flush needed",
                        "parallelism": "1 GPU" if world == 1 else
                        f"row bands, one per GPU; NCCL halo rows + boundary-graph tables (DESIGN.md section 4)",
+                       "step": ("litap_grid_flow_form: calc_form on the caller's stream beside calc_ddir2 + calc_shed4 on a "
+                                "high-priority stream; per_kernel / roofline come from a separate serial pass"
+                                if fused else "calc_form, calc_ddir2, calc_shed4 as three calls"),
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
             "clocks": clocks, "e2e": e2e, "gpu_launches": nl,
             "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti, "slope_gc": gc,
@@ -372,6 +388,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-weti", action="store_true")
+    ap.add_argument("--serial-stages", action="store_true", help="N = 1: form, ddir, shed as three calls (no stream overlap)")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)

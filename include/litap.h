@@ -122,6 +122,8 @@ int litap_grid_shed(litap_grid* g);
 int litap_grid_form(litap_grid* g, double grid_m);
 int litap_grid_weti(litap_grid* g, double grid_m);
 int litap_grid_slope_gc(litap_grid* g, double grid_m);
+/* calc_form + calc_ddir2 + calc_shed4 as one call: form overlaps the flow stages on a second stream */
+int litap_grid_flow_form(litap_grid* g, double grid_m, int invert);
 /* copy results out (dense NR*NC); name is one of: elev ddir flatcell shed upslope ridge
  * slope_pct slope_deg aspect prof plan qarea1 qarea2 qweti1 qweti2
  * sgre sgr sgcn sgc scr scc hill_r_dir hill_c_dir hill_r_n hill_r_cell hill_c_n hill_c_cell */

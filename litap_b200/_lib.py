@@ -13,7 +13,7 @@ SYMBOLS = [
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
     "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_slope_gc", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
-    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_slope_gc",
+    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
@@ -71,6 +71,7 @@ def load():
     L.litap_grid_form.argtypes = [vp, dbl]
     L.litap_grid_weti.argtypes = [vp, dbl]
     L.litap_grid_slope_gc.argtypes = [vp, dbl]
+    L.litap_grid_flow_form.argtypes = [vp, dbl, ci]
     L.litap_grid_download.argtypes = [vp, C.c_char_p, vp]
     L.litap_grid_npits.argtypes = [vp]
     L.litap_grid_npits.restype = i64

@@ -245,6 +245,10 @@ class DeviceGrid:
     def slope_gc(self, grid):
         check(lib().litap_grid_slope_gc(self._h, float(grid)))
 
+    def flow_form(self, grid, invert=False):
+        """form + ddir + shed in one call (form overlaps the flow stages on a second stream)"""
+        check(lib().litap_grid_flow_form(self._h, float(grid), int(bool(invert))))
+
     def download(self, name):
         a = np.empty((self.NR, self.NC), self._DT.get(name, np.float64))
         check(lib().litap_grid_download(self._h, name.encode(), a.ctypes.data))

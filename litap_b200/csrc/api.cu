@@ -10,6 +10,8 @@
 static thread_local std::string g_err;
 static Ctx g_ctx;
 static bool g_own_stream = true;  // false after litap_set_stream(non-NULL)
+static cudaStream_t g_hi_stream = nullptr;  // litap_grid_flow_form: the flow stages beside calc_form
+static cudaEvent_t g_ev_fork = nullptr, g_ev_join = nullptr;
 Ctx& ctx() { return g_ctx; }
 
 int set_error(int code, const std::string& msg) {
@@ -89,6 +91,7 @@ extern "C" void litap_shutdown(void) {
   form_forget_trig();
   for (auto& ev : c.ev) if (ev) { cudaEventDestroy(ev); ev = nullptr; }
   if (g_own_stream) cudaStreamDestroy(c.stream);
+  if (g_hi_stream) { cudaStreamDestroy(g_hi_stream); cudaEventDestroy(g_ev_fork); cudaEventDestroy(g_ev_join); g_hi_stream = nullptr; }
   g_own_stream = true;
   c.stream = nullptr;
   c.ready = false;
@@ -235,6 +238,60 @@ extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
   rc = t.finish();
   ctx().tm.kernel_launches = ctx().launches - l0;
   return rc;
+}
+
+// calc_form + calc_ddir2 + calc_shed4 of one resident DEM as ONE call: calc_form does not depend on the
+// flow stages, so it runs on the caller's stream while ddir / shed run on a high-priority stream of the
+// library.  The flow stages are chains of small kernels, host read-backs and one cooperative launch; the
+// form blocks (fp64-bound) fill the SMs those leave idle, and priority keeps them out of the way when a
+// flow kernel has blocks to place.  The call returns after both streams have finished.
+struct StreamSwap {  // ctx().stream is what every stage driver enqueues on
+  cudaStream_t keep;
+  explicit StreamSwap(cudaStream_t s) : keep(ctx().stream) { ctx().stream = s; }
+  ~StreamSwap() { ctx().stream = keep; }
+};
+extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
+  if (!g) return set_error(LITAP_EARG, "litap_grid_flow_form: NULL");
+  if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_flow_form: grid must be > 0");
+  if (g->nbands > 0) return set_error(LITAP_EARG, "litap_grid_flow_form: row bands use litap_bands_*");
+  Ctx& c = ctx();
+  if (!g_hi_stream) {
+    int lo = 0, hi = 0;
+    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CUDA_TRY(cudaStreamCreateWithPriority(&g_hi_stream, cudaStreamNonBlocking, hi));
+    CUDA_TRY(cudaEventCreateWithFlags(&g_ev_fork, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&g_ev_join, cudaEventDisableTiming));
+  }
+  const int64_t l0 = c.launches;
+  cudaStream_t user = c.stream;
+  CUDA_TRY(cudaEventRecord(g_ev_fork, user));            // elev (upload / synth) is ordered on the caller's stream
+  CUDA_TRY(cudaStreamWaitEvent(g_hi_stream, g_ev_fork, 0));
+  // form is queued first and returns at once; the flow kernels then take the SMs as its blocks retire
+  CUDA_TRY(cudaEventRecord(c.ev[4], user));
+  int rc = run_form(g, grid_m);
+  if (rc) return rc;
+  CUDA_TRY(cudaEventRecord(c.ev[5], user));
+  {
+    StreamSwap sw(g_hi_stream);
+    CUDA_TRY(cudaEventRecord(c.ev[0], g_hi_stream));
+    rc = run_ddir(g, invert);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(c.ev[1], g_hi_stream));
+    CUDA_TRY(cudaEventRecord(c.ev[2], g_hi_stream));
+    rc = run_shed(g);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(c.ev[3], g_hi_stream));
+    CUDA_TRY(cudaEventRecord(g_ev_join, g_hi_stream));
+  }
+  CUDA_TRY(cudaStreamWaitEvent(user, g_ev_join, 0));
+  CUDA_TRY(cudaStreamSynchronize(user));
+  cudaEventElapsedTime(&c.tm.ddir_ms, c.ev[0], c.ev[1]);
+  cudaEventElapsedTime(&c.tm.shed_ms, c.ev[2], c.ev[3]);
+  cudaEventElapsedTime(&c.tm.form_ms, c.ev[4], c.ev[5]);  // while the flow stages share the device
+  g->have_ddir = g->have_shed = true;
+  c.tm.npits = g->npits;
+  c.tm.kernel_launches = c.launches - l0;
+  return LITAP_OK;
 }
 
 extern "C" int litap_grid_slope_gc(litap_grid* g, double grid_m) {

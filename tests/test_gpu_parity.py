@@ -373,3 +373,22 @@ def test_bad_arguments_raise():
         lb.calc_form(lb.add_buffer(np.ones((4, 4))), 0.0)
     with pytest.raises(lb.LitapError):
         lb.DeviceGrid(2, 2)
+
+
+def test_device_resident_fused_call_matches_stage_calls():
+    """litap_grid_flow_form (calc_form overlapping the flow stages on a second stream) == the three stage calls."""
+    e = oracle.synth_dem(900, 1100, seed=12)
+    a, b = lb.DeviceGrid(*e.shape), lb.DeviceGrid(*e.shape)
+    a.upload_elev(e); b.upload_elev(e)
+    for _ in range(3):   # repeated calls reuse the pooled scratch across the two streams
+        a.flow_form(5.0)
+    b.form(5.0); b.ddir(); b.shed()
+    for k in ("ddir", "flatcell", "shed", "upslope", "ridge") + FORM:
+        assert a.checksum(k) == b.checksum(k), k
+        assert eq_na(a.download(k).ravel().astype(np.float64), b.download(k).ravel().astype(np.float64)).all(), k
+    assert a.npits == b.npits
+    a.flow_form(5.0, invert=True)
+    b.ddir(invert=True); b.shed()
+    for k in ("ddir", "shed", "upslope", "ridge"):
+        assert a.checksum(k) == b.checksum(k), "inverted " + k
+    a.close(); b.close()
