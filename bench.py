@@ -178,7 +178,7 @@ def run_ours(a):
         g = lb.DeviceGrid(NR, NC)
         g.synth(seed=SEED, quant=QUANT)
 
-    fused = world == 1 and not a.serial_stages
+    fused = not a.serial_stages
 
     def step():
         if fused:
@@ -361,7 +361,7 @@ def run_ours(a):
                        "cells_per_gpu": n * ncols, "l2": "inputs (537 MB elev per GPU) larger than L2; no flush needed",
                        "parallelism": "1 GPU" if world == 1 else
                        f"row bands, one per GPU; NCCL halo rows + boundary-graph tables (DESIGN.md section 4)",
-                       "step": ("litap_grid_flow_form: calc_form on the caller's stream beside calc_ddir2 + calc_shed4 on a "
+                       "step": ("litap_grid_flow_form / litap_bands_flow_form: calc_form on the caller's stream beside calc_ddir2 + calc_shed4 on a "
                                 "high-priority stream; per_kernel / roofline come from a separate serial pass"
                                 if fused else "calc_form, calc_ddir2, calc_shed4 as three calls"),
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
@@ -388,7 +388,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-weti", action="store_true")
-    ap.add_argument("--serial-stages", action="store_true", help="N = 1: form, ddir, shed as three calls (no stream overlap)")
+    ap.add_argument("--serial-stages", action="store_true", help="form, ddir, shed as three calls (no stream overlap)")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)

@@ -154,6 +154,8 @@ int litap_band_upload_rows(litap_grid* band, const double* rows);
 int litap_bands_ddir(litap_grid** bands, int n, int invert);
 int litap_bands_shed(litap_grid** bands, int n);
 int litap_bands_form(litap_grid** bands, int n, double grid_m);
+/* form + ddir + shed of the local bands as one call (calc_form overlaps the flow stages, see litap_grid_flow_form) */
+int litap_bands_flow_form(litap_grid** bands, int n, double grid_m, int invert);
 /* the rows of the full buffered DEM this band answers for (own rows; + the NA ring row for the
  * first / last band): first row and row count; litap_band_download copies exactly those rows */
 int litap_band_rows(const litap_grid* band, int64_t* row0, int64_t* nrows);

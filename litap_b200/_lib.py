@@ -17,7 +17,7 @@ SYMBOLS = [
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
-    "litap_bands_form", "litap_band_rows", "litap_band_download",
+    "litap_bands_form", "litap_bands_flow_form", "litap_band_rows", "litap_band_download",
 ]
 
 
@@ -86,6 +86,7 @@ def load():
     L.litap_bands_ddir.argtypes = [C.POINTER(vp), ci, ci]
     L.litap_bands_shed.argtypes = [C.POINTER(vp), ci]
     L.litap_bands_form.argtypes = [C.POINTER(vp), ci, dbl]
+    L.litap_bands_flow_form.argtypes = [C.POINTER(vp), ci, dbl, ci]
     L.litap_band_rows.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
     L.litap_band_download.argtypes = [vp, C.c_char_p, vp]
     _lib = L

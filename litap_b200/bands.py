@@ -95,6 +95,10 @@ class BandedDEM:
     def form(self, grid):
         check(lib().litap_bands_form(self._arr, len(self._h), float(grid)))
 
+    def flow_form(self, grid, invert=False):
+        """form + ddir + shed in one call (calc_form overlaps the flow stages and their exchanges)"""
+        check(lib().litap_bands_flow_form(self._arr, len(self._h), float(grid), int(bool(invert))))
+
     def rows(self, i=0):
         """(first row, row count) in the buffered DEM of the rows local band i answers for."""
         r0, n = C.c_int64(0), C.c_int64(0)

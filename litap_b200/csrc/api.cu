@@ -245,22 +245,28 @@ extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
 // library.  The flow stages are chains of small kernels, host read-backs and one cooperative launch; the
 // form blocks (fp64-bound) fill the SMs those leave idle, and priority keeps them out of the way when a
 // flow kernel has blocks to place.  The call returns after both streams have finished.
-struct StreamSwap {  // ctx().stream is what every stage driver enqueues on
-  cudaStream_t keep;
-  explicit StreamSwap(cudaStream_t s) : keep(ctx().stream) { ctx().stream = s; }
-  ~StreamSwap() { ctx().stream = keep; }
-};
+int flow_streams(cudaStream_t* hi, cudaEvent_t* fork, cudaEvent_t* join) {
+  if (!g_hi_stream) {
+    int lo = 0, top = 0;
+    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &top));
+    CUDA_TRY(cudaStreamCreateWithPriority(&g_hi_stream, cudaStreamNonBlocking, top));
+    CUDA_TRY(cudaEventCreateWithFlags(&g_ev_fork, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&g_ev_join, cudaEventDisableTiming));
+  }
+  *hi = g_hi_stream;
+  *fork = g_ev_fork;
+  *join = g_ev_join;
+  return LITAP_OK;
+}
 extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
   if (!g) return set_error(LITAP_EARG, "litap_grid_flow_form: NULL");
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_flow_form: grid must be > 0");
   if (g->nbands > 0) return set_error(LITAP_EARG, "litap_grid_flow_form: row bands use litap_bands_*");
   Ctx& c = ctx();
-  if (!g_hi_stream) {
-    int lo = 0, hi = 0;
-    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    CUDA_TRY(cudaStreamCreateWithPriority(&g_hi_stream, cudaStreamNonBlocking, hi));
-    CUDA_TRY(cudaEventCreateWithFlags(&g_ev_fork, cudaEventDisableTiming));
-    CUDA_TRY(cudaEventCreateWithFlags(&g_ev_join, cudaEventDisableTiming));
+  {
+    cudaStream_t hs; cudaEvent_t ef, ej;
+    int rc0 = flow_streams(&hs, &ef, &ej);
+    if (rc0) return rc0;
   }
   const int64_t l0 = c.launches;
   cudaStream_t user = c.stream;
@@ -271,6 +277,10 @@ extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
   int rc = run_form(g, grid_m);
   if (rc) return rc;
   CUDA_TRY(cudaEventRecord(c.ev[5], user));
+  if (invert) {  // invert() rewrites elev in place: the flow stages then wait for calc_form (no overlap)
+    CUDA_TRY(cudaEventRecord(g_ev_fork, user));
+    CUDA_TRY(cudaStreamWaitEvent(g_hi_stream, g_ev_fork, 0));
+  }
   {
     StreamSwap sw(g_hi_stream);
     CUDA_TRY(cudaEventRecord(c.ev[0], g_hi_stream));

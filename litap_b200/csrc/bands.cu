@@ -439,6 +439,42 @@ extern "C" int litap_bands_form(litap_grid** B, int n, double grid_m) {
 
 // ------------------------------------------------------------------------------------------------
 // calc_shed4 over row bands (R/flow_02_calc_shed.R:10-145)
+extern "C" int litap_bands_shed(litap_grid** B, int n);
+// form + ddir + shed of the local bands as one call: calc_form on the caller's stream, the flow stages (with
+// their exchanges) on the library's high-priority stream, like litap_grid_flow_form
+extern "C" int litap_bands_flow_form(litap_grid** B, int n, double grid_m, int invert) {
+  int rc = check_bands(B, n);
+  if (rc) return rc;
+  if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_bands_flow_form: grid must be > 0");
+  Ctx& c = ctx();
+  cudaStream_t hi;
+  cudaEvent_t fork, join;
+  if ((rc = flow_streams(&hi, &fork, &join))) return rc;
+  cudaStream_t user = c.stream;
+  const int64_t l0 = c.launches;
+  CUDA_TRY(cudaEventRecord(fork, user));
+  CUDA_TRY(cudaStreamWaitEvent(hi, fork, 0));
+  CUDA_TRY(cudaEventRecord(c.ev[4], user));
+  for (int i = 0; i < n; ++i)
+    if ((rc = run_form(B[i], grid_m))) return rc;
+  CUDA_TRY(cudaEventRecord(c.ev[5], user));
+  if (invert) {  // invert() rewrites elev in place: the flow stages then wait for calc_form (no overlap)
+    CUDA_TRY(cudaEventRecord(fork, user));
+    CUDA_TRY(cudaStreamWaitEvent(hi, fork, 0));
+  }
+  {
+    StreamSwap sw(hi);
+    if ((rc = litap_bands_ddir(B, n, invert))) return rc;
+    if ((rc = litap_bands_shed(B, n))) return rc;
+    CUDA_TRY(cudaEventRecord(join, hi));
+  }
+  CUDA_TRY(cudaStreamWaitEvent(user, join, 0));
+  CUDA_TRY(cudaStreamSynchronize(user));
+  cudaEventElapsedTime(&c.tm.form_ms, c.ev[4], c.ev[5]);
+  c.tm.kernel_launches = c.launches - l0;
+  return LITAP_OK;
+}
+
 namespace bg {
 using namespace shed;
 

@@ -90,6 +90,16 @@ Ctx& ctx();
 int set_error(int code, const std::string& msg);
 int ensure_init();
 
+// litap_*_flow_form: the flow stages run on a high-priority stream of the library beside calc_form on the
+// caller's stream; ctx().stream is what every stage driver enqueues on, so the flow stages are redirected
+// by swapping it for their duration
+int flow_streams(cudaStream_t* hi, cudaEvent_t* fork, cudaEvent_t* join);  // api.cu (created on first use)
+struct StreamSwap {
+  cudaStream_t keep;
+  explicit StreamSwap(cudaStream_t s) : keep(ctx().stream) { ctx().stream = s; }
+  ~StreamSwap() { ctx().stream = keep; }
+};
+
 // pooled device allocations (freed by litap_shutdown); zero = cudaMemsetAsync to 0
 void* pool_alloc(size_t bytes);
 void pool_free(void* p);

@@ -115,3 +115,25 @@ def test_band_synth_matches_whole_generator():
     got = B.download("elev")
     assert ((got == ref) | (np.isnan(got) & np.isnan(ref))).all()
     B.close()
+
+
+@pytest.mark.parametrize("P,invert", [(3, False), (4, True)])
+def test_fused_band_call_matches_stage_calls(P, invert):
+    """litap_bands_flow_form (calc_form beside the flow stages on a second stream) == form, ddir, shed in turn."""
+    e = oracle.synth_dem(700, 333, seed=31, quant=100.0)
+    gnr, nc = e.shape[0] - 2, e.shape[1] - 2
+    B = BandedDEM(gnr, nc, P)
+    B.upload_elev(e)
+    for _ in range(2):
+        if invert:
+            B.upload_elev(e)   # invert() rewrites elev in place
+        B.flow_form(5.0, invert=invert)
+    a = {k: B.download(k) for k in ("ddir", "flatcell", "shed", "upslope", "ridge") + FORM}
+    a["npits"] = B.npits
+    B.close()
+    b = run_whole(e, invert=invert)
+    if invert:   # form is computed on the elevations as given: compare it with the non-inverted run
+        b_form = run_whole(e)
+        for k in FORM:
+            b[k] = b_form[k]
+    assert_same(a, b, f"fused bands P={P} invert={invert}")

@@ -391,4 +391,6 @@ def test_device_resident_fused_call_matches_stage_calls():
     b.ddir(invert=True); b.shed()
     for k in ("ddir", "shed", "upslope", "ridge"):
         assert a.checksum(k) == b.checksum(k), "inverted " + k
+    for k in FORM:   # calc_form saw the elevations as given, before invert() rewrote them in place
+        assert a.checksum(k) == b.checksum(k), "form beside inverted flow: " + k
     a.close(); b.close()
