@@ -383,7 +383,11 @@ extern "C" int litap_bands_ddir(litap_grid** B, int n, int invert) {
   if ((rc = gather_words_host(B, n, mine, 1, counts))) return rc;
   unsigned long long total = 0, mx = 0, flat_total = 0;
   for (int b = 0; b < P; ++b) { total += counts[b]; mx = std::max(mx, counts[b]); }
-  for (int i = 0; i < n; ++i) flat_total += nflat[i];
+  for (int i = 0; i < n; ++i) {
+    flat_total += nflat[i];
+    // pits of the band in calc_shed4: own cells that stay flat + one portal per halo cell
+    B[i]->pit_bound = (int64_t)nflat[i] + 2 * (int64_t)B[i]->d.NC;
+  }
   if (total) {
     std::vector<void*> ksend(n), krecv(n);
     for (int i = 0; i < n; ++i) {

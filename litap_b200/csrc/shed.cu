@@ -488,9 +488,9 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   if (!counters) return set_error(LITAP_ENOMEM, "device allocation failed (shed scratch)");
   CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), st));
   // capacity of the pit arrays: the flat-cell count of the D8 stencil when calc_ddir2 ran on this grid
-  // (pits are a subset), else an exact count (one more pass over ddir and a host sync)
+  // (pits are a subset; a row band adds its portals), else an exact count (one more pass over ddir and a host sync)
   size_t np = 1;
-  if (g->pit_bound >= 0 && g->nbands == 0) np = g->pit_bound ? (size_t)g->pit_bound : 1;
+  if (g->pit_bound >= 0) np = g->pit_bound ? (size_t)g->pit_bound : 1;
   else {
     dim3 grid((d.NC - 1 + 255) / 256, d.NR - 1 < 256 ? d.NR - 1 : 256);
     KERNEL("k_count_pits", k_count_pits<<<grid, 256, 0, st>>>(g->ddir, d, counters));
