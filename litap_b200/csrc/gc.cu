@@ -12,9 +12,9 @@
 //     Jacobi rounds of the oracle).
 //   * :145-160  cumsum / factor / 1:n() per row and per column are a second sweep with a handful of
 //     counters (label_step): NA gradients poison the rest of the line exactly like cumsum(NA).
-// A line is inherently sequential in this formulation; all lines run in parallel:
-//   k_gc_rows   a block owns 16 rows and walks along them in 32-column chunks staged through shared
-//               memory (coalesced loads / stores by the whole block, one lane per row in between)
+// All lines run in parallel:
+//   k_gc_rows   a warp owns a row and walks along it 32 columns at a time; the sweeps become warp scans
+//               (ballot / popc / clz / shuffle) with the carried state in warp-uniform registers
 //   k_gc_cols_stencil / _fix / _label  a plain stencil, then one thread per column south -> north (zero signs)
 //               and north -> south (hill_c_dir / n / cell)
 // The NA ring of add_buffer() is required (like everywhere on this path): it is what makes the
@@ -83,9 +83,12 @@ __device__ __forceinline__ void label_step(LabelState& s, double v, bool elev_na
 }
 
 // ---- rows ------------------------------------------------------------------------------------------
-constexpr int GR_ROWS = 8;      // rows per block = lanes of the sweep; many small blocks per SM overlap their phases
-constexpr int GR_CH = 32;       // columns per chunk
-constexpr int GR_THREADS = 64;
+// One warp per row, 32 columns per step, lane = column.  Both sweeps are scans whose operators are
+// cheap on a warp: every state variable of fix_step / label_step is a prefix count, a prefix OR or
+// "the value at the last marked lane", i.e. ballot + popc / clz + one shuffle, with the state at the
+// end of the chunk carried in warp-uniform registers.  (fix_step / label_step stay the definition
+// and run as they are in the column kernels; test_gpu_slope_gc checks both against the oracle.)
+constexpr int GR_WARPS = 4;     // rows per block
 
 // elevation of linear neighbour seqno - 1 / seqno + 1 exactly as nb_values addresses it (no wrap check)
 __device__ __forceinline__ double gc_elev_lin(const double* __restrict__ elev, const GridDims& d, int r, int c) {
@@ -101,88 +104,111 @@ __device__ __forceinline__ void gc_row_cell(double e5, double n4, double n6, dou
   ge = (n4 - n6) / two_g;
   cr = (2 * e5 - n4 - n6) / g2;
 }
+__device__ __forceinline__ int gc_top(unsigned m) { return 31 - __clz(m); }   // highest set bit, m != 0
 
-constexpr int GR_LD = (GR_ROWS * (GR_CH + 3) + GR_THREADS - 1) / GR_THREADS;  // elevations a thread stages per chunk
-
-__global__ void __launch_bounds__(GR_THREADS) k_gc_rows(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
-  __shared__ double s_e[GR_ROWS][GR_CH + 5];     // columns cb-1 .. cb+GR_CH+1 of the block's rows
-  __shared__ double s_ge[GR_ROWS][GR_CH + 3];    // gradient of columns cb .. cb+GR_CH (one ahead of the sign rule)
-  __shared__ double s_v[GR_ROWS][GR_CH + 1];     // gradient with its zero signs settled
-  __shared__ int s_n[GR_ROWS][GR_CH + 1], s_cell[GR_ROWS][GR_CH + 1];
-  const int r0 = blockIdx.x * GR_ROWS;
+__global__ void __launch_bounds__(GR_WARPS * 32) k_gc_rows(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int r = blockIdx.x * GR_WARPS + (threadIdx.x >> 5);
+  if (r >= d.NR) return;
   const double two_g = 2 * grid_m, g2 = grid_m * grid_m;
-  FixState fs;
-  LabelState ls;
-  fix_init(fs);
-  label_init(ls);
-  // the chunk after the current one travels in registers while the current one is worked on
-  double pre[GR_LD];
-  auto fetch = [&](int cb) {
-#pragma unroll
-    for (int q = 0; q < GR_LD; ++q) {
-      const int i = threadIdx.x + q * GR_THREADS;
-      const int rr = i / (GR_CH + 3), k = i - rr * (GR_CH + 3);
-      const int r = r0 + rr;
-      pre[q] = (rr < GR_ROWS && r < d.NR && cb < d.NC) ? gc_elev_lin(elev, d, r, cb - 1 + k) : gc_na();
+  const double* __restrict__ row = elev + (size_t)r * d.pitch;
+  const unsigned le = (2u << lane) - 1u;   // lanes <= mine
+  const unsigned lt = le >> 1;             // lanes <  mine
+  auto ld = [&](int cb) { const int c = cb + lane; return c < d.NC ? __ldg(row + c) : gc_na(); };
+  const double e_west = gc_elev_lin(elev, d, r, -1), e_east = gc_elev_lin(elev, d, r, d.NC);
+  // carried state, identical in all lanes
+  double c_elast = e_west;         // elevation of the column before the chunk
+  double c_glast = gc_na();        // raw gradient of that column
+  double c_runval = 0;
+  bool c_inrun = false;
+  bool c_lag_na = true, c_lag_pos = false, c_poisoned = false, c_have_last = false;
+  int c_cum = 0, c_dense = 0, c_last_val = 0, c_cnt = 0, c_na = 0;
+  double E0 = ld(0), E1 = ld(32), E2 = ld(64);
+  for (int cb = 0; cb < d.NC; cb += 32) {
+    const double E3 = ld(cb + 96);   // three chunks ahead of the arithmetic
+    const int c = cb + lane;
+    const bool active = c < d.NC;
+    // gradient, magnitude, curvature
+    const double e5 = E0;
+    double n4 = __shfl_up_sync(FULL, E0, 1);
+    double n6 = __shfl_down_sync(FULL, E0, 1);
+    const double e1_0 = __shfl_sync(FULL, E1, 0), e1_1 = __shfl_sync(FULL, E1, 1), e0_31 = __shfl_sync(FULL, E0, 31);
+    if (lane == 0) n4 = c_elast;
+    if (lane == 31) n6 = e1_0;
+    if (c == d.NC - 1) n6 = e_east;
+    double ge, cr;
+    gc_row_cell(e5, n4, n6, two_g, g2, ge, cr);
+    if (!active) ge = gc_na();
+    // raw gradient of the first column of the next chunk (the sign rule looks one cell ahead)
+    double g_next0 = gc_na();
+    if (cb + 32 < d.NC) {
+      double crx;
+      gc_row_cell(e1_0, e0_31, cb + 33 < d.NC ? e1_1 : e_east, two_g, g2, g_next0, crx);
     }
-  };
-  fetch(0);
-  for (int cb = 0; cb < d.NC; cb += GR_CH) {
-    __syncthreads();  // the previous chunk's tiles have been consumed
-#pragma unroll
-    for (int q = 0; q < GR_LD; ++q) {
-      const int i = threadIdx.x + q * GR_THREADS;
-      const int rr = i / (GR_CH + 3), k = i - rr * (GR_CH + 3);
-      if (rr < GR_ROWS) s_e[rr][k] = pre[q];
+    const size_t o = (size_t)r * d.pitch + c;
+    if (active) {
+      double ar = fabs(ge);
+      if (ar == 0) ar = GC_TINY;
+      P.sgr[o] = ar;
+      P.scr[o] = cr;
     }
-    __syncthreads();
-    fetch(cb + GR_CH);
-    // data-parallel part, all threads: gradient (one column ahead for the sign rule), magnitude, curvature
-    for (int i = threadIdx.x; i < GR_ROWS * (GR_CH + 1); i += GR_THREADS) {
-      const int rr = i / (GR_CH + 1), j = i - rr * (GR_CH + 1);
-      const int r = r0 + rr, c = cb + j;
-      double ge = gc_na(), cr = gc_na();
-      if (r < d.NR && c < d.NC) gc_row_cell(s_e[rr][j + 1], s_e[rr][j], s_e[rr][j + 2], two_g, g2, ge, cr);
-      s_ge[rr][j] = ge;
-      if (j < GR_CH && r < d.NR && c < d.NC) {
-        const size_t o = (size_t)r * d.pitch + c;
-        double ar = fabs(ge);
-        if (ar == 0) ar = GC_TINY;
-        P.sgr[o] = ar;
-        P.scr[o] = cr;
-      }
-    }
-    __syncthreads();
-    // sequential part, one lane per row: the two sweeps over the chunk
-    if (threadIdx.x < GR_ROWS && r0 + (int)threadIdx.x < d.NR) {
-      const int rr = threadIdx.x;
-      const int nc = min(GR_CH, d.NC - cb);
-      double g_cur = s_ge[rr][0];
-#pragma unroll 4
-      for (int j = 0; j < nc; ++j) {
-        const double g_nxt = s_ge[rr][j + 1];   // NA past the last column
-        const double e5 = s_e[rr][j + 1];
-        const double v = fix_step(fs, g_cur, g_nxt);
-        int hn, hc;
-        label_step(ls, v, e5 != e5, hn, hc);
-        s_v[rr][j] = v;
-        s_n[rr][j] = hn;
-        s_cell[rr][j] = hc;
-        g_cur = g_nxt;
-      }
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < GR_ROWS * GR_CH; i += GR_THREADS) {
-      const int rr = i / GR_CH, j = i - rr * GR_CH;
-      const int r = r0 + rr, c = cb + j;
-      if (r >= d.NR || c >= d.NC) continue;
-      const size_t o = (size_t)r * d.pitch + c;
-      const double v = s_v[rr][j];
+    // ---- zero signs (fix_step as a scan) ----
+    const bool z = active && ge == 0.0;
+    const unsigned zmask = __ballot_sync(FULL, z);
+    double g_prev = __shfl_up_sync(FULL, ge, 1);
+    double g_nxt = __shfl_down_sync(FULL, ge, 1);
+    if (lane == 0) g_prev = c_glast;
+    if (lane == 31) g_nxt = g_next0;
+    const bool prev_zero = lane > 0 ? ((zmask >> (lane - 1)) & 1u) != 0 : c_inrun;
+    const bool runstart = z && !prev_zero;
+    const double rv_prev = g_prev > 0 ? GC_TINY : -GC_TINY;
+    const double rv_next = g_nxt != g_nxt ? gc_na() : (g_nxt > 0 ? GC_TINY : -GC_TINY);
+    const double rv = g_prev == g_prev ? rv_prev : (g_nxt == 0.0 ? GC_TINY : rv_next);
+    const unsigned sbelow = __ballot_sync(FULL, runstart) & le;
+    const double rv_s = __shfl_sync(FULL, rv, sbelow ? gc_top(sbelow) : lane);
+    const double v = z ? (sbelow ? rv_s : c_runval) : ge;
+    // ---- run labels (label_step as a scan) ----
+    const bool ena = e5 != e5;
+    const bool s_na = v != v, pos = v > 0;
+    int lag_na = __shfl_up_sync(FULL, (int)s_na, 1), lag_pos = __shfl_up_sync(FULL, (int)pos, 1);
+    if (lane == 0) { lag_na = c_lag_na; lag_pos = c_lag_pos; }
+    const unsigned pmask = __ballot_sync(FULL, active && !lag_na && s_na);
+    const bool poisoned = c_poisoned || (pmask & le) != 0;
+    const unsigned imask = __ballot_sync(FULL, active && !poisoned && (lag_na || (int)pos != lag_pos));
+    const int cum = c_cum + __popc(imask & le);
+    const bool valid = active && !ena && !poisoned;
+    const unsigned vmask = __ballot_sync(FULL, valid);
+    const unsigned vlow = vmask & lt;
+    const int cum_pv = __shfl_sync(FULL, cum, vlow ? gc_top(vlow) : lane);
+    const bool newlab = valid && (vlow ? cum != cum_pv : (!c_have_last || cum != c_last_val));
+    const unsigned nlmask = __ballot_sync(FULL, newlab);
+    const unsigned nlb = nlmask & le;
+    const int dense = c_dense + __popc(nlb);
+    const int cnt = nlb ? __popc(vmask & le & ~((1u << gc_top(nlb)) - 1u)) : c_cnt + __popc(vmask & le);
+    const unsigned colmask = __ballot_sync(FULL, active);
+    const int na_cnt = c_na + __popc(~vmask & colmask & le);
+    if (active) {
       P.sgre[o] = v;
-      P.rdir[o] = v != v ? 0 : (v > 0 ? 2 : 4);
-      P.rn[o] = s_n[rr][j];
-      P.rcell[o] = s_cell[rr][j];
+      P.rdir[o] = s_na ? 0 : (pos ? 2 : 4);
+      P.rn[o] = valid ? dense : 0;
+      P.rcell[o] = valid ? cnt : (ena ? 0 : na_cnt);
     }
+    // ---- carry to the next chunk ----
+    c_elast = e0_31;
+    c_glast = __shfl_sync(FULL, ge, 31);
+    c_inrun = (zmask >> 31) != 0;
+    c_runval = __shfl_sync(FULL, v, 31);   // only read while c_inrun
+    c_lag_na = __shfl_sync(FULL, (int)s_na, 31) != 0;
+    c_lag_pos = __shfl_sync(FULL, (int)pos, 31) != 0;
+    c_poisoned = c_poisoned || pmask != 0;
+    c_cum += __popc(imask);
+    const int cum_lastvalid = __shfl_sync(FULL, cum, vmask ? gc_top(vmask) : 0);
+    if (vmask) { c_last_val = cum_lastvalid; c_have_last = true; }
+    c_dense += __popc(nlmask);
+    c_cnt = nlmask ? __popc(vmask & ~((1u << gc_top(nlmask)) - 1u)) : c_cnt + __popc(vmask);
+    c_na += __popc(~vmask & colmask);
+    E0 = E1; E1 = E2; E2 = E3;
   }
 }
 
@@ -303,7 +329,7 @@ int run_slope_gc(litap_grid* g, double grid_m) {
   P.scr = g->gc_f64[4]; P.scc = g->gc_f64[5];
   P.rdir = g->gc_u8[0]; P.cdir = g->gc_u8[1];
   P.rn = g->gc_i32[0]; P.rcell = g->gc_i32[1]; P.cn = g->gc_i32[2]; P.ccell = g->gc_i32[3];
-  KERNEL("k_gc_rows", k_gc_rows<<<(d.NR + GR_ROWS - 1) / GR_ROWS, GR_THREADS, 0, st>>>(g->elev, d, grid_m, P));
+  KERNEL("k_gc_rows", k_gc_rows<<<(d.NR + GR_WARPS - 1) / GR_WARPS, GR_WARPS * 32, 0, st>>>(g->elev, d, grid_m, P));
   const int cblk = (d.NC + GC_THREADS - 1) / GC_THREADS;
   KERNEL("k_gc_cols_stencil", k_gc_cols_stencil<<<dim3((d.NC + 255) / 256, d.NR), 256, 0, st>>>(g->elev, d, grid_m, P));
   KERNEL("k_gc_cols_fix", k_gc_cols_fix<<<cblk, GC_THREADS, 0, st>>>(d, P));
