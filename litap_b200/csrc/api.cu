@@ -140,6 +140,7 @@ extern "C" void litap_grid_destroy(litap_grid* g) {
   for (auto& p : g->gc_f64) grid_free_array(p);
   for (auto& p : g->gc_u8) grid_free_array(p);
   for (auto& p : g->gc_i32) grid_free_array(p);
+  if (g->gc_sum) { pool_free(g->gc_sum); g->gc_sum = nullptr; }
   if (g->dd_list) pool_free(g->dd_list);
   if (g->dd_cand) pool_free(g->dd_cand);
   if (g->dd_keys) pool_free(g->dd_keys);

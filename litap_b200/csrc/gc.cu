@@ -15,8 +15,8 @@
 // All lines run in parallel:
 //   k_gc_rows   a warp owns a row and walks along it 32 columns at a time; the sweeps become warp scans
 //               (ballot / popc / clz / shuffle) with the carried state in warp-uniform registers
-//   k_gc_cols_stencil / _fix / _label  a plain stencil, then one thread per column south -> north (zero signs)
-//               and north -> south (hill_c_dir / n / cell)
+//   k_gc_cols_stencil / _fix / _sum / _label  a plain stencil, then one thread per (column, row segment):
+//               south -> north (zero signs), north -> south (hill_c_dir / n / cell), see "columns" below
 // The NA ring of add_buffer() is required (like everywhere on this path): it is what makes the
 // reference's linear seqno +- 1 addressing row-local.
 #include "cellmath.h"
@@ -213,14 +213,22 @@ __global__ void __launch_bounds__(GR_WARPS * 32) k_gc_rows(const double* __restr
 }
 
 // ---- columns ---------------------------------------------------------------------------------------
-// k_gc_cols_stencil  data-parallel: sgcn as computed, sgc, scc; hill_c_dir temporarily holds "elev is NA"
-// k_gc_cols_fix      one thread per column, south -> north: zero gradients take their sign (only those cells
-//                    are rewritten)
-// k_gc_cols_label    one thread per column, north -> south: hill_c_dir / n / cell
-// The sweeps read 8-9 bytes per cell and keep GC_PF x 2 rows in flight per thread: with one thread per
-// column there are only NC/32 warps, so latency has to be covered inside the thread.
-constexpr int GC_THREADS = 32;
-constexpr int GC_PF = 16;  // rows per group; two groups are in flight
+// A column is cut into segments of GC_SEG rows and a thread owns one (column, segment), so that there
+// are NC x NR / GC_SEG threads instead of NC; lanes are consecutive columns (coalesced).  What a segment
+// needs from the rest of its column:
+//   k_gc_cols_stencil  data-parallel: sgcn as computed, sgc, scc; hill_c_dir temporarily holds two flags,
+//                      0x80 "elev is NA" and 0x40 "gradient is 0" (zero cells are rewritten in place by
+//                      the next kernel, the flag is what other threads look at)
+//   k_gc_cols_fix      south -> north.  The state entering a segment is settled by the first non-zero
+//                      cell south of it: the thread starts there and runs fix_step over the zeros in
+//                      between without storing (usually no cell at all; a lake costs its extent).
+//   k_gc_cols_sum      north -> south.  label_step's counters are prefix sums, so a segment is first run
+//                      from a blank state (with its true lag, the cell above it) and summarised ...
+//   k_gc_cols_label    ... then every thread folds the summaries of the segments above its own (gc_fold)
+//                      and runs label_step for real: hill_c_dir / n / cell.
+constexpr int GC_THREADS = 128;
+constexpr int GC_PF = 8;  // rows per group; the next group is in flight while one is worked on
+constexpr int GC_NSUM = 8;
 
 __device__ __forceinline__ void gc_col_cell(double e5, double n2, double n8, double two_g, double g2, double& gn, double& cc) {
   if (n2 != n2) n2 = e5;
@@ -244,72 +252,144 @@ __global__ void __launch_bounds__(256) k_gc_cols_stencil(const double* __restric
   P.sgcn[o] = gn;
   P.sgc[o] = ac;
   P.scc[o] = cc;
-  P.cdir[o] = e5 != e5 ? 0x80 : 0;
+  P.cdir[o] = (e5 != e5 ? 0x80 : 0) | (gn == 0.0 ? 0x40 : 0);
 }
 
-__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_fix(GridDims d, GcPtrs P) {
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_fix(GridDims d, GcPtrs P, int seg_rows) {
   const int c = blockIdx.x * GC_THREADS + threadIdx.x;
   if (c >= d.NC) return;
+  const int r_lo = blockIdx.y * seg_rows, r_hi = min(d.NR, r_lo + seg_rows) - 1;
   double* g = P.sgcn + c;
-  auto G = [&](int r) { return (r < 0 || r >= d.NR) ? gc_na() : g[(size_t)r * d.pitch]; };
+  const uint8_t* f = P.cdir + c;
+  // gradient as computed: zero cells are read through their flag (their value may already be rewritten)
+  auto G = [&](int r) {
+    if (r < 0 || r >= d.NR) return gc_na();
+    const size_t o = (size_t)r * d.pitch;
+    const double v = g[o];
+    return (f[o] & 0x40) ? 0.0 : v;
+  };
   FixState fs;
   fix_init(fs);
-  // rows are visited from NR-1 down to 0; a[k] = row rt-k, b[k] = row rt-GC_PF-k, then one more group is fetched
-  double a[GC_PF], b[GC_PF];
+  {
+    int q = r_hi + 1;
+    while (q < d.NR && (f[(size_t)q * d.pitch] & 0x40)) ++q;
+    if (q < d.NR) fs.prev = g[(size_t)q * d.pitch];
+    for (int r = q - 1; r > r_hi; --r) fix_step(fs, 0.0, G(r - 1));
+  }
+  // rows are visited from r_hi down to r_lo; a[k] = row rt-k, n[k] = row rt-GC_PF-k
+  double a[GC_PF];
 #pragma unroll
-  for (int k = 0; k < GC_PF; ++k) { a[k] = G(d.NR - 1 - k); b[k] = G(d.NR - 1 - GC_PF - k); }
-  for (int rt = d.NR - 1; rt >= 0; rt -= GC_PF) {
+  for (int k = 0; k < GC_PF; ++k) a[k] = G(r_hi - k);
+  for (int rt = r_hi; rt >= r_lo; rt -= GC_PF) {
     double n[GC_PF];
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) n[k] = G(rt - 2 * GC_PF - k);
+    for (int k = 0; k < GC_PF; ++k) n[k] = G(rt - GC_PF - k);
 #pragma unroll
     for (int k = 0; k < GC_PF; ++k) {
       const int r = rt - k;
-      if (r >= 0) {
-        const double cur = a[k], nxt = k + 1 < GC_PF ? a[k + 1] : b[0];  // (rows below 0 read as NA)
+      if (r >= r_lo) {
+        const double cur = a[k], nxt = k + 1 < GC_PF ? a[k + 1] : n[0];  // (rows below 0 read as NA)
         const double v = fix_step(fs, cur, nxt);
         if (cur == 0.0) g[(size_t)r * d.pitch] = v;
       }
     }
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) { a[k] = b[k]; b[k] = n[k]; }
+    for (int k = 0; k < GC_PF; ++k) a[k] = n[k];
   }
 }
 
-__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_label(GridDims d, GcPtrs P) {
-  const int c = blockIdx.x * GC_THREADS + threadIdx.x;
-  if (c >= d.NC) return;
+// label_step over rows [r_lo, r_hi] of a column; STORE = false: only the state is wanted.  first_cum = cum at
+// the first valid cell (-1: none)
+template <bool STORE>
+__device__ __forceinline__ void gc_col_label_run(const GridDims& d, const GcPtrs& P, int c, int r_lo, int r_hi, LabelState& ls,
+                                                 int& first_cum) {
   const double* g = P.sgcn + c;
   uint8_t* dir = P.cdir + c;
-  auto G = [&](int r) { return r < d.NR ? g[(size_t)r * d.pitch] : gc_na(); };
-  auto D = [&](int r) { return r < d.NR ? dir[(size_t)r * d.pitch] : (uint8_t)0; };
-  LabelState ls;
-  label_init(ls);
-  double ga[GC_PF], gb[GC_PF];
-  uint8_t da[GC_PF], db[GC_PF];
+  auto G = [&](int r) { return r <= r_hi ? g[(size_t)r * d.pitch] : gc_na(); };
+  auto D = [&](int r) { return r <= r_hi ? dir[(size_t)r * d.pitch] : (uint8_t)0; };
+  if (r_lo > 0) {  // lag: the fixed gradient of the cell above the segment
+    const double vl = g[(size_t)(r_lo - 1) * d.pitch];
+    ls.lag_na = vl != vl;
+    ls.lag_pos = vl > 0;
+  }
+  first_cum = -1;
+  double ga[GC_PF];
+  uint8_t da[GC_PF];
 #pragma unroll
-  for (int k = 0; k < GC_PF; ++k) { ga[k] = G(k); da[k] = D(k); gb[k] = G(GC_PF + k); db[k] = D(GC_PF + k); }
-  for (int rt = 0; rt < d.NR; rt += GC_PF) {
+  for (int k = 0; k < GC_PF; ++k) { ga[k] = G(r_lo + k); da[k] = D(r_lo + k); }
+  for (int rt = r_lo; rt <= r_hi; rt += GC_PF) {
     double gn[GC_PF];
     uint8_t dn[GC_PF];
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) { gn[k] = G(rt + 2 * GC_PF + k); dn[k] = D(rt + 2 * GC_PF + k); }
+    for (int k = 0; k < GC_PF; ++k) { gn[k] = G(rt + GC_PF + k); dn[k] = D(rt + GC_PF + k); }
 #pragma unroll
     for (int k = 0; k < GC_PF; ++k) {
       const int r = rt + k;
-      if (r < d.NR) {
+      if (r <= r_hi) {
         int hn, hc;
         const double v = ga[k];
         label_step(ls, v, (da[k] & 0x80) != 0, hn, hc);
-        const size_t o = (size_t)r * d.pitch + c;
-        dir[(size_t)r * d.pitch] = v != v ? 0 : (v > 0 ? 1 : 3);
-        P.cn[o] = hn;
-        P.ccell[o] = hc;
+        if (STORE) {
+          const size_t o = (size_t)r * d.pitch + c;
+          dir[(size_t)r * d.pitch] = v != v ? 0 : (v > 0 ? 1 : 3);
+          P.cn[o] = hn;
+          P.ccell[o] = hc;
+        } else if (hn > 0 && first_cum < 0) first_cum = ls.cum;
       }
     }
 #pragma unroll
-    for (int k = 0; k < GC_PF; ++k) { ga[k] = gb[k]; gb[k] = gn[k]; da[k] = db[k]; db[k] = dn[k]; }
+    for (int k = 0; k < GC_PF; ++k) { ga[k] = gn[k]; da[k] = dn[k]; }
   }
+}
+
+// summary of a segment run from a blank state: [0] cum at the first valid cell (-1: no valid cell), [1] labels
+// started (the first valid cell always starts one here), [2] cnt at the end, [3] cum at the last valid cell,
+// [4] cum at the end, [5] poisoned, [6] cells counted as NA
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_sum(GridDims d, GcPtrs P, int seg_rows, int32_t* __restrict__ sum) {
+  const int c = blockIdx.x * GC_THREADS + threadIdx.x;
+  if (c >= d.NC) return;
+  const int r_lo = blockIdx.y * seg_rows, r_hi = min(d.NR, r_lo + seg_rows) - 1;
+  LabelState ls;
+  label_init(ls);
+  int first_cum;
+  gc_col_label_run<false>(d, P, c, r_lo, r_hi, ls, first_cum);
+  int32_t* o = sum + ((size_t)blockIdx.y * GC_NSUM) * d.NC + c;
+  o[0 * (size_t)d.NC] = first_cum;
+  o[1 * (size_t)d.NC] = ls.dense;
+  o[2 * (size_t)d.NC] = ls.cnt;
+  o[3 * (size_t)d.NC] = ls.last_val;
+  o[4 * (size_t)d.NC] = ls.cum;
+  o[5 * (size_t)d.NC] = ls.poisoned ? 1 : 0;
+  o[6 * (size_t)d.NC] = ls.na_cnt;
+}
+
+// state after a segment, from the state before it and the segment's summary (rows = its length)
+__device__ __forceinline__ void gc_fold(LabelState& s, const int32_t* __restrict__ o, size_t stride, int rows) {
+  if (s.poisoned) { s.na_cnt += rows; return; }   // cumsum is NA: every cell below is in the NA group
+  const int first_cum = o[0], dense = o[stride], cnt = o[2 * stride], last_val = o[3 * stride];
+  if (first_cum >= 0) {
+    // only the first valid cell's "new label?" depends on what came before; all later ones compare inside
+    const bool first_new = !s.have_last || s.cum + first_cum != s.last_val;
+    s.cnt = (dense == 1 && !first_new) ? s.cnt + cnt : cnt;
+    s.dense += dense - (first_new ? 0 : 1);
+    s.last_val = s.cum + last_val;
+    s.have_last = true;
+  }
+  s.cum += o[4 * stride];
+  s.poisoned = o[5 * stride] != 0;
+  s.na_cnt += o[6 * stride];
+}
+
+__global__ void __launch_bounds__(GC_THREADS) k_gc_cols_label(GridDims d, GcPtrs P, int seg_rows, const int32_t* __restrict__ sum) {
+  const int c = blockIdx.x * GC_THREADS + threadIdx.x;
+  if (c >= d.NC) return;
+  const int r_lo = blockIdx.y * seg_rows, r_hi = min(d.NR, r_lo + seg_rows) - 1;
+  LabelState ls;
+  label_init(ls);
+  for (int j = 0; j < (int)blockIdx.y; ++j)
+    gc_fold(ls, sum + ((size_t)j * GC_NSUM) * d.NC + c, (size_t)d.NC, seg_rows);
+  int first_cum;
+  gc_col_label_run<true>(d, P, c, r_lo, r_hi, ls, first_cum);
 }
 
 }  // namespace
@@ -330,9 +410,14 @@ int run_slope_gc(litap_grid* g, double grid_m) {
   P.rdir = g->gc_u8[0]; P.cdir = g->gc_u8[1];
   P.rn = g->gc_i32[0]; P.rcell = g->gc_i32[1]; P.cn = g->gc_i32[2]; P.ccell = g->gc_i32[3];
   KERNEL("k_gc_rows", k_gc_rows<<<(d.NR + GR_WARPS - 1) / GR_WARPS, GR_WARPS * 32, 0, st>>>(g->elev, d, grid_m, P));
-  const int cblk = (d.NC + GC_THREADS - 1) / GC_THREADS;
+  const int seg_rows = d.NR < 2048 ? 64 : 512;
+  const int nseg = (d.NR + seg_rows - 1) / seg_rows;
+  if (!g->gc_sum) g->gc_sum = (int32_t*)pool_alloc((size_t)nseg * GC_NSUM * d.NC * sizeof(int32_t));
+  if (!g->gc_sum) return set_error(LITAP_ENOMEM, "device allocation failed (slope_gc summaries)");
+  const dim3 cgrid((d.NC + GC_THREADS - 1) / GC_THREADS, nseg);
   KERNEL("k_gc_cols_stencil", k_gc_cols_stencil<<<dim3((d.NC + 255) / 256, d.NR), 256, 0, st>>>(g->elev, d, grid_m, P));
-  KERNEL("k_gc_cols_fix", k_gc_cols_fix<<<cblk, GC_THREADS, 0, st>>>(d, P));
-  KERNEL("k_gc_cols_label", k_gc_cols_label<<<cblk, GC_THREADS, 0, st>>>(d, P));
+  KERNEL("k_gc_cols_fix", k_gc_cols_fix<<<cgrid, GC_THREADS, 0, st>>>(d, P, seg_rows));
+  KERNEL("k_gc_cols_sum", k_gc_cols_sum<<<cgrid, GC_THREADS, 0, st>>>(d, P, seg_rows, g->gc_sum));
+  KERNEL("k_gc_cols_label", k_gc_cols_label<<<cgrid, GC_THREADS, 0, st>>>(d, P, seg_rows, g->gc_sum));
   return LITAP_OK;
 }

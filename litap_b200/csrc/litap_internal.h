@@ -56,6 +56,7 @@ struct litap_grid {
   double* gc_f64[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   uint8_t* gc_u8[2] = {nullptr, nullptr};
   int32_t* gc_i32[4] = {nullptr, nullptr, nullptr, nullptr};
+  int32_t* gc_sum = nullptr;   // slope_gc: per (column, row segment) label summaries (gc.cu)
   int64_t npits = 0;
   bool have_ddir = false, have_shed = false;
   // row-band geometry: rows [own_lo, own_hi) are this grid's own cells; row 0 / NR-1 are the NA ring

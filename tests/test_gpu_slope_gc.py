@@ -94,6 +94,27 @@ def test_degenerate_surfaces():
     assert_gc_parity(holes, 1.0, "terraces with holes")
 
 
+@pytest.mark.parametrize("nr", [200, 2100])   # 64-row and 512-row column segments (gc.cu: GC_SEG)
+def test_degenerate_surfaces_across_column_segments(nr):
+    """Columns are swept in row segments: zero runs and NA-poisoned stretches that cross segment borders."""
+    nc = 45
+    yy, xx = np.mgrid[0:nr, 0:nc]
+    assert_gc_parity(oracle.add_buffer(np.full((nr, nc), 7.0)), 5.0, "tall flat")
+    assert_gc_parity(oracle.add_buffer(100.0 + xx * 0.5), 5.0, "tall plane east")        # whole columns of zeros
+    terr = 100.0 + (xx // 7) * 1.0 + (yy // 50) * 2.0 * np.where((yy // 50) % 2 == 0, 1, -1)
+    assert_gc_parity(oracle.add_buffer(terr), 1.0, "tall terraces")                       # 50-row zero runs, both signs
+    holes = oracle.add_buffer(terr)
+    holes[60:70, 5:9] = np.nan
+    holes[nr // 2, 20] = np.nan
+    holes[nr - 70:nr - 3, 30] = np.nan                                                    # NA down to the south edge
+    holes[1:66, 33] = np.nan                                                              # NA from the north edge across a border
+    assert_gc_parity(holes, 1.0, "tall terraces with holes")
+    rng = np.random.default_rng(nr)
+    rag = np.round(rng.random((nr, nc)) * 0.3, 1) + 50.0                                  # many ties, short runs everywhere
+    rag[rng.random((nr, nc)) < 0.02] = np.nan
+    assert_gc_parity(oracle.add_buffer(rag), 2.0, "tall ragged")
+
+
 def test_device_resident_matches_host_call():
     e = oracle.synth_dem(300, 300, seed=9)
     g = lb.DeviceGrid(*e.shape)
