@@ -106,6 +106,9 @@ __device__ __forceinline__ void gc_row_cell(double e5, double n4, double n6, dou
 }
 __device__ __forceinline__ int gc_top(unsigned m) { return 31 - __clz(m); }   // highest set bit, m != 0
 
+// class of a gradient value as three warp masks (bit = lane): NA, zero, positive
+struct GcMasks { unsigned na, z, pos; };
+
 __global__ void __launch_bounds__(GR_WARPS * 32) k_gc_rows(const double* __restrict__ elev, GridDims d, double grid_m, GcPtrs P) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -117,35 +120,40 @@ __global__ void __launch_bounds__(GR_WARPS * 32) k_gc_rows(const double* __restr
   const unsigned lt = le >> 1;             // lanes <  mine
   auto ld = [&](int cb) { const int c = cb + lane; return c < d.NC ? __ldg(row + c) : gc_na(); };
   const double e_west = gc_elev_lin(elev, d, r, -1), e_east = gc_elev_lin(elev, d, r, d.NC);
-  // carried state, identical in all lanes
-  double c_elast = e_west;         // elevation of the column before the chunk
-  double c_glast = gc_na();        // raw gradient of that column
-  double c_runval = 0;
-  bool c_inrun = false;
-  bool c_lag_na = true, c_lag_pos = false, c_poisoned = false, c_have_last = false;
+  // gradient / curvature of the chunk at cb from its elevations, the last one before it and the chunk after it;
+  // lanes past the last column come out NA (that is what the cell after the last one reads as)
+  auto grad = [&](int cb, double Ec, double e_before, double En, double& ge, double& cr, GcMasks& m) {
+    const int c = cb + lane;
+    double n4 = __shfl_up_sync(FULL, Ec, 1), n6 = __shfl_down_sync(FULL, Ec, 1);
+    const double en0 = __shfl_sync(FULL, En, 0);
+    if (lane == 0) n4 = e_before;
+    if (lane == 31) n6 = en0;
+    if (c == d.NC - 1) n6 = e_east;
+    gc_row_cell(Ec, n4, n6, two_g, g2, ge, cr);
+    if (c >= d.NC) ge = gc_na();
+    m.na = __ballot_sync(FULL, ge != ge);
+    m.z = __ballot_sync(FULL, ge == 0.0);
+    m.pos = __ballot_sync(FULL, ge > 0);
+  };
+  // carried state, identical in all lanes (bits 0/1)
+  unsigned c_prev_na = 1, c_prev_pos = 0, c_inrun = 0;      // class of the raw gradient before the chunk
+  unsigned c_run_na = 0, c_run_pos = 0;                     // value of the zero run that is open (while c_inrun)
+  unsigned c_lag_na = 1, c_lag_pos = 0;
+  bool c_poisoned = false, c_have_last = false;
   int c_cum = 0, c_dense = 0, c_last_val = 0, c_cnt = 0, c_na = 0;
-  double E0 = ld(0), E1 = ld(32), E2 = ld(64);
+  double E0 = ld(0), E1 = ld(32), E2 = ld(64), E3 = ld(96);
+  double ge, cr;
+  GcMasks m;
+  grad(0, E0, e_west, E1, ge, cr, m);
   for (int cb = 0; cb < d.NC; cb += 32) {
-    const double E3 = ld(cb + 96);   // three chunks ahead of the arithmetic
+    const double E4 = ld(cb + 128);   // four chunks ahead of the arithmetic
     const int c = cb + lane;
     const bool active = c < d.NC;
-    // gradient, magnitude, curvature
-    const double e5 = E0;
-    double n4 = __shfl_up_sync(FULL, E0, 1);
-    double n6 = __shfl_down_sync(FULL, E0, 1);
-    const double e1_0 = __shfl_sync(FULL, E1, 0), e1_1 = __shfl_sync(FULL, E1, 1), e0_31 = __shfl_sync(FULL, E0, 31);
-    if (lane == 0) n4 = c_elast;
-    if (lane == 31) n6 = e1_0;
-    if (c == d.NC - 1) n6 = e_east;
-    double ge, cr;
-    gc_row_cell(e5, n4, n6, two_g, g2, ge, cr);
-    if (!active) ge = gc_na();
-    // raw gradient of the first column of the next chunk (the sign rule looks one cell ahead)
-    double g_next0 = gc_na();
-    if (cb + 32 < d.NC) {
-      double crx;
-      gc_row_cell(e1_0, e0_31, cb + 33 < d.NC ? e1_1 : e_east, two_g, g2, g_next0, crx);
-    }
+    const unsigned colmask = d.NC - cb >= 32 ? FULL : (1u << (d.NC - cb)) - 1u;
+    // the next chunk's gradients: the sign rule looks one cell ahead
+    double ge_n, cr_n;
+    GcMasks mn;
+    grad(cb + 32, E1, __shfl_sync(FULL, E0, 31), E2, ge_n, cr_n, mn);
     const size_t o = (size_t)r * d.pitch + c;
     if (active) {
       double ar = fabs(ge);
@@ -153,40 +161,38 @@ __global__ void __launch_bounds__(GR_WARPS * 32) k_gc_rows(const double* __restr
       P.sgr[o] = ar;
       P.scr[o] = cr;
     }
-    // ---- zero signs (fix_step as a scan) ----
-    const bool z = active && ge == 0.0;
-    const unsigned zmask = __ballot_sync(FULL, z);
-    double g_prev = __shfl_up_sync(FULL, ge, 1);
-    double g_nxt = __shfl_down_sync(FULL, ge, 1);
-    if (lane == 0) g_prev = c_glast;
-    if (lane == 31) g_nxt = g_next0;
-    const bool prev_zero = lane > 0 ? ((zmask >> (lane - 1)) & 1u) != 0 : c_inrun;
-    const bool runstart = z && !prev_zero;
-    const double rv_prev = g_prev > 0 ? GC_TINY : -GC_TINY;
-    const double rv_next = g_nxt != g_nxt ? gc_na() : (g_nxt > 0 ? GC_TINY : -GC_TINY);
-    const double rv = g_prev == g_prev ? rv_prev : (g_nxt == 0.0 ? GC_TINY : rv_next);
-    const unsigned sbelow = __ballot_sync(FULL, runstart) & le;
-    const double rv_s = __shfl_sync(FULL, rv, sbelow ? gc_top(sbelow) : lane);
-    const double v = z ? (sbelow ? rv_s : c_runval) : ge;
-    // ---- run labels (label_step as a scan) ----
-    const bool ena = e5 != e5;
-    const bool s_na = v != v, pos = v > 0;
-    int lag_na = __shfl_up_sync(FULL, (int)s_na, 1), lag_pos = __shfl_up_sync(FULL, (int)pos, 1);
-    if (lane == 0) { lag_na = c_lag_na; lag_pos = c_lag_pos; }
-    const unsigned pmask = __ballot_sync(FULL, active && !lag_na && s_na);
-    const bool poisoned = c_poisoned || (pmask & le) != 0;
-    const unsigned imask = __ballot_sync(FULL, active && !poisoned && (lag_na || (int)pos != lag_pos));
-    const int cum = c_cum + __popc(imask & le);
-    const bool valid = active && !ena && !poisoned;
-    const unsigned vmask = __ballot_sync(FULL, valid);
+    // ---- zero signs (fix_step as mask arithmetic) ----
+    const unsigned p_na = (m.na << 1) | c_prev_na, p_pos = (m.pos << 1) | c_prev_pos, p_z = (m.z << 1) | c_inrun;
+    const unsigned n_na = (m.na >> 1) | (mn.na << 31), n_pos = (m.pos >> 1) | (mn.pos << 31), n_z = (m.z >> 1) | (mn.z << 31);
+    const unsigned rs = m.z & ~p_z;                                             // run starts
+    const unsigned rv_na = p_na & ~n_z & n_na;                                  // value a run starting here takes: NA ...
+    const unsigned rv_pos = (~p_na & p_pos) | (p_na & (n_z | (~n_na & n_pos)));  // ... or +0.00001 (else -0.00001)
+    const bool z = (m.z >> lane) & 1u;
+    const unsigned sb = rs & le;
+    const int s_at = sb ? gc_top(sb) : 0;
+    const bool run_na = sb ? (rv_na >> s_at) & 1u : c_run_na != 0;
+    const bool run_pos = sb ? (rv_pos >> s_at) & 1u : c_run_pos != 0;
+    const double v = z ? (run_na ? gc_na() : (run_pos ? GC_TINY : -GC_TINY)) : ge;
+    // ---- run labels (label_step as mask arithmetic) ----
+    const bool ena = E0 != E0;
+    const bool s_na = z ? run_na : ((m.na >> lane) & 1u) != 0;
+    const bool pos = z ? (!run_na && run_pos) : ((m.pos >> lane) & 1u) != 0;
+    const unsigned v_na = __ballot_sync(FULL, s_na), v_pos = __ballot_sync(FULL, pos), e_na = __ballot_sync(FULL, ena);
+    const unsigned lag_na = (v_na << 1) | c_lag_na, lag_pos = (v_pos << 1) | c_lag_pos;
+    const unsigned pmask = colmask & ~lag_na & v_na;                            // (NA | FALSE) = NA: cumsum is NA from here on
+    const unsigned pz = c_poisoned ? FULL : (pmask ? ~((pmask & (0u - pmask)) - 1u) : 0u);   // poisoned lanes
+    const unsigned imask = colmask & ~pz & (lag_na | (v_pos ^ lag_pos));        // cumsum increments
+    const unsigned vmask = colmask & ~e_na & ~pz;                               // cells with a label
+    const bool valid = (vmask >> lane) & 1u;
+    const int inc_le = __popc(imask & le);
+    const int cum = c_cum + inc_le;
     const unsigned vlow = vmask & lt;
-    const int cum_pv = __shfl_sync(FULL, cum, vlow ? gc_top(vlow) : lane);
-    const bool newlab = valid && (vlow ? cum != cum_pv : (!c_have_last || cum != c_last_val));
+    // a label starts where the cumsum moved since the previous labelled cell
+    const bool newlab = valid && (vlow ? (imask & le & ~((2u << gc_top(vlow)) - 1u)) != 0 : (!c_have_last || cum != c_last_val));
     const unsigned nlmask = __ballot_sync(FULL, newlab);
     const unsigned nlb = nlmask & le;
     const int dense = c_dense + __popc(nlb);
     const int cnt = nlb ? __popc(vmask & le & ~((1u << gc_top(nlb)) - 1u)) : c_cnt + __popc(vmask & le);
-    const unsigned colmask = __ballot_sync(FULL, active);
     const int na_cnt = c_na + __popc(~vmask & colmask & le);
     if (active) {
       P.sgre[o] = v;
@@ -195,20 +201,17 @@ __global__ void __launch_bounds__(GR_WARPS * 32) k_gc_rows(const double* __restr
       P.rcell[o] = valid ? cnt : (ena ? 0 : na_cnt);
     }
     // ---- carry to the next chunk ----
-    c_elast = e0_31;
-    c_glast = __shfl_sync(FULL, ge, 31);
-    c_inrun = (zmask >> 31) != 0;
-    c_runval = __shfl_sync(FULL, v, 31);   // only read while c_inrun
-    c_lag_na = __shfl_sync(FULL, (int)s_na, 31) != 0;
-    c_lag_pos = __shfl_sync(FULL, (int)pos, 31) != 0;
-    c_poisoned = c_poisoned || pmask != 0;
+    c_prev_na = m.na >> 31; c_prev_pos = m.pos >> 31; c_inrun = m.z >> 31;
+    if (rs) { const int t = gc_top(rs); c_run_na = (rv_na >> t) & 1u; c_run_pos = (rv_pos >> t) & 1u; }
+    c_lag_na = v_na >> 31; c_lag_pos = v_pos >> 31;
+    if (vmask) { c_last_val = c_cum + __popc(imask & ((2u << gc_top(vmask)) - 1u)); c_have_last = true; }
     c_cum += __popc(imask);
-    const int cum_lastvalid = __shfl_sync(FULL, cum, vmask ? gc_top(vmask) : 0);
-    if (vmask) { c_last_val = cum_lastvalid; c_have_last = true; }
+    c_poisoned = c_poisoned || pmask != 0;
     c_dense += __popc(nlmask);
     c_cnt = nlmask ? __popc(vmask & ~((1u << gc_top(nlmask)) - 1u)) : c_cnt + __popc(vmask);
     c_na += __popc(~vmask & colmask);
-    E0 = E1; E1 = E2; E2 = E3;
+    E0 = E1; E1 = E2; E2 = E3; E3 = E4;
+    ge = ge_n; cr = cr_n; m = mn;
   }
 }
 
