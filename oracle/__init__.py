@@ -40,6 +40,9 @@ def lib():
         L.oracle_form.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 5 + [C.c_int]
         L.oracle_weti.argtypes = [_f64p, _u8p, _f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 4
         L.oracle_slope_gc.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_double] + [_f64p] * 6 + [_u8p] * 2 + [_i32p] * 4
+        L.oracle_relz.argtypes = ([C.c_int64, C.c_int64, _f64p, _u8p, _i32p, _i32p, _i32p, _i32p, _f64p, _u8p, _i32p, _i32p, _i32p,
+                                   C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
+                                   C.c_double, C.POINTER(C.c_void_p)])
         L.oracle_r_round.argtypes = [C.c_double, C.c_int]
         L.oracle_r_round.restype = C.c_double
         L.oracle_synth_dem.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_uint32,
@@ -125,6 +128,38 @@ def slope_gc(elev_b, grid):
     out.update({k: np.empty(e.shape, np.uint8) for k in GC_U8})
     out.update({k: np.empty(e.shape, np.int32) for k in GC_I32})
     lib().oracle_slope_gc(e, e.shape[0], e.shape[1], float(grid), *[out[k] for k in GC_F64 + GC_U8 + GC_I32])
+    return out
+
+
+RELZ_NAMES = ("st_row", "st_col", "st_elev", "z2st", "n2st", "cr_row", "cr_col", "cr_elev", "z2cr", "n2cr",
+              "pit_row", "pit_col", "pit_elev", "z2pit", "n2pit", "peak_row", "peak_col", "peak_elev", "z2peak", "n2peak",
+              "z2top", "zpit2peak", "zcr2st", "zcr2pit", "ztop2pit", "ncr2st", "pmin2max", "pctz2st", "pctz2pit",
+              "pctz2top", "pctn2st", "l2pit", "l2peak", "lpit2peak", "ppit2peakl", "l2str", "l2div", "lstr2div",
+              "pstr2divl")
+
+
+def relz_args(db, idb, pond):
+    """The array arguments shared by oracle.relz and litap_b200.relz: buffered 2-D grids, integers with 0 = NA.
+    db: elev, ddir, drec, upslope, fill_shed, local_shed; idb: elev, ddir, drec, upslope, inv_local_shed;
+    pond (or None): shedno, pit_row, pit_col, pit_elev (buffered row / col)."""
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    i = lambda a: np.ascontiguousarray(np.nan_to_num(np.asarray(a, dtype=np.float64), nan=0.0), dtype=np.int32)
+    u = lambda a: np.ascontiguousarray(np.nan_to_num(np.asarray(a, dtype=np.float64), nan=0.0), dtype=np.uint8)
+    grids = [f(db["elev"]), u(db["ddir"]), i(db["drec"]), i(db["upslope"]), i(db["fill_shed"]), i(db["local_shed"]),
+             f(idb["elev"]), u(idb["ddir"]), i(idb["drec"]), i(idb["upslope"]), i(idb["inv_local_shed"])]
+    if pond is None or len(pond["shedno"]) == 0:
+        return grids, 0, [None] * 4
+    return grids, len(pond["shedno"]), [i(pond["shedno"]), i(pond["pit_row"]), i(pond["pit_col"]), f(pond["pit_elev"])]
+
+
+def relz(db, idb, pond, str_val, ridge_val, grid):
+    """calc_relz + calc_length (R/form_03_calc_relz.R, R/form_04_calc_length.R) -> dict of RELZ_NAMES grids."""
+    grids, npond, parr = relz_args(db, idb, pond)
+    NR, NC = grids[0].shape
+    out = {k: np.empty((NR, NC)) for k in RELZ_NAMES}
+    ptrs = (C.c_void_p * len(RELZ_NAMES))(*[out[k].ctypes.data for k in RELZ_NAMES])
+    pp = [None if a is None else a.ctypes.data for a in parr]
+    lib().oracle_relz(NR, NC, *grids, npond, *pp, float(str_val), float(ridge_val), float(grid), ptrs)
     return out
 
 

@@ -9,6 +9,8 @@ Sources decoded (formats per SURVEY.md Appendix B), no R needed:
   inst/extdata/testELEV/flow/dem_fill.rds               uncompressed XDR RDS
   inst/extdata/testELEV/flow/dem_inverted.rds
   inst/extdata/testELEV/form/dem_form.rds
+  inst/extdata/testELEV/form/dem_length.rds             relief + slope length (calc_relz, calc_length)
+  inst/extdata/testELEV/flow/stats_pond.rds             pond table (pit of every local shed)
   data/test_dem.rda                                     bzip2 RData (RDX2)
   tests/testthat/_snaps/02_flow_internal.md             testthat json2 snapshots
   tests/testthat/_snaps/10_long_tests.md
@@ -183,7 +185,8 @@ def main():
 
     # ---- shipped full-grid run (grid=5, max_area=1, max_depth=0.1)
     for name, rel in (("dem_fill", "flow/dem_fill.rds"), ("dem_inverted", "flow/dem_inverted.rds"),
-                      ("dem_form", "form/dem_form.rds")):
+                      ("dem_form", "form/dem_form.rds"), ("dem_length", "form/dem_length.rds"),
+                      ("stats_pond", "flow/stats_pond.rds")):
         df = read_rds(f"{REF}/inst/extdata/testELEV/{rel}")
         cols = {n: col_to_f64(v) for n, v in df.items() if isinstance(v, np.ndarray)}
         np.savez_compressed(f"{OUT}/{name}.npz", **cols)

@@ -186,3 +186,26 @@ def test_slope_gc_test_dem_kats(golden):
     cell = o["hill_c_cell"][1:-1, 1:-1][:, 121]
     assert (col[0:10] == 1).all() and (cell[0:10] == np.arange(1, 11)).all()
     assert (col[58:68] == 5).all() and (cell[58:68] == np.arange(1, 11)).all()
+
+
+# ---- calc_relz + calc_length against form/dem_length.rds ------------------------------
+def test_relz_oracle_reproduces_dem_length_golden():
+    """All 39 relief / length columns of the shipped testELEV run (str_val = ridge_val = 1000, grid = 5),
+    from the shipped dem_fill / dem_inverted / stats_pond: exact doubles."""
+    import relz_fixture as rf
+    db, idb, pond, want = rf.load()
+    got = oracle.relz(db, idb, pond, rf.STR_VAL, rf.RIDGE_VAL, rf.GRID)
+    rf.assert_matches_golden(got, want, oracle.RELZ_NAMES)
+
+
+def test_relz_oracle_without_pond_uses_pit_cells():
+    """calc_pit3(pond = NULL) takes the ddir == 5 cells (R/form_03_calc_relz.R:426-430): with the pond table
+    reduced to exactly those pits nothing may change."""
+    import relz_fixture as rf
+    db, idb, pond, _ = rf.load()
+    pits = np.argwhere(db["ddir"] == 5)
+    sub = {"shedno": np.array([db["local_shed"][r, c] for r, c in pits]), "pit_row": pits[:, 0] + 1.0,
+           "pit_col": pits[:, 1] + 1.0, "pit_elev": np.array([db["elev"][r, c] for r, c in pits])}
+    a = oracle.relz(db, idb, sub, 300.0, 200.0, rf.GRID)
+    b = oracle.relz(db, idb, None, 300.0, 200.0, rf.GRID)
+    rf.assert_same(a, b, oracle.RELZ_NAMES)
