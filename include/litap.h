@@ -54,6 +54,7 @@ typedef struct litap_timings {
   int64_t flat_cells, patch_cells, npits;
   int64_t kernel_launches; /* kernels of this library launched by the call */
   float gc_ms;      /* slope_gc */
+  float relz_ms;    /* calc_relz + calc_length (device part of litap_relz) */
 } litap_timings;
 
 int litap_init(int device);        /* selects the device and creates the stream; idempotent */
@@ -99,6 +100,23 @@ int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double grid,
                    double* sgre, double* sgr, double* sgcn, double* sgc, double* scr, double* scc,
                    uint8_t* hill_r_dir, uint8_t* hill_c_dir, int32_t* hill_r_n, int32_t* hill_r_cell,
                    int32_t* hill_c_n, int32_t* hill_c_cell);
+
+/* calc_relz + calc_length (R/form_03_calc_relz.R:3-48,194-276,424-514; R/form_04_calc_length.R:3-35; called
+ * R/form_mapper.R:154,177) on the buffered grids form_mapper works on: db = the filled DEM of flow_mapper
+ * (elev, ddir, drec, upslope, fill_shed, local_shed), idb = the inverted DEM (elev, ddir, drec, upslope,
+ * inv_local_shed), the pond table = pit of every local shed (npond = 0: calc_pit3's "ddir == 5 cells" branch,
+ * ddir required; otherwise ddir may be NULL).  Integer inputs: 0 = NA; drec is R's 1-based seqno.
+ * out[k], k < LITAP_RELZ_NOUT (any may be NULL): the columns calc_length returns, in the order of
+ * litap_relz_names(); NaN = NA; *_row / *_col are buffered 1-based numbers as in R before remove_buffer().
+ * Errors: LITAP_EARG for drec / shed numbers outside the grid or flow paths that never end. */
+#define LITAP_RELZ_NOUT 39
+int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint8_t* ddir, const int32_t* drec,
+               const int32_t* upslope, const int32_t* fill_shed, const int32_t* local_shed,
+               const double* ielev, const uint8_t* iddir, const int32_t* idrec, const int32_t* iupslope,
+               const int32_t* inv_local_shed, int64_t npond, const int32_t* pond_shedno,
+               const int32_t* pond_row, const int32_t* pond_col, const double* pond_elev, double str_val,
+               double ridge_val, double grid, double* const* out);
+const char* litap_relz_names(void);   /* the LITAP_RELZ_NOUT column names, comma-separated */
 
 /* Fused composite (ddir -> shed/upslope/ridge -> form) with one upload of elev; the
  * intermediate ddir never leaves the device.  Any output may be NULL (then not downloaded). */

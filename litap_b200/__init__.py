@@ -11,6 +11,7 @@ from .api import (  # noqa: F401
     add_buffer,
     calc_ddir2,
     calc_form,
+    calc_relz,
     calc_shed4,
     calc_weti2,
     slope_gc,

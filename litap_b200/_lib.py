@@ -11,7 +11,7 @@ _lib = None
 SYMBOLS = [
     "litap_init", "litap_shutdown", "litap_last_error", "litap_version", "litap_get_timings",
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
-    "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_slope_gc", "litap_flow_form",
+    "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
     "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
@@ -31,7 +31,7 @@ class Timings(C.Structure):
                 ("total_ms", C.c_float), ("plateau_rounds", C.c_int), ("weti_waves", C.c_int),
                 ("flat_cells", C.c_int64),
                 ("patch_cells", C.c_int64), ("npits", C.c_int64), ("kernel_launches", C.c_int64),
-                ("gc_ms", C.c_float)]
+                ("gc_ms", C.c_float), ("relz_ms", C.c_float)]
 
     def asdict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -60,6 +60,9 @@ def load():
     L.litap_form.argtypes = [vp, i64, i64, dbl] + [vp] * 5
     L.litap_weti.argtypes = [vp, vp, vp, i64, i64, dbl] + [vp] * 4
     L.litap_slope_gc.argtypes = [vp, i64, i64, dbl] + [vp] * 12
+    L.litap_relz.argtypes = [i64, i64] + [vp] * 11 + [i64] + [vp] * 4 + [dbl] * 3 + [vp]
+    L.litap_relz_names.restype = C.c_char_p
+    L.litap_relz_names.argtypes = []
     L.litap_flow_form.argtypes = [vp, i64, i64, dbl, ci, vp, vp, vp, vp, vp, C.POINTER(i64)] + [vp] * 5
     L.litap_grid_create.argtypes = [i64, i64, C.POINTER(vp)]
     L.litap_grid_destroy.argtypes = [vp]

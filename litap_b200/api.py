@@ -154,6 +154,45 @@ def slope_gc(db, grid=1):
     return out
 
 
+def relz_names():
+    return tuple(lib().litap_relz_names().decode().split(","))
+
+
+def _i32_na0(a):
+    return np.ascontiguousarray(np.nan_to_num(np.asarray(a, dtype=np.float64), nan=0.0), dtype=np.int32)
+
+
+def calc_relz(db, idb, str_val, ridge_val, pond=None, grid=1):
+    """calc_relz() followed by calc_length() (R/form_03_calc_relz.R:3-48, R/form_04_calc_length.R:3-35; the two
+    steps of form_mapper after calc_weti, R/form_mapper.R:154,177).  db / idb: dicts of buffered 2-D grids like
+    the data frames form_mapper passes (db: elev, ddir, drec, upslope, fill_shed, local_shed; idb: elev, ddir,
+    drec, upslope, inv_local_shed; NaN = NA, drec = 1-based seqno); pond: shedno, pit_row, pit_col, pit_elev
+    (buffered row / col) or None.  Returns a dict of the 39 relief / length columns (NaN = NA)."""
+    f = _f64
+    u8 = lambda a: np.ascontiguousarray(np.nan_to_num(np.asarray(a, dtype=np.float64), nan=0.0), dtype=np.uint8)
+    e = f(db["elev"])
+    if e.ndim != 2:
+        raise LitapError("calc_relz: db$elev must be a 2-D buffered grid")
+    NR, NC = e.shape
+    grids = [e, u8(db["ddir"]) if "ddir" in db else None, _i32_na0(db["drec"]), _i32_na0(db["upslope"]),
+             _i32_na0(db["fill_shed"]), _i32_na0(db["local_shed"]), f(idb["elev"]), u8(idb["ddir"]),
+             _i32_na0(idb["drec"]), _i32_na0(idb["upslope"]), _i32_na0(idb["inv_local_shed"])]
+    for a in grids:
+        if a is not None and a.shape != (NR, NC):
+            raise LitapError("calc_relz: all grids must have the shape of db$elev")
+    npond, parr = 0, [None] * 4
+    if pond is not None and len(pond["shedno"]):
+        npond = len(pond["shedno"])
+        parr = [_i32_na0(pond["shedno"]), _i32_na0(pond["pit_row"]), _i32_na0(pond["pit_col"]), f(pond["pit_elev"])]
+    names = relz_names()
+    out = {k: np.empty((NR, NC)) for k in names}
+    ptrs = (C.c_void_p * len(names))(*[out[k].ctypes.data for k in names])
+    p = lambda a: None if a is None else a.ctypes.data
+    check(lib().litap_relz(NR, NC, *[p(a) for a in grids], npond, *[p(a) for a in parr], float(str_val),
+                           float(ridge_val), float(grid), ptrs))
+    return out
+
+
 def calc_weti2(db, grid, verbose=False):
     """R/form_02b_calc_weti.R:3-110.  Needs elev, ddir, upslope; returns db + qarea1/2, qweti1/2."""
     NR, NC = _dims(db)

@@ -118,6 +118,20 @@ LITAP_HD double r_round3(double x) {
   return x < 0 ? -r : r;
 }
 
+// base R round(x, 1), same algorithm (calc_length rounds its lengths to 0.1): the "enough digits already"
+// cut-off log10(2)*(0.5+logb(x)) + 1 > DBL_DIG is logb(x) >= 47
+LITAP_HD double r_round1(double x) {
+  if (is_nan(x) || x == 0.0) return x;
+  double ax = x < 0 ? -x : x;
+  if (ax >= 140737488355328.0 /* 2^47 */) return x;
+  double x10 = 10.0 * ax, i10 = floor(x10);
+  double xd = i10 / 10.0, xu = ceil(x10) / 10.0;
+  double du = xu - ax, dd = ax - xd;
+  bool even = (((long long)i10) & 1LL) == 0;
+  double r = (dd < du || (dd == du && even)) ? xd : xu;
+  return x < 0 ? -r : r;
+}
+
 // ---------------------------------------------------------------------------------------------
 // calc_form for one cell (R/form_01_calc_form.R:9-47).  e[n] = elev_n (NOT yet *100), n = 1..9,
 // e[5] = centre.  sin_t / cos_t: tables of sin((A*pi)/180), cos((A*pi)/180) for integer A = 0..180,
