@@ -6,11 +6,12 @@
 #   calc_form(db, grid, verbose)   replaces R/form_01_calc_form.R:4-67    (caller  R/form_mapper.R:103)
 #   calc_weti2(db, grid, verbose)  replaces R/form_02b_calc_weti.R:3-110  (caller  R/form_mapper.R:127)
 #   slope_gc(db, grid)             replaces R/flow_05_slope_gc.R:73-164   (caller  R/flow_mapper.R:307)
+#   calc_relz_length(db, idb, ...) replaces R/form_03_calc_relz.R:3-48 + R/form_04_calc_length.R:3-35 (callers R/form_mapper.R:154,177)
 #
 # Every function calls the CUDA library through .Call unconditionally: there is no CPU fallback
 # (an error from the library, e.g. "no CUDA device", surfaces as an R error).  flow_mapper() and
 # form_mapper() keep their signatures and their output column layout; pit removal (flow_03/04),
-# relief and the I/O stay the reference's R code.
+# the I/O stays the reference's R code.
 #
 # `db` is the reference's buffered tibble: one row per cell of the (nrow+2) x (ncol+2) grid,
 # sorted by seqno (R/LITAP_load.R:273-332).
@@ -74,6 +75,25 @@ slope_gc <- function(db, grid = 1) {
   r <- .Call("litap_R_slope_gc", as.double(db$elev), d[1], d[2], as.double(grid))
   for (n in names(r)) db[[n]] <- r[[n]]                # same twelve columns, same order as the reference appends them
   db
+}
+
+# calc_relz() and calc_length() in one call: form_mapper() (R/form_mapper.R:154,177) may replace
+#   db_relz <- calc_relz(db, idb, str_val, ridge_val, pond, verbose); db_length <- calc_length(db, db_relz, grid, verbose)
+# by db_length <- calc_relz_length(db, idb, str_val, ridge_val, pond, grid); db_relz is db_length without the
+# eight length columns (l2pit .. pstr2divl).  db / idb are the buffered tibbles form_mapper holds.
+calc_relz_length <- function(db, idb, str_val, ridge_val, pond = NULL, grid = 1, verbose = FALSE) {
+  d <- litap_dims(db)
+  if (verbose) message("  Calculating relief and slope lengths on the GPU")
+  if (is.null(pond) || nrow(pond) == 0)
+    pond <- data.frame(shedno = integer(0), pit_row = integer(0), pit_col = integer(0), pit_elev = double(0))
+  r <- .Call("litap_R_relz", d[1], d[2],
+             list(as.double(db$elev), db$ddir, db$drec, db$upslope, db$fill_shed, db$local_shed),
+             list(as.double(idb$elev), idb$ddir, idb$drec, idb$upslope, idb$inv_local_shed),
+             list(pond$shedno, pond$pit_row, pond$pit_col, pond$pit_elev),
+             as.double(str_val), as.double(ridge_val), as.double(grid))
+  out <- db[, c("seqno", "elev", "row", "col", "buffer", "fill_shed")]
+  for (n in names(r)) out[[n]] <- r[[n]]
+  out
 }
 
 # The second traversal of flow_mapper() (R/flow_mapper.R:343-377) may skip the R-side invert()

@@ -179,6 +179,58 @@ SEXP litap_R_slope_gc(SEXP elev, SEXP nrow, SEXP ncol, SEXP grid) {
   return out;
 }
 
+/* calc_relz + calc_length: db / idb columns as vectors over the buffered grid (integers: NA -> 0 here),
+ * the pond table (may have 0 rows); returns the 39 columns of litap_relz_names() as doubles (NaN -> NA) */
+static int* na0(SEXP v, R_xlen_t n, const char* what) {
+  if (XLENGTH(v) != n) Rf_error("litap_R_relz: %s has the wrong length", what);
+  SEXP iv = PROTECT(Rf_coerceVector(v, INTSXP));
+  int* o = (int*)R_alloc((size_t)(n ? n : 1), sizeof(int));
+  for (R_xlen_t i = 0; i < n; ++i) o[i] = INTEGER(iv)[i] == NA_INTEGER ? 0 : INTEGER(iv)[i];
+  UNPROTECT(1);
+  return o;
+}
+static uint8_t* na0_u8(SEXP v, R_xlen_t n, const char* what) {
+  int* t = na0(v, n, what);
+  uint8_t* o = (uint8_t*)R_alloc((size_t)(n ? n : 1), 1);
+  for (R_xlen_t i = 0; i < n; ++i) o[i] = (uint8_t)t[i];
+  return o;
+}
+SEXP litap_R_relz(SEXP nrow, SEXP ncol, SEXP db, SEXP idb, SEXP pond, SEXP str_val, SEXP ridge_val, SEXP grid) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  /* db: elev, ddir, drec, upslope, fill_shed, local_shed; idb: elev, ddir, drec, upslope, inv_local_shed;
+   * pond: shedno, pit_row, pit_col, pit_elev (lists in this order, see calc_relz() in litap_cuda.R) */
+  SEXP e = VECTOR_ELT(db, 0), ie = VECTOR_ELT(idb, 0);
+  if (TYPEOF(e) != REALSXP || XLENGTH(e) != n || TYPEOF(ie) != REALSXP || XLENGTH(ie) != n)
+    Rf_error("litap_R_relz: elev must be double with nrow*ncol entries");
+  const R_xlen_t np = XLENGTH(VECTOR_ELT(pond, 0));
+  SEXP pe = PROTECT(Rf_coerceVector(VECTOR_ELT(pond, 3), REALSXP));
+  const char* names = litap_relz_names();
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, LITAP_RELZ_NOUT));
+  SEXP nms = PROTECT(Rf_allocVector(STRSXP, LITAP_RELZ_NOUT));
+  double* o[LITAP_RELZ_NOUT];
+  for (int k = 0; k < LITAP_RELZ_NOUT; ++k) {
+    const char* end = strchr(names, ',');
+    const size_t len = end ? (size_t)(end - names) : strlen(names);
+    SET_STRING_ELT(nms, k, Rf_mkCharLen(names, (int)len));
+    names += len + 1;
+    SEXP v = Rf_allocVector(REALSXP, n);
+    SET_VECTOR_ELT(out, k, v);
+    o[k] = REAL(v);
+  }
+  Rf_setAttrib(out, R_NamesSymbol, nms);
+  fail_if(litap_relz(NR, NC, REAL(e), na0_u8(VECTOR_ELT(db, 1), n, "db$ddir"), na0(VECTOR_ELT(db, 2), n, "db$drec"),
+                     na0(VECTOR_ELT(db, 3), n, "db$upslope"), na0(VECTOR_ELT(db, 4), n, "db$fill_shed"),
+                     na0(VECTOR_ELT(db, 5), n, "db$local_shed"), REAL(ie), na0_u8(VECTOR_ELT(idb, 1), n, "idb$ddir"),
+                     na0(VECTOR_ELT(idb, 2), n, "idb$drec"), na0(VECTOR_ELT(idb, 3), n, "idb$upslope"),
+                     na0(VECTOR_ELT(idb, 4), n, "idb$inv_local_shed"), np, na0(VECTOR_ELT(pond, 0), np, "pond$shedno"),
+                     na0(VECTOR_ELT(pond, 1), np, "pond$pit_row"), na0(VECTOR_ELT(pond, 2), np, "pond$pit_col"), REAL(pe),
+                     Rf_asReal(str_val), Rf_asReal(ridge_val), Rf_asReal(grid), o), "relz");
+  for (int k = 0; k < LITAP_RELZ_NOUT; ++k)
+    for (R_xlen_t i = 0; i < n; ++i) if (o[k][i] != o[k][i]) o[k][i] = NA_REAL;
+  UNPROTECT(3);
+  return out;
+}
+
 SEXP litap_R_init(SEXP device) {
   fail_if(litap_init(Rf_asInteger(device)), "litap_init");
   return Rf_mkString(litap_version());
@@ -203,7 +255,7 @@ SEXP litap_R_timings(void) {
 static const R_CallMethodDef call_methods[] = {
     {"litap_R_ddir", (DL_FUNC)&litap_R_ddir, 4},     {"litap_R_shed", (DL_FUNC)&litap_R_shed, 4},
     {"litap_R_form", (DL_FUNC)&litap_R_form, 4},     {"litap_R_weti", (DL_FUNC)&litap_R_weti, 6},
-    {"litap_R_slope_gc", (DL_FUNC)&litap_R_slope_gc, 4},
+    {"litap_R_slope_gc", (DL_FUNC)&litap_R_slope_gc, 4}, {"litap_R_relz", (DL_FUNC)&litap_R_relz, 8},
     {"litap_R_init", (DL_FUNC)&litap_R_init, 1},     {"litap_R_shutdown", (DL_FUNC)&litap_R_shutdown, 0},
     {"litap_R_timings", (DL_FUNC)&litap_R_timings, 0}, {NULL, NULL, 0}};
 
