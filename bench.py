@@ -340,6 +340,23 @@ def run_ours(a):
         gc = {"ms": tg["gc_ms"], "Mcells_per_s": n * n / tg["gc_ms"] / 1e3, "alg_bytes_per_cell": 74,
               "frac_of_hbm_peak": round(74 * n * n / (tg["gc_ms"] * 1e-3) / 1e9 / peak, 4)}
 
+    # ---- calc_relz + calc_length (not part of the composite metric) on the flow field of a
+    # 4096^2 DEM through the host-buffer C ABI (11 input grids up, 39 double grids down)
+    relz = None
+    if world == 1 and not a.no_weti:
+        m = min(n, 4096)
+        rdb, ridb = relz_flow_fields(m)
+        for _ in range(2):
+            t0 = time.perf_counter()
+            out = lb.calc_relz(rdb, ridb, 1000, 1000, pond=None, grid=GRID_M)
+            wall = (time.perf_counter() - t0) * 1e3
+        tz = lb.timings()
+        relz = {"workload": f"flow field of the hash-fBm DEM {m}x{m}, str_val = ridge_val = 1000", "device_ms": tz["relz_ms"],
+                "Mcells_per_s_device": (m + 2) ** 2 / tz["relz_ms"] / 1e3, "h2d_ms": tz["h2d_ms"], "d2h_ms": tz["d2h_ms"],
+                "call_wall_ms": wall, "jump_rounds": tz["plateau_rounds"], "kernel_launches": tz["kernel_launches"],
+                "longest_path": int(np.nanmax(out["n2pit"])), "host_buffers": "pageable numpy arrays"}
+        del rdb, ridb, out
+
     # ---- CPU baseline (rank 0, N = 1): the oracle on a bounded sample, single thread
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
@@ -366,13 +383,37 @@ def run_ours(a):
                                 if fused else "calc_form, calc_ddir2, calc_shed4 as three calls"),
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
             "clocks": clocks, "e2e": e2e, "gpu_launches": nl,
-            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti, "slope_gc": gc,
+            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti, "slope_gc": gc, "relz": relz,
             "cpu_baseline": cpu}) + "\n").encode())
     g.close()
     if world > 1:
         from litap_b200.bands import destroy_comm
         destroy_comm()
         dist.destroy_process_group()
+
+
+def relz_flow_fields(n):
+    """db / idb for calc_relz from the device stages on an n x n synthetic DEM: elev, ddir, drec, upslope and the
+    initial sheds (used as fill_shed / local_shed / inv_local_shed) of the DEM and of the inverted DEM."""
+    import numpy as np
+    import litap_b200 as lb
+    from litap_b200.api import _OFF_DC, _OFF_DR
+    g = lb.DeviceGrid(n + 2, n + 2)
+    g.synth(SEED)
+    out = []
+    sh = (n + 2, n + 2)
+    for inv in (False, True):
+        g.ddir(invert=inv)          # invert = True turns elev over in place first
+        g.shed()
+        d = g.download("ddir").reshape(sh)
+        seq = np.arange(1, d.size + 1, dtype=np.int64).reshape(sh)
+        drec = (seq + _OFF_DR[d].astype(np.int64) * (n + 2) + _OFF_DC[d]).astype(np.int32)
+        drec[d == 0] = 0
+        out.append({"elev": g.download("elev").reshape(sh), "ddir": d, "drec": drec,
+                    "upslope": g.download("upslope").reshape(sh).astype(np.int32), "shed": g.download("shed").reshape(sh)})
+    g.close()
+    f, i = out
+    return dict(f, fill_shed=f["shed"], local_shed=f["shed"]), dict(i, inv_local_shed=i["shed"])
 
 
 def main():

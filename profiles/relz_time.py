@@ -10,28 +10,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import litap_b200 as lb  # noqa: E402
-from litap_b200.api import _OFF_DC, _OFF_DR  # noqa: E402
-
-
-def flow_fields(n):
-    g = lb.DeviceGrid(n + 2, n + 2)
-    g.synth()
-    out = []
-    for inv in (False, True):
-        g.ddir(invert=inv)          # invert = True turns elev over in place first
-        g.shed()
-        sh = (n + 2, n + 2)
-        d = g.download("ddir").reshape(sh)
-        seq = np.arange(1, d.size + 1, dtype=np.int64).reshape(sh)
-        drec = (seq + _OFF_DR[d].astype(np.int64) * (n + 2) + _OFF_DC[d]).astype(np.int32)
-        drec[d == 0] = 0
-        out.append({"elev": g.download("elev").reshape(sh), "ddir": d, "drec": drec,
-                    "upslope": g.download("upslope").reshape(sh).astype(np.int32),
-                    "shed": g.download("shed").reshape(sh)})
-    g.close()
-    f, i = out
-    return dict(f, fill_shed=f["shed"], local_shed=f["shed"]), dict(i, inv_local_shed=i["shed"])
-
+from bench import relz_flow_fields as flow_fields  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 m = int(sys.argv[2]) if len(sys.argv) > 2 else 1024

@@ -30,6 +30,8 @@ SEXP Rf_setAttrib(SEXP, SEXP, SEXP);
 SEXP Rf_coerceVector(SEXP, unsigned int);
 void SET_STRING_ELT(SEXP, R_xlen_t, SEXP);
 SEXP SET_VECTOR_ELT(SEXP, R_xlen_t, SEXP);
+SEXP VECTOR_ELT(SEXP, R_xlen_t);
+SEXP Rf_mkCharLen(const char*, int);
 int TYPEOF(SEXP);
 R_xlen_t XLENGTH(SEXP);
 double* REAL(SEXP);
