@@ -13,7 +13,7 @@
 //   k_relz_init   pair[c] = (c, 0) if c stops the walk, else (drec[c], 1)           (target, steps) in one 64-bit word
 //   k_relz_jump   pair[c] = (target of my target, my steps + its steps), in place: a pair is always a true
 //                 statement about c's path, so reading a neighbour's pair mid-update is harmless; ~log2(longest
-//                 path) rounds.  The four traces (stream, path end, ridge, inverted path end) share the launches.
+//                 path) rounds; a cell whose target is a stopping cell is marked final and costs one load after that.  The four traces (stream, path end, ridge, inverted path end) share the launches.
 //   k_relz_sheds  pit / peak of every shed id (pond table or ddir == 5 cells), max elevation per fill_shed, DEM min / max
 //   k_relz_cells  everything else is per-cell arithmetic in the reference's operation order (no FMA)
 // drec is a global cell number, so the arrays are dense NR x NC (no pitch) on this path.
@@ -26,6 +26,7 @@ namespace {
 constexpr int RELZ_NOUT = LITAP_RELZ_NOUT;
 constexpr int RZ_THREADS = 256;
 constexpr int RZ_MAX_ROUNDS = 64;
+constexpr unsigned long long RZ_FINAL = 1ULL << 63;
 
 __device__ __forceinline__ double rz_na() { return __longlong_as_double(0x7ff8000000000000LL); }
 // order-preserving map double -> uint64 (for atomicMin / atomicMax)
@@ -58,24 +59,26 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_init(Traces T, int64_t n, i
   if (!stop && ((int64_t)d < 1 || (int64_t)d > n)) { *bad = 1; stop = true; }
   if (T.sheds[blockIdx.y]) { const int32_t s = T.sheds[blockIdx.y][i]; if (s < 0 || (int64_t)s > n) *bad = 2; }
   if (!stop && t.use_val) { const int32_t u = t.upslope[i]; stop = u != 0 && (double)u >= t.val; }
-  t.pair[i] = stop ? (unsigned long long)(uint32_t)i : ((1ULL << 32) | (uint32_t)(d - 1));
+  t.pair[i] = stop ? (RZ_FINAL | (unsigned long long)(uint32_t)i) : ((1ULL << 32) | (uint32_t)(d - 1));
 }
 
-__global__ void __launch_bounds__(RZ_THREADS) k_relz_jump(Traces T, int64_t n, int* __restrict__ changed) {
+// bit 63 of a pair: its target is where the walk stops (nothing left to do for this cell)
+__global__ void __launch_bounds__(RZ_THREADS) k_relz_jump(Traces T, int64_t n, int* __restrict__ flags) {
   const int64_t i = (int64_t)blockIdx.x * RZ_THREADS + threadIdx.x;
   if (i >= n) return;
   volatile unsigned long long* pair = T.t[blockIdx.y].pair;
   unsigned long long p = pair[i];
-  bool moved = false;
+  if (p & RZ_FINAL) return;
 #pragma unroll 1
   for (int k = 0; k < 4; ++k) {   // a few hops per launch: fewer rounds, each ends with a host check
-    const uint32_t tg = (uint32_t)p;
-    const unsigned long long q = pair[tg];
-    if ((uint32_t)q == tg) break;
-    p = (((p >> 32) + (q >> 32)) << 32) | (uint32_t)q;
-    moved = true;
+    const unsigned long long q = pair[(uint32_t)p];
+    const unsigned long long steps = (p >> 32) + ((q & ~RZ_FINAL) >> 32);
+    if (steps > (unsigned long long)n) { flags[1] = 3; return; }   // longer than the grid: the path runs in a circle
+    p = (steps << 32) | (uint32_t)q | (q & RZ_FINAL);
+    if (p & RZ_FINAL) break;
   }
-  if (moved) { pair[i] = p; *changed = 1; }
+  pair[i] = p;
+  if (!(p & RZ_FINAL)) flags[0] = 1;
 }
 
 struct ShedTab { int32_t* row; int32_t* col; double* elev; };   // by shed id; row 0 = no pit known
@@ -97,11 +100,13 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_pitcells(int64_t n, int NC,
   const int32_t s = shed[i];
   tab.row[s] = (int32_t)(i / NC) + 1; tab.col[s] = (int32_t)(i % NC) + 1; tab.elev[s] = elev[i];
 }
-// mm[0] = min, mm[1] = max of the DEM, shed_max[id] = max elevation of the fill_shed (encoded doubles; 0 = none)
+// mm[0] = min, mm[1] = max of the DEM (one atomic pair per block), shed_max[id] = max elevation of the fill_shed
+// (encoded doubles; 0 = none)
 __global__ void __launch_bounds__(RZ_THREADS) k_relz_sheds(int64_t n, const double* __restrict__ elev,
                                                            const int32_t* __restrict__ fill_shed,
                                                            unsigned long long* __restrict__ mm,
                                                            unsigned long long* __restrict__ shed_max) {
+  __shared__ unsigned long long s_hi[RZ_THREADS / 32], s_lo[RZ_THREADS / 32];
   const int64_t i = (int64_t)blockIdx.x * RZ_THREADS + threadIdx.x;
   const double e = i < n ? elev[i] : rz_na();
   const bool ok = e == e;
@@ -109,16 +114,22 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_sheds(int64_t n, const doub
   unsigned long long hi = ok ? rz_enc(e) : 0ULL, lo = ok ? rz_enc(e) : ~0ULL;
   int same;
   __match_all_sync(0xffffffffu, s, &same);
-  unsigned long long shi = hi;
+  const unsigned long long shi = hi;
 #pragma unroll
   for (int o = 16; o; o >>= 1) {
     const unsigned long long a = __shfl_xor_sync(0xffffffffu, hi, o), b = __shfl_xor_sync(0xffffffffu, lo, o);
     hi = a > hi ? a : hi;
     lo = b < lo ? b : lo;
   }
-  if ((threadIdx.x & 31) == 0 && hi) { atomicMax(mm + 1, hi); atomicMin(mm, lo); }
   if (same) { if ((threadIdx.x & 31) == 0 && ok) atomicMax(shed_max + s, hi); }   // the whole warp in one shed: one atomic
   else if (ok) atomicMax(shed_max + s, shi);
+  if ((threadIdx.x & 31) == 0) { s_hi[threadIdx.x >> 5] = hi; s_lo[threadIdx.x >> 5] = lo; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 1; w < RZ_THREADS / 32; ++w) { hi = s_hi[w] > hi ? s_hi[w] : hi; lo = s_lo[w] < lo ? s_lo[w] : lo; }
+    if (hi) { atomicMax(mm + 1, hi); atomicMin(mm, lo); }
+  }
 }
 
 struct RelzIn {
@@ -152,7 +163,7 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
     const int64_t t = (uint32_t)p;
     st_row = (double)(t / NC + 1); st_col = (double)(t % NC + 1); st_elev = I.elev[t];
     z2st = e - st_elev; if (z2st < 0) z2st = 0;
-    n2st = (double)(uint32_t)(p >> 32);
+    n2st = (double)(uint32_t)((p & ~RZ_FINAL) >> 32);
   }
   double cr_row = NA, cr_col = NA, cr_ie = NA, z2cr = NA, n2cr = NA;
   if (ie == ie) {
@@ -160,7 +171,7 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
     const int64_t t = (uint32_t)p;
     cr_row = (double)(t / NC + 1); cr_col = (double)(t % NC + 1); cr_ie = I.ielev[t];
     z2cr = ie - cr_ie; if (z2cr < 0) z2cr = 0;
-    n2cr = (double)(uint32_t)(p >> 32);
+    n2cr = (double)(uint32_t)((p & ~RZ_FINAL) >> 32);
   }
   if (e != e) { z2st = NA; z2cr = NA; }                                     // calc_relz :41
   // pits / peaks: by shed id
@@ -170,14 +181,14 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
     pit_row = I.pits.row[ls]; pit_col = I.pits.col[ls]; pit_elev = I.pits.elev[ls];
     z2pit = e - pit_elev; if (z2pit < 0) z2pit = 0;
   }
-  if (ls && e == e) n2pit = (double)(uint32_t)(I.p_pit[i] >> 32);
+  if (ls && e == e) n2pit = (double)(uint32_t)((I.p_pit[i] & ~RZ_FINAL) >> 32);
   double pk_row = NA, pk_col = NA, pk_ie = NA, z2peak = NA, n2peak = NA;
   const int32_t is = I.inv_local_shed[i];
   if (is && I.peaks.row[is]) {
     pk_row = I.peaks.row[is]; pk_col = I.peaks.col[is]; pk_ie = I.peaks.elev[is];
     z2peak = ie - pk_ie; if (z2peak < 0) z2peak = 0;
   }
-  if (is && ie == ie) n2peak = (double)(uint32_t)(I.p_peak[i] >> 32);
+  if (is && ie == ie) n2peak = (double)(uint32_t)((I.p_peak[i] & ~RZ_FINAL) >> 32);
   v[0] = st_row; v[1] = st_col; v[2] = st_elev; v[3] = z2st; v[4] = n2st;
   v[5] = cr_row; v[6] = cr_col; v[7] = mx - cr_ie; v[8] = z2cr; v[9] = n2cr;
   v[10] = pit_row; v[11] = pit_col; v[12] = pit_elev; v[13] = z2pit; v[14] = n2pit;
@@ -297,6 +308,7 @@ extern "C" int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint
     int h[2];
     CUDA_TRY(cudaMemcpyAsync(h, flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    if (h[1] == 3) return set_error(LITAP_EARG, "litap_relz: flow paths do not end (cycle in drec)");
     if (h[1]) return set_error(LITAP_EARG, h[1] == 2 ? "litap_relz: shed number outside 0 .. NR * NC" : "litap_relz: drec outside 1 .. NR * NC");
     if (!h[0]) break;
   }
