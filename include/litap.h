@@ -105,7 +105,9 @@ int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double grid,
  * R/form_mapper.R:154,177) on the buffered grids form_mapper works on: db = the filled DEM of flow_mapper
  * (elev, ddir, drec, upslope, fill_shed, local_shed), idb = the inverted DEM (elev, ddir, drec, upslope,
  * inv_local_shed), the pond table = pit of every local shed (npond = 0: calc_pit3's "ddir == 5 cells" branch,
- * ddir required; otherwise ddir may be NULL).  Integer inputs: 0 = NA; drec is R's 1-based seqno.
+ * ddir required; otherwise ddir may be NULL).  Integer inputs: 0 = NA; drec is R's 1-based seqno.  Cells
+ * without elevation are expected to be NA in every column and not to be drained into, as in LITAP's grids;
+ * n2pit / n2peak are reported for cells that have a shed number.
  * out[k], k < LITAP_RELZ_NOUT (any may be NULL): the columns calc_length returns, in the order of
  * litap_relz_names(); NaN = NA; *_row / *_col are buffered 1-based numbers as in R before remove_buffer().
  * Errors: LITAP_EARG for drec / shed numbers outside the grid or flow paths that never end. */

@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
   const double mn = rz_dec(I.mm[0]), mx = rz_dec(I.mm[1]);   // (an all-NA DEM never gets here with e valid)
   double v[RELZ_NOUT];
   // streams / ridges: the cell the trace stopped at
-  double st_row = NA, st_col = NA, st_elev = NA, z2st = NA, n2st = NA;
+  double st_row = NA, st_col = NA, st_elev = NA, z2st = 0, n2st = NA;   // z2st starts as 0 in the reference (:198)
   if (e == e) {
     const unsigned long long p = I.p_st[i];
     const int64_t t = (uint32_t)p;
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
     z2st = e - st_elev; if (z2st < 0) z2st = 0;
     n2st = (double)(uint32_t)((p & ~RZ_FINAL) >> 32);
   }
-  double cr_row = NA, cr_col = NA, cr_ie = NA, z2cr = NA, n2cr = NA;
+  double cr_row = NA, cr_col = NA, cr_ie = NA, z2cr = 0, n2cr = NA;
   if (ie == ie) {
     const unsigned long long p = I.p_cr[i];
     const int64_t t = (uint32_t)p;

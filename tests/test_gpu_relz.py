@@ -70,6 +70,55 @@ def test_synthetic_flow_fields_vs_oracle(dem, str_val, ridge_val, min_path):
     assert 0 < np.nanmax(got["n2st"]) < np.nanmax(got["n2pit"])     # and some of them stop at a channel cell
 
 
+def test_missing_pits_and_na_cells_vs_oracle():
+    """NA in the places the reference tolerates it: sheds without a row in the pond table (pit_* = NA and every
+    column derived from them), cells without a shed number, a hole of NA cells in both DEMs."""
+    db, idb, pond, _ = rf.load()
+    keep = np.arange(len(pond["shedno"])) % 3 != 0
+    part = {k: np.asarray(v)[keep] for k, v in pond.items()}
+    db = {k: v.copy() for k, v in db.items()}
+    idb = {k: v.copy() for k, v in idb.items()}
+    # no shed number: no pit, no n2pit (cells nothing drains through: litap.h narrows n2pit / n2peak to cells
+    # with a shed number, the reference would also fill shed-less cells on the path of a cell with one)
+    for d, shed in ((db, "local_shed"), (idb, "inv_local_shed")):
+        lone = d["upslope"] == 1
+        lone[:, 1::2] = False
+        lone[::2, :] = False
+        d[shed][lone] = np.nan
+    # holes: cells that nothing flows into (upslope == 1) become missing cells of that DEM, i.e. NA in every
+    # column, as missing cells are in the reference's grids
+    for d, shed in ((db, "local_shed"), (idb, "inv_local_shed")):
+        leaf = d["upslope"] == 1
+        leaf[:, ::2] = False
+        assert leaf.sum() > 50
+        for k in d:
+            d[k][leaf] = np.nan
+    got = lb.calc_relz(db, idb, 200, 150, pond=part, grid=5.0)
+    want = oracle.relz(db, idb, part, 200, 150, 5.0)
+    rf.assert_same(got, want, oracle.RELZ_NAMES, "partial pond")
+    assert np.isnan(got["pit_row"][1:-1, 1:-1]).any() and not np.isnan(got["pit_row"][1:-1, 1:-1]).all()
+
+
+def test_degenerate_grids_vs_oracle():
+    """One shed draining to one pit; a flat DEM (elev_range == 0: the percentages that divide by it are set to 0);
+    an all-NA DEM."""
+    nr, nc = 12, 15
+    yy, xx = np.mgrid[0:nr, 0:nc]
+    for name, surf in (("cone", 50.0 + np.hypot(yy - 6, xx - 7)), ("flat", np.full((nr, nc), 9.0))):
+        e = oracle.add_buffer(np.round(surf, 3))
+        f, i = flow_field(e, False), flow_field(e, True)
+        db = dict(f, fill_shed=f["shed"], local_shed=f["shed"])
+        idb = dict(i, inv_local_shed=i["shed"])
+        rf.assert_same(lb.calc_relz(db, idb, 20, 20, pond=None, grid=2.0), oracle.relz(db, idb, None, 20, 20, 2.0),
+                       oracle.RELZ_NAMES, name)
+    na = np.full((6, 7), np.nan)
+    z = np.zeros((6, 7))
+    db = {"elev": na, "ddir": z, "drec": z, "upslope": z, "fill_shed": z, "local_shed": z}
+    idb = {"elev": na, "ddir": z, "drec": z, "upslope": z, "inv_local_shed": z}
+    got = lb.calc_relz(db, idb, 5, 5, pond=None, grid=1.0)
+    rf.assert_same(got, oracle.relz(db, idb, None, 5, 5, 1.0), oracle.RELZ_NAMES, "all NA")
+
+
 def test_bad_arguments_raise():
     db, idb, pond, _ = rf.load()
     bad = dict(db, drec=np.where(np.isnan(db["drec"]), np.nan, 10 ** 6))
