@@ -158,8 +158,16 @@ def relz_names():
     return tuple(lib().litap_relz_names().decode().split(","))
 
 
+def _int_na0(a, dt):
+    """integer column of the C ABI (0 = NA) from an R-like numeric column (NaN = NA) or an integer array as it is"""
+    a = np.asarray(a)
+    if np.issubdtype(a.dtype, np.integer):
+        return np.ascontiguousarray(a, dtype=dt)
+    return np.ascontiguousarray(np.nan_to_num(a.astype(np.float64, copy=False), nan=0.0), dtype=dt)
+
+
 def _i32_na0(a):
-    return np.ascontiguousarray(np.nan_to_num(np.asarray(a, dtype=np.float64), nan=0.0), dtype=np.int32)
+    return _int_na0(a, np.int32)
 
 
 def calc_relz(db, idb, str_val, ridge_val, pond=None, grid=1):
@@ -169,7 +177,7 @@ def calc_relz(db, idb, str_val, ridge_val, pond=None, grid=1):
     drec, upslope, inv_local_shed; NaN = NA, drec = 1-based seqno); pond: shedno, pit_row, pit_col, pit_elev
     (buffered row / col) or None.  Returns a dict of the 39 relief / length columns (NaN = NA)."""
     f = _f64
-    u8 = lambda a: np.ascontiguousarray(np.nan_to_num(np.asarray(a, dtype=np.float64), nan=0.0), dtype=np.uint8)
+    u8 = lambda a: _int_na0(a, np.uint8)
     e = f(db["elev"])
     if e.ndim != 2:
         raise LitapError("calc_relz: db$elev must be a 2-D buffered grid")

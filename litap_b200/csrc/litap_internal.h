@@ -105,6 +105,7 @@ struct StreamSwap {
 void* pool_alloc(size_t bytes);
 void pool_free(void* p);
 void pool_release_all();
+void relz_forget_staging();   // relz.cu: pinned staging buffers of the result download
 
 template <typename T>
 inline T* grid_alloc_array(const GridDims& d, int fill_byte) {
