@@ -89,7 +89,7 @@ extern "C" void litap_shutdown(void) {
   cudaStreamSynchronize(c.stream);
   pool_release_all();
   form_forget_trig();
-  relz_forget_staging();
+  hostcopy_forget_staging();
   for (auto& ev : c.ev) if (ev) { cudaEventDestroy(ev); ev = nullptr; }
   if (g_own_stream) cudaStreamDestroy(c.stream);
   if (g_hi_stream) { cudaStreamDestroy(g_hi_stream); cudaEventDestroy(g_ev_fork); cudaEventDestroy(g_ev_join); g_hi_stream = nullptr; }

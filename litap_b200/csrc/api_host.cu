@@ -25,9 +25,7 @@ template <typename T>
 int down(T* dst, const GridDims& d, const T* src) {
   if (!dst) return LITAP_OK;
   if (!src) return set_error(LITAP_ECUDA, "internal: result array missing on the device");
-  CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)d.NC * sizeof(T), src, (size_t)d.pitch * sizeof(T),
-                             (size_t)d.NC * sizeof(T), d.NR, cudaMemcpyDeviceToHost, ctx().stream));
-  return LITAP_OK;
+  return d2h_2d(dst, (size_t)d.NC * sizeof(T), src, (size_t)d.pitch * sizeof(T), (size_t)d.NC * sizeof(T), d.NR, ctx().stream);
 }
 int timed_sync(float* slot, cudaEvent_t a, cudaEvent_t b) {
   CUDA_TRY(cudaEventRecord(b, ctx().stream));
@@ -114,8 +112,8 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
     CUDA_TRY(cudaStreamWaitEvent(P.copy, P.ev.back(), 0));
     for (int i = 0; i < 5; ++i)
       if (fouts[i])
-        CUDA_TRY(cudaMemcpy2DAsync(fouts[i] + (size_t)form_done * d.NC, (size_t)d.NC * 8, g->form[i] + (size_t)form_done * d.pitch,
-                                   (size_t)d.pitch * 8, (size_t)d.NC * 8, hi - form_done, cudaMemcpyDeviceToHost, P.copy));
+        RC(d2h_2d(fouts[i] + (size_t)form_done * d.NC, (size_t)d.NC * 8, g->form[i] + (size_t)form_done * d.pitch,
+                  (size_t)d.pitch * 8, (size_t)d.NC * 8, hi - form_done, P.copy));
     form_done = hi;
   }
   RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));  // uploads + the form kernels between them

@@ -105,7 +105,9 @@ struct StreamSwap {
 void* pool_alloc(size_t bytes);
 void pool_free(void* p);
 void pool_release_all();
-void relz_forget_staging();   // relz.cu: pinned staging buffers of the result download
+// hostcopy.cu: device -> caller memory; pageable destinations go through pinned staging buffers + host threads
+int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st);
+void hostcopy_forget_staging();
 
 template <typename T>
 inline T* grid_alloc_array(const GridDims& d, int fill_byte) {

@@ -17,10 +17,6 @@
 //   k_relz_sheds  pit / peak of every shed id (pond table or ddir == 5 cells), max elevation per fill_shed, DEM min / max
 //   k_relz_cells  everything else is per-cell arithmetic in the reference's operation order (no FMA)
 // drec is a global cell number, so the arrays are dense NR x NC (no pitch) on this path.
-#include <algorithm>
-#include <cstdlib>
-#include <cstring>
-#include <thread>
 #include <vector>
 #include "cellmath.h"
 #include "litap_internal.h"
@@ -236,69 +232,7 @@ int to_dev(PoolScratch& S, T** dst, const T* src, size_t n) {
   return LITAP_OK;
 }
 
-// ---- results back to pageable host memory -----------------------------------------------------------------
-// The 39 result columns go to vectors the caller allocated with malloc (R vectors, numpy arrays): fresh,
-// pageable pages.  cudaMemcpy into such memory is staged by the driver on one thread and ends up bound by
-// page faults (~4 GB/s measured).  Here the device writes into two pinned staging buffers in turn and a few
-// host threads copy the previous chunk out while the next one crosses PCIe.
-constexpr size_t RZ_STAGE = 64u << 20;
-void* g_stage[2] = {nullptr, nullptr};
-cudaEvent_t g_stage_ev[2] = {nullptr, nullptr};
-
-int stage_init() {
-  for (int b = 0; b < 2; ++b) {
-    if (!g_stage[b]) CUDA_TRY(cudaHostAlloc(&g_stage[b], RZ_STAGE, cudaHostAllocDefault));
-    if (!g_stage_ev[b]) CUDA_TRY(cudaEventCreateWithFlags(&g_stage_ev[b], cudaEventDisableTiming));
-  }
-  return LITAP_OK;
-}
-int copy_threads() {
-  const char* e = getenv("LITAP_COPY_THREADS");
-  int t = e ? atoi(e) : 8;
-  const int hw = (int)std::thread::hardware_concurrency();
-  if (hw > 0) t = std::min(t, hw);
-  return std::max(t, 1);
-}
-void host_copy(char* dst, const char* src, size_t bytes, int nt) {
-  if (nt <= 1 || bytes < (4u << 20)) { memcpy(dst, src, bytes); return; }
-  std::vector<std::thread> th;
-  const size_t per = ((bytes + nt - 1) / nt + 4095) & ~(size_t)4095;
-  for (int t = 1; t < nt; ++t) {
-    const size_t lo = std::min(bytes, per * t), hi = std::min(bytes, per * (t + 1));
-    if (hi > lo) th.emplace_back([=] { memcpy(dst + lo, src + lo, hi - lo); });
-  }
-  memcpy(dst, src, std::min(bytes, per));
-  for (auto& x : th) x.join();
-}
-struct Piece { char* dst; const char* src; size_t bytes; };
-// all pieces, in order, through the two staging buffers
-int staged_d2h(const std::vector<Piece>& arrays, cudaStream_t st) {
-  RC(stage_init());
-  const int nt = copy_threads();
-  std::vector<Piece> ch;
-  for (const Piece& a : arrays)
-    for (size_t o = 0; o < a.bytes; o += RZ_STAGE) ch.push_back({a.dst + o, a.src + o, std::min(RZ_STAGE, a.bytes - o)});
-  auto issue = [&](size_t j) -> int {
-    CUDA_TRY(cudaMemcpyAsync(g_stage[j & 1], ch[j].src, ch[j].bytes, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(g_stage_ev[j & 1], st));
-    return LITAP_OK;
-  };
-  if (!ch.empty()) RC(issue(0));
-  for (size_t j = 0; j < ch.size(); ++j) {
-    if (j + 1 < ch.size()) RC(issue(j + 1));      // buffer (j + 1) & 1 was drained by the host copy of chunk j - 1
-    CUDA_TRY(cudaEventSynchronize(g_stage_ev[j & 1]));
-    host_copy(ch[j].dst, (const char*)g_stage[j & 1], ch[j].bytes, nt);
-  }
-  return LITAP_OK;
-}
 }  // namespace
-
-void relz_forget_staging() {   // litap_shutdown
-  for (int b = 0; b < 2; ++b) {
-    if (g_stage[b]) { cudaFreeHost(g_stage[b]); g_stage[b] = nullptr; }
-    if (g_stage_ev[b]) { cudaEventDestroy(g_stage_ev[b]); g_stage_ev[b] = nullptr; }
-  }
-}
 
 extern "C" const char* litap_relz_names(void) {
   return "st_row,st_col,st_elev,z2st,n2st,cr_row,cr_col,cr_elev,z2cr,n2cr,pit_row,pit_col,pit_elev,z2pit,n2pit,"
@@ -397,10 +331,8 @@ extern "C" int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint
   RelzIn I{d_elev, d_ielev, d_fs, d_ls, d_ils, pairs, pairs + n, pairs + 2 * n, pairs + 3 * n, pits, peaks, mm, shed_max};
   KERNEL("k_relz_cells", k_relz_cells<<<nb, RZ_THREADS, 0, st>>>(n, (int)NC, grid, I, O));
   CUDA_TRY(cudaEventRecord(c.ev[4], st));
-  std::vector<Piece> down;
-  for (int k = 0; k < RELZ_NOUT; ++k)
-    if (out[k]) down.push_back({(char*)out[k], (const char*)O.o[k], (size_t)n * sizeof(double)});
-  RC(staged_d2h(down, st));
+  for (int k = 0; k < RELZ_NOUT; ++k)   // pageable destinations (R vectors, numpy arrays) go through pinned staging buffers
+    if (out[k]) RC(d2h_2d(out[k], (size_t)n * sizeof(double), O.o[k], (size_t)n * sizeof(double), (size_t)n * sizeof(double), 1, st));
   CUDA_TRY(cudaEventRecord(c.ev[5], st));
   CUDA_TRY(cudaStreamSynchronize(st));
   cudaEventElapsedTime(&c.tm.h2d_ms, c.ev[6], c.ev[7]);
