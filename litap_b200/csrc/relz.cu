@@ -148,14 +148,15 @@ __device__ __forceinline__ double rz_len3(double r2, double c2, double z, double
   return sqrt(rz_sq(l) + rz_sq(z * grid));
 }
 
-__global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, double grid, RelzIn I, RelzOut O) {
+__global__ void __launch_bounds__(RZ_THREADS, 3) k_relz_cells(int64_t n, int NC, double grid, RelzIn I, RelzOut O) {
   const int64_t i = (int64_t)blockIdx.x * RZ_THREADS + threadIdx.x;
   if (i >= n) return;
   const double NA = rz_na();
   const double e = I.elev[i], ie = I.ielev[i];
   const double row = (double)(i / NC + 1), col = (double)(i % NC + 1);
   const double mn = rz_dec(I.mm[0]), mx = rz_dec(I.mm[1]);   // (an all-NA DEM never gets here with e valid)
-  double v[RELZ_NOUT];
+  // every column is stored as soon as it is known (39 live doubles would cost the occupancy)
+  auto put = [&](int k, double x) { if (O.o[k]) O.o[k][i] = x; };
   // streams / ridges: the cell the trace stopped at
   double st_row = NA, st_col = NA, st_elev = NA, z2st = 0, n2st = NA;   // z2st starts as 0 in the reference (:198)
   if (e == e) {
@@ -189,10 +190,10 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
     z2peak = ie - pk_ie; if (z2peak < 0) z2peak = 0;
   }
   if (is && ie == ie) n2peak = (double)(uint32_t)((I.p_peak[i] & ~RZ_FINAL) >> 32);
-  v[0] = st_row; v[1] = st_col; v[2] = st_elev; v[3] = z2st; v[4] = n2st;
-  v[5] = cr_row; v[6] = cr_col; v[7] = mx - cr_ie; v[8] = z2cr; v[9] = n2cr;
-  v[10] = pit_row; v[11] = pit_col; v[12] = pit_elev; v[13] = z2pit; v[14] = n2pit;
-  v[15] = pk_row; v[16] = pk_col; v[17] = mx - pk_ie; v[18] = z2peak; v[19] = n2peak;
+  put(0, st_row); put(1, st_col); put(2, st_elev); put(3, z2st); put(4, n2st);
+  put(5, cr_row); put(6, cr_col); put(7, mx - cr_ie); put(8, z2cr); put(9, n2cr);
+  put(10, pit_row); put(11, pit_col); put(12, pit_elev); put(13, z2pit); put(14, n2pit);
+  put(15, pk_row); put(16, pk_col); put(17, mx - pk_ie); put(18, z2peak); put(19, n2peak);
   // calc_relief
   double max_shed = NA;
   if (e == e) { const unsigned long long u = I.shed_max[I.fill_shed[i]]; if (u) max_shed = rz_dec(u); }
@@ -206,8 +207,8 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
   if (zcr2st == 0) pctz2st = 0;
   if (ncr2st == 0) pctn2st = 0;
   if (range == 0) pmin2max = 0;
-  v[20] = z2top; v[21] = zpit2peak; v[22] = zcr2st; v[23] = zcr2pit; v[24] = ztop2pit; v[25] = ncr2st;
-  v[26] = pmin2max; v[27] = pctz2st; v[28] = pctz2pit; v[29] = pctz2top; v[30] = pctn2st;
+  put(20, z2top); put(21, zpit2peak); put(22, zcr2st); put(23, zcr2pit); put(24, ztop2pit); put(25, ncr2st);
+  put(26, pmin2max); put(27, pctz2st); put(28, pctz2pit); put(29, pctz2top); put(30, pctn2st);
   // calc_length
   const double l2pit = rz_len3(pit_row, pit_col, z2pit, row, col, grid), l2peak = rz_len3(pk_row, pk_col, z2peak, row, col, grid);
   const double l2str = rz_len3(st_row, st_col, z2st, row, col, grid), l2div = rz_len3(cr_row, cr_col, z2cr, row, col, grid);
@@ -216,10 +217,8 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_cells(int64_t n, int NC, do
   const double r_lpit2peak = r_round1(lpit2peak), r_lstr2div = r_round1(lstr2div);
   if (r_lpit2peak == 0) ppit2peakl = 0;
   if (r_lstr2div == 0) pstr2divl = 0;
-  v[31] = r_round1(l2pit); v[32] = r_round1(l2peak); v[33] = r_lpit2peak; v[34] = ppit2peakl;
-  v[35] = r_round1(l2str); v[36] = r_round1(l2div); v[37] = r_lstr2div; v[38] = pstr2divl;
-#pragma unroll
-  for (int k = 0; k < RELZ_NOUT; ++k) if (O.o[k]) O.o[k][i] = v[k];
+  put(31, r_round1(l2pit)); put(32, r_round1(l2peak)); put(33, r_lpit2peak); put(34, ppit2peakl);
+  put(35, r_round1(l2str)); put(36, r_round1(l2div)); put(37, r_lstr2div); put(38, pstr2divl);
 }
 
 #define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
