@@ -62,23 +62,46 @@ __global__ void __launch_bounds__(RZ_THREADS) k_relz_init(Traces T, int64_t n, i
   t.pair[i] = stop ? (RZ_FINAL | (unsigned long long)(uint32_t)i) : ((1ULL << 32) | (uint32_t)(d - 1));
 }
 
-// bit 63 of a pair: its target is where the walk stops (nothing left to do for this cell)
+// bit 63 of a pair: its target is where the walk stops (nothing left to do for this cell).
+// A thread advances RZ_U cells at once: the hops of one cell depend on each other, the cells do not, and the
+// kernel is bound by the latency of the scattered loads.
+constexpr int RZ_U = 4;
 __global__ void __launch_bounds__(RZ_THREADS) k_relz_jump(Traces T, int64_t n, int* __restrict__ flags) {
-  const int64_t i = (int64_t)blockIdx.x * RZ_THREADS + threadIdx.x;
-  if (i >= n) return;
-  volatile unsigned long long* pair = T.t[blockIdx.y].pair;
-  unsigned long long p = pair[i];
-  if (p & RZ_FINAL) return;
+  // plain (L1-cached) loads: a stale pair is still a true statement about that cell's path, it only delays the
+  // jump to the next launch
+  unsigned long long* pair = T.t[blockIdx.y].pair;
+  const int64_t base = ((int64_t)blockIdx.x * RZ_THREADS + (threadIdx.x & ~31)) * RZ_U + (threadIdx.x & 31);
+  unsigned long long p[RZ_U];
+  bool act[RZ_U], moved[RZ_U];
+#pragma unroll
+  for (int u = 0; u < RZ_U; ++u) {
+    const int64_t i = base + 32 * u;
+    p[u] = i < n ? pair[i] : RZ_FINAL;
+    act[u] = !(p[u] & RZ_FINAL);
+    moved[u] = false;
+  }
 #pragma unroll 1
   for (int k = 0; k < 4; ++k) {   // a few hops per launch: fewer rounds, each ends with a host check
-    const unsigned long long q = pair[(uint32_t)p];
-    const unsigned long long steps = (p >> 32) + ((q & ~RZ_FINAL) >> 32);
-    if (steps > (unsigned long long)n) { flags[1] = 3; return; }   // longer than the grid: the path runs in a circle
-    p = (steps << 32) | (uint32_t)q | (q & RZ_FINAL);
-    if (p & RZ_FINAL) break;
+    unsigned long long q[RZ_U];
+#pragma unroll
+    for (int u = 0; u < RZ_U; ++u) q[u] = act[u] ? pair[(uint32_t)p[u]] : 0ULL;
+#pragma unroll
+    for (int u = 0; u < RZ_U; ++u) {
+      if (!act[u]) continue;
+      const unsigned long long steps = (p[u] >> 32) + ((q[u] & ~RZ_FINAL) >> 32);
+      if (steps > (unsigned long long)n) { flags[1] = 3; act[u] = false; continue; }   // longer than the grid: a circle
+      p[u] = (steps << 32) | (uint32_t)q[u] | (q[u] & RZ_FINAL);
+      moved[u] = true;
+      act[u] = !(p[u] & RZ_FINAL);
+    }
   }
-  pair[i] = p;
-  if (!(p & RZ_FINAL)) flags[0] = 1;
+  bool open = false;
+#pragma unroll
+  for (int u = 0; u < RZ_U; ++u) {
+    if (moved[u]) pair[base + 32 * u] = p[u];
+    open = open || act[u];
+  }
+  if (open) flags[0] = 1;
 }
 
 struct ShedTab { int32_t* row; int32_t* col; double* elev; };   // by shed id; row 0 = no pit known
@@ -304,7 +327,7 @@ extern "C" int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint
   for (;; ++rounds) {
     if (rounds >= RZ_MAX_ROUNDS) return set_error(LITAP_EARG, "litap_relz: flow paths do not end (cycle in drec)");
     CUDA_TRY(cudaMemsetAsync(flags, 0, sizeof(int), st));
-    KERNEL("k_relz_jump", k_relz_jump<<<dim3(nb, 4), RZ_THREADS, 0, st>>>(T, n, flags));
+    KERNEL("k_relz_jump", k_relz_jump<<<dim3((nb + RZ_U - 1) / RZ_U, 4), RZ_THREADS, 0, st>>>(T, n, flags));
     int h[2];
     CUDA_TRY(cudaMemcpyAsync(h, flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
