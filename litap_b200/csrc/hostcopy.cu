@@ -63,15 +63,19 @@ int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
   }
   RC(stage_init());
   const int nt = copy_threads();
+  // chunk size: the staging buffer, or less when LITAP_STAGE_KB says so (read per call: the tests use it to push
+  // small grids through the multi-chunk paths)
+  size_t stage = HC_STAGE;
+  if (const char* e = getenv("LITAP_STAGE_KB")) stage = std::min(HC_STAGE, std::max<size_t>(4096, (size_t)atol(e) << 10));
   // chunks: whole rows while a row fits the staging buffer, else pieces of the one long row
   struct Chunk { size_t row, off, nrows, bytes; };
   std::vector<Chunk> ch;
-  if (width <= HC_STAGE) {
-    const size_t per = std::max<size_t>(1, HC_STAGE / width);
+  if (width <= stage) {
+    const size_t per = std::max<size_t>(1, stage / width);
     for (size_t r = 0; r < rows; r += per) ch.push_back({r, 0, std::min(per, rows - r), 0});
   } else {
     for (size_t r = 0; r < rows; ++r)
-      for (size_t o = 0; o < width; o += HC_STAGE) ch.push_back({r, o, 0, std::min(HC_STAGE, width - o)});
+      for (size_t o = 0; o < width; o += stage) ch.push_back({r, o, 0, std::min(stage, width - o)});
   }
   auto issue = [&](size_t j) -> int {
     const Chunk& c = ch[j];
