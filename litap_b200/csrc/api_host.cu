@@ -28,6 +28,7 @@ int down(T* dst, const GridDims& d, const T* src) {
   return d2h_2d(dst, (size_t)d.NC * sizeof(T), src, (size_t)d.pitch * sizeof(T), (size_t)d.NC * sizeof(T), d.NR, ctx().stream);
 }
 int timed_sync(float* slot, cudaEvent_t a, cudaEvent_t b) {
+  { int rc = hostcopy_flush(); if (rc) return rc; }   // staged downloads into pageable memory end here
   CUDA_TRY(cudaEventRecord(b, ctx().stream));
   CUDA_TRY(cudaEventSynchronize(b));
   float ms = 0;
@@ -62,6 +63,7 @@ struct Pipe {
 int begin_call(int64_t NR, int64_t NC, const void* must, GridGuard& gg) {
   if (!must) return set_error(LITAP_EARG, "NULL input array");
   RC(ensure_init());
+  hostcopy_reset();
   litap_timings keep = ctx().tm;
   (void)keep;
   ctx().tm = litap_timings{};

@@ -67,9 +67,35 @@ bool pageable(const void* p) {
   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return true; }
   return at.type == cudaMemoryTypeUnregistered;
 }
+// A chunk that is on its way into a staging buffer: the host copy happens when the buffer is needed again or at
+// hostcopy_flush(), so that the copy of one chunk overlaps the transfer of the next one across calls too.
+struct Pending { bool on = false; char* dst = nullptr; size_t dpitch = 0, width = 0, nrows = 0, bytes = 0; };
+Pending g_pend[2];
+int g_next = 0;
+double g_wait_ms = 0, g_copy_ms = 0, g_bytes = 0;
+
+int complete(int b) {
+  Pending& p = g_pend[b];
+  if (!p.on) return LITAP_OK;
+  p.on = false;
+  const auto t0 = std::chrono::steady_clock::now();
+  CUDA_TRY(cudaEventSynchronize(g_stage_ev[b]));
+  const auto t1 = std::chrono::steady_clock::now();
+  const int nt = copy_threads();
+  const char* s = (const char*)g_stage[b];
+  if (!p.nrows) host_copy(p.dst, s, p.bytes, nt);
+  else if (p.dpitch == p.width) host_copy(p.dst, s, p.nrows * p.width, nt);
+  else for (size_t r = 0; r < p.nrows; ++r) memcpy(p.dst + r * p.dpitch, s + r * p.width, p.width);
+  const auto t2 = std::chrono::steady_clock::now();
+  g_wait_ms += std::chrono::duration<double, std::milli>(t1 - t0).count();
+  g_copy_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
+  g_bytes += p.nrows ? (double)p.nrows * p.width : (double)p.bytes;
+  return LITAP_OK;
+}
 }  // namespace
 
-// rows x width bytes from pitched device memory into dense-or-pitched host memory
+// rows x width bytes from pitched device memory into dense-or-pitched host memory.  Pageable destinations are
+// complete after hostcopy_flush() (every entry point calls it before it returns).
 int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st) {
   if (!rows || !width) return LITAP_OK;
   if (!pageable(dst)) {
@@ -77,51 +103,47 @@ int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
     return LITAP_OK;
   }
   RC(stage_init());
-  const int nt = copy_threads();
   advise_hugepages(dst, (rows - 1) * dpitch + width);
   // chunk size: the staging buffer, or less when LITAP_STAGE_KB says so (read per call: the tests use it to push
   // small grids through the multi-chunk paths)
   size_t stage = HC_STAGE;
   if (const char* e = getenv("LITAP_STAGE_KB")) stage = std::min(HC_STAGE, std::max<size_t>(4096, (size_t)atol(e) << 10));
   // chunks: whole rows while a row fits the staging buffer, else pieces of the one long row
-  struct Chunk { size_t row, off, nrows, bytes; };
-  std::vector<Chunk> ch;
-  if (width <= stage) {
-    const size_t per = std::max<size_t>(1, stage / width);
-    for (size_t r = 0; r < rows; r += per) ch.push_back({r, 0, std::min(per, rows - r), 0});
-  } else {
-    for (size_t r = 0; r < rows; ++r)
-      for (size_t o = 0; o < width; o += stage) ch.push_back({r, o, 0, std::min(stage, width - o)});
-  }
-  auto issue = [&](size_t j) -> int {
-    const Chunk& c = ch[j];
-    const char* s = (const char*)src + c.row * spitch + c.off;
-    if (c.nrows) CUDA_TRY(cudaMemcpy2DAsync(g_stage[j & 1], width, s, spitch, width, c.nrows, cudaMemcpyDeviceToHost, st));
-    else CUDA_TRY(cudaMemcpyAsync(g_stage[j & 1], s, c.bytes, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(g_stage_ev[j & 1], st));
+  auto send = [&](size_t row, size_t off, size_t nrows, size_t bytes) -> int {
+    const int b = g_next;
+    RC(complete(b));                               // the buffer's previous chunk goes out while the other buffer fills
+    const char* s = (const char*)src + row * spitch + off;
+    if (nrows) CUDA_TRY(cudaMemcpy2DAsync(g_stage[b], width, s, spitch, width, nrows, cudaMemcpyDeviceToHost, st));
+    else CUDA_TRY(cudaMemcpyAsync(g_stage[b], s, bytes, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(g_stage_ev[b], st));
+    Pending& p = g_pend[b];
+    p.on = true; p.dst = (char*)dst + row * dpitch + off; p.dpitch = dpitch; p.width = width; p.nrows = nrows; p.bytes = bytes;
+    g_next ^= 1;
     return LITAP_OK;
   };
-  static const bool debug = getenv("LITAP_COPY_DEBUG") != nullptr;
-  static double t_wait = 0, t_copy = 0, t_bytes = 0;
-  auto now = [] { return std::chrono::steady_clock::now(); };
-  RC(issue(0));
-  for (size_t j = 0; j < ch.size(); ++j) {
-    if (j + 1 < ch.size()) RC(issue(j + 1));      // buffer (j + 1) & 1 was drained by the host copy of chunk j - 1
-    const auto t0 = now();
-    CUDA_TRY(cudaEventSynchronize(g_stage_ev[j & 1]));
-    const auto t1 = now();
-    struct Acc { decltype(t1) a; double& slot; ~Acc() { slot += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - a).count(); } } acc{t1, t_copy};
-    t_wait += std::chrono::duration<double, std::milli>(t1 - t0).count();
-    const Chunk& c = ch[j];
-    t_bytes += c.nrows ? (double)c.nrows * width : (double)c.bytes;
-    char* d = (char*)dst + c.row * dpitch + c.off;
-    const char* s = (const char*)g_stage[j & 1];
-    if (!c.nrows) host_copy(d, s, c.bytes, nt);
-    else if (dpitch == width) host_copy(d, s, c.nrows * width, nt);
-    else for (size_t r = 0; r < c.nrows; ++r) memcpy(d + r * dpitch, s + r * width, width);
+  if (width <= stage) {
+    const size_t per = std::max<size_t>(1, stage / width);
+    for (size_t r = 0; r < rows; r += per) RC(send(r, 0, std::min(per, rows - r), 0));
+  } else {
+    for (size_t r = 0; r < rows; ++r)
+      for (size_t o = 0; o < width; o += stage) RC(send(r, o, 0, std::min(stage, width - o)));
   }
-  if (debug) fprintf(stderr, "[hostcopy] cumulative: %.0f MB, waiting for the device %.1f ms, host copies %.1f ms\n", t_bytes / 1e6, t_wait, t_copy);
   return LITAP_OK;
+}
+
+// completes the staged downloads (older buffer first)
+int hostcopy_flush() {
+  RC(complete(g_next));
+  RC(complete(g_next ^ 1));
+  static const bool debug = getenv("LITAP_COPY_DEBUG") != nullptr;
+  if (debug && g_bytes > 0)
+    fprintf(stderr, "[hostcopy] cumulative: %.0f MB, waiting for the device %.1f ms, host copies %.1f ms\n", g_bytes / 1e6, g_wait_ms, g_copy_ms);
+  return LITAP_OK;
+}
+// a call that failed half way may have left chunks pending: their destination belongs to that call, drop them
+void hostcopy_reset() {
+  if (g_pend[0].on || g_pend[1].on) cudaDeviceSynchronize();
+  g_pend[0].on = g_pend[1].on = false;
 }
 
 void hostcopy_forget_staging() {   // litap_shutdown

@@ -279,6 +279,7 @@ extern "C" int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint
   for (int64_t k = 0; k < npond; ++k)
     if (pond_shedno[k] < 1 || pond_shedno[k] > n) return set_error(LITAP_EARG, "litap_relz: pond shedno out of range");
   RC(ensure_init());
+  hostcopy_reset();
   Ctx& c = ctx();
   cudaStream_t st = c.stream;
   c.tm = litap_timings{};
@@ -355,6 +356,7 @@ extern "C" int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint
   CUDA_TRY(cudaEventRecord(c.ev[4], st));
   for (int k = 0; k < RELZ_NOUT; ++k)   // pageable destinations (R vectors, numpy arrays) go through pinned staging buffers
     if (out[k]) RC(d2h_2d(out[k], (size_t)n * sizeof(double), O.o[k], (size_t)n * sizeof(double), (size_t)n * sizeof(double), 1, st));
+  RC(hostcopy_flush());
   CUDA_TRY(cudaEventRecord(c.ev[5], st));
   CUDA_TRY(cudaStreamSynchronize(st));
   cudaEventElapsedTime(&c.tm.h2d_ms, c.ev[6], c.ev[7]);
