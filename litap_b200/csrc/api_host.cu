@@ -17,9 +17,7 @@ struct Wall {
 
 template <typename T>
 int up(T* dst, const GridDims& d, const T* src) {
-  CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)d.pitch * sizeof(T), src, (size_t)d.NC * sizeof(T),
-                             (size_t)d.NC * sizeof(T), d.NR, cudaMemcpyHostToDevice, ctx().stream));
-  return LITAP_OK;
+  return h2d_2d(dst, (size_t)d.pitch * sizeof(T), src, (size_t)d.NC * sizeof(T), (size_t)d.NC * sizeof(T), d.NR, ctx().stream);
 }
 template <typename T>
 int down(T* dst, const GridDims& d, const T* src) {
@@ -103,8 +101,8 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   int form_done = 0;  // rows [0, form_done) of the form outputs are computed
   for (int a = 0; a < d.NR; a += crows) {
     const int b = a + crows < d.NR ? a + crows : d.NR;
-    CUDA_TRY(cudaMemcpy2DAsync(g->elev + (size_t)a * d.pitch, (size_t)d.pitch * 8, elev + (size_t)a * d.NC, (size_t)d.NC * 8,
-                               (size_t)d.NC * 8, b - a, cudaMemcpyHostToDevice, c.stream));
+    RC(h2d_2d(g->elev + (size_t)a * d.pitch, (size_t)d.pitch * 8, elev + (size_t)a * d.NC, (size_t)d.NC * 8,
+              (size_t)d.NC * 8, b - a, c.stream));
     if (!want_form) continue;
     const int hi = b == d.NR ? d.NR : b - 1;  // row hi is needed as the window row below hi - 1
     if (hi <= form_done) continue;

@@ -131,6 +131,50 @@ int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
   return LITAP_OK;
 }
 
+// ---- uploads from pageable caller memory ------------------------------------------------------------------
+// Same idea the other way round (own pair of staging buffers): host threads fill buffer b while the copy engine
+// drains buffer b ^ 1.  Nothing refers to the caller's memory any more when the call returns; the last chunks
+// are still on their way from the staging buffers, in stream order before whatever the caller enqueues next.
+namespace {
+void* g_up[2] = {nullptr, nullptr};
+cudaEvent_t g_up_ev[2] = {nullptr, nullptr};
+int g_up_next = 0;
+int up_init() {
+  for (int b = 0; b < 2; ++b) {
+    if (!g_up[b]) CUDA_TRY(cudaHostAlloc(&g_up[b], HC_STAGE, cudaHostAllocDefault));
+    if (!g_up_ev[b]) CUDA_TRY(cudaEventCreateWithFlags(&g_up_ev[b], cudaEventDisableTiming));
+  }
+  return LITAP_OK;
+}
+}  // namespace
+
+int h2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st) {
+  if (!rows || !width) return LITAP_OK;
+  if (!pageable(src) || width > HC_STAGE || spitch != width) {
+    CUDA_TRY(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, rows, cudaMemcpyHostToDevice, st));
+    return LITAP_OK;
+  }
+  RC(up_init());
+  const int nt = copy_threads();
+  size_t stage = HC_STAGE;
+  if (const char* e = getenv("LITAP_STAGE_KB")) stage = std::min(HC_STAGE, std::max<size_t>(4096, (size_t)atol(e) << 10));
+  const size_t per = std::max<size_t>(1, stage / width);
+  if (width > stage) {   // (only with a test-sized LITAP_STAGE_KB)
+    CUDA_TRY(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, rows, cudaMemcpyHostToDevice, st));
+    return LITAP_OK;
+  }
+  for (size_t r = 0; r < rows; r += per) {
+    const size_t nr = std::min(per, rows - r);
+    const int b = g_up_next;
+    CUDA_TRY(cudaEventSynchronize(g_up_ev[b]));     // the copy engine is done with this buffer (no-op the first time)
+    host_copy((char*)g_up[b], (const char*)src + r * spitch, nr * width, nt);
+    CUDA_TRY(cudaMemcpy2DAsync((char*)dst + r * dpitch, dpitch, g_up[b], width, width, nr, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaEventRecord(g_up_ev[b], st));
+    g_up_next ^= 1;
+  }
+  return LITAP_OK;
+}
+
 // completes the staged downloads (older buffer first)
 int hostcopy_flush() {
   RC(complete(g_next));
@@ -150,5 +194,7 @@ void hostcopy_forget_staging() {   // litap_shutdown
   for (int b = 0; b < 2; ++b) {
     if (g_stage[b]) { cudaFreeHost(g_stage[b]); g_stage[b] = nullptr; }
     if (g_stage_ev[b]) { cudaEventDestroy(g_stage_ev[b]); g_stage_ev[b] = nullptr; }
+    if (g_up[b]) { cudaFreeHost(g_up[b]); g_up[b] = nullptr; }
+    if (g_up_ev[b]) { cudaEventDestroy(g_up_ev[b]); g_up_ev[b] = nullptr; }
   }
 }

@@ -107,6 +107,7 @@ void pool_free(void* p);
 void pool_release_all();
 // hostcopy.cu: device -> caller memory; pageable destinations go through pinned staging buffers + host threads
 int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st);
+int h2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st);
 int hostcopy_flush();    // pageable destinations are complete after this
 void hostcopy_reset();   // start of a call: forget chunks a failed call left pending
 void hostcopy_forget_staging();

@@ -250,7 +250,13 @@ template <typename T>
 int to_dev(PoolScratch& S, T** dst, const T* src, size_t n) {
   *dst = S.get<T>(n);
   if (!*dst) return set_error(LITAP_ENOMEM, "device allocation failed (relz inputs)");
-  CUDA_TRY(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx().stream));
+  // as rows of at most 32 MB so that pageable sources go through the staged upload
+  const size_t bytes = n * sizeof(T), row = 32u << 20, full = bytes / row;
+  if (full) { int rc = h2d_2d(*dst, row, src, row, row, full, ctx().stream); if (rc) return rc; }
+  if (bytes > full * row) {
+    int rc = h2d_2d((char*)*dst + full * row, bytes - full * row, (const char*)src + full * row, bytes - full * row, bytes - full * row, 1, ctx().stream);
+    if (rc) return rc;
+  }
   return LITAP_OK;
 }
 
