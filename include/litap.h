@@ -50,7 +50,7 @@ typedef struct litap_timings {
   float weti_ms;
   float total_ms;   /* whole call, incl. copies */
   int plateau_rounds;
-  int weti_waves;   /* dependency waves of the last calc_weti2 (depth of the flow DAG) */
+  int weti_queued;  /* calc_weti2: cells handed over through the global ready queues (the others were kept by the lane that released them) */
   int64_t flat_cells, patch_cells, npits;
   int64_t kernel_launches; /* kernels of this library launched by the call */
   float gc_ms;      /* slope_gc */

@@ -28,7 +28,7 @@ class LitapError(RuntimeError):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("d2h_ms", C.c_float), ("ddir_ms", C.c_float),
                 ("shed_ms", C.c_float), ("form_ms", C.c_float), ("weti_ms", C.c_float),
-                ("total_ms", C.c_float), ("plateau_rounds", C.c_int), ("weti_waves", C.c_int),
+                ("total_ms", C.c_float), ("plateau_rounds", C.c_int), ("weti_queued", C.c_int),
                 ("flat_cells", C.c_int64),
                 ("patch_cells", C.c_int64), ("npits", C.c_int64), ("kernel_launches", C.c_int64),
                 ("gc_ms", C.c_float), ("relz_ms", C.c_float)]

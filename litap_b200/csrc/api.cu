@@ -232,6 +232,8 @@ extern "C" int litap_grid_form(litap_grid* g, double grid_m) {
 extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
   if (!g) return set_error(LITAP_EARG, "litap_grid_weti: NULL");
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_weti: grid must be > 0");
+  if (g->nbands > 0)   // the visiting order couples all bands: a band on its own would give a band-local (wrong) answer
+    return set_error(LITAP_EARG, "litap_grid_weti: not available on a row band (run it on a whole-DEM grid)");
   if (!g->ddir || !g->upslope) return set_error(LITAP_EARG, "litap_grid_weti: needs ddir and upslope on the grid");
   int64_t l0 = ctx().launches;
   StageTimer t(&ctx().tm.weti_ms, 6);

@@ -17,7 +17,7 @@ g.ddir(); g.shed()
 for it in range(reps):
     g.weti(5.0)
     t = lb.timings()
-    print(f"rep {it}: weti {t['weti_ms']:.3f} ms  waves {t['weti_waves']}  launches {t['kernel_launches']}  "
+    print(f"rep {it}: weti {t['weti_ms']:.3f} ms  queued {t['weti_queued']}  launches {t['kernel_launches']}  "
           f"-> {n * n / t['weti_ms'] / 1e3:.1f} Mcells/s")
 _lib.profile(True)
 g.weti(5.0)
