@@ -659,15 +659,38 @@ LITAP_HD double ld80_to_double(Ld80 a) {
 // ---------------------------------------------------------------------------------------------
 // calc_weti2 per-cell pieces (R/form_02b_calc_weti.R:47-67).  Window visit order of the reference:
 // NW,N,NE,W,self,E,SW,S,SE = neighbour codes 7,8,9,4,5,6,1,2,3.
-struct WetiK { double l1, l2, orth, diag, g2; };  // grid*0.5, grid*0.354, grid, grid*sqrt(2), grid^2
+struct WetiK {
+  double l1, l2, orth, diag, g2;   // grid*0.5, grid*0.354, grid, grid*sqrt(2), grid^2
+  double rorth, rdiag, r1e4;       // RN(1/orth), RN(1/diag), RN(1/0.0001) for div_rcp (0 = use the IEEE division)
+};
+// a / b, correctly rounded, from y = RN(1/b) computed once: two Newton corrections with exact residuals
+// (Markstein 1990: if y is the correctly rounded reciprocal and q is within 1 ulp of a/b, then
+// RN(q + (a - b q) y) = RN(a/b); the first correction makes q faithful, the second one applies the theorem).
+// Five dependent operations instead of the ~12 + range check of the generic division; bit-identical results
+// (checked against the division on 4e9 random and structured operands by tests/test_host_cpu.py).  Operands
+// outside the range in which the residuals are exact (|a| outside 2^-900 .. 2^900, zero, inf, NaN) and
+// callers without a usable reciprocal (y == 0) take the IEEE division.
+LITAP_HD double div_rcp(double a, double b, double y) {
+  const unsigned ex = (unsigned)((ld80_bits(a) >> 52) & 0x7FFull);
+  if (ex - 123u > 1800u || y == 0.0) return a / b;
+  double q = a * y;
+  double r = fma(-q, b, a);
+  q = fma(r, y, q);
+  r = fma(-q, b, a);
+  return fma(r, y, q);
+}
+// reciprocal usable by div_rcp, else 0: b must be far from the ends of the exponent range
+LITAP_HD double div_rcp_prepare(double b) {
+  const double ab = b < 0 ? -b : b;
+  return (ab > 1e-30 && ab < 1e30) ? 1.0 / b : 0.0;
+}
 LITAP_HD bool weti_is_diag(int n) { return n == 1 || n == 3 || n == 7 || n == 9; }
 // tan_k of a cell at elevation f towards a neighbour at elevation nv in direction n (:64-65);
 // NaN neighbour -> NaN, neighbour not lower -> 0
 LITAP_HD double weti_tan(double f, double nv, int n, const WetiK& K) {
+  if (!(nv < f)) return is_nan(nv) ? nv : 0.0;
   const bool dg = weti_is_diag(n);
-  double t = ((f - nv) / (dg ? K.diag : K.orth)) * (dg ? K.l2 : K.l1);
-  if (nv >= f) t = 0;
-  return t;
+  return div_rcp(f - nv, dg ? K.diag : K.orth, dg ? K.rdiag : K.rorth) * (dg ? K.l2 : K.l1);
 }
 // S = sum(tan, na.rm = TRUE) with R's long double accumulator; e[n] = elevation of neighbour n
 // (e[5] = the cell itself).  *lower gets bit n set for every strictly lower neighbour.

@@ -121,3 +121,31 @@ extern "C" double host_real_ld_sum(const double* t, int n) {
   for (int i = 0; i < n; ++i) s += t[i];
   return (double)s;
 }
+
+// div_rcp (Markstein division from a precomputed reciprocal) vs the IEEE division: number of operand pairs, out of
+// n, whose results differ in any bit.  Operands: random mantissas over a range of exponents, mantissas with long
+// runs of ones / zeros, quotients next to a power of two, and dividends that are (nearly) integer multiples of b.
+extern "C" long long host_div_rcp_check(long long n, unsigned long long seed) {
+  unsigned long long s = seed * 0x9E3779B97F4A7C15ull + 1;
+  auto next = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return s; };
+  auto mk = [&](unsigned long long mant, int ex) {
+    unsigned long long b = ((unsigned long long)(ex + 1023) << 52) | (mant & 0x000FFFFFFFFFFFFFull);
+    double x; __builtin_memcpy(&x, &b, 8); return x;
+  };
+  long long bad = 0;
+  for (long long i = 0; i < n; ++i) {
+    unsigned long long ma = next(), mb = next();
+    const unsigned kind = (unsigned)(next() & 7);
+    if (kind == 1) { ma |= ~0ull << (next() & 31); mb |= ~0ull << (next() & 31); }       // runs of ones
+    if (kind == 2) { ma &= ~0ull << (next() & 47); mb &= ~0ull << (next() & 47); }       // few significant bits
+    if (kind == 3) mb = 0x000FFFFFFFFFFFFFull - (next() & 15);                            // b just below a power of two
+    const int ea = (int)(next() % 61) - 30, eb = (int)(next() % 41) - 20;
+    double b = mk(mb, eb), a = mk(ma, ea);
+    if (kind == 4) a = b * (double)(1 + (next() & 1023));                                 // exact or near-exact quotients
+    if (kind == 5) a = b * (double)(1 + (next() & 1023)) + mk(0, eb - 52 + (int)(next() & 3));
+    const double y = div_rcp_prepare(b);
+    const double q1 = div_rcp(a, b, y), q2 = a / b;
+    bad += __builtin_memcmp(&q1, &q2, 8) != 0;
+  }
+  return bad;
+}

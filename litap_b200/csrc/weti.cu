@@ -24,9 +24,14 @@
 //   k_weti_flow     persistent kernel, no grid barrier: a lane visits a ready cell (adds its donors'
 //                   contributions in the reference's order — no FP atomics —, derives qc, publishes
 //                   its state, decrements its successors' pending counters) and KEEPS one of the cells
-//                   it released for itself, so a dependency chain costs one atomic + two memory round
-//                   trips per hop; other released cells go to free lanes of the warp, the rest to one
-//                   of 64 global ready queues that idle lanes wait on (each waits on its own slot)
+//                   it released for itself.  A hop of a dependency chain costs TWO memory round trips:
+//                   (1) the donors' state, (2) the 64-bit atomic decrement of the successors' topology
+//                   words, which hands the releasing lane the released cell's whole topology (donor
+//                   codes, successor mask, class).  There is no fence between a cell's state stores and
+//                   its decrements: states start as an all-ones pattern and a reader that still sees it
+//                   loads again (data as flag).  Other released cells go to free lanes of the warp, the
+//                   rest to one of 64 global ready queues that idle lanes wait on (each on its own slot);
+//                   queue claims and polls are issued under the shadow of the visit's loads
 //   k_weti_qflags + cub scans   the reference's qc1/qc2 are variables that survive between loop
 //                   iterations (:70-71,:80 vs :87-88): a B cell reads the qc2, a pit the qc1 and qc2
 //                   of the last cell before it in the visiting order that assigned them -> prefix
@@ -54,36 +59,34 @@ constexpr int WT = 256;                  // threads per block
 constexpr int WPB = WT / 32;
 constexpr int WBUF = 32 * 7;             // cells a warp can release beyond the ones its lanes keep
 
-struct __align__(32) Node {   // everything a visit needs about the cell itself: one 32-byte sector
-  double S;          // sum(tan) of the cell (A cells: != 0)
-  double f;          // its elevation
-  uint32_t donors;   // up to 8 nibbles: direction codes (from the cell towards the donor) in visiting order, 0 ends
-  uint16_t succ;     // bit n: neighbour n waits for this cell (lower neighbours of an A cell; drec of an early B cell)
-  uint8_t cls;       // CLS_*
-  uint8_t bmask;     // bit j: j-th donor is a B donor (contributes its whole qa)
-  uint32_t pad0, pad1;
-};
-struct __align__(32) State {
-  double qc1, qc2;   // as assigned by the cell itself (NaN where the reference leaves the variable stale)
-  double qa1, qa2;   // qa at processing time
-};
+// topology word of a cell, 64 bits.  The lane that drops the pending counter to zero gets the whole word back from
+// its atomic decrement and needs no further load to start the visit:
+//   [0,4) pending donors   [4,36) donor codes (direction from the cell towards the donor), 4 bits each, in visiting
+//   order, 0 ends   [36,45) bit 36+n-1: neighbour n waits for this cell (lower neighbours of an A cell; drec of an
+//   early B cell)   [45,47) class   [47,55) bit 47+j: the j-th donor is a B donor (contributes its whole qa)
+constexpr int TP_DON = 4, TP_SUCC = 36, TP_CLS = 45, TP_BM = 47;
+// state of a cell: 8 doubles = two 32-byte sectors.  A receiver reads one sector per donor.
+//   [0] qc1 [1] qc2 (as assigned by the cell itself; NaN where the reference leaves the variable stale) [2] f [3] S
+//   [4] qa1 [5] qa2 (qa at processing time) [6] RN(1/S) or 0 [7] -
+// qc* / qa* hold the all-ones pattern until the cell has been visited
+constexpr int ST_QC = 0, ST_F = 2, ST_S = 3, ST_QA = 4, ST_RS = 6, ST_N = 8;
+constexpr unsigned long long UNSET = ~0ull;
 // visiting-order key: later visited <=> (hi, lo) larger.  hi = ~orderable(elev), lo = upslope << 32 | cell id
 struct __align__(16) K128 { unsigned long long lo, hi; };
 struct __align__(128) QCount { unsigned v; unsigned pad[31]; };
 struct Ctl {
   unsigned nvalid, nq, done, finished, abort, pad[3];
-  unsigned long long st_pushed, st_popped, st_kept, st_shared, st_iters, st_idle;
+  unsigned long long st_pushed, st_popped, st_kept, st_shared, st_iters, st_idle, st_respin;
 };
 
 struct Arrays {
   const double* elev;
   const uint8_t* ddir;
   const uint32_t* upslope;
-  Node* node;
-  State* state;
+  unsigned long long* topo;
+  double* st;          // ST_N doubles per cell
   uint8_t* cls;        // CLS_* only (neighbour lookups)
-  uint32_t* pend32;    // packed 8-bit pending-donor counters
-  uint32_t* order;     // NQ ready queues of qcap slots each, NONE = not yet written
+  ulonglong2* order;   // NQ ready queues of qcap entries {topology word, cell id}; all ones = not yet written
   QCount* qtail;       // [NQ]
   QCount* qhead;       // [NQ]
   unsigned qcap;
@@ -247,32 +250,64 @@ __device__ __forceinline__ void slot_max(K128* p, const K128& k) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// ready queues.  Queue q owns order[q*qcap, (q+1)*qcap); a slot is written once (NONE -> cell id) and
-// read by the one lane that claimed its index from qhead.  Items that do not fit a queue go to the next
-// one; a claim beyond qcap is void and sends the claiming warp on to the next queue.  Total capacity
-// exceeds cells + waiting lanes, so neither side can run out.
+// memory accesses of the dataflow, all at L2 (the data is shared between SMs), in program order (asm volatile)
+__device__ __forceinline__ double2 ld_cg_f64x2(const double* p) {
+  double2 v;
+  asm volatile("ld.global.cg.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double ld_cg_f64(const double* p) {
+  double v;
+  asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_cg_f64x2(double* p, double x, double y) {
+  asm volatile("st.global.cg.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(x), "d"(y) : "memory");
+}
+__device__ __forceinline__ ulonglong2 ld_entry(const ulonglong2* p) {
+  ulonglong2 v;
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_entry(ulonglong2* p, unsigned long long tp, uint32_t id) {
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(tp), "l"((unsigned long long)id) : "memory");
+}
+__device__ __forceinline__ unsigned long long atom_dec_u64(unsigned long long* p) {
+  unsigned long long old;
+  asm volatile("atom.global.relaxed.gpu.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(~0ull) : "memory");
+  return old;
+}
 __device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 __device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+__device__ __forceinline__ bool is_unset(double x) { return (unsigned long long)__double_as_longlong(x) == UNSET; }
 
-// the whole warp pushes items[0, n) (shared memory)
-__device__ __forceinline__ void warp_push(const Arrays& A, unsigned& pushq, const uint32_t* items, unsigned n, int lane) {
+// ready queues.  Queue q owns order[q*qcap, (q+1)*qcap); an entry is written once (all ones -> {topology, cell})
+// and read by the one lane that claimed its index from qhead.  Items that do not fit a queue go to the next
+// one; a claim beyond qcap is void and sends the claiming warp on to the next queue.  Total capacity
+// exceeds cells + waiting lanes, so neither side can run out.
+// the whole warp pushes n items (shared memory)
+__device__ __forceinline__ void warp_push(const Arrays& A, unsigned& pushq, const uint32_t* ids, const unsigned long long* tps,
+                                          unsigned n, int lane) {
   while (n) {
     unsigned base = 0;
     if (lane == 0) base = atomicAdd(&A.qtail[pushq].v, n);
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     const unsigned fit = base >= A.qcap ? 0u : min(n, A.qcap - base);
-    uint32_t* dst = A.order + (size_t)pushq * A.qcap + base;
-    for (unsigned k = lane; k < fit; k += 32) st_volatile(dst + k, items[k]);
-    items += fit;
+    ulonglong2* dst = A.order + (size_t)pushq * A.qcap + base;
+    for (unsigned k = lane; k < fit; k += 32) st_entry(dst + k, tps[k], ids[k]);
+    ids += fit;
+    tps += fit;
     n -= fit;
     pushq = (pushq + 1) % NQ;
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// node of every cell: S, donors in visiting order, successors, pending counter; seeds; last-setter slots
+// topology word and state of every cell: S, donors in visiting order, successors, pending counter; seeds;
+// last-setter slots
 __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K) {
   __shared__ uint32_t s_ids[WT];
+  __shared__ unsigned long long s_tps[WT];
   __shared__ unsigned s_n;
   if (threadIdx.x == 0) s_n = 0;
   __syncthreads();
@@ -281,21 +316,19 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
   if (c < d.NC) {
     const size_t id = (size_t)r * d.pitch + c;
     const uint8_t cls = A.cls[id];
-    Node m;
-    m.S = 0; m.f = 0; m.donors = 0; m.succ = 0; m.cls = cls; m.bmask = 0; m.pad0 = 0; m.pad1 = 0;
+    unsigned long long tp = 0;
     if (cls != CLS_NA) {
       double e[10];
 #pragma unroll
       for (int n = 1; n <= 9; ++n) e[n] = A.elev[id + nb_off(n, d.pitch)];
       const double f = e[5];
-      m.f = f;
-      unsigned lower = 0;
-      if (cls == CLS_A) m.S = weti_S(e, K, &lower);
-      m.succ = (uint16_t)lower;
+      double S = 0;
+      unsigned succ = 0;
+      if (cls == CLS_A) S = weti_S(e, K, &succ);
       const int dv = A.ddir[id];
       if (cls == CLS_B && dv >= 1 && dv <= 9) {   // an early B cell pushes its qa into drec before drec is visited
         const size_t tid = id + nb_off(dv, d.pitch);
-        if (A.cls[tid] != CLS_NA && visited_before(A, f, id, e[dv], tid)) m.succ = (uint16_t)(1u << dv);
+        if (A.cls[tid] != CLS_NA && visited_before(A, f, id, e[dv], tid)) succ = 1u << dv;
       }
       // donors that precede the cell: strictly higher neighbours (they are A cells and push qc*tan, :74-75) and B
       // neighbours whose drec is this cell and that are visited first (they push their whole qa, :82-83)
@@ -330,11 +363,19 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
 #pragma unroll
       for (int n = 1; n <= 9; ++n) {
         if (n == 5 || !((dmask >> n) & 1)) continue;
-        m.donors |= (uint32_t)n << (4 * pos[n]);
-        if ((bdon >> n) & 1) m.bmask |= (uint8_t)(1u << pos[n]);
+        tp |= (unsigned long long)n << (TP_DON + 4 * pos[n]);
+        if ((bdon >> n) & 1) tp |= 1ull << (TP_BM + pos[n]);
       }
-      reinterpret_cast<uint8_t*>(A.pend32)[id] = (uint8_t)nd;
-      if (nd == 0) s_ids[atomicAdd(&s_n, 1u)] = (uint32_t)id;
+      tp |= (unsigned long long)nd | ((unsigned long long)succ << (TP_SUCC - 1)) | ((unsigned long long)cls << TP_CLS);
+      if (nd == 0) {
+        const unsigned k = atomicAdd(&s_n, 1u);
+        s_ids[k] = (uint32_t)id;
+        s_tps[k] = tp;
+      }
+      const double unset = __longlong_as_double((long long)UNSET);
+      double4* sp = reinterpret_cast<double4*>(A.st + id * ST_N);
+      sp[0] = make_double4(unset, unset, f, S);
+      sp[1] = make_double4(unset, unset, cls == CLS_A ? div_rcp_prepare(S) : 0.0, 0.0);
       // last-setter candidate: the A cell records itself in the interval between two queries it falls in
       if (cls == CLS_A && A.nq) {
         const K128 k = make_key(f, A.upslope[id], (uint32_t)id);
@@ -342,8 +383,7 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
         slot_max(&A.slotA[locate(A, bm, f, k)], k);
       }
     }
-    *reinterpret_cast<uint4*>(&A.node[id]) = *reinterpret_cast<const uint4*>(&m);
-    *(reinterpret_cast<uint4*>(&A.node[id]) + 1) = *(reinterpret_cast<const uint4*>(&m) + 1);
+    A.topo[id] = tp;
   }
   __syncthreads();
   // seeds of this block -> one ready queue (overflow goes on to the next)
@@ -351,14 +391,15 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
   if (!n) return;
   __shared__ unsigned s_base;
   unsigned q = (blockIdx.y * gridDim.x + blockIdx.x) % NQ;
-  const uint32_t* items = s_ids;
+  unsigned at = 0;
   while (n) {
     if (threadIdx.x == 0) s_base = atomicAdd(&A.qtail[q].v, n);
     __syncthreads();
     const unsigned base = s_base;
     const unsigned fit = base >= A.qcap ? 0u : min(n, A.qcap - base);
-    for (unsigned k = threadIdx.x; k < fit; k += blockDim.x) A.order[(size_t)q * A.qcap + base + k] = items[k];
-    items += fit;
+    for (unsigned k = threadIdx.x; k < fit; k += blockDim.x)
+      A.order[(size_t)q * A.qcap + base + k] = make_ulonglong2(s_tps[at + k], (unsigned long long)s_ids[at + k]);
+    at += fit;
     n -= fit;
     q = (q + 1) % NQ;
     __syncthreads();
@@ -366,148 +407,152 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
 }
 
 // ------------------------------------------------------------------------------------------------
-// visit one ready cell: add the donors' contributions in the reference's order, derive qc, publish the
-// state, release the successors.  Returns the mask of neighbour codes whose cells became ready.
-__device__ __forceinline__ unsigned visit(const Arrays& A, int pitch, const WetiK& K, size_t id, int flags) {
-  Node m;
-  {
-    const uint4* p = reinterpret_cast<const uint4*>(&A.node[id]);
-    const uint4 a = __ldg(p), b = __ldg(p + 1);
-    *reinterpret_cast<uint4*>(&m) = a;
-    *(reinterpret_cast<uint4*>(&m) + 1) = b;
-  }
-  const double f = m.f;
-  // all donor loads are issued before the (ordered) additions: one memory round trip, not eight
-  double2 dv[8];
-  double de[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int n = (m.donors >> (4 * j)) & 15;
-    dv[j] = make_double2(0.0, 0.0);
-    de[j] = 0.0;
-    if (n) {
-      const size_t nid = id + nb_off(n, pitch);
-      const bool isb = (m.bmask >> j) & 1;
-      dv[j] = __ldcg(reinterpret_cast<const double2*>(&A.state[nid]) + (isb ? 1 : 0));
-      if (!isb) de[j] = __ldg(&A.elev[nid]);
-    }
-  }
-  if (flags & 1) {   // pull the successors' nodes towards L2 while the donors' state is in flight
-#pragma unroll
-    for (int n = 1; n <= 9; ++n)
-      if ((m.succ >> n) & 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(&A.node[id + nb_off(n, pitch)]));
-  }
-  double qa1 = 1.0, qa2 = K.g2;  // :35-36
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int n = (m.donors >> (4 * j)) & 15;
-    if (!n) break;
-    if ((m.bmask >> j) & 1) {  // :82-83, the donor's whole qa
-      qa1 = qa1 + dv[j].x;
-      qa2 = qa2 + dv[j].y;
-    } else {                   // :74-75, qc * tan of the donor towards this cell
-      const double t = weti_tan(de[j], f, n, K);
-      qa1 = qa1 + (dv[j].x * t);
-      qa2 = qa2 + (dv[j].y * t);
-    }
-  }
-  const double nan = __longlong_as_double(0x7ff8000000000000LL);
-  double2 qc;
-  if (m.cls == CLS_A) { qc.x = qa1 / m.S; qc.y = qa2 / m.S; }       // :70-71
-  else if (m.cls == CLS_B) { qc.x = qa1 / 0.0001; qc.y = nan; }      // :80 (qc2 keeps its old value)
-  else { qc.x = nan; qc.y = nan; }
-  double2* op = reinterpret_cast<double2*>(&A.state[id]);
-  __stcg(op, qc);
-  __stcg(op + 1, make_double2(qa1, qa2));
-  unsigned rel = 0;
-  if (m.succ) {
-    __threadfence();
-    unsigned old[10];
-#pragma unroll
-    for (int n = 1; n <= 9; ++n) {
-      old[n] = 0;
-      if ((m.succ >> n) & 1) {
-        const size_t tid = id + nb_off(n, pitch);
-        old[n] = atomicSub(&A.pend32[tid >> 2], 1u << (8u * (unsigned)(tid & 3)));
-      }
-    }
-#pragma unroll
-    for (int n = 1; n <= 9; ++n) {
-      if ((m.succ >> n) & 1) {
-        const size_t tid = id + nb_off(n, pitch);
-        if (((old[n] >> (8u * (unsigned)(tid & 3))) & 0xFFu) == 1u) rel |= 1u << n;
-      }
-    }
-  }
-  return rel;
-}
-
-__global__ void __launch_bounds__(WT) k_weti_flow(Arrays A, GridDims d, WetiK K, int flags, unsigned idle_limit) {
-  __shared__ uint32_t s_buf[WPB][WBUF];
+// The dataflow.  A lane owns at most one ready cell (cur, with its topology word tp).  Per iteration of a warp:
+//   issue   the queue claim of the lanes that have nothing, and the loads of the lanes that visit: own f / S / 1/S and the
+//           donors' states (NB at a time)
+//   wait    for the claim, issue the poll of the claimed entries
+//   visit   add the donors' contributions in the reference's order, derive qc, store the state, decrement the successors
+//   wait    for the decrements: cells whose counter dropped to zero are released; the lane keeps the first one, free
+//           lanes of the warp take the next ones, the rest goes to a ready queue; polled entries that were ready are taken
+template <int NB>
+__global__ void __launch_bounds__(WT, NB == 8 ? 2 : (NB == 6 ? 3 : 4)) k_weti_flow(Arrays A, GridDims d, WetiK K, unsigned idle_limit) {
+  __shared__ uint32_t s_id[WPB][WBUF];
+  __shared__ unsigned long long s_tp[WPB][WBUF];
+  __shared__ int s_off[16];   // neighbour code -> cell offset (the donors' codes are data, not loop indices)
+  if (threadIdx.x < 16) s_off[threadIdx.x] = (threadIdx.x >= 1 && threadIdx.x <= 9) ? nb_off((int)threadIdx.x, d.pitch) : 0;
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
   const unsigned gw = blockIdx.x * WPB + wib;   // global warp number
-  uint32_t* wbuf = s_buf[wib];
+  uint32_t* wid = s_id[wib];
+  unsigned long long* wtp = s_tp[wib];
   const unsigned lt = (1u << lane) - 1;
+  const int pitch = d.pitch;
   unsigned home = gw % NQ, pushq = (gw * 7 + 3) % NQ;
   uint32_t cur = NONE, claim = NONE;
+  unsigned long long tp = 0;
   unsigned visited = 0, idle = 0;
-  unsigned long long n_pushed = 0, n_popped = 0, n_kept = 0, n_shared = 0, n_iters = 0, n_idle = 0;
+  unsigned n_pushed = 0, n_popped = 0, n_kept = 0, n_shared = 0, n_iters = 0, n_idle = 0, n_respin = 0;
   const unsigned nvalid = A.ctl->nvalid;
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
   for (;;) {
-    // lanes without a cell and without a claim take the next index of the warp's home queue
+    // ---- issue: queue claim
     const unsigned need = __ballot_sync(0xFFFFFFFFu, cur == NONE && claim == NONE);
+    const int leader = __ffs(need) - 1;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(&A.qhead[home].v, (unsigned)__popc(need));
+    // ---- issue: loads of the visit
+    const bool go = cur != NONE;
+    const size_t id = go ? cur : 0;
+    const double* sp = A.st + id * ST_N;
+    double2 fs = make_double2(0.0, 0.0), dv[NB];
+    double rs = 0.0, de[NB];
+    if (go) {
+      fs = ld_cg_f64x2(sp + ST_F);
+      rs = ld_cg_f64(sp + ST_RS);
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        const int n = (int)(tp >> (TP_DON + 4 * j)) & 15;
+        dv[j] = make_double2(0.0, 0.0);
+        de[j] = 0.0;
+        if (n) {
+          const double* dp = A.st + (id + s_off[n]) * ST_N;
+          if ((tp >> (TP_BM + j)) & 1) dv[j] = ld_cg_f64x2(dp + ST_QA);
+          else { dv[j] = ld_cg_f64x2(dp + ST_QC); de[j] = ld_cg_f64(dp + ST_F); }
+        }
+      }
+    }
+    // ---- the claim comes back; poll the claimed entries
     if (need) {
-      const int leader = __ffs(need) - 1;
-      const unsigned n = __popc(need);
-      unsigned base = 0;
-      if (lane == leader) base = atomicAdd(&A.qhead[home].v, n);
       base = __shfl_sync(0xFFFFFFFFu, base, leader);
+      const unsigned n = __popc(need);
       if ((need >> lane) & 1) {
         const unsigned idx = base + __popc(need & lt);
         if (idx < A.qcap) claim = home * A.qcap + idx;
       }
       if (base + n > A.qcap) home = (home + 1) % NQ;   // that queue is used up
     }
-    if (cur == NONE && claim != NONE) {
-      const uint32_t v = ld_volatile(&A.order[claim]);
-      if (v != NONE) { cur = v; claim = NONE; ++n_popped; }
-    }
-    const unsigned active = __ballot_sync(0xFFFFFFFFu, cur != NONE);
+    ulonglong2 polled = make_ulonglong2(UNSET, UNSET);
+    if (!go && claim != NONE) polled = ld_entry(&A.order[claim]);
     ++n_iters;
-    if (!active) {
-      ++n_idle;
-      if (visited) {
-        if (lane == 0) {
-          const unsigned before = atomicAdd(&A.ctl->done, visited);
-          if (before + visited == nvalid) { __threadfence(); st_volatile(&A.ctl->finished, 1u); }
-        }
-        visited = 0;
-      }
-      unsigned fin = 0;
-      if (lane == 0) fin = ld_volatile(&A.ctl->finished);
-      fin = __shfl_sync(0xFFFFFFFFu, fin, 0);
-      if (fin) break;
-      if (++idle > idle_limit) {   // watchdog: a stalled dataflow must not hang the device
-        if (lane == 0) { st_volatile(&A.ctl->abort, 1u); __threadfence(); st_volatile(&A.ctl->finished, 1u); }
-        break;
-      }
-      if (idle > 16) __nanosleep(idle > 256 ? 400 : 100);
-      continue;
-    }
-    idle = 0;
+    // ---- visit
     unsigned rel = 0;
-    size_t id = cur;
-    if (cur != NONE) rel = visit(A, d.pitch, K, id, flags);
-    __syncwarp();
+    unsigned long long old[10];
+    if (go) {
+      const double f = fs.x;
+      double qa1 = 1.0, qa2 = K.g2;  // :35-36
+#pragma unroll
+      for (int h = 0; h < 8; h += NB) {
+        if (h) {   // donors NB .. 7 (few cells have that many)
+          if (!((tp >> (TP_DON + 4 * h)) & 15)) break;
+#pragma unroll
+          for (int j = 0; j < NB; ++j) {
+            const int n = h + j < 8 ? (int)(tp >> (TP_DON + 4 * (h + j))) & 15 : 0;
+            if (n) {
+              const double* dp = A.st + (id + s_off[n]) * ST_N;
+              if ((tp >> (TP_BM + h + j)) & 1) dv[j] = ld_cg_f64x2(dp + ST_QA);
+              else { dv[j] = ld_cg_f64x2(dp + ST_QC); de[j] = ld_cg_f64(dp + ST_F); }
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+          const int n = h + j < 8 ? (int)(tp >> (TP_DON + 4 * (h + j))) & 15 : 0;
+          if (!n) break;
+          const bool isb = (tp >> (TP_BM + h + j)) & 1;
+          while (is_unset(dv[j].x) || is_unset(dv[j].y)) {   // the donor's decrement overtook its state stores
+            dv[j] = ld_cg_f64x2(A.st + (id + s_off[n]) * ST_N + (isb ? ST_QA : ST_QC));
+            ++n_respin;
+          }
+          if (isb) {  // :82-83, the donor's whole qa
+            qa1 = qa1 + dv[j].x;
+            qa2 = qa2 + dv[j].y;
+          } else {    // :74-75, qc * tan of the donor towards this cell
+            const double t = weti_tan(de[j], f, n, K);
+            qa1 = qa1 + (dv[j].x * t);
+            qa2 = qa2 + (dv[j].y * t);
+          }
+        }
+      }
+      const int cls = (int)(tp >> TP_CLS) & 3;
+      double qc1 = nan, qc2 = nan;
+      if (cls == CLS_A) { qc1 = div_rcp(qa1, fs.y, rs); qc2 = div_rcp(qa2, fs.y, rs); }   // :70-71
+      else if (cls == CLS_B) qc1 = div_rcp(qa1, 0.0001, K.r1e4);                           // :80 (qc2 keeps its old value)
+      double* op = A.st + id * ST_N;
+      st_cg_f64x2(op + ST_QC, qc1, qc2);
+      st_cg_f64x2(op + ST_QA, qa1, qa2);
+      const unsigned succ = (unsigned)(tp >> (TP_SUCC - 1)) & 0x3FEu;
+#pragma unroll
+      for (int n = 1; n <= 9; ++n) {
+        old[n] = 0;
+        if ((succ >> n) & 1) old[n] = atom_dec_u64(&A.topo[id + nb_off(n, pitch)]);
+      }
+#pragma unroll
+      for (int n = 1; n <= 9; ++n)
+        if ((old[n] & 15ull) == 1ull) rel |= 1u << n;
+    }
+    // ---- hand out the released cells: the lane keeps the first one, free lanes of the warp take the next ones
+    const unsigned active = __ballot_sync(0xFFFFFFFFu, go);
     visited += __popc(active);
-    // the lane keeps the first cell it released; the others go to free lanes of the warp, then to a queue
-    uint32_t next = NONE;
-    if (rel) {
-      const int n0 = __ffs(rel) - 1;
-      next = (uint32_t)(id + nb_off(n0, d.pitch));
-      rel &= rel - 1;
-      ++n_kept;
+    if (go) {
+      cur = NONE;
+      tp = 0;
+      if (rel) {
+        const int n0 = __ffs(rel) - 1;
+#pragma unroll
+        for (int n = 1; n <= 9; ++n)
+          if (n == n0) tp = old[n] - 1;
+        cur = (uint32_t)(id + s_off[n0]);
+        rel &= rel - 1;
+        ++n_kept;
+      }
+    }
+    // a polled entry that was ready
+    if (polled.x != UNSET && polled.y != UNSET) {
+      cur = (uint32_t)polled.y;
+      tp = polled.x;
+      claim = NONE;
+      ++n_popped;
     }
     const unsigned nextra = __popc(rel);
     if (__ballot_sync(0xFFFFFFFFu, nextra != 0)) {
@@ -519,43 +564,64 @@ __global__ void __launch_bounds__(WT) k_weti_flow(Arrays A, GridDims d, WetiK K,
       }
       const unsigned total = __shfl_sync(0xFFFFFFFFu, x, 31);
       unsigned at = x - nextra;
-      while (rel) {
-        const int n = __ffs(rel) - 1;
-        rel &= rel - 1;
-        wbuf[at++] = (uint32_t)(id + nb_off(n, d.pitch));
+#pragma unroll
+      for (int n = 1; n <= 9; ++n) {
+        if ((rel >> n) & 1) {
+          wid[at] = (uint32_t)(id + nb_off(n, pitch));
+          wtp[at] = old[n] - 1;
+          ++at;
+        }
       }
       __syncwarp();
-      if (cur != NONE) cur = next;
       const unsigned freem = __ballot_sync(0xFFFFFFFFu, cur == NONE && claim == NONE);
-      const unsigned nfree = __popc(freem);
-      const unsigned give = min(total, nfree);
+      const unsigned give = min(total, (unsigned)__popc(freem));
       if ((freem >> lane) & 1) {
         const unsigned rk = __popc(freem & lt);
-        if (rk < give) { cur = wbuf[rk]; ++n_shared; }
+        if (rk < give) { cur = wid[rk]; tp = wtp[rk]; ++n_shared; }
       }
       __syncwarp();
       if (total > give) {
-        warp_push(A, pushq, wbuf + give, total - give, lane);
+        warp_push(A, pushq, wid + give, wtp + give, total - give, lane);
         if (lane == 0) n_pushed += total - give;
       }
       __syncwarp();
-    } else {
-      if (cur != NONE) cur = next;
     }
+    if (active) { idle = 0; continue; }
+    // ---- nothing to visit in this warp
+    ++n_idle;
+    if (__ballot_sync(0xFFFFFFFFu, cur != NONE)) continue;   // a poll just delivered
+    if (visited) {
+      if (lane == 0) {
+        const unsigned before = atomicAdd(&A.ctl->done, visited);
+        if (before + visited == nvalid) { __threadfence(); st_volatile(&A.ctl->finished, 1u); }
+      }
+      visited = 0;
+    }
+    unsigned fin = 0;
+    if (lane == 0) fin = ld_volatile(&A.ctl->finished);
+    fin = __shfl_sync(0xFFFFFFFFu, fin, 0);
+    if (fin) break;
+    if (++idle > idle_limit) {   // watchdog: a stalled dataflow must not hang the device
+      if (lane == 0) { st_volatile(&A.ctl->abort, 1u); __threadfence(); st_volatile(&A.ctl->finished, 1u); }
+      break;
+    }
+    if (idle > 2) __nanosleep(idle > 64 ? 400 : 100);   // idle warps must not take issue slots from the visiting ones
   }
   // statistics (tuning aid)
   for (int o = 16; o; o >>= 1) {
     n_popped += __shfl_xor_sync(0xFFFFFFFFu, n_popped, o);
     n_kept += __shfl_xor_sync(0xFFFFFFFFu, n_kept, o);
     n_shared += __shfl_xor_sync(0xFFFFFFFFu, n_shared, o);
+    n_respin += __shfl_xor_sync(0xFFFFFFFFu, n_respin, o);
   }
   if (lane == 0) {
-    atomicAdd(&A.ctl->st_pushed, n_pushed);
-    atomicAdd(&A.ctl->st_popped, n_popped);
-    atomicAdd(&A.ctl->st_kept, n_kept);
-    atomicAdd(&A.ctl->st_shared, n_shared);
-    atomicAdd(&A.ctl->st_iters, n_iters);
-    atomicAdd(&A.ctl->st_idle, n_idle);
+    atomicAdd(&A.ctl->st_pushed, (unsigned long long)n_pushed);
+    atomicAdd(&A.ctl->st_popped, (unsigned long long)n_popped);
+    atomicAdd(&A.ctl->st_kept, (unsigned long long)n_kept);
+    atomicAdd(&A.ctl->st_shared, (unsigned long long)n_shared);
+    atomicAdd(&A.ctl->st_iters, (unsigned long long)n_iters);
+    atomicAdd(&A.ctl->st_idle, (unsigned long long)n_idle);
+    atomicAdd(&A.ctl->st_respin, (unsigned long long)n_respin);
   }
 }
 
@@ -587,8 +653,10 @@ __global__ void __launch_bounds__(WT) k_weti_final(Arrays A, GridDims d, OutPtrs
     for (int k = 0; k < 4; ++k) P.o[k][id] = nan;
     return;
   }
-  const State s = A.state[id];
-  double qa1 = s.qa1, qa2 = s.qa2;
+  const double* sp = A.st + id * ST_N;
+  const double2 sqc = *reinterpret_cast<const double2*>(sp + ST_QC);
+  const double2 sqa = *reinterpret_cast<const double2*>(sp + ST_QA);
+  double qa1 = sqa.x, qa2 = sqa.y;
   // B neighbours that drain into this cell but are visited after it: they only change the final qa
   {
     uint8_t lcode[8];
@@ -615,13 +683,13 @@ __global__ void __launch_bounds__(WT) k_weti_final(Arrays A, GridDims d, OutPtrs
       }
     }
     for (int a = 0; a < nl; ++a) {
-      const State t = A.state[id + nb_off(lcode[a], d.pitch)];
-      qa1 = qa1 + t.qa1;
-      qa2 = qa2 + t.qa2;
+      const double2 t = *reinterpret_cast<const double2*>(A.st + (id + nb_off(lcode[a], d.pitch)) * ST_N + ST_QA);
+      qa1 = qa1 + t.x;
+      qa2 = qa2 + t.y;
     }
   }
   // effective qc1 / qc2 at the time the reference evaluates :87-88
-  double qc1 = s.qc1, qc2 = s.qc2;
+  double qc1 = sqc.x, qc2 = sqc.y;
   if (cls != CLS_A) {
     const double f = A.elev[id];
     const K128 k = make_key(f, A.upslope[id], (uint32_t)id);
@@ -629,7 +697,7 @@ __global__ void __launch_bounds__(WT) k_weti_final(Arrays A, GridDims d, OutPtrs
     const unsigned j = locate(A, bm, f, k);       // this cell's own place among the queries
     const K128 a = A.slotA[j];                     // latest A cell before it
     const bool havea = (a.lo | a.hi) != 0;
-    qc2 = havea ? A.state[a.lo & 0xFFFFFFFFu].qc2 : nan;
+    qc2 = havea ? A.st[(size_t)(a.lo & 0xFFFFFFFFu) * ST_N + ST_QC + 1] : nan;
     if (cls == CLS_C) {
       const int b = A.lastB[j];                    // latest B cell before it
       uint32_t src = havea ? (uint32_t)(a.lo & 0xFFFFFFFFu) : NONE;
@@ -638,7 +706,7 @@ __global__ void __launch_bounds__(WT) k_weti_final(Arrays A, GridDims d, OutPtrs
         kb.hi = A.qhi[b]; kb.lo = A.qlo[b];
         if (!havea || key_less(a, kb)) src = (uint32_t)(kb.lo & 0xFFFFFFFFu);
       }
-      qc1 = src != NONE ? A.state[src].qc1 : nan;
+      qc1 = src != NONE ? A.st[(size_t)src * ST_N + ST_QC] : nan;
     }
   }
   double qw1 = (qc1 > 1) ? log(qc1) : log(1 + qc1);
@@ -674,18 +742,23 @@ int run_weti(litap_grid* g, double grid_m) {
   K.orth = grid_m;
   K.diag = grid_m * std::sqrt(2.0);
   K.g2 = grid_m * grid_m;
+  K.rorth = div_rcp_prepare(K.orth);
+  K.rdiag = div_rcp_prepare(K.diag);
+  K.r1e4 = div_rcp_prepare(0.0001);
 
   // launch shape of the dataflow kernel: as many blocks as are resident (waiting lanes must never keep a block from running)
-  static int flow_blocks = 0;
+  static int flow_blocks = 0, flow_nb = 8;
   if (!flow_blocks) {
+    if (const char* e = getenv("LITAP_WETI_NB")) flow_nb = atoi(e);  // tuning aid: donors loaded per batch (8, 6 or 4)
+    if (flow_nb != 6 && flow_nb != 4) flow_nb = 8;
     int per_sm = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_weti_flow, WT, 0));
+    if (flow_nb == 8) CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_weti_flow<8>, WT, 0));
+    else if (flow_nb == 6) CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_weti_flow<6>, WT, 0));
+    else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_weti_flow<4>, WT, 0));
     if (per_sm < 1) return set_error(LITAP_ECUDA, "k_weti_flow cannot be made resident");
     if (const char* e = getenv("LITAP_WETI_BPS")) per_sm = std::max(1, std::min(per_sm, atoi(e)));  // tuning aid
     flow_blocks = c.sm_count * per_sm;
   }
-  int flags = 1;
-  if (const char* e = getenv("LITAP_WETI_FLAGS")) flags = atoi(e);  // tuning aid: bit 0 = prefetch successor nodes
 
   const size_t ncell = (size_t)d.cells + 64;          // pitched ids
   const size_t nd = (size_t)d.NR * d.NC;
@@ -696,15 +769,14 @@ int run_weti(litap_grid* g, double grid_m) {
   A.elev = g->elev;
   A.ddir = g->ddir;
   A.upslope = g->upslope;
-  A.node = S.get<Node>(ncell);
-  A.state = S.get<State>(ncell);
+  A.topo = S.get<unsigned long long>(ncell);
+  A.st = S.get<double>(ncell * ST_N);
   A.cls = S.get<uint8_t>(ncell);
-  A.pend32 = S.get<uint32_t>(ncell / 4 + 2);
-  A.order = S.get<uint32_t>((size_t)NQ * qcap);
+  A.order = S.get<ulonglong2>((size_t)NQ * qcap);
   A.qcap = qcap;
   unsigned char* ctlmem = S.get<unsigned char>(sizeof(Ctl) + 2 * NQ * sizeof(QCount) + 256);
   unsigned* table = S.get<unsigned>(NT + 1);
-  if (!A.node || !A.state || !A.cls || !A.pend32 || !A.order || !ctlmem || !table)
+  if (!A.topo || !A.st || !A.cls || !A.order || !ctlmem || !table)
     return set_error(LITAP_ENOMEM, "device allocation failed (weti scratch)");
   A.qtail = reinterpret_cast<QCount*>(ctlmem);
   A.qhead = A.qtail + NQ;
@@ -712,7 +784,7 @@ int run_weti(litap_grid* g, double grid_m) {
   A.table = table;
   CUDA_TRY(cudaMemsetAsync(ctlmem, 0, sizeof(Ctl) + 2 * NQ * sizeof(QCount), st));
   CUDA_TRY(cudaMemsetAsync(A.cls, 0, ncell, st));  // pad columns read as NA
-  CUDA_TRY(cudaMemsetAsync(A.order, 0xFF, (size_t)NQ * qcap * sizeof(uint32_t), st));
+  CUDA_TRY(cudaMemsetAsync(A.order, 0xFF, (size_t)NQ * qcap * sizeof(ulonglong2), st));
 
   dim3 cgrid(nblk(d.NC, WT), d.NR);
   KERNEL("k_weti_cls", k_weti_cls<<<cgrid, WT, 0, st>>>(A, d, K));
@@ -764,7 +836,9 @@ int run_weti(litap_grid* g, double grid_m) {
       KERNEL("k_weti_nodes", k_weti_nodes<<<cgrid, WT, 0, st>>>(A, d, K));
     }
     unsigned idle_limit = 1u << 22;   // ~ 2 s of polling without any progress anywhere
-    KERNEL("k_weti_flow", k_weti_flow<<<flow_blocks, WT, 0, st>>>(A, d, K, flags, idle_limit));
+    if (flow_nb == 8) KERNEL("k_weti_flow", k_weti_flow<8><<<flow_blocks, WT, 0, st>>>(A, d, K, idle_limit));
+    else if (flow_nb == 6) KERNEL("k_weti_flow", k_weti_flow<6><<<flow_blocks, WT, 0, st>>>(A, d, K, idle_limit));
+    else KERNEL("k_weti_flow", k_weti_flow<4><<<flow_blocks, WT, 0, st>>>(A, d, K, idle_limit));
   }
   KERNEL("k_weti_final", k_weti_final<<<cgrid, WT, 0, st>>>(A, d, P));
   CUDA_TRY(cudaMemcpyAsync(&hctl, A.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
@@ -774,8 +848,8 @@ int run_weti(litap_grid* g, double grid_m) {
   if (getenv("LITAP_WETI_STATS"))
     fprintf(stderr,
             "weti: cells %u queries %u | kept by the releasing lane %llu, shared in the warp %llu, queued %llu (popped %llu) | "
-            "warp iterations %llu (idle %llu), %d blocks\n",
+            "warp iterations %llu (idle %llu), state re-reads %llu, %d blocks, %d donors per batch\n",
             hctl.nvalid, hctl.nq, hctl.st_kept, hctl.st_shared, hctl.st_pushed, hctl.st_popped, hctl.st_iters, hctl.st_idle,
-            flow_blocks);
+            hctl.st_respin, flow_blocks, flow_nb);
   return LITAP_OK;
 }

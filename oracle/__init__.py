@@ -43,6 +43,7 @@ def lib():
         L.oracle_relz.argtypes = ([C.c_int64, C.c_int64, _f64p, _u8p, _i32p, _i32p, _i32p, _i32p, _f64p, _u8p, _i32p, _i32p, _i32p,
                                    C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                    C.c_double, C.POINTER(C.c_void_p)])
+        L.oracle_uced.argtypes = [_f64p, _u8p, _i32p, C.c_int64, C.c_int64, _f64p, C.POINTER(C.c_int64)]
         L.oracle_r_round.argtypes = [C.c_double, C.c_int]
         L.oracle_r_round.restype = C.c_double
         L.oracle_synth_dem.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_uint32,
@@ -114,6 +115,18 @@ def weti(elev_b, ddir_b, upslope_b, grid):
     outs = [np.empty((NR, NC)) for _ in range(4)]
     lib().oracle_weti(e, d, u, NR, NC, float(grid), *outs)
     return dict(zip(("qarea1", "qarea2", "qweti1", "qweti2"), outs))
+
+
+def uced(elev_b, ddir_b, shed_b):
+    """calc_upslopes(type = "uced") on a buffered grid (R/flow_02_calc_shed.R:60-145).  shed 0 = NA; NaN = NA."""
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    d = np.ascontiguousarray(ddir_b, dtype=np.uint8)
+    s = np.ascontiguousarray(shed_b, dtype=np.int32)
+    out = np.empty(e.shape)
+    w = C.c_int64(0)
+    lib().oracle_uced(e, d, s, e.shape[0], e.shape[1], out, C.byref(w))
+    uced.work = w.value
+    return out
 
 
 GC_F64 = ("sgre", "sgr", "sgcn", "sgc", "scr", "scc")

@@ -182,3 +182,11 @@ def test_ld80_sum_emulation_equals_x87(cellmath):
         t = np.ascontiguousarray(t, dtype=np.float64)
         nbad += cellmath.host_ld80_sum(t, n) != cellmath.host_real_ld_sum(t, n)
     assert nbad == 0
+
+
+def test_div_rcp_equals_ieee_division(cellmath):
+    """calc_weti2's divisions by the cell sizes / by S go through a precomputed reciprocal (cellmath.h div_rcp,
+    Markstein's correction); the quotient must be the IEEE one in every bit."""
+    cellmath.host_div_rcp_check.restype = C.c_longlong
+    cellmath.host_div_rcp_check.argtypes = [C.c_longlong, C.c_ulonglong]
+    assert cellmath.host_div_rcp_check(30_000_000, 20261104) == 0

@@ -209,3 +209,32 @@ def test_relz_oracle_without_pond_uses_pit_cells():
     a = oracle.relz(db, idb, sub, 300.0, 200.0, rf.GRID)
     b = oracle.relz(db, idb, None, 300.0, 200.0, rf.GRID)
     rf.assert_same(a, b, oracle.RELZ_NAMES)
+
+
+UCED_KATS = [
+    (KATS[0][0], [0, 0, 0, 0, 5, 0, 0, 15, 0]),
+    (KATS[1][0], [0, 0, 0, 0, 0, 3, 0, 5, 0, 8, 0, 41, 50, 0, 0, 0]),
+    (KATS[2][0], [0, 0, 0, 13, 0, 2, 0, 3, 0, 20, 0, 0, 0, 8, 0, 169, 0, 0, 45, 0, 0, 23, 29, 15, 107, 38, 7, 0, 9, 6,
+                  0, 0, 0, 0, 0, 0]),
+]
+
+
+@pytest.mark.parametrize("dem,uced", UCED_KATS)
+def test_uced_kats(dem, uced):
+    """calc_upslopes(type = "uced"): tests/testthat/test_02_flow_internal.R:83-153."""
+    e = oracle.add_buffer(np.array(dem, dtype=float))
+    d = oracle.ddir(e)["ddir"]
+    s = oracle.shed(e, d)
+    assert oracle.uced(e, d, s["shed"])[1:-1, 1:-1].ravel().tolist() == [float(x) for x in uced]
+
+
+def test_uced_fullgrid_golden(golden):
+    """flow/dem_fill.rds$uced: the last calc_upslopes(type = "uced") of pit removal (R/flow_04_remove_pit_fast.R:345),
+    on the post-removal ddir with fill_shed as shedno.  Exact doubles on all 8 100 cells."""
+    g = golden["dem_fill"]
+    e = oracle.add_buffer(g["elev"].reshape(90, 90))
+    dd = np.nan_to_num(oracle.add_buffer(g["ddir"].reshape(90, 90)), nan=0).astype(np.uint8)
+    sh = np.nan_to_num(oracle.add_buffer(g["fill_shed"].reshape(90, 90)), nan=0).astype(np.int32)
+    u = oracle.uced(e, dd, sh)
+    assert np.isnan(u[0]).all() and np.isnan(u[:, 0]).all()
+    assert (u[1:-1, 1:-1].ravel() == g["uced"]).all()
