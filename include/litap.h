@@ -55,6 +55,9 @@ typedef struct litap_timings {
   int64_t kernel_launches; /* kernels of this library launched by the call */
   float gc_ms;      /* slope_gc */
   float relz_ms;    /* calc_relz + calc_length (device part of litap_relz) */
+  float uced_ms;    /* calc_upslopes(type = "uced") */
+  int uced_ranges;  /* cell ranges the contributions were processed in (1 unless they exceed the memory budget) */
+  double uced_pairs; /* (head, cell below it) contributions = long double sums computed */
 } litap_timings;
 
 int litap_init(int device);        /* selects the device and creates the stream; idempotent */
@@ -91,6 +94,13 @@ int litap_form(const double* elev, int64_t NR, int64_t NC, double grid,
 int litap_weti(const double* elev, const uint8_t* ddir, const uint32_t* upslope,
                int64_t NR, int64_t NC, double grid,
                double* qarea1, double* qarea2, double* qweti1, double* qweti2);
+
+/* calc_upslopes(db, type = "uced")  R/flow_02_calc_shed.R:60-145 (uced_values :118-130), called by pit removal at
+ * R/flow_04_remove_pit_fast.R:73,345: upslope cumulative elevation drop.  shed = the shedno column of db (0 = NA:
+ * those cells keep NA); ddir as in litap_shed (drec is derived from it, R/LITAP_functions.R:237-254).
+ * uced: NaN = NA (cells without a shed, pits nothing flows into).  Bit-identical with the reference's
+ * long double sum() per track and its order of additions. */
+int litap_uced(const double* elev, const uint8_t* ddir, const int32_t* shed, int64_t NR, int64_t NC, double* uced);
 
 /* slope_gc: gradients towards east / north with their zero signs settled, magnitudes (0 -> 0.00001),
  * row / column curvatures, hillslope run labels per row and per column.  f64 outputs NaN = NA;
@@ -141,6 +151,7 @@ int litap_grid_ddir(litap_grid* g, int invert);
 int litap_grid_shed(litap_grid* g);
 int litap_grid_form(litap_grid* g, double grid_m);
 int litap_grid_weti(litap_grid* g, double grid_m);
+int litap_grid_uced(litap_grid* g);   /* needs ddir and shed on the grid (litap_grid_ddir + litap_grid_shed); result "uced" */
 int litap_grid_slope_gc(litap_grid* g, double grid_m);
 /* calc_form + calc_ddir2 + calc_shed4 as one call: form overlaps the flow stages on a second stream */
 int litap_grid_flow_form(litap_grid* g, double grid_m, int invert);
@@ -180,6 +191,9 @@ int litap_bands_flow_form(litap_grid** bands, int n, double grid_m, int invert);
  * first / last band): first row and row count; litap_band_download copies exactly those rows */
 int litap_band_rows(const litap_grid* band, int64_t* row0, int64_t* nrows);
 int litap_band_download(litap_grid* band, const char* name, void* dst);
+/* the band's share of litap_grid_checksum of the whole DEM (same rows as litap_band_download, hashed with their cell
+ * numbers in the whole DEM): the wrapping sum over all bands equals the checksum of the unsharded result */
+int litap_band_checksum(litap_grid* band, const char* name, uint64_t* out);
 
 #ifdef __cplusplus
 }

@@ -13,6 +13,7 @@ from .api import (  # noqa: F401
     calc_form,
     calc_relz,
     calc_shed4,
+    calc_upslopes,
     calc_weti2,
     slope_gc,
     flow_form,

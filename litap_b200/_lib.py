@@ -11,9 +11,9 @@ _lib = None
 SYMBOLS = [
     "litap_init", "litap_shutdown", "litap_last_error", "litap_version", "litap_get_timings",
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
-    "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
+    "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_uced", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
-    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_slope_gc", "litap_grid_flow_form",
+    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
@@ -31,7 +31,8 @@ class Timings(C.Structure):
                 ("total_ms", C.c_float), ("plateau_rounds", C.c_int), ("weti_queued", C.c_int),
                 ("flat_cells", C.c_int64),
                 ("patch_cells", C.c_int64), ("npits", C.c_int64), ("kernel_launches", C.c_int64),
-                ("gc_ms", C.c_float), ("relz_ms", C.c_float)]
+                ("gc_ms", C.c_float), ("relz_ms", C.c_float), ("uced_ms", C.c_float), ("uced_ranges", C.c_int),
+                ("uced_pairs", C.c_double)]
 
     def asdict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -73,12 +74,15 @@ def load():
     L.litap_grid_shed.argtypes = [vp]
     L.litap_grid_form.argtypes = [vp, dbl]
     L.litap_grid_weti.argtypes = [vp, dbl]
+    L.litap_grid_uced.argtypes = [vp]
+    L.litap_uced.argtypes = [vp, vp, vp, i64, i64, vp]
     L.litap_grid_slope_gc.argtypes = [vp, dbl]
     L.litap_grid_flow_form.argtypes = [vp, dbl, ci]
     L.litap_grid_download.argtypes = [vp, C.c_char_p, vp]
     L.litap_grid_npits.argtypes = [vp]
     L.litap_grid_npits.restype = i64
     L.litap_grid_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
+    L.litap_band_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
     L.litap_comm_unique_id.argtypes = [vp]
     L.litap_comm_init.argtypes = [ci, ci, vp]
     L.litap_comm_destroy.restype = None

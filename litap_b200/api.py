@@ -115,6 +115,37 @@ def calc_shed4(db, verbose=False):
     rg[r == 2] = np.nan
     out["ridge"] = rg
     out["npits"] = n.value
+    # side columns of calc_upslopes (R/flow_02_calc_shed.R:62-68): seqno_shed = running number of the cell inside its
+    # shed in seqno order -- group_by(shedno) numbers the NA group as well --, drec_shed = seqno_shed[drec]
+    key = np.where(s > 0, s, 0).astype(np.int64)
+    order = np.argsort(key, kind="stable")
+    first = np.r_[0, np.flatnonzero(np.diff(key[order])) + 1]
+    start = np.repeat(first, np.diff(np.r_[first, key.size]))
+    seq_shed = np.empty(key.size, np.float64)
+    seq_shed[order] = np.arange(key.size) - start + 1
+    out["seqno_shed"] = seq_shed
+    drec = np.arange(NR * NC, dtype=np.int64) + _OFF_DR[d] * NC + _OFF_DC[d]
+    ok = (d > 0) & (drec >= 0) & (drec < NR * NC)
+    ds = np.full(NR * NC, np.nan)
+    ds[ok] = seq_shed[drec[ok]]
+    out["drec_shed"] = ds
+    return out
+
+
+def calc_upslopes(db, type="uced"):
+    """R/flow_02_calc_shed.R:60-79 with type = "uced" (uced_values :118-130; pit removal calls it at
+    R/flow_04_remove_pit_fast.R:73,345).  Needs elev, ddir and shedno; returns db + uced (NaN = NA).
+    type = "upslope" is what calc_shed4 already returns."""
+    if type != "uced":
+        raise LitapError('calc_upslopes: only type = "uced" is a separate call (calc_shed4 returns upslope)')
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    d = _ddir_u8(db["ddir_u8"] if "ddir_u8" in db else db["ddir"])
+    s = _i32_na0(db["shedno"])
+    u = np.empty(NR * NC)
+    check(lib().litap_uced(e.ctypes.data, d.ctypes.data, s.ctypes.data, NR, NC, u.ctypes.data))
+    out = dict(db)
+    out["uced"] = u
     return out
 
 
@@ -225,7 +256,10 @@ def flow_form(elev_b, grid, invert=False, want=("ddir", "shed", "upslope", "ridg
     def buf(name, dt):
         if name not in out:
             out[name] = np.empty((NR, NC), dt)
-        return out[name].ctypes.data
+        a = out[name]   # a caller-provided array goes to the C ABI as a bare pointer: it must be exactly what is written
+        if not isinstance(a, np.ndarray) or a.dtype != dt or a.shape != (NR, NC) or not a.flags.c_contiguous:
+            raise LitapError(f"flow_form: out[{name!r}] must be a C-contiguous {np.dtype(dt).name} array of shape {(NR, NC)}")
+        return a.ctypes.data
 
     p = {k: None for k in ("ddir", "flatcell", "shed", "upslope", "ridge", "slope_pct", "slope_deg", "aspect",
                            "prof", "plan")}
@@ -241,10 +275,12 @@ def flow_form(elev_b, grid, invert=False, want=("ddir", "shed", "upslope", "ridg
         for k in ("slope_pct", "slope_deg", "aspect", "prof", "plan"):
             p[k] = buf(k, np.float64)
     n = C.c_int64(0)
+    need_shed = any(k in want for k in ("shed", "upslope", "ridge"))   # npits == NULL: calc_shed4 is not run at all
     check(lib().litap_flow_form(e.ctypes.data, NR, NC, float(grid), int(bool(invert)), p["ddir"], p["flatcell"],
-                                p["shed"], p["upslope"], p["ridge"], C.byref(n), p["slope_pct"], p["slope_deg"],
-                                p["aspect"], p["prof"], p["plan"]))
-    out["npits"] = n.value
+                                p["shed"], p["upslope"], p["ridge"], C.byref(n) if need_shed else None, p["slope_pct"],
+                                p["slope_deg"], p["aspect"], p["prof"], p["plan"]))
+    if need_shed:
+        out["npits"] = n.value
     return out
 
 
@@ -288,6 +324,9 @@ class DeviceGrid:
 
     def weti(self, grid):
         check(lib().litap_grid_weti(self._h, float(grid)))
+
+    def uced(self):
+        check(lib().litap_grid_uced(self._h))
 
     def slope_gc(self, grid):
         check(lib().litap_grid_slope_gc(self._h, float(grid)))

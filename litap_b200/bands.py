@@ -127,6 +127,15 @@ class BandedDEM:
         check(lib().litap_grid_checksum(self._h[i], name.encode(), C.byref(v)))
         return v.value
 
+    def band_checksum(self, name):
+        """Share of the local bands in DeviceGrid.checksum(name) of the unsharded DEM (wrapping sum over bands)."""
+        tot = 0
+        for h in self._h:
+            v = C.c_uint64(0)
+            check(lib().litap_band_checksum(h, name.encode(), C.byref(v)))
+            tot = (tot + v.value) & 0xFFFFFFFFFFFFFFFF
+        return tot
+
     @property
     def npits(self):
         return lib().litap_grid_npits(self._h[0])

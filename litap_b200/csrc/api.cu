@@ -138,6 +138,7 @@ extern "C" void litap_grid_destroy(litap_grid* g) {
   grid_free_array(g->ridge);
   for (auto& p : g->form) grid_free_array(p);
   for (auto& p : g->weti) grid_free_array(p);
+  grid_free_array(g->uced);
   for (auto& p : g->gc_f64) grid_free_array(p);
   for (auto& p : g->gc_u8) grid_free_array(p);
   for (auto& p : g->gc_i32) grid_free_array(p);
@@ -244,6 +245,20 @@ extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
   return rc;
 }
 
+extern "C" int litap_grid_uced(litap_grid* g) {
+  if (!g) return set_error(LITAP_EARG, "litap_grid_uced: NULL");
+  if (g->nbands > 0)   // a track crosses band edges; not sharded
+    return set_error(LITAP_EARG, "litap_grid_uced: not available on a row band (run it on a whole-DEM grid)");
+  if (!g->ddir || !g->shed) return set_error(LITAP_EARG, "litap_grid_uced: needs ddir and shed on the grid");
+  int64_t l0 = ctx().launches;
+  StageTimer t(&ctx().tm.uced_ms, 6);
+  int rc = run_uced(g);
+  if (rc) return rc;
+  rc = t.finish();
+  ctx().tm.kernel_launches = ctx().launches - l0;
+  return rc;
+}
+
 // calc_form + calc_ddir2 + calc_shed4 of one resident DEM as ONE call: calc_form does not depend on the
 // flow stages, so it runs on the caller's stream while ddir / shed run on a high-priority stream of the
 // library.  The flow stages are chains of small kernels, host read-backs and one cooperative launch; the
@@ -335,6 +350,7 @@ static ArrRef find_array(litap_grid* g, const char* name) {
   if (!strcmp(name, "ridge")) return {g->ridge, 1};
   for (int i = 0; i < 5; ++i) if (!strcmp(name, fn[i])) return {g->form[i], 8};
   for (int i = 0; i < 4; ++i) if (!strcmp(name, wn[i])) return {g->weti[i], 8};
+  if (!strcmp(name, "uced")) return {g->uced, 8};
   static const char* gf[6] = {"sgre", "sgr", "sgcn", "sgc", "scr", "scc"};
   static const char* gu[2] = {"hill_r_dir", "hill_c_dir"};
   static const char* gi[4] = {"hill_r_n", "hill_r_cell", "hill_c_n", "hill_c_cell"};
@@ -376,6 +392,16 @@ extern "C" int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* ou
   ArrRef a = find_array(g, name);
   if (!a.p) return set_error(LITAP_EARG, std::string("litap_grid_checksum: no such result on the grid: ") + name);
   return run_checksum(a.p, a.esize, g->d, out);
+}
+
+// a band's share of litap_grid_checksum of the whole DEM: the rows litap_band_rows names, hashed with their cell
+// numbers in the whole buffered DEM.  The (wrapping) sum over all bands equals the checksum of the unsharded result.
+extern "C" int litap_band_checksum(litap_grid* g, const char* name, uint64_t* out) {
+  if (!g || !name || !out || g->nbands < 1) return set_error(LITAP_EARG, "litap_band_checksum: bad arguments");
+  ArrRef a = find_array(g, name);
+  if (!a.p) return set_error(LITAP_EARG, std::string("litap_band_checksum: no such result on the band: ") + name);
+  const int lo = g->halo_top ? g->own_lo : g->own_lo - 1, hi = g->halo_bot ? g->own_hi : g->own_hi + 1;
+  return run_checksum_rows(a.p, a.esize, g->d, lo, hi, g->row_off, out);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -217,6 +217,31 @@ extern "C" int litap_weti(const double* elev, const uint8_t* ddir, const uint32_
   return LITAP_OK;
 }
 
+extern "C" int litap_uced(const double* elev, const uint8_t* ddir, const int32_t* shed, int64_t NR, int64_t NC, double* uced) {
+  Wall w;
+  GridGuard gg;
+  if (!ddir || !shed || !uced) return set_error(LITAP_EARG, "litap_uced: NULL ddir/shed/uced");
+  RC(begin_call(NR, NC, elev, gg));
+  litap_grid* g = gg.g;
+  Ctx& c = ctx();
+  int64_t l0 = c.launches;
+  g->ddir = grid_alloc_array<uint8_t>(g->d, 0);
+  g->shed = grid_alloc_array<int32_t>(g->d, 0);
+  if (!g->ddir || !g->shed) return set_error(LITAP_ENOMEM, "device allocation failed (ddir/shed)");
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  RC(up(g->elev, g->d, elev));
+  RC(up(g->ddir, g->d, ddir));
+  RC(up(g->shed, g->d, shed));
+  RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));
+  RC(litap_grid_uced(g));
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  RC(down(uced, g->d, g->uced));
+  RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));
+  c.tm.kernel_launches = c.launches - l0;
+  c.tm.total_ms = w.ms();
+  return LITAP_OK;
+}
+
 extern "C" int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double grid, double* sgre, double* sgr,
                               double* sgcn, double* sgc, double* scr, double* scc, uint8_t* hill_r_dir,
                               uint8_t* hill_c_dir, int32_t* hill_r_n, int32_t* hill_r_cell, int32_t* hill_c_n,

@@ -656,6 +656,69 @@ LITAP_HD double ld80_to_double(Ld80 a) {
   return ld80_from_bits(((unsigned long long)(e + 1023) << 52) | (m53 & 0x000FFFFFFFFFFFFFull));
 }
 
+// signed variant (calc_upslopes(type = "uced") sums elevation differences of either sign, R/flow_02_calc_shed.R:126):
+// value = (-1)^neg * m * 2^(e - 63)
+struct Lds {
+  unsigned long long m;
+  int e;
+  int neg;
+};
+LITAP_HD Lds lds_from_double(double x) {   // x finite
+  const Ld80 u = ld80_from_double(x < 0 ? -x : x);
+  Lds r;
+  r.m = u.m; r.e = u.e; r.neg = x < 0;
+  return r;
+}
+LITAP_HD Lds lds_add(Lds a, Lds b) {
+  if (b.m == 0) return a;
+  if (a.m == 0) return b;
+  if (a.neg == b.neg) {
+    Ld80 x, y;
+    x.m = a.m; x.e = a.e; y.m = b.m; y.e = b.e;
+    const Ld80 r = ld80_add(x, y);
+    Lds o;
+    o.m = r.m; o.e = r.e; o.neg = a.neg;
+    return o;
+  }
+  // |a| - |b| with |a| >= |b|, exact in 128 bits (+ a sticky fraction when b lies more than 64 bits below a)
+  if (a.e < b.e || (a.e == b.e && a.m < b.m)) { const Lds t = a; a = b; b = t; }
+  const int sh = a.e - b.e;
+  unsigned long long yh, yl;
+  bool sticky = false;
+  if (sh == 0) { yh = b.m; yl = 0; }
+  else if (sh < 64) { yh = b.m >> sh; yl = b.m << (64 - sh); }
+  else if (sh == 64) { yh = 0; yl = b.m; }
+  else if (sh < 128) { yh = 0; yl = b.m >> (sh - 64); sticky = (b.m << (128 - sh)) != 0; }
+  else { yh = 0; yl = 0; sticky = true; }
+  unsigned long long dl = 0ull - yl;
+  unsigned long long dh = a.m - yh - (yl != 0 ? 1ull : 0ull);
+  if (sticky) {   // true difference = (dh:dl - 1) + a fraction in (0, 1)
+    if (dl == 0) --dh;
+    --dl;
+  }
+  Lds o;
+  o.neg = a.neg;
+  if (dh == 0 && dl == 0) { o.m = 0; o.e = 0; o.neg = 0; return o; }   // x + (-x) = +0
+  const int s = dh ? ld80_clz64(dh) : 64 + ld80_clz64(dl);   // sticky implies s <= 1: the fraction stays below the rounding bit
+  if (s >= 64) { dh = dl << (s - 64); dl = 0; }
+  else if (s) { dh = (dh << s) | (dl >> (64 - s)); dl <<= s; }
+  int e = a.e - s;
+  const unsigned long long half = 0x8000000000000000ull;
+  if (dl > half || (dl == half && (sticky || (dh & 1ull)))) {
+    ++dh;
+    if (dh == 0) { dh = half; ++e; }
+  }
+  o.m = dh;
+  o.e = e;
+  return o;
+}
+LITAP_HD double lds_to_double(Lds a) {
+  Ld80 u;
+  u.m = a.m; u.e = a.e;
+  const double v = ld80_to_double(u);
+  return a.neg ? -v : v;
+}
+
 // ---------------------------------------------------------------------------------------------
 // calc_weti2 per-cell pieces (R/form_02b_calc_weti.R:47-67).  Window visit order of the reference:
 // NW,N,NE,W,self,E,SW,S,SE = neighbour codes 7,8,9,4,5,6,1,2,3.

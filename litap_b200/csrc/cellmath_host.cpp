@@ -149,3 +149,11 @@ extern "C" long long host_div_rcp_check(long long n, unsigned long long seed) {
   }
   return bad;
 }
+
+// the signed accumulator (calc_upslopes "uced") vs the host's long double
+extern "C" double host_lds_sum(const double* t, int n) {
+  Lds s;
+  s.m = 0; s.e = 0; s.neg = 0;
+  for (int i = 0; i < n; ++i) s = lds_add(s, lds_from_double(t[i]));
+  return lds_to_double(s);
+}

@@ -52,6 +52,7 @@ struct litap_grid {
   uint8_t* ridge = nullptr;
   double* form[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   double* weti[4] = {nullptr, nullptr, nullptr, nullptr};
+  double* uced = nullptr;
   // slope_gc: sgre, sgr, sgcn, sgc, scr, scc / hill_r_dir, hill_c_dir / hill_r_n, hill_r_cell, hill_c_n, hill_c_cell
   double* gc_f64[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   uint8_t* gc_u8[2] = {nullptr, nullptr};
@@ -174,6 +175,8 @@ int run_form(litap_grid* g, double grid_m);            // form.cu
 int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi);  // form.cu: a row range (pipelined upload)
 void form_forget_trig();                               // form.cu (pool-owned table dropped at shutdown)
 int run_weti(litap_grid* g, double grid_m);            // weti.cu
+int run_uced(litap_grid* g);                           // uced.cu
 int run_slope_gc(litap_grid* g, double grid_m);        // gc.cu
 int run_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille);  // synth.cu
 int run_checksum(const void* arr, int elem_size, const GridDims& d, uint64_t* out);                     // synth.cu
+int run_checksum_rows(const void* arr, int elem_size, const GridDims& d, int row_lo, int row_hi, long long row_off, uint64_t* out);

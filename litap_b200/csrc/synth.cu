@@ -46,10 +46,11 @@ __global__ void k_synth(double* __restrict__ elev, GridDims d, long long row0, l
   elev[(size_t)R * d.pitch + C] = v;
 }
 
+// rows [row_lo, row_hi) of the array, hashed with the cell numbers of a DEM in which local row 0 is row `row_off`
 template <typename T>
-__global__ void k_checksum(const T* __restrict__ a, GridDims d, unsigned long long* out) {
+__global__ void k_checksum(const T* __restrict__ a, GridDims d, unsigned long long* out, int row_lo, int row_hi, long long row_off) {
   unsigned long long acc = 0;
-  for (int r = blockIdx.y; r < d.NR; r += gridDim.y)
+  for (int r = row_lo + blockIdx.y; r < row_hi; r += gridDim.y)
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < d.NC; c += gridDim.x * blockDim.x) {
       unsigned long long v;
       if (sizeof(T) == 8) {
@@ -58,7 +59,7 @@ __global__ void k_checksum(const T* __restrict__ a, GridDims d, unsigned long lo
       } else {
         v = (unsigned long long)a[(size_t)r * d.pitch + c];
       }
-      unsigned long long idx = (unsigned long long)r * (unsigned long long)d.NC + (unsigned long long)c + 1ull;
+      unsigned long long idx = (unsigned long long)(row_off + r) * (unsigned long long)d.NC + (unsigned long long)c + 1ull;
       unsigned long long h = (v + 0x9E3779B97F4A7C15ull) * (idx * 0xBF58476D1CE4E5B9ull | 1ull);
       h ^= h >> 29;
       acc += h;
@@ -80,15 +81,17 @@ int run_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double qu
   return LITAP_OK;
 }
 
-int run_checksum(const void* arr, int esize, const GridDims& d, uint64_t* out) {
+int run_checksum(const void* arr, int esize, const GridDims& d, uint64_t* out) { return run_checksum_rows(arr, esize, d, 0, d.NR, 0, out); }
+
+int run_checksum_rows(const void* arr, int esize, const GridDims& d, int row_lo, int row_hi, long long row_off, uint64_t* out) {
   cudaStream_t st = ctx().stream;
   unsigned long long* acc = (unsigned long long*)pool_alloc(sizeof(unsigned long long));
   if (!acc) return set_error(LITAP_ENOMEM, "device allocation failed (checksum)");
   CUDA_TRY(cudaMemsetAsync(acc, 0, sizeof(*acc), st));
   dim3 grid((d.NC + 255) / 256 < 32 ? (d.NC + 255) / 256 : 32, d.NR < 2048 ? d.NR : 2048);
-  if (esize == 8) k_checksum<<<grid, 256, 0, st>>>((const unsigned long long*)arr, d, acc);
-  else if (esize == 4) k_checksum<<<grid, 256, 0, st>>>((const uint32_t*)arr, d, acc);
-  else k_checksum<<<grid, 256, 0, st>>>((const uint8_t*)arr, d, acc);
+  if (esize == 8) k_checksum<<<grid, 256, 0, st>>>((const unsigned long long*)arr, d, acc, row_lo, row_hi, row_off);
+  else if (esize == 4) k_checksum<<<grid, 256, 0, st>>>((const uint32_t*)arr, d, acc, row_lo, row_hi, row_off);
+  else k_checksum<<<grid, 256, 0, st>>>((const uint8_t*)arr, d, acc, row_lo, row_hi, row_off);
   ctx().launches++;
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(out, acc, sizeof(*acc), cudaMemcpyDeviceToHost, st);

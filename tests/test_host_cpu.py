@@ -190,3 +190,36 @@ def test_div_rcp_equals_ieee_division(cellmath):
     cellmath.host_div_rcp_check.restype = C.c_longlong
     cellmath.host_div_rcp_check.argtypes = [C.c_longlong, C.c_ulonglong]
     assert cellmath.host_div_rcp_check(30_000_000, 20261104) == 0
+
+
+def test_signed_ld80_sum_equals_x87(cellmath):
+    """R's sum() over elevation differences of either sign (uced_values, R/flow_02_calc_shed.R:126) as emulated for
+    the GPU (cellmath.h lds_*), incl. cancellation and addends far below the running sum."""
+    f64 = np.ctypeslib.ndpointer(np.float64, flags="C")
+    for fn in (cellmath.host_lds_sum, cellmath.host_real_ld_sum):
+        fn.argtypes = [f64, C.c_int]
+        fn.restype = C.c_double
+    rng = np.random.default_rng(5)
+    nbad = 0
+    for trial in range(60000):
+        n = int(rng.integers(1, 12))
+        mode = trial % 5
+        if mode == 0:
+            t = rng.uniform(-1, 1, n)
+        elif mode == 1:
+            t = rng.uniform(-1, 1, n) * 2.0 ** rng.integers(-70, 70, n)
+        elif mode == 2:
+            e = np.round(rng.uniform(500, 800, n + 1), 3)
+            t = e[:-1] - e[-1]
+        elif mode == 3:
+            a = rng.uniform(0, 1, n) * 2.0 ** rng.integers(-5, 5)
+            t = a.copy()
+            k = len(t[1::2])
+            t[1::2] = -a[:-1:2][:k] * (1 + rng.integers(-3, 4, k) * 2.0 ** -52)
+        else:
+            big = rng.uniform(1, 2) * 2.0 ** rng.integers(60, 70) * rng.choice([-1, 1])
+            t = np.concatenate([[big], rng.uniform(-1, 1, n - 1) * 2.0 ** rng.integers(-10, 3, n - 1)])
+        t = np.ascontiguousarray(t, dtype=np.float64)
+        a, b = cellmath.host_lds_sum(t, len(t)), cellmath.host_real_ld_sum(t, len(t))
+        nbad += (a != b) or (np.signbit(a) != np.signbit(b))
+    assert nbad == 0

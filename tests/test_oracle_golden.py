@@ -238,3 +238,58 @@ def test_uced_fullgrid_golden(golden):
     u = oracle.uced(e, dd, sh)
     assert np.isnan(u[0]).all() and np.isnan(u[:, 0]).all()
     assert (u[1:-1, 1:-1].ravel() == g["uced"]).all()
+
+
+def test_g5_long_tests_snapshot(golden):
+    """G5, tests/testthat/_snaps/10_long_tests.md (test_10_long_tests.R: flow_mapper + form_mapper on testELEV with the
+    DEFAULT parameters max_area = 10, max_depth = 0.5 = BASELINE.json configs[0]).  Pit removal (flow_03/04, stays in R)
+    with those limits fills other pits than the shipped full-grid run (max_area = 1, max_depth = 0.1), so the 484-cell
+    samples differ from dem_fill.rds in elev (12 cells), ddir, upslope, uced, the slope_gc columns and everything in
+    form/: those columns are functions of a filled DEM that only exists at the sampled cells and cannot be recomputed.
+    What the hot path determines on its own - the labels and ridge cells of calc_shed4 on the unfilled DEM - must agree."""
+    snap = golden["snap_10_long_tests"]
+    e = oracle.add_buffer(golden["dems"]["testELEV"])
+    s = oracle.shed(e, oracle.ddir(e)["ddir"])
+    seq = snap["b0__seqno"].astype(int) - 1
+    assert len(seq) == 484
+    sh = s["shed"][1:-1, 1:-1].ravel().astype(np.float64)
+    rg = s["ridge"][1:-1, 1:-1].ravel().astype(np.float64)
+    assert (sh[seq] == snap["b0__initial_shed"]).all()
+    assert (rg[seq] == snap["b0__ridge"]).all()
+    # and the sample is consistent with the full-grid golden wherever pit removal did not reach
+    g = golden["dem_fill"]
+    same = snap["b0__elev"] == np.round(g["elev"][seq], 5)
+    assert same.sum() >= 470
+    assert (snap["b0__initial_shed"] == g["initial_shed"][seq]).all()
+
+
+@pytest.mark.parametrize("inverted", [False, True])
+def test_snapshot_seqno_shed_drec_shed(golden, inverted):
+    """The side columns of calc_upslopes in the reference's own snapshot (blocks 1 / 9 of _snaps/02_flow_internal.md,
+    R/flow_02_calc_shed.R:62-68): seqno_shed numbers the cells of a shed in seqno order (the NA group too),
+    drec_shed = seqno_shed[drec].  The host mirror derives them from the device's labels; here from the oracle's."""
+    snap = golden["snap_02_flow_internal"]
+    e = oracle.add_buffer(golden["dems"]["testELEV"])
+    ts = "inv_shed" if inverted else "shed"
+    if inverted:
+        e = oracle.invert(e)
+    r = oracle.ddir(e)
+    s = oracle.shed(e, r["ddir"])
+    seq_shed, drec_shed = side_columns(s["shed"].ravel(), r["drec"].ravel())
+    seq = snap[ts + "__seqno"].astype(int) - 1
+    assert eq_na(seq_shed[seq], snap[ts + "__seqno_shed"]).all()
+    assert eq_na(drec_shed[seq], snap[ts + "__drec_shed"]).all()
+
+
+def side_columns(shed, drec1):
+    """seqno_shed / drec_shed from labels (0 = NA) and 1-based drec (0 = NA), like litap_b200.api.calc_shed4."""
+    key = np.where(shed > 0, shed, 0).astype(np.int64)
+    order = np.argsort(key, kind="stable")
+    first = np.r_[0, np.flatnonzero(np.diff(key[order])) + 1]
+    start = np.repeat(first, np.diff(np.r_[first, key.size]))
+    seq_shed = np.empty(key.size, np.float64)
+    seq_shed[order] = np.arange(key.size) - start + 1
+    ds = np.full(key.size, np.nan)
+    ok = drec1 > 0
+    ds[ok] = seq_shed[drec1[ok] - 1]
+    return seq_shed, ds
