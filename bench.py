@@ -1,15 +1,20 @@
 #!/usr/bin/env python3
 """bench.py — Mcells/s of the LITAP raster hot path (ddir + shed + upslope + form) on B200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--size S] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--size S] [--impl reference] [--weak]
 
 A step = one pass of calc_ddir2 -> calc_shed4 (labels, upslope, ridge) + calc_form over one
-synthetic hash-fBm DEM (BASELINE.json configs[2]: 8192 x 8192, 0.001 m quantisation, grid = 5,
-seed 20261104) that is already resident in HBM.  `value` = cells of the whole job / device time
-(CUDA events, max over ranks).  `e2e` = the same composite through the host-buffer C-ABI call
-litap_flow_form (pinned host arrays, H2D + D2H inside the timed region).
+synthetic hash-fBm DEM (0.001 m quantisation, grid = 5, seed 20261104) that is already resident in HBM.
+  N = 1   BASELINE.json configs[2]: 8192 x 8192 on one GPU
+  N > 1   BASELINE.json configs[3]: ONE 32768 x 32768 DEM cut into N row bands ("scaling": "strong"); after the
+          timed region the bench proves the sharded bits: conservation (every cell drains into exactly one pit),
+          npits equal on all ranks, and the band checksums of ddir / shed / upslope / ridge / slope_pct equal
+          those of the same DEM processed unsharded on rank 0.  At N = 8 an `extra` block adds configs[4]:
+          65536 x 65536 in 8 bands of 8192 rows.  --weak restores round 1's (N * 8192) x 8192 workload.
+`value` = cells of the whole job / device time (CUDA events, max over ranks).  `e2e` = the same composite
+through the host-buffer C-ABI call (pinned host arrays, H2D + D2H inside the timed region).
 `--impl reference` times the CPU restatement of the reference's R code (the oracle; R itself is
-not installed) on a bounded sample of the same DEM with all host threads.
+not installed) on the N = 1 workload with all host threads.
 """
 import argparse
 import json
@@ -113,7 +118,9 @@ def cpu_sample(size, rows):
     rows = min(rows, size)
     e = oracle.synth_dem(rows, size, seed=SEED, quant=QUANT, row0=0, gnr=size)
     e[-1, :] = np.nan  # the band is processed as a DEM of its own: close the ring
-    return e, rows * size, f"rows 0-{rows - 1} of the same {size}x{size} DEM ({rows * size / 1e6:.1f} Mcells)"
+    what = (f"the whole {size}x{size} DEM" if rows == size else
+            f"rows 0-{rows - 1} of the same {size}x{size} DEM") + f" ({rows * size / 1e6:.1f} Mcells)"
+    return e, rows * size, what
 
 
 def run_reference(a):
@@ -121,7 +128,9 @@ def run_reference(a):
     if rank != 0:
         return
     nthreads = os.cpu_count() or 1
-    e, cells, what = cpu_sample(a.size, a.cpu_rows)
+    a.size = a.size or 8192
+    # the whole N = 1 workload unless --cpu-rows bounds the sample (12-13 Mcells/s with 16 threads: ~5 s per pass)
+    e, cells, what = cpu_sample(a.size, a.cpu_rows or a.size)
     for _ in range(min(a.warmup, 1)):
         cpu_port_pass(e, nthreads)
     t0 = time.perf_counter()
@@ -164,19 +173,30 @@ def run_ours(a):
     stream = torch.cuda.current_stream()
     _lib.set_stream(stream.cuda_stream)
 
-    n = a.size
-    ncols = a.cols or n          # --cols: wider bands (e.g. 8 x 8192 rows x 65536 cols = 65536^2 on 8 GPUs)
-    NR, NC = n + 2, ncols + 2
     if world > 1:
-        # one DEM of (world * n) x n cells cut into row bands, one band per GPU (weak scaling); halo rows
-        # and boundary tables travel over NCCL inside the library (litap_b200/csrc/bands.cu)
-        from litap_b200.bands import BandedDEM, init_comm
+        # ONE DEM cut into row bands, one band per GPU; halo rows and boundary tables travel over NCCL inside the
+        # library (litap_b200/csrc/bands.cu).  Default: BASELINE.json configs[3], 32768 x 32768 (strong scaling);
+        # --weak: (world * size) x size, 8192-row bands of 8192 columns as in round 1.
+        from litap_b200.bands import BandedDEM, band_rows, init_comm
         init_comm(rank, world)
-        g = BandedDEM(n * world, ncols, world, band=rank)
+        if a.weak or a.size:
+            n = a.size or 8192                    # rows per band
+            ncols = a.cols or n
+            gnr = n * world
+        else:
+            gnr = ncols = a.dem
+            n = gnr // world
+        scaling = "weak" if (a.weak or a.size) else "strong"
+        g = BandedDEM(gnr, ncols, world, band=rank)
         g.synth(seed=SEED, quant=QUANT)
     else:
-        g = lb.DeviceGrid(NR, NC)
+        n = a.size or 8192
+        ncols = a.cols or n
+        gnr = n
+        scaling = "weak"
+        g = lb.DeviceGrid(n + 2, ncols + 2)
         g.synth(seed=SEED, quant=QUANT)
+    NR, NC = n + 2, ncols + 2
 
     fused = not a.serial_stages
 
@@ -225,9 +245,24 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    cells_job = n * ncols * world
+    cells_job = gnr * ncols
     value = cells_job * a.steps / (ms * 1e-3) / 1e6
     stage = lb.timings()
+
+    # ---- the sharded bits (outside the timed region): conservation, npits, band checksums
+    CHECKED = ("ddir", "shed", "upslope", "ridge", "slope_pct")
+    checks = None
+    band_sums = None
+    if world > 1:
+        cells_b, pits_b = g.conservation()
+        mine = [cells_b, pits_b, int(g.npits)] + [g.band_checksum(k) for k in CHECKED]
+        allv = [None] * world
+        dist.all_gather_object(allv, mine)
+        cells_all, pits_all = sum(v[0] for v in allv), sum(v[1] for v in allv)
+        band_sums = {k: sum(v[3 + i] for v in allv) & 0xFFFFFFFFFFFFFFFF for i, k in enumerate(CHECKED)}
+        checks = {"cells_with_a_shed": cells_all, "sum_upslope_at_pits": pits_all,
+                  "conservation": cells_all == pits_all and cells_all == cells_job,
+                  "npits": allv[0][2], "npits_equal_on_all_ranks": len({v[2] for v in allv}) == 1}
 
     # ---- per-kernel pass (untimed, CUDA events around every launch) -> roofline of the dominant kernel
     _lib.profile(True)
@@ -263,11 +298,18 @@ def run_ours(a):
         g.weti(GRID_M)
         tw = lb.timings()
         weti = {"ms": tw["weti_ms"], "Mcells_per_s": n * n / tw["weti_ms"] / 1e3, "cells_through_ready_queues": tw["weti_queued"],
-                "note": "order-dependent fp64 accumulation, bit-exact vs the reference order; latency-bound"}
+                "alg_bytes_per_cell": 45, "frac_of_hbm_peak": round(45 * n * n / (tw["weti_ms"] * 1e-3) / 1e9 / peak, 4),
+                "note": "order-dependent fp64 accumulation, bit-exact vs the reference order; barrier-free dataflow, latency-bound"}
 
     # ---- end to end through the host-buffer C ABI (pinned host arrays)
     e2e = None
+    e2e_note = None
     if not a.no_e2e and world > 1:
+        import psutil
+        need = (n + 3) * NC * 8 + (n + 1) * NC * 51
+        if need * world > 0.5 * psutil.virtual_memory().available:
+            e2e_note = f"skipped: {need * world / 1e9:.0f} GB of pinned host buffers exceed half of the host's free memory"
+    if not a.no_e2e and world > 1 and e2e_note is None:
         # every rank: its band's rows from pinned host memory -> stages -> its rows of every output back
         hr = torch.empty((n + 3, NC), dtype=torch.float64).pin_memory()
         _lib.check(lb.lib().litap_grid_download(g._h[0], b"elev", hr.numpy().ctypes.data))
@@ -288,7 +330,7 @@ def run_ours(a):
         d2h = sum(v.numel() * v.element_size() for v in pinned.values()) * world
         e2e_step()
         barrier()
-        es = max(1, min(a.steps, a.e2e_steps))
+        es = max(1, min(a.steps, a.e2e_steps if n * ncols <= 2 ** 27 else 2))
         ev0.record(stream)
         for _ in range(es):
             e2e_step()
@@ -328,7 +370,20 @@ def run_ours(a):
         e2e = {"value": cells_job / (e2e_ms * 1e-3) / 1e6, "unit": "Mcells/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": es,
                "api": "litap_flow_form (C ABI, pinned host buffers)"}
-        del pinned, host_in
+        del pinned
+        # the same call with PAGEABLE buffers, fresh result arrays every call: what an R caller (fresh R vectors) sees
+        e_page = np.array(e_np)
+        del host_in, e_np
+        pw = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            res = lb.flow_form(e_page, GRID_M)
+            pw.append((time.perf_counter() - t0) * 1e3)
+            del res
+        e2e["pageable"] = {"ms_per_step": min(pw[1:]), "value": cells_job / (min(pw[1:]) * 1e-3) / 1e6, "unit": "Mcells/s",
+                           "what": "litap_flow_form with numpy (pageable) input and freshly allocated numpy outputs, "
+                                   "wall clock, best of 2 after 1 warm-up; staged through pinned buffers by the library"}
+        del e_page
 
     # ---- slope_gc (not part of the composite metric), reported beside it
     gc = None
@@ -339,6 +394,19 @@ def run_ours(a):
         # compulsory traffic: elev read once, 6 f64 + 2 u8 + 4 i32 outputs written once = 74 B/cell
         gc = {"ms": tg["gc_ms"], "Mcells_per_s": n * n / tg["gc_ms"] / 1e3, "alg_bytes_per_cell": 74,
               "frac_of_hbm_peak": round(74 * n * n / (tg["gc_ms"] * 1e-3) / 1e9 / peak, 4)}
+
+    # ---- calc_upslopes(type = "uced") (not part of the composite metric)
+    uced = None
+    if world == 1 and not a.no_weti:
+        g.uced()
+        g.uced()
+        tu = lb.timings()
+        uced = {"ms": tu["uced_ms"], "Mcells_per_s": n * n / tu["uced_ms"] / 1e3, "alg_bytes_per_cell": 21,
+                "frac_of_hbm_peak": round(21 * n * n / (tu["uced_ms"] * 1e-3) / 1e9 / peak, 4),
+                "contributions": tu["uced_pairs"], "ranges": tu["uced_ranges"],
+                "note": "bit-exact restatement of the reference's per-track long double sums: work = the sum over all cells of "
+                        "the cells upslope of them, not one pass over the DEM; alg. bytes = elev 8 + ddir 1 + shed 4 + uced 8"}
+        lb.lib().litap_pool_trim()
 
     # ---- calc_relz + calc_length (not part of the composite metric) on the flow field of a
     # 4096^2 DEM through the host-buffer C ABI (11 input grids up, 39 double grids down)
@@ -360,32 +428,98 @@ def run_ours(a):
     # ---- CPU baseline (rank 0, N = 1): the oracle on a bounded sample, single thread
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
-        e, cells, what = cpu_sample(n, a.cpu_rows)
+        e, cells, what = cpu_sample(n, a.cpu_rows or 2048)
         t0 = time.perf_counter()
         cpu_port_pass(e, 1)
         dt = time.perf_counter() - t0
+        nth = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        cpu_port_pass(e, nth)
+        dta = time.perf_counter() - t0
         cpu = {"value": cells / dt / 1e6, "unit": "Mcells/s", "cores": 1, "kind": "port", "sample": what,
-               "seconds": dt}
+               "seconds": dt,
+               "all_cores": {"value": cells / dta / 1e6, "cores": nth, "seconds": dta,
+                             "note": "OpenMP in the data-parallel stages (D8 stencil, calc_form); plateau rounds, patches and calc_shed4 serial"}}
+
+    # ---- N > 1: the same DEM unsharded on rank 0 (it fits one B200 up to 32768^2): checksums must equal the bands'
+    extra = None
+    if world > 1:
+        g.close()
+        lb.lib().litap_pool_trim()
+        fits = (gnr + 2) * (((ncols + 2 + 31 + 31) // 32) * 32) < 2 ** 31 and gnr * ncols * 130 < 170e9
+        if rank == 0 and fits and not a.no_whole:
+            t0 = time.perf_counter()
+            w = lb.DeviceGrid(gnr + 2, ncols + 2)
+            w.synth(seed=SEED, quant=QUANT)
+            w.flow_form(GRID_M)
+            whole = {k: w.checksum(k) for k in CHECKED}
+            wn = int(w.npits)
+            w.close()
+            lb.lib().litap_pool_trim()
+            checks["sharded_equals_whole"] = all(whole[k] == band_sums[k] for k in CHECKED) and wn == checks["npits"]
+            checks["whole_dem"] = {"what": f"the same {gnr}x{ncols} DEM as one grid on rank 0 (litap_grid_flow_form), "
+                                           f"checksums of {', '.join(CHECKED)} and npits", "seconds": time.perf_counter() - t0,
+                                   "checksums": {k: hex(v) for k, v in whole.items()},
+                                   "band_checksums": {k: hex(v) for k, v in band_sums.items()}}
+        elif rank == 0:
+            checks["sharded_equals_whole"] = None
+            checks["whole_dem"] = "not run: the DEM does not fit one device" if not fits else "not run (--no-whole)"
+        barrier()
+        # ---- N = 8: BASELINE.json configs[4], 65536 x 65536 in 8 bands of 8192 rows (device-resident, generated on the device)
+        if world == 8 and scaling == "strong" and not a.no_64k:
+            g64 = BandedDEM(65536, 65536, world, band=rank)
+            g64.synth(seed=SEED, quant=QUANT)
+            for _ in range(2):
+                g64.flow_form(GRID_M)
+            barrier()
+            k64 = max(2, min(a.steps, 5))
+            ev0.record(stream)
+            for _ in range(k64):
+                g64.flow_form(GRID_M)
+            ev1.record(stream)
+            barrier()
+            t = torch.tensor([ev0.elapsed_time(ev1)], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms64 = float(t.item()) / k64
+            c64 = g64.conservation()
+            allv = [None] * world
+            dist.all_gather_object(allv, [c64[0], c64[1], int(g64.npits)])
+            cells64, pits64 = sum(v[0] for v in allv), sum(v[1] for v in allv)
+            extra = {"workload": "hash-fBm DEM 65536x65536 in 8 row bands of 8192 rows (BASELINE.json configs[4])",
+                     "ms_per_step": ms64, "steps": k64, "value": 65536 * 65536 / (ms64 * 1e-3) / 1e6, "unit": "Mcells/s",
+                     "npits": allv[0][2], "npits_equal_on_all_ranks": len({v[2] for v in allv}) == 1,
+                     "cells_with_a_shed": cells64, "sum_upslope_at_pits": pits64,
+                     "conservation": cells64 == pits64 == 65536 * 65536,
+                     "note": "upslope is a 32-bit count: litap_bands_shed refuses a DEM in which a basin reaches 2^32 cells "
+                             "(this conservation test, inside the library); e2e at this size: see profiles/"}
+            g64.close()
 
     if rank == 0:
+        if world == 1:
+            wl = f"hash-fBm DEM {n}x{ncols} (BASELINE.json configs[2])"
+        elif scaling == "strong":
+            wl = f"hash-fBm DEM {gnr}x{ncols} in {world} row bands of {n} rows (BASELINE.json configs[3])"
+        else:
+            wl = f"hash-fBm DEM {gnr}x{ncols} in {world} row bands of {n} rows (--weak)"
         os.write(real_out, (json.dumps({
             "metric": METRIC, "value": value, "unit": "Mcells/s", "n_gpus": world, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": (f"hash-fBm DEM {n}x{n}" if world == 1 else
-                                    f"hash-fBm DEM {n * world}x{ncols} in {world} row bands of {n} rows")
-                       + f", quant 0.001 m, grid 5 m, seed {SEED}",
-                       "cells_per_gpu": n * ncols, "l2": "inputs (537 MB elev per GPU) larger than L2; no flush needed",
+            "config": {"workload": wl + f", quant 0.001 m, grid 5 m, seed {SEED}",
+                       "cells_per_gpu": n * ncols,
+                       "l2": f"inputs ({n * ncols * 8 / 1e6:.0f} MB elev per GPU) larger than L2; no flush needed",
                        "parallelism": "1 GPU" if world == 1 else
                        f"row bands, one per GPU; NCCL halo rows + boundary-graph tables (DESIGN.md section 4)",
                        "step": ("litap_grid_flow_form / litap_bands_flow_form: calc_form on the caller's stream beside calc_ddir2 + calc_shed4 on a "
                                 "high-priority stream; per_kernel / roofline come from a separate serial pass"
                                 if fused else "calc_form, calc_ddir2, calc_shed4 as three calls"),
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": nl,
-            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti, "slope_gc": gc, "relz": relz,
+            "clocks": clocks, "e2e": e2e if e2e is not None else ({"value": None, "note": e2e_note} if e2e_note else None),
+            "gpu_launches": nl, "checks": checks, "extra": extra,
+            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "weti": weti, "slope_gc": gc, "uced": uced, "relz": relz,
             "cpu_baseline": cpu}) + "\n").encode())
-    g.close()
+    if world == 1:
+        g.close()
     if world > 1:
         from litap_b200.bands import destroy_comm
         destroy_comm()
@@ -421,10 +555,15 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--size", type=int, default=8192, help="DEM rows per GPU (and columns unless --cols)")
+    ap.add_argument("--size", type=int, default=0, help="DEM rows per GPU (and columns unless --cols); default 8192 at N = 1; "
+                                                        "at N > 1 it selects the weak-scaling workload")
     ap.add_argument("--cols", type=int, default=0, help="DEM columns (multi-GPU band mode), default = --size")
+    ap.add_argument("--dem", type=int, default=32768, help="N > 1: side of the one DEM that is cut into N row bands")
+    ap.add_argument("--weak", action="store_true", help="N > 1: (N * size) x size cells, one size-row band per GPU")
+    ap.add_argument("--no-whole", action="store_true", help="N > 1: skip the unsharded run of the same DEM on rank 0")
+    ap.add_argument("--no-64k", action="store_true", help="N = 8: skip the 65536 x 65536 extra block")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-rows", type=int, default=2048, help="rows of the DEM in the CPU sample")
+    ap.add_argument("--cpu-rows", type=int, default=0, help="rows of the DEM in the CPU sample (default: 2048 for the in-line cpu_baseline, the whole DEM for --impl reference)")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -62,6 +62,7 @@ typedef struct litap_timings {
 
 int litap_init(int device);        /* selects the device and creates the stream; idempotent */
 void litap_shutdown(void);         /* frees pooled device memory */
+void litap_pool_trim(void);        /* frees the pooled device memory that is not in use by a grid */
 const char* litap_last_error(void);
 const char* litap_version(void);
 int litap_get_timings(litap_timings* out);
@@ -162,6 +163,9 @@ int litap_grid_download(litap_grid* g, const char* name, void* dst);
 int64_t litap_grid_npits(const litap_grid* g);
 /* order-independent checksum (sum of value*index hashes) of a result array, computed on the device */
 int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* out);
+/* conservation check of calc_shed4: number of cells with a shed and the sum of upslope over the pits among them (a band:
+ * its own rows); over a whole DEM the two are equal.  litap_bands_shed uses it to refuse DEMs in which a 32-bit count wrapped. */
+int litap_grid_conservation(litap_grid* g, uint64_t* cells, uint64_t* pit_upslope);
 
 /* ---- row bands: one DEM sharded over several GPUs ----------------------- */
 /* The DEM (gnr rows x nc cols, unbuffered) is cut into nbands contiguous row bands; band b owns rows

@@ -13,7 +13,7 @@ SYMBOLS = [
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
     "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_uced", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
-    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_slope_gc", "litap_grid_flow_form",
+    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
@@ -50,6 +50,7 @@ def load():
     vp, i64, dbl, ci = C.c_void_p, C.c_int64, C.c_double, C.c_int
     L.litap_init.argtypes = [ci]
     L.litap_shutdown.restype = None
+    L.litap_pool_trim.restype = None
     L.litap_last_error.restype = C.c_char_p
     L.litap_version.restype = C.c_char_p
     L.litap_get_timings.argtypes = [C.POINTER(Timings)]
@@ -83,6 +84,7 @@ def load():
     L.litap_grid_npits.restype = i64
     L.litap_grid_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
     L.litap_band_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
+    L.litap_grid_conservation.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.litap_comm_unique_id.argtypes = [vp]
     L.litap_comm_init.argtypes = [ci, ci, vp]
     L.litap_comm_destroy.restype = None

@@ -345,6 +345,12 @@ class DeviceGrid:
         check(lib().litap_grid_checksum(self._h, name.encode(), C.byref(v)))
         return v.value
 
+    def conservation(self):
+        """(cells with a shed, sum of upslope over the pits): equal for a whole DEM."""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        check(lib().litap_grid_conservation(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     @property
     def npits(self):
         return lib().litap_grid_npits(self._h)

@@ -127,6 +127,16 @@ class BandedDEM:
         check(lib().litap_grid_checksum(self._h[i], name.encode(), C.byref(v)))
         return v.value
 
+    def conservation(self):
+        """(cells with a shed, sum of upslope over the pits) of the local bands' own rows."""
+        cells = pits = 0
+        for h in self._h:
+            a, b = C.c_uint64(0), C.c_uint64(0)
+            check(lib().litap_grid_conservation(h, C.byref(a), C.byref(b)))
+            cells += a.value
+            pits += b.value
+        return cells, pits
+
     def band_checksum(self, name):
         """Share of the local bands in DeviceGrid.checksum(name) of the unsharded DEM (wrapping sum over bands)."""
         tot = 0

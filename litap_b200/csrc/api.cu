@@ -78,6 +78,12 @@ void pool_free(void* p) {
   for (auto& b : g_pool)
     if (b.p == p) { b.used = false; return; }
 }
+// give unused cached blocks back to the driver (between phases with very different working sets)
+extern "C" void litap_pool_trim(void) {
+  if (ctx().ready) cudaStreamSynchronize(ctx().stream);
+  for (size_t i = 0; i < g_pool.size();)
+    if (!g_pool[i].used) { cudaFree(g_pool[i].p); g_pool.erase(g_pool.begin() + i); } else ++i;
+}
 void pool_release_all() {
   for (auto& b : g_pool) cudaFree(b.p);
   g_pool.clear();

@@ -786,6 +786,52 @@ __global__ void k_band_ring_row(GridDims d, int row, int32_t* __restrict__ shed_
 }
 }  // namespace bg
 
+// cells with a shed number and the upslope counts of the pits (ddir 5) among them, rows [row_lo, row_hi): every cell drains
+// into exactly one pit, so over a whole DEM the two numbers are equal -- unless a 32-bit count wrapped
+__global__ void k_conservation(const int32_t* __restrict__ shed, const uint8_t* __restrict__ ddir, const uint32_t* __restrict__ up,
+                               GridDims d, int row_lo, int row_hi, unsigned long long* __restrict__ out) {
+  unsigned long long cells = 0, pits = 0;
+  for (int r = row_lo + blockIdx.y; r < row_hi; r += gridDim.y)
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < d.NC; c += gridDim.x * blockDim.x) {
+      const size_t id = (size_t)r * d.pitch + c;
+      if (shed[id] > 0) {
+        ++cells;
+        if (ddir[id] == 5) pits += up[id];
+      }
+    }
+  for (int o = 16; o; o >>= 1) {
+    cells += __shfl_xor_sync(0xffffffffu, cells, o);
+    pits += __shfl_xor_sync(0xffffffffu, pits, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (cells) atomicAdd(&out[0], cells);
+    if (pits) atomicAdd(&out[1], pits);
+  }
+}
+static int conservation_enqueue(litap_grid* g, unsigned long long* out2) {
+  const int lo = g->nbands ? g->own_lo : 1, hi = g->nbands ? g->own_hi : g->d.NR - 1;
+  CUDA_TRY(cudaMemsetAsync(out2, 0, 16, ctx().stream));
+  dim3 grid(std::min((g->d.NC + 255) / 256, 32), std::min(std::max(hi - lo, 1), 2048));
+  KERNEL("k_conservation", k_conservation<<<grid, 256, 0, ctx().stream>>>(g->shed, g->ddir, g->upslope, g->d, lo, hi, out2));
+  return LITAP_OK;
+}
+// (cells with a shed, sum of upslope over the pits) of a grid or of a band's own rows
+extern "C" int litap_grid_conservation(litap_grid* g, uint64_t* cells, uint64_t* pit_upslope) {
+  if (!g || !cells || !pit_upslope) return set_error(LITAP_EARG, "litap_grid_conservation: NULL");
+  if (!g->shed || !g->ddir || !g->upslope) return set_error(LITAP_EARG, "litap_grid_conservation: needs ddir, shed and upslope on the grid");
+  PoolScratch S;
+  unsigned long long* o = S.get<unsigned long long>(2);
+  if (!o) return set_error(LITAP_ENOMEM, "device allocation failed (conservation)");
+  int rc = conservation_enqueue(g, o);
+  if (rc) return rc;
+  unsigned long long h[2];
+  CUDA_TRY(cudaMemcpyAsync(h, o, 16, cudaMemcpyDeviceToHost, ctx().stream));
+  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  *cells = h[0];
+  *pit_upslope = h[1];
+  return LITAP_OK;
+}
+
 extern "C" int litap_bands_shed(litap_grid** B, int n) {
   using namespace bg;
   int rc = check_bands(B, n);
@@ -933,6 +979,23 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
   cudaEventRecord(c.ev[3], st);
   CUDA_TRY(cudaStreamSynchronize(st));
   cudaEventElapsedTime(&c.tm.shed_ms, c.ev[2], c.ev[3]);
+  // upslope is a 32-bit count (include/litap.h): a DEM of 2^32 or more cells (65536 x 65536 is exactly 2^32) could hold a
+  // basin whose count wraps.  A wrapped count also wraps at the basin's pit, and then the pit counts no longer add up to
+  // the number of cells: detect that and fail instead of returning wrapped numbers.
+  if ((double)B[0]->gnr * (double)(NC - 2) >= 4294967296.0) {
+    std::vector<std::vector<unsigned long long>> cons(n, std::vector<unsigned long long>(2));
+    for (int i = 0; i < n; ++i) {
+      uint64_t a = 0, b = 0;
+      if ((rc = litap_grid_conservation(B[i], &a, &b))) return rc;
+      cons[i][0] = a; cons[i][1] = b;
+    }
+    std::vector<unsigned long long> all;
+    if ((rc = gather_words_host(B, n, cons, 2, all))) return rc;
+    unsigned long long cells = 0, pits = 0;
+    for (int b = 0; b < P; ++b) { cells += all[2 * b]; pits += all[2 * b + 1]; }
+    if (cells != pits)
+      return set_error(LITAP_EARG, "litap_bands_shed: a basin of this DEM has 2^32 or more cells: upslope (32-bit) would wrap");
+  }
   for (int i = 0; i < n; ++i) {
     B[i]->npits = (int64_t)npits_global;
     B[i]->have_shed = true;
