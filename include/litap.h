@@ -138,9 +138,28 @@ int litap_flow_form(const double* elev, int64_t NR, int64_t NC, double grid, int
                     uint8_t* ridge, int64_t* npits, double* slope_pct, double* slope_deg,
                     double* aspect, double* prof, double* plan);
 
+/* ---- rasters on disk: ESRI floating-point raster = <name>.flt (float32, row-major, north row first)
+ * + <name>.hdr (ncols, nrows, xllcorner, yllcorner, cellsize, NODATA_value, byteorder).  Replaces, for big DEMs, the
+ * raster::raster() %>% as.data.frame() path of load_file (R/LITAP_load.R:77-79,187-192) and the .rds / .csv tibbles of
+ * save_output (R/LITAP_read_write.R:8-66). */
+typedef struct litap_raster_info {
+  int64_t nrow, ncol;
+  double xll, yll, cellsize, nodata;
+  int big_endian;
+} litap_raster_info;
+typedef struct litap_grid litap_grid;
+int litap_flt_info(const char* path /* .flt or .hdr */, litap_raster_info* out);
+/* a new grid (NA ring added like add_buffer(), NODATA_value and missing_value -> NA like db_format()) from the file, read
+ * in row chunks through pinned buffers: the disk, PCIe and the float32 -> fp64 kernel overlap.  info may be NULL. */
+int litap_grid_read_flt(const char* path, double missing_value, litap_grid** out, litap_raster_info* info);
+/* one result of the grid without its ring (remove_buffer()) as a headerless little-endian binary file in its own dtype
+ * (as_flt = 0: f64 / i32 / u32 / u8; NA = NaN or 0) or narrowed to float32 (as_flt = 1), plus <path minus extension>.hdr.
+ * georef (may be NULL) supplies xllcorner / yllcorner / cellsize for the header. */
+int litap_grid_write_raw(litap_grid* g, const char* name, const char* path, int as_flt, const litap_raster_info* georef);
+
 /* ---- device-resident entry points (bench / large DEMs that never exist on the host) -------- */
 
-typedef struct litap_grid litap_grid; /* opaque: one DEM (or one row band) resident in HBM */
+/* litap_grid is opaque: one DEM (or one row band) resident in HBM */
 
 int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out);
 void litap_grid_destroy(litap_grid* g);

@@ -13,7 +13,7 @@ SYMBOLS = [
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
     "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_uced", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
-    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_grid_slope_gc", "litap_grid_flow_form",
+    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_flt_info", "litap_grid_read_flt", "litap_grid_write_raw", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
@@ -23,6 +23,14 @@ SYMBOLS = [
 
 class LitapError(RuntimeError):
     """Mirrors the R shim's Rf_error(): raised for every non-zero status of the C ABI."""
+
+
+class RasterInfo(C.Structure):
+    _fields_ = [("nrow", C.c_int64), ("ncol", C.c_int64), ("xll", C.c_double), ("yll", C.c_double),
+                ("cellsize", C.c_double), ("nodata", C.c_double), ("big_endian", C.c_int)]
+
+    def asdict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
 
 
 class Timings(C.Structure):
@@ -50,6 +58,9 @@ def load():
     vp, i64, dbl, ci = C.c_void_p, C.c_int64, C.c_double, C.c_int
     L.litap_init.argtypes = [ci]
     L.litap_shutdown.restype = None
+    L.litap_flt_info.argtypes = [C.c_char_p, C.POINTER(RasterInfo)]
+    L.litap_grid_read_flt.argtypes = [C.c_char_p, C.c_double, C.POINTER(C.c_void_p), C.POINTER(RasterInfo)]
+    L.litap_grid_write_raw.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(RasterInfo)]
     L.litap_pool_trim.restype = None
     L.litap_last_error.restype = C.c_char_p
     L.litap_version.restype = C.c_char_p

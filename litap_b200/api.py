@@ -7,6 +7,7 @@ argument meaning, returned columns and NA conventions follow the R functions; ev
 calls the CUDA library through the C ABI and raises LitapError on failure.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -291,10 +292,30 @@ class DeviceGrid:
            "ridge": np.uint8, "hill_r_dir": np.uint8, "hill_c_dir": np.uint8, "hill_r_n": np.int32,
            "hill_r_cell": np.int32, "hill_c_n": np.int32, "hill_c_cell": np.int32}
 
-    def __init__(self, NR, NC):
+    def __init__(self, NR, NC, _handle=None):
         self.NR, self.NC = int(NR), int(NC)
+        self.georef = None
+        if _handle is not None:
+            self._h = _handle
+            return
         self._h = C.c_void_p()
         check(lib().litap_grid_create(self.NR, self.NC, C.byref(self._h)))
+
+    @classmethod
+    def read_flt(cls, path, missing_value=-9999.0):
+        """load_file() for an ESRI .flt / .hdr raster (R/LITAP_load.R:77-79,187-213) straight into HBM: NODATA and
+        missing_value -> NA, NA ring added (add_buffer)."""
+        from ._lib import RasterInfo
+        h, info = C.c_void_p(), RasterInfo()
+        check(lib().litap_grid_read_flt(os.fsencode(path), float(missing_value), C.byref(h), C.byref(info)))
+        g = cls(info.nrow + 2, info.ncol + 2, _handle=h)
+        g.georef = info
+        return g
+
+    def write_raw(self, name, path, as_flt=False):
+        """One result without its ring (remove_buffer) as a raw little-endian binary file (+ .hdr)."""
+        check(lib().litap_grid_write_raw(self._h, name.encode(), os.fsencode(path), int(bool(as_flt)),
+                                         C.byref(self.georef) if self.georef is not None else None))
 
     def close(self):
         if self._h:

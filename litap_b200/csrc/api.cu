@@ -8,6 +8,9 @@
 
 // ------------------------------------------------------------------------------------------------
 static thread_local std::string g_err;
+static std::recursive_mutex g_api_mutex;
+ApiLock::ApiLock() { g_api_mutex.lock(); }
+ApiLock::~ApiLock() { g_api_mutex.unlock(); }
 static Ctx g_ctx;
 static bool g_own_stream = true;  // false after litap_set_stream(non-NULL)
 static cudaStream_t g_hi_stream = nullptr;  // litap_grid_flow_form: the flow stages beside calc_form
@@ -22,6 +25,7 @@ extern "C" const char* litap_last_error(void) { return g_err.c_str(); }
 extern "C" const char* litap_version(void) { return "litap_b200 0.1 (sm_100a)"; }
 
 extern "C" int litap_init(int device) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Ctx& c = ctx();
   if (c.ready && (device < 0 || device == c.device)) return LITAP_OK;
   int n = 0;
@@ -80,6 +84,7 @@ void pool_free(void* p) {
 }
 // give unused cached blocks back to the driver (between phases with very different working sets)
 extern "C" void litap_pool_trim(void) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (ctx().ready) cudaStreamSynchronize(ctx().stream);
   for (size_t i = 0; i < g_pool.size();)
     if (!g_pool[i].used) { cudaFree(g_pool[i].p); g_pool.erase(g_pool.begin() + i); } else ++i;
@@ -90,6 +95,7 @@ void pool_release_all() {
 }
 
 extern "C" void litap_shutdown(void) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Ctx& c = ctx();
   if (!c.ready) return;
   cudaStreamSynchronize(c.stream);
@@ -105,6 +111,7 @@ extern "C" void litap_shutdown(void) {
 }
 
 extern "C" int litap_get_timings(litap_timings* out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!out) return set_error(LITAP_EARG, "litap_get_timings: NULL");
   *out = ctx().tm;
   return LITAP_OK;
@@ -112,6 +119,7 @@ extern "C" int litap_get_timings(litap_timings* out) {
 
 // ------------------------------------------------------------------------------------------------
 extern "C" int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!out) return set_error(LITAP_EARG, "litap_grid_create: NULL out");
   *out = nullptr;
   if (NR < 3 || NC < 3) return set_error(LITAP_EARG, "grid must be at least 3 x 3 buffered cells (1 x 1 DEM + NA ring)");
@@ -134,6 +142,7 @@ extern "C" int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out) {
 }
 
 extern "C" void litap_grid_destroy(litap_grid* g) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return;
   if (ctx().ready) cudaStreamSynchronize(ctx().stream);
   grid_free_array(g->elev);
@@ -170,6 +179,7 @@ static int download2d(T* dst, const GridDims& d, const T* src) {
 }
 
 extern "C" int litap_grid_upload_elev(litap_grid* g, const double* elev) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || !elev) return set_error(LITAP_EARG, "litap_grid_upload_elev: NULL");
   int rc = upload2d(g->elev, g->d, elev);
   if (rc) return rc;
@@ -179,6 +189,7 @@ extern "C" int litap_grid_upload_elev(litap_grid* g, const double* elev) {
 }
 
 extern "C" int litap_grid_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_synth: NULL");
   g->have_ddir = g->have_shed = false;
   int rc = run_synth(g, row0, gnr, seed, quant, na_permille);
@@ -203,6 +214,7 @@ struct StageTimer {
 };
 
 extern "C" int litap_grid_ddir(litap_grid* g, int invert) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_ddir: NULL");
   int64_t l0 = ctx().launches;
   StageTimer t(&ctx().tm.ddir_ms, 0);
@@ -214,6 +226,7 @@ extern "C" int litap_grid_ddir(litap_grid* g, int invert) {
   return rc;
 }
 extern "C" int litap_grid_shed(litap_grid* g) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_shed: NULL");
   if (!g->ddir) return set_error(LITAP_EARG, "litap_grid_shed: no ddir on the grid (run litap_grid_ddir first)");
   int64_t l0 = ctx().launches;
@@ -226,6 +239,7 @@ extern "C" int litap_grid_shed(litap_grid* g) {
   return rc;
 }
 extern "C" int litap_grid_form(litap_grid* g, double grid_m) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_form: NULL");
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_form: grid must be > 0");
   int64_t l0 = ctx().launches;
@@ -237,6 +251,7 @@ extern "C" int litap_grid_form(litap_grid* g, double grid_m) {
   return rc;
 }
 extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_weti: NULL");
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_weti: grid must be > 0");
   if (g->nbands > 0)   // the visiting order couples all bands: a band on its own would give a band-local (wrong) answer
@@ -252,6 +267,7 @@ extern "C" int litap_grid_weti(litap_grid* g, double grid_m) {
 }
 
 extern "C" int litap_grid_uced(litap_grid* g) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_uced: NULL");
   if (g->nbands > 0)   // a track crosses band edges; not sharded
     return set_error(LITAP_EARG, "litap_grid_uced: not available on a row band (run it on a whole-DEM grid)");
@@ -284,6 +300,7 @@ int flow_streams(cudaStream_t* hi, cudaEvent_t* fork, cudaEvent_t* join) {
   return LITAP_OK;
 }
 extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_flow_form: NULL");
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_flow_form: grid must be > 0");
   if (g->nbands > 0) return set_error(LITAP_EARG, "litap_grid_flow_form: row bands use litap_bands_*");
@@ -317,6 +334,7 @@ extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(c.ev[3], g_hi_stream));
     CUDA_TRY(cudaEventRecord(g_ev_join, g_hi_stream));
+    sw.joined = true;
   }
   CUDA_TRY(cudaStreamWaitEvent(user, g_ev_join, 0));
   CUDA_TRY(cudaStreamSynchronize(user));
@@ -330,6 +348,7 @@ extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
 }
 
 extern "C" int litap_grid_slope_gc(litap_grid* g, double grid_m) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g) return set_error(LITAP_EARG, "litap_grid_slope_gc: NULL");
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_grid_slope_gc: grid must be > 0");
   if (g->nbands > 0) return set_error(LITAP_EARG, "litap_grid_slope_gc: not available on a row band (columns span all bands)");
@@ -344,8 +363,9 @@ extern "C" int litap_grid_slope_gc(litap_grid* g, double grid_m) {
 
 extern "C" int64_t litap_grid_npits(const litap_grid* g) { return g ? g->npits : -1; }
 
-struct ArrRef { const void* p; int esize; };
-static ArrRef find_array(litap_grid* g, const char* name) {
+ArrRef grid_find_array(litap_grid* g, const char* name) { return find_array_impl(g, name); }
+static ArrRef find_array(litap_grid* g, const char* name) { return find_array_impl(g, name); }
+ArrRef find_array_impl(litap_grid* g, const char* name) {
   static const char* fn[5] = {"slope_pct", "slope_deg", "aspect", "prof", "plan"};
   static const char* wn[4] = {"qarea1", "qarea2", "qweti1", "qweti2"};
   if (!strcmp(name, "elev")) return {g->elev, 8};
@@ -367,6 +387,7 @@ static ArrRef find_array(litap_grid* g, const char* name) {
 }
 
 extern "C" int litap_grid_download(litap_grid* g, const char* name, void* dst) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || !name || !dst) return set_error(LITAP_EARG, "litap_grid_download: NULL");
   ArrRef a = find_array(g, name);
   if (!a.p) return set_error(LITAP_EARG, std::string("litap_grid_download: no such result on the grid: ") + name);
@@ -381,6 +402,7 @@ extern "C" int litap_grid_download(litap_grid* g, const char* name, void* dst) {
 
 // a band's share of the full buffered DEM (see litap_band_rows), copied densely into dst
 extern "C" int litap_band_download(litap_grid* g, const char* name, void* dst) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || !name || !dst || g->nbands < 1) return set_error(LITAP_EARG, "litap_band_download: bad arguments");
   ArrRef a = find_array(g, name);
   if (!a.p) return set_error(LITAP_EARG, std::string("litap_band_download: no such result on the band: ") + name);
@@ -394,6 +416,7 @@ extern "C" int litap_band_download(litap_grid* g, const char* name, void* dst) {
 }
 
 extern "C" int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || !name || !out) return set_error(LITAP_EARG, "litap_grid_checksum: NULL");
   ArrRef a = find_array(g, name);
   if (!a.p) return set_error(LITAP_EARG, std::string("litap_grid_checksum: no such result on the grid: ") + name);
@@ -403,6 +426,7 @@ extern "C" int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* ou
 // a band's share of litap_grid_checksum of the whole DEM: the rows litap_band_rows names, hashed with their cell
 // numbers in the whole buffered DEM.  The (wrapping) sum over all bands equals the checksum of the unsharded result.
 extern "C" int litap_band_checksum(litap_grid* g, const char* name, uint64_t* out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || !name || !out || g->nbands < 1) return set_error(LITAP_EARG, "litap_band_checksum: bad arguments");
   ArrRef a = find_array(g, name);
   if (!a.p) return set_error(LITAP_EARG, std::string("litap_band_checksum: no such result on the band: ") + name);
@@ -415,6 +439,7 @@ extern "C" int litap_band_checksum(litap_grid* g, const char* name, uint64_t* ou
 // bracket this library's work) and the optional per-kernel profiler
 
 extern "C" int litap_set_stream(void* cuda_stream) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   int rc = ensure_init();
   if (rc) return rc;
   Ctx& c = ctx();
@@ -452,11 +477,13 @@ ProfScope::~ProfScope() {
 }
 
 extern "C" int litap_profile_enable(int on) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   g_prof_on = on != 0;
   return LITAP_OK;
 }
 // CSV "kernel,launches,total_ms\n" of everything recorded since the last report; clears the log
 extern "C" int litap_profile_report(char* buf, int64_t cap) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!buf || cap < 1) return set_error(LITAP_EARG, "litap_profile_report: bad buffer");
   if (ctx().ready) cudaStreamSynchronize(ctx().stream);
   std::vector<std::string> names;

@@ -71,6 +71,7 @@ int begin_call(int64_t NR, int64_t NC, const void* must, GridGuard& gg) {
 }  // namespace
 
 extern "C" int litap_ddir(const double* elev, int64_t NR, int64_t NC, int invert, uint8_t* ddir, uint8_t* flatcell) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   return litap_flow_form(elev, NR, NC, 0.0, invert, ddir, flatcell, nullptr, nullptr, nullptr, nullptr, nullptr,
                          nullptr, nullptr, nullptr, nullptr);
 }
@@ -78,6 +79,7 @@ extern "C" int litap_ddir(const double* elev, int64_t NR, int64_t NC, int invert
 extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, double grid, int invert, uint8_t* ddir,
                                uint8_t* flatcell, int32_t* shed, uint32_t* upslope, uint8_t* ridge, int64_t* npits,
                                double* slope_pct, double* slope_deg, double* aspect, double* prof, double* plan) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Wall w;
   GridGuard gg;
   RC(begin_call(NR, NC, elev, gg));
@@ -142,6 +144,7 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
 
 extern "C" int litap_shed(const double* elev, const uint8_t* ddir, int64_t NR, int64_t NC, int32_t* shed,
                           uint32_t* upslope, uint8_t* ridge, int64_t* npits) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Wall w;
   GridGuard gg;
   if (!ddir) return set_error(LITAP_EARG, "litap_shed: NULL ddir");
@@ -169,6 +172,7 @@ extern "C" int litap_shed(const double* elev, const uint8_t* ddir, int64_t NR, i
 
 extern "C" int litap_form(const double* elev, int64_t NR, int64_t NC, double grid, double* slope_pct,
                           double* slope_deg, double* aspect, double* prof, double* plan) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Wall w;
   GridGuard gg;
   if (!(grid > 0)) return set_error(LITAP_EARG, "litap_form: grid must be > 0");
@@ -191,6 +195,7 @@ extern "C" int litap_form(const double* elev, int64_t NR, int64_t NC, double gri
 
 extern "C" int litap_weti(const double* elev, const uint8_t* ddir, const uint32_t* upslope, int64_t NR, int64_t NC,
                           double grid, double* qarea1, double* qarea2, double* qweti1, double* qweti2) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Wall w;
   GridGuard gg;
   if (!ddir || !upslope) return set_error(LITAP_EARG, "litap_weti: NULL ddir/upslope");
@@ -218,6 +223,7 @@ extern "C" int litap_weti(const double* elev, const uint8_t* ddir, const uint32_
 }
 
 extern "C" int litap_uced(const double* elev, const uint8_t* ddir, const int32_t* shed, int64_t NR, int64_t NC, double* uced) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Wall w;
   GridGuard gg;
   if (!ddir || !shed || !uced) return set_error(LITAP_EARG, "litap_uced: NULL ddir/shed/uced");
@@ -246,6 +252,7 @@ extern "C" int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double
                               double* sgcn, double* sgc, double* scr, double* scc, uint8_t* hill_r_dir,
                               uint8_t* hill_c_dir, int32_t* hill_r_n, int32_t* hill_r_cell, int32_t* hill_c_n,
                               int32_t* hill_c_cell) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   Wall w;
   GridGuard gg;
   if (!(grid > 0)) return set_error(LITAP_EARG, "litap_slope_gc: grid must be > 0");

@@ -100,6 +100,7 @@ int nccl_load() {
 }  // namespace
 
 extern "C" int litap_comm_unique_id(void* id128) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!id128) return set_error(LITAP_EARG, "litap_comm_unique_id: NULL");
   int rc = nccl_load();
   if (rc) return rc;
@@ -109,6 +110,7 @@ extern "C" int litap_comm_unique_id(void* id128) {
   return LITAP_OK;
 }
 extern "C" int litap_comm_init(int rank, int nranks, const void* id128) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!id128 || nranks < 1 || rank < 0 || rank >= nranks) return set_error(LITAP_EARG, "litap_comm_init: bad arguments");
   int rc = ensure_init();
   if (rc) return rc;
@@ -123,6 +125,7 @@ extern "C" int litap_comm_init(int rank, int nranks, const void* id128) {
   return LITAP_OK;
 }
 extern "C" void litap_comm_destroy(void) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (g_comm) g_nccl.CommDestroy(g_comm);
   g_comm = nullptr;
   g_rank = 0;
@@ -228,6 +231,7 @@ int gather_words_host(litap_grid** B, int n, const std::vector<std::vector<unsig
 }  // namespace
 
 extern "C" int litap_band_create(int64_t gnr, int64_t nc, int band, int nbands, litap_grid** out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!out) return set_error(LITAP_EARG, "litap_band_create: NULL out");
   *out = nullptr;
   if (nbands < 1 || band < 0 || band >= nbands) return set_error(LITAP_EARG, "litap_band_create: bad band index");
@@ -251,6 +255,7 @@ extern "C" int litap_band_create(int64_t gnr, int64_t nc, int band, int nbands, 
 
 // synthetic DEM of the band, halo rows included (bit-identical with the unsharded generator)
 extern "C" int litap_band_synth(litap_grid* g, uint32_t seed, double quant, int na_permille) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || g->nbands < 1) return set_error(LITAP_EARG, "litap_band_synth: not a band grid");
   // run_synth maps local row R to DEM row row0 + R - 1; local row 2 is DEM row r0
   int rc = run_synth(g, g->row_off, g->gnr, seed, quant, na_permille);
@@ -263,6 +268,7 @@ extern "C" int litap_band_synth(litap_grid* g, uint32_t seed, double quant, int 
 
 // the band's own copy of its rows: local rows 1 .. NR-1 (halo rows included), NC wide, dense
 extern "C" int litap_band_upload_rows(litap_grid* g, const double* rows) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || g->nbands < 1 || !rows) return set_error(LITAP_EARG, "litap_band_upload_rows: bad arguments");
   const GridDims d = g->d;
   CUDA_TRY(cudaMemcpy2DAsync(g->elev + d.pitch, (size_t)d.pitch * 8, rows, (size_t)d.NC * 8, (size_t)d.NC * 8, d.NR - 1,
@@ -275,6 +281,7 @@ extern "C" int litap_band_upload_rows(litap_grid* g, const double* rows) {
 
 // rows of the full buffered DEM (gnr+2 rows, NC wide) that belong to this band, halo rows included
 extern "C" int litap_band_upload_elev(litap_grid* g, const double* elev_full) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || g->nbands < 1 || !elev_full) return set_error(LITAP_EARG, "litap_band_upload_elev: bad arguments");
   const GridDims d = g->d;
   // local rows 1 .. NR-1 are buffered DEM rows row_off+1 .. row_off+NR-1
@@ -300,6 +307,7 @@ __global__ void k_max_words(const unsigned long long* __restrict__ w, int n, uns
 }  // namespace
 
 extern "C" int litap_bands_ddir(litap_grid** B, int n, int invert) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   int rc = check_bands(B, n);
   if (rc) return rc;
   Ctx& c = ctx();
@@ -426,6 +434,7 @@ extern "C" int litap_bands_ddir(litap_grid** B, int n, int invert) {
 }
 
 extern "C" int litap_bands_form(litap_grid** B, int n, double grid_m) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   int rc = check_bands(B, n);
   if (rc) return rc;
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_bands_form: grid must be > 0");
@@ -447,6 +456,7 @@ extern "C" int litap_bands_shed(litap_grid** B, int n);
 // form + ddir + shed of the local bands as one call: calc_form on the caller's stream, the flow stages (with
 // their exchanges) on the library's high-priority stream, like litap_grid_flow_form
 extern "C" int litap_bands_flow_form(litap_grid** B, int n, double grid_m, int invert) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   int rc = check_bands(B, n);
   if (rc) return rc;
   if (!(grid_m > 0)) return set_error(LITAP_EARG, "litap_bands_flow_form: grid must be > 0");
@@ -471,6 +481,7 @@ extern "C" int litap_bands_flow_form(litap_grid** B, int n, double grid_m, int i
     if ((rc = litap_bands_ddir(B, n, invert))) return rc;
     if ((rc = litap_bands_shed(B, n))) return rc;
     CUDA_TRY(cudaEventRecord(join, hi));
+    sw.joined = true;
   }
   CUDA_TRY(cudaStreamWaitEvent(user, join, 0));
   CUDA_TRY(cudaStreamSynchronize(user));
@@ -817,6 +828,7 @@ static int conservation_enqueue(litap_grid* g, unsigned long long* out2) {
 }
 // (cells with a shed, sum of upslope over the pits) of a grid or of a band's own rows
 extern "C" int litap_grid_conservation(litap_grid* g, uint64_t* cells, uint64_t* pit_upslope) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (!g || !cells || !pit_upslope) return set_error(LITAP_EARG, "litap_grid_conservation: NULL");
   if (!g->shed || !g->ddir || !g->upslope) return set_error(LITAP_EARG, "litap_grid_conservation: needs ddir, shed and upslope on the grid");
   PoolScratch S;
@@ -833,6 +845,7 @@ extern "C" int litap_grid_conservation(litap_grid* g, uint64_t* cells, uint64_t*
 }
 
 extern "C" int litap_bands_shed(litap_grid** B, int n) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   using namespace bg;
   int rc = check_bands(B, n);
   if (rc) return rc;

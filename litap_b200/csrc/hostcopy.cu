@@ -52,10 +52,11 @@ void host_copy(char* dst, const char* src, size_t bytes, int nt) {
 // Fresh anonymous memory is faulted in page by page while it is written; asking for transparent huge pages on the
 // 2 MB-aligned inside of the destination makes that 512 x fewer faults where the system allows it
 // (transparent_hugepage = madvise or always).  Advice only: it does not change what the caller's memory holds.
-// LITAP_D2H_HUGEPAGE=0 turns it off.
+// The memory belongs to the caller, so this is OPT-IN: LITAP_D2H_HUGEPAGE=1 (the pageable figures of the bench say
+// which way they were taken).
 void advise_hugepages(void* dst, size_t bytes) {
-  static const bool off = [] { const char* e = getenv("LITAP_D2H_HUGEPAGE"); return e && e[0] == '0'; }();
-  if (off) return;
+  static const bool on = [] { const char* e = getenv("LITAP_D2H_HUGEPAGE"); return e && e[0] == '1'; }();
+  if (!on) return;
   const uintptr_t H = (uintptr_t)2 << 20;
   const uintptr_t lo = ((uintptr_t)dst + H - 1) & ~(H - 1), hi = ((uintptr_t)dst + bytes) & ~(H - 1);
   if (hi > lo) (void)madvise((void*)lo, hi - lo, MADV_HUGEPAGE);
@@ -172,6 +173,22 @@ int h2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
     CUDA_TRY(cudaEventRecord(g_up_ev[b], st));
     g_up_next ^= 1;
   }
+  return LITAP_OK;
+}
+
+// the pinned staging pairs for code that moves files (rasterio.cu): which = 0 the upload pair, 1 the download pair
+// (pending downloads are completed first)
+int hostcopy_staging(int which, void* buf[2], cudaEvent_t ev[2], size_t* bytes) {
+  if (which == 0) {
+    RC(up_init());
+    for (int b = 0; b < 2; ++b) { buf[b] = g_up[b]; ev[b] = g_up_ev[b]; }
+  } else {
+    RC(stage_init());
+    RC(complete(g_next));
+    RC(complete(g_next ^ 1));
+    for (int b = 0; b < 2; ++b) { buf[b] = g_stage[b]; ev[b] = g_stage_ev[b]; }
+  }
+  *bytes = HC_STAGE;
   return LITAP_OK;
 }
 

@@ -90,6 +90,13 @@ struct Ctx {
 };
 Ctx& ctx();
 int set_error(int code, const std::string& msg);
+// The library keeps process-wide state (pool, staging buffers, timings, the stream swap of *_flow_form) and is driven
+// by one host thread at a time; callers that release a global lock around foreign calls (ctypes does) could still
+// enter twice, so every extern "C" entry point takes this (recursive: entry points call each other) mutex.
+struct ApiLock {
+  ApiLock();
+  ~ApiLock();
+};
 int ensure_init();
 
 // litap_*_flow_form: the flow stages run on a high-priority stream of the library beside calc_form on the
@@ -98,8 +105,13 @@ int ensure_init();
 int flow_streams(cudaStream_t* hi, cudaEvent_t* fork, cudaEvent_t* join);  // api.cu (created on first use)
 struct StreamSwap {
   cudaStream_t keep;
+  bool joined = false;   // set once the join event is recorded; a scope left early (an error) drains the swapped-in
+                         // stream so that nothing is still running on it when scratch goes back to the pool
   explicit StreamSwap(cudaStream_t s) : keep(ctx().stream) { ctx().stream = s; }
-  ~StreamSwap() { ctx().stream = keep; }
+  ~StreamSwap() {
+    if (!joined) cudaStreamSynchronize(ctx().stream);
+    ctx().stream = keep;
+  }
 };
 
 // pooled device allocations (freed by litap_shutdown); zero = cudaMemsetAsync to 0
@@ -112,6 +124,7 @@ int h2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
 int hostcopy_flush();    // pageable destinations are complete after this
 void hostcopy_reset();   // start of a call: forget chunks a failed call left pending
 void hostcopy_forget_staging();
+int hostcopy_staging(int which, void* buf[2], cudaEvent_t ev[2], size_t* bytes);   // pinned pairs for file I/O (rasterio.cu)
 
 template <typename T>
 inline T* grid_alloc_array(const GridDims& d, int fill_byte) {
@@ -167,6 +180,10 @@ struct ProfScope {
     __VA_ARGS__;            \
     LAUNCH_CHECK();         \
   } while (0)
+
+struct ArrRef { const void* p; int esize; };
+ArrRef find_array_impl(litap_grid* g, const char* name);   // api.cu: result array of a grid by name
+ArrRef grid_find_array(litap_grid* g, const char* name);
 
 // ---- stage drivers (each enqueues on ctx().stream; host syncs only where stated) --------------
 int run_ddir(litap_grid* g, int invert);               // ddir.cu

@@ -1,0 +1,200 @@
+// rasterio.cu — big DEMs from and to disk without a tibble (first half).
+//
+// The reference loads rasters through raster::raster(file) %>% as.data.frame(xy = TRUE) (R/LITAP_load.R:187-192, the
+// ".flt" branch of load_file, :77-79), turns the missing value into NA (db_format, :194-213), wraps the grid in a ring of
+// NA (add_buffer, :273-332) and saves every stage as an .rds / .csv of the whole tibble (R/LITAP_read_write.R:8-66).
+// At 8192^2 and above those tibbles are what limits the size and the speed, so this file moves the raster the direct way:
+//
+//   litap_flt_info        parses the ESRI header (.hdr: ncols, nrows, xllcorner / xllcenter, yll*, cellsize,
+//                         NODATA_value, byteorder)
+//   litap_grid_read_flt   .flt (float32, row-major, north row first) -> a litap_grid: the file is read in chunks of whole
+//                         rows into two pinned buffers in turn, chunk j + 1 is read from disk while chunk j crosses PCIe
+//                         and k_flt_rows widens it to fp64 in place in the pitched elev array (NODATA / missing_value ->
+//                         NaN, optional byte swap); the NA ring is the grid's initial fill
+//   litap_grid_write_raw  one result of the grid (ring removed, like remove_buffer(), R/LITAP_load.R:334-340) as a
+//                         headerless little-endian binary in its own dtype (+ an ESRI-style .hdr that says which), or as
+//                         float32 .flt; the device rows travel through the download pair of pinned buffers while the
+//                         previous chunk is written to the file
+#include <algorithm>
+#include <cctype>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include "cellmath.h"
+#include "litap_internal.h"
+
+namespace {
+#define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
+
+std::string with_ext(const std::string& path, const char* ext) {
+  const size_t dot = path.find_last_of('.'), slash = path.find_last_of('/');
+  const bool has = dot != std::string::npos && (slash == std::string::npos || dot > slash);
+  return (has ? path.substr(0, dot) : path) + ext;
+}
+
+// rows [row0, row0 + nrows) of the raster, float32 in `src` (dense), -> elev rows 1 + row0 .. (ring offset), fp64
+__global__ void k_flt_rows(const float* __restrict__ src, double* __restrict__ elev, GridDims d, int row0, int nrows, int ncol,
+                           float nodata, float missing, int swap) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y;
+  if (c >= ncol || r >= nrows) return;
+  uint32_t b = reinterpret_cast<const uint32_t*>(src)[(size_t)r * ncol + c];
+  if (swap) b = __byte_perm(b, 0, 0x0123);
+  const float v = __uint_as_float(b);
+  double e = (double)v;
+  if (v != v || v == nodata || v == missing) e = __longlong_as_double(0x7ff8000000000000LL);
+  elev[(size_t)(1 + row0 + r) * d.pitch + 1 + c] = e;
+}
+
+// interior rows [row0, row0 + nrows) of a result -> dense buffer, optionally narrowed to float32
+template <typename T, typename O>
+__global__ void k_pack_rows(const T* __restrict__ a, O* __restrict__ dst, GridDims d, int row0, int nrows, int ncol) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y;
+  if (c >= ncol || r >= nrows) return;
+  dst[(size_t)r * ncol + c] = (O)a[(size_t)(1 + row0 + r) * d.pitch + 1 + c];
+}
+
+bool parse_hdr(FILE* f, litap_raster_info* o, std::string* err) {
+  char key[64], val[128];
+  bool have_nr = false, have_nc = false;
+  o->xll = o->yll = 0;
+  o->cellsize = 1;
+  o->nodata = -9999;
+  o->big_endian = 0;
+  while (fscanf(f, "%63s %127s", key, val) == 2) {
+    std::string k(key);
+    std::transform(k.begin(), k.end(), k.begin(), [](unsigned char ch) { return (char)std::tolower(ch); });
+    if (k == "ncols") { o->ncol = atoll(val); have_nc = true; }
+    else if (k == "nrows") { o->nrow = atoll(val); have_nr = true; }
+    else if (k == "xllcorner" || k == "xllcenter") o->xll = atof(val);
+    else if (k == "yllcorner" || k == "yllcenter") o->yll = atof(val);
+    else if (k == "cellsize") o->cellsize = atof(val);
+    else if (k == "nodata_value" || k == "nodata") o->nodata = atof(val);
+    else if (k == "byteorder") o->big_endian = (val[0] == 'M' || val[0] == 'm');
+  }
+  if (!have_nr || !have_nc || o->nrow < 1 || o->ncol < 1) { *err = "header lacks ncols / nrows"; return false; }
+  return true;
+}
+}  // namespace
+
+extern "C" int litap_flt_info(const char* path, litap_raster_info* out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
+  if (!path || !out) return set_error(LITAP_EARG, "litap_flt_info: NULL");
+  const std::string hdr = with_ext(path, ".hdr");
+  FILE* f = fopen(hdr.c_str(), "r");
+  if (!f) return set_error(LITAP_EARG, "litap_flt_info: cannot open " + hdr);
+  std::string err;
+  const bool ok = parse_hdr(f, out, &err);
+  fclose(f);
+  if (!ok) return set_error(LITAP_EARG, "litap_flt_info: " + hdr + ": " + err);
+  return LITAP_OK;
+}
+
+extern "C" int litap_grid_read_flt(const char* path, double missing_value, litap_grid** out, litap_raster_info* info_out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
+  if (!path || !out) return set_error(LITAP_EARG, "litap_grid_read_flt: NULL");
+  *out = nullptr;
+  litap_raster_info info;
+  RC(litap_flt_info(path, &info));
+  if (info_out) *info_out = info;
+  const std::string flt = with_ext(path, ".flt");
+  FILE* f = fopen(flt.c_str(), "rb");
+  if (!f) return set_error(LITAP_EARG, "litap_grid_read_flt: cannot open " + flt);
+  struct Closer { FILE* f; ~Closer() { if (f) fclose(f); } } closer{f};
+  litap_grid* g = nullptr;
+  RC(litap_grid_create(info.nrow + 2, info.ncol + 2, &g));   // elev starts as NaN everywhere: the NA ring of add_buffer()
+  struct Guard { litap_grid* g; ~Guard() { if (g) litap_grid_destroy(g); } } guard{g};
+  Ctx& c = ctx();
+  cudaStream_t st = c.stream;
+  void* buf[2];
+  cudaEvent_t ev[2];
+  size_t cap = 0;
+  RC(hostcopy_staging(0, buf, ev, &cap));
+  const size_t rowb = (size_t)info.ncol * 4;
+  if (rowb > cap) return set_error(LITAP_EARG, "litap_grid_read_flt: a raster row does not fit the staging buffer");
+  const int per = (int)std::min<size_t>(32768, std::max<size_t>(1, cap / rowb));   // rows are blocks of the grid's y dimension
+  PoolScratch S;
+  float* dev[2] = {S.get<float>((size_t)per * info.ncol), S.get<float>((size_t)per * info.ncol)};
+  if (!dev[0] || !dev[1]) return set_error(LITAP_ENOMEM, "device allocation failed (raster rows)");
+  int b = 0;
+  for (int64_t r = 0; r < info.nrow; r += per, b ^= 1) {
+    const int nr = (int)std::min<int64_t>(per, info.nrow - r);
+    CUDA_TRY(cudaEventSynchronize(ev[b]));   // the copy engine is done with this buffer (and the kernel with dev[b])
+    if (fread(buf[b], rowb, nr, f) != (size_t)nr)
+      return set_error(LITAP_EARG, "litap_grid_read_flt: " + flt + " is shorter than its header says");
+    CUDA_TRY(cudaMemcpyAsync(dev[b], buf[b], rowb * nr, cudaMemcpyHostToDevice, st));
+    dim3 grid((unsigned)((info.ncol + 255) / 256), (unsigned)nr);
+    KERNEL("k_flt_rows", k_flt_rows<<<grid, 256, 0, st>>>(dev[b], g->elev, g->d, (int)r, nr, (int)info.ncol, (float)info.nodata,
+                                                         (float)missing_value, info.big_endian));
+    CUDA_TRY(cudaEventRecord(ev[b], st));
+  }
+  CUDA_TRY(cudaStreamSynchronize(st));
+  guard.g = nullptr;
+  *out = g;
+  return LITAP_OK;
+}
+
+extern "C" int litap_grid_write_raw(litap_grid* g, const char* name, const char* path, int as_flt, const litap_raster_info* georef) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
+  if (!g || !name || !path) return set_error(LITAP_EARG, "litap_grid_write_raw: NULL");
+  const ArrRef a = grid_find_array(g, name);
+  if (!a.p) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: no such result on the grid: ") + name);
+  const GridDims d = g->d;
+  const int nrow = d.NR - 2, ncol = d.NC - 2;
+  const int osize = as_flt ? 4 : a.esize;
+  FILE* f = fopen(path, "wb");
+  if (!f) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: cannot create ") + path);
+  struct Closer { FILE* f; ~Closer() { if (f) fclose(f); } } closer{f};
+  Ctx& c = ctx();
+  cudaStream_t st = c.stream;
+  void* buf[2];
+  cudaEvent_t ev[2];
+  size_t cap = 0;
+  RC(hostcopy_staging(1, buf, ev, &cap));
+  const size_t rowb = (size_t)ncol * osize;
+  if (rowb > cap) return set_error(LITAP_EARG, "litap_grid_write_raw: a row does not fit the staging buffer");
+  const int per = (int)std::min<size_t>(32768, std::max<size_t>(1, cap / rowb));   // rows are blocks of the grid's y dimension
+  PoolScratch S;
+  char* dev[2] = {S.get<char>((size_t)per * rowb), S.get<char>((size_t)per * rowb)};
+  if (!dev[0] || !dev[1]) return set_error(LITAP_ENOMEM, "device allocation failed (raster rows)");
+  int pending_rows[2] = {0, 0};
+  auto drain = [&](int b) -> int {
+    if (!pending_rows[b]) return LITAP_OK;
+    CUDA_TRY(cudaEventSynchronize(ev[b]));
+    if (fwrite(buf[b], rowb, pending_rows[b], f) != (size_t)pending_rows[b])
+      return set_error(LITAP_EARG, std::string("litap_grid_write_raw: short write to ") + path);
+    pending_rows[b] = 0;
+    return LITAP_OK;
+  };
+  int b = 0;
+  for (int r = 0; r < nrow; r += per, b ^= 1) {
+    const int nr = std::min(per, nrow - r);
+    RC(drain(b));   // the chunk this buffer held goes to the file while the other buffer's chunk crosses PCIe
+    dim3 grid((unsigned)((ncol + 255) / 256), (unsigned)nr);
+    if (as_flt) {
+      if (a.esize == 8) KERNEL("k_pack_rows", k_pack_rows<<<grid, 256, 0, st>>>((const double*)a.p, (float*)dev[b], d, r, nr, ncol));
+      else if (a.esize == 4) KERNEL("k_pack_rows", k_pack_rows<<<grid, 256, 0, st>>>((const int32_t*)a.p, (float*)dev[b], d, r, nr, ncol));
+      else KERNEL("k_pack_rows", k_pack_rows<<<grid, 256, 0, st>>>((const uint8_t*)a.p, (float*)dev[b], d, r, nr, ncol));
+      CUDA_TRY(cudaMemcpyAsync(buf[b], dev[b], rowb * nr, cudaMemcpyDeviceToHost, st));
+    } else {   // own dtype: the copy engine strips the ring and the pitch
+      const char* src = (const char*)a.p + ((size_t)(1 + r) * d.pitch + 1) * a.esize;
+      CUDA_TRY(cudaMemcpy2DAsync(buf[b], rowb, src, (size_t)d.pitch * a.esize, rowb, nr, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaEventRecord(ev[b], st));
+    pending_rows[b] = nr;
+  }
+  RC(drain(b));
+  RC(drain(b ^ 1));
+  // header: what is in the file and where it lies
+  const std::string hdr = with_ext(path, ".hdr");
+  FILE* h = fopen(hdr.c_str(), "w");
+  if (!h) return set_error(LITAP_EARG, "litap_grid_write_raw: cannot create " + hdr);
+  const bool is_float = as_flt || a.esize == 8;
+  fprintf(h, "ncols %d\nnrows %d\nxllcorner %.10g\nyllcorner %.10g\ncellsize %.10g\nNODATA_value %s\nbyteorder LSBFIRST\n", ncol, nrow,
+          georef ? georef->xll : 0.0, georef ? georef->yll : 0.0, georef ? georef->cellsize : 1.0, is_float ? "nan" : "0");
+  fprintf(h, "nbits %d\npixeltype %s\nlayer %s\n", osize * 8, is_float ? "FLOAT" : (a.esize == 4 && !strcmp(name, "shed") ? "SIGNEDINT" : "UNSIGNEDINT"), name);
+  fclose(h);
+  return LITAP_OK;
+}

@@ -274,6 +274,7 @@ extern "C" int litap_relz(int64_t NR, int64_t NC, const double* elev, const uint
                           const int32_t* inv_local_shed, int64_t npond, const int32_t* pond_shedno,
                           const int32_t* pond_row, const int32_t* pond_col, const double* pond_elev, double str_val,
                           double ridge_val, double grid, double* const* out) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
   if (NR < 3 || NC < 3 || NR * NC > 0x7fffffffLL) return set_error(LITAP_EARG, "litap_relz: grid must be 3 x 3 .. 2^31 - 1 cells");
   if (!elev || !drec || !upslope || !fill_shed || !local_shed || !ielev || !iddir || !idrec || !iupslope || !inv_local_shed || !out)
     return set_error(LITAP_EARG, "litap_relz: NULL input array");

@@ -223,3 +223,17 @@ def test_signed_ld80_sum_equals_x87(cellmath):
         a, b = cellmath.host_lds_sum(t, len(t)), cellmath.host_real_ld_sum(t, len(t))
         nbad += (a != b) or (np.signbit(a) != np.signbit(b))
     assert nbad == 0
+
+
+def test_flt_header_parser_needs_no_device(tmp_path):
+    """litap_flt_info (the .hdr of an ESRI float raster, R/LITAP_load.R:77-79) is host code: it works without a GPU."""
+    import litap_b200 as lb
+    from litap_b200._lib import RasterInfo
+    p = tmp_path / "dem.hdr"
+    p.write_text("NCOLS 8192\nNROWS 4096\nXLLCORNER 12.5\nYLLCORNER -3\nCELLSIZE 2.5\nNODATA_VALUE -32768\nBYTEORDER MSBFIRST\n")
+    info = RasterInfo()
+    assert lb.lib().litap_flt_info(str(tmp_path / "dem.flt").encode(), C.byref(info)) == 0
+    assert info.asdict() == dict(nrow=4096, ncol=8192, xll=12.5, yll=-3.0, cellsize=2.5, nodata=-32768.0, big_endian=1)
+    (tmp_path / "bad.hdr").write_text("cellsize 1\n")
+    assert lb.lib().litap_flt_info(str(tmp_path / "bad.hdr").encode(), C.byref(info)) != 0
+    assert b"ncols" in lb.lib().litap_last_error()
