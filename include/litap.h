@@ -57,6 +57,7 @@ typedef struct litap_timings {
   float relz_ms;    /* calc_relz + calc_length (device part of litap_relz) */
   float uced_ms;    /* calc_upslopes(type = "uced") */
   int uced_ranges;  /* cell ranges the contributions were processed in (1 unless they exceed the memory budget) */
+  int host_syncs;   /* host waits on the device inside the stages since the last *_flow_form / stage call began */
   double uced_pairs; /* (head, cell below it) contributions = long double sums computed */
 } litap_timings;
 

@@ -39,7 +39,7 @@ class Timings(C.Structure):
                 ("total_ms", C.c_float), ("plateau_rounds", C.c_int), ("weti_queued", C.c_int),
                 ("flat_cells", C.c_int64),
                 ("patch_cells", C.c_int64), ("npits", C.c_int64), ("kernel_launches", C.c_int64),
-                ("gc_ms", C.c_float), ("relz_ms", C.c_float), ("uced_ms", C.c_float), ("uced_ranges", C.c_int),
+                ("gc_ms", C.c_float), ("relz_ms", C.c_float), ("uced_ms", C.c_float), ("uced_ranges", C.c_int), ("host_syncs", C.c_int),
                 ("uced_pairs", C.c_double)]
 
     def asdict(self):

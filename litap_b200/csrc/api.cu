@@ -311,6 +311,7 @@ extern "C" int litap_grid_flow_form(litap_grid* g, double grid_m, int invert) {
     if (rc0) return rc0;
   }
   const int64_t l0 = c.launches;
+  c.tm.host_syncs = 0;
   cudaStream_t user = c.stream;
   CUDA_TRY(cudaEventRecord(g_ev_fork, user));            // elev (upload / synth) is ordered on the caller's stream
   CUDA_TRY(cudaStreamWaitEvent(g_hi_stream, g_ev_fork, 0));

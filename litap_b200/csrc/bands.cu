@@ -225,7 +225,7 @@ int gather_words_host(litap_grid** B, int n, const std::vector<std::vector<unsig
   if (rc) return rc;
   all.resize((size_t)nwords * P);
   CUDA_TRY(cudaMemcpyAsync(all.data(), recv[0], all.size() * 8, cudaMemcpyDeviceToHost, ctx().stream));
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  STREAM_SYNC(ctx().stream);
   return LITAP_OK;
 }
 }  // namespace
@@ -262,7 +262,7 @@ extern "C" int litap_band_synth(litap_grid* g, uint32_t seed, double quant, int 
   if (rc) return rc;
   CUDA_TRY(cudaMemsetAsync(g->elev, 0xFF, (size_t)g->d.pitch * sizeof(double), ctx().stream));  // row 0 = NA
   g->have_ddir = g->have_shed = false;
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  STREAM_SYNC(ctx().stream);
   return LITAP_OK;
 }
 
@@ -275,7 +275,7 @@ extern "C" int litap_band_upload_rows(litap_grid* g, const double* rows) {
                              cudaMemcpyHostToDevice, ctx().stream));
   CUDA_TRY(cudaMemsetAsync(g->elev, 0xFF, (size_t)d.pitch * sizeof(double), ctx().stream));
   g->have_ddir = g->have_shed = false;
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  STREAM_SYNC(ctx().stream);
   return LITAP_OK;
 }
 
@@ -290,7 +290,7 @@ extern "C" int litap_band_upload_elev(litap_grid* g, const double* elev_full) {
                              cudaMemcpyHostToDevice, ctx().stream));
   CUDA_TRY(cudaMemsetAsync(g->elev, 0xFF, (size_t)d.pitch * sizeof(double), ctx().stream));
   g->have_ddir = g->have_shed = false;
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  STREAM_SYNC(ctx().stream);
   return LITAP_OK;
 }
 
@@ -353,48 +353,61 @@ extern "C" int litap_bands_ddir(litap_grid** B, int n, int invert) {
 
   // plateau rounds: probe everywhere (reads the previous round), apply everywhere, exchange the
   // boundary rows, stop when no band changed anything
+  // The rounds keep their Jacobi semantics (every round ends with the halo rows exchanged, in stream order), but the
+  // "did anything change" flags are only looked at every KR rounds: one all-gather + host read-back per batch instead
+  // of per round.  A round after the fixed point changes nothing, so running up to KR - 1 of them is harmless.
+  constexpr int KR = 3;
   std::vector<void*> fsend(n), frecv(n);
   for (int i = 0; i < n; ++i) {
-    fsend[i] = S.get<unsigned long long>(1);
-    frecv[i] = S.get<unsigned long long>(P);
+    fsend[i] = S.get<unsigned long long>(KR);
+    frecv[i] = S.get<unsigned long long>((size_t)KR * P);
     if (!fsend[i] || !frecv[i]) return set_error(LITAP_ENOMEM, "device allocation failed (round flags)");
   }
   int rounds = 0;
-  std::vector<unsigned long long> flags(P);
-  while (true) {
-    for (int i = 0; i < n; ++i) {
-      CUDA_TRY(cudaMemsetAsync(fsend[i], 0, 8, st));
-      if ((rc = ddir_band_probe(B[i], (unsigned)nflat[i], (unsigned*)fsend[i]))) return rc;
+  std::vector<unsigned long long> flags((size_t)KR * P);
+  for (bool open = true; open;) {
+    for (int i = 0; i < n; ++i) CUDA_TRY(cudaMemsetAsync(fsend[i], 0, 8 * KR, st));
+    for (int k = 0; k < KR; ++k) {
+      for (int i = 0; i < n; ++i)
+        if ((rc = ddir_band_probe(B[i], (unsigned)nflat[i], (unsigned*)((unsigned long long*)fsend[i] + k)))) return rc;
+      for (int i = 0; i < n; ++i)
+        if ((rc = ddir_band_apply(B[i], (unsigned)nflat[i]))) return rc;
+      if ((rc = halo_exchange(B, n, &litap_grid::ddir))) return rc;
     }
-    for (int i = 0; i < n; ++i)
-      if ((rc = ddir_band_apply(B[i], (unsigned)nflat[i]))) return rc;
-    if ((rc = halo_exchange(B, n, &litap_grid::ddir))) return rc;
-    if ((rc = all_gather(B, n, fsend.data(), frecv.data(), 8))) return rc;
-    CUDA_TRY(cudaMemcpyAsync(flags.data(), frecv[0], (size_t)P * 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
-    bool any = false;
-    for (int b = 0; b < P; ++b) any |= flags[b] != 0;
-    if (!any) break;
-    ++rounds;
+    if ((rc = all_gather(B, n, fsend.data(), frecv.data(), 8 * KR))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(flags.data(), frecv[0], (size_t)KR * P * 8, cudaMemcpyDeviceToHost, st));
+    STREAM_SYNC(st);
+    for (int k = 0; k < KR && open; ++k) {
+      bool any = false;
+      for (int b = 0; b < P; ++b) any |= flags[(size_t)b * KR + k] != 0;
+      if (any) ++rounds; else open = false;
+    }
   }
 
   // flat-pit patches: every band marks its own patch cells; all bands resolve all patches
-  std::vector<std::vector<unsigned long long>> mine(n, std::vector<unsigned long long>(1));
+  std::vector<std::vector<unsigned long long>> mine(n, std::vector<unsigned long long>(2));
   for (int i = 0; i < n; ++i)
     if ((rc = ddir_band_mark(B[i]))) return rc;
   for (int i = 0; i < n; ++i) {
     unsigned np = 0;
     if ((rc = ddir_band_counts(B[i], nullptr, &np))) return rc;
     mine[i][0] = np;
+    mine[i][1] = nflat[i];   // travels along: calc_shed4 sizes the global pit table from it without a gather of its own
   }
-  std::vector<unsigned long long> counts;
-  if ((rc = gather_words_host(B, n, mine, 1, counts))) return rc;
-  unsigned long long total = 0, mx = 0, flat_total = 0;
-  for (int b = 0; b < P; ++b) { total += counts[b]; mx = std::max(mx, counts[b]); }
+  std::vector<unsigned long long> both, counts(P);
+  if ((rc = gather_words_host(B, n, mine, 2, both))) return rc;
+  unsigned long long total = 0, mx = 0, flat_total = 0, flat_max = 0;
+  for (int b = 0; b < P; ++b) {
+    counts[b] = both[2 * b];
+    total += counts[b];
+    mx = std::max(mx, counts[b]);
+    flat_max = std::max(flat_max, both[2 * b + 1]);
+  }
   for (int i = 0; i < n; ++i) {
     flat_total += nflat[i];
     // pits of the band in calc_shed4: own cells that stay flat + one portal per halo cell
     B[i]->pit_bound = (int64_t)nflat[i] + 2 * (int64_t)B[i]->d.NC;
+    B[i]->pit_bound_all = (int64_t)flat_max + 2 * (int64_t)B[i]->d.NC;   // the same bound for the largest band
   }
   if (total) {
     std::vector<void*> ksend(n), krecv(n);
@@ -423,7 +436,7 @@ extern "C" int litap_bands_ddir(litap_grid** B, int n, int invert) {
     }
   }
   cudaEventRecord(c.ev[1], st);
-  CUDA_TRY(cudaStreamSynchronize(st));
+  STREAM_SYNC(st);
   cudaEventElapsedTime(&c.tm.ddir_ms, c.ev[0], c.ev[1]);
   c.tm.plateau_rounds = rounds;
   c.tm.flat_cells = (int64_t)flat_total;  // of the bands of this process
@@ -444,7 +457,7 @@ extern "C" int litap_bands_form(litap_grid** B, int n, double grid_m) {
   for (int i = 0; i < n; ++i)
     if ((rc = run_form(B[i], grid_m))) return rc;
   cudaEventRecord(c.ev[5], c.stream);
-  CUDA_TRY(cudaStreamSynchronize(c.stream));
+  STREAM_SYNC(c.stream);
   cudaEventElapsedTime(&c.tm.form_ms, c.ev[4], c.ev[5]);
   c.tm.kernel_launches = c.launches - l0;
   return LITAP_OK;
@@ -466,6 +479,7 @@ extern "C" int litap_bands_flow_form(litap_grid** B, int n, double grid_m, int i
   if ((rc = flow_streams(&hi, &fork, &join))) return rc;
   cudaStream_t user = c.stream;
   const int64_t l0 = c.launches;
+  c.tm.host_syncs = 0;
   CUDA_TRY(cudaEventRecord(fork, user));
   CUDA_TRY(cudaStreamWaitEvent(hi, fork, 0));
   CUDA_TRY(cudaEventRecord(c.ev[4], user));
@@ -484,7 +498,7 @@ extern "C" int litap_bands_flow_form(litap_grid** B, int n, double grid_m, int i
     sw.joined = true;
   }
   CUDA_TRY(cudaStreamWaitEvent(user, join, 0));
-  CUDA_TRY(cudaStreamSynchronize(user));
+  STREAM_SYNC(user);
   cudaEventElapsedTime(&c.tm.form_ms, c.ev[4], c.ev[5]);
   c.tm.kernel_launches = c.launches - l0;
   return LITAP_OK;
@@ -838,7 +852,7 @@ extern "C" int litap_grid_conservation(litap_grid* g, uint64_t* cells, uint64_t*
   if (rc) return rc;
   unsigned long long h[2];
   CUDA_TRY(cudaMemcpyAsync(h, o, 16, cudaMemcpyDeviceToHost, ctx().stream));
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  STREAM_SYNC(ctx().stream);
   *cells = h[0];
   *pit_upslope = h[1];
   return LITAP_OK;
@@ -865,12 +879,20 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
     KERNEL("k_band_portals", k_band_portals<<<cblk, 256, 0, st>>>(g->ddir, g->elev, g->d, g->halo_top, g->halo_bot));
     if ((rc = shed_phase_local(g, W[i]))) return rc;
   }
-  std::vector<std::vector<unsigned long long>> mine(n, std::vector<unsigned long long>(1));
-  for (int i = 0; i < n; ++i) mine[i][0] = W[i].npits;
-  std::vector<unsigned long long> np_all;
-  if ((rc = gather_words_host(B, n, mine, 1, np_all))) return rc;
+  // slots per band in the global pit table: the largest pit count of any band -- or, when calc_ddir2 ran on these
+  // bands, its bound on that (flat cells of the D8 stencil + portals), which saves a gather + host round trip
   unsigned long long stride64 = 1;
-  for (int b = 0; b < P; ++b) stride64 = std::max(stride64, np_all[b]);
+  bool bounded = true;
+  for (int i = 0; i < n; ++i) bounded = bounded && B[i]->pit_bound_all > 0;   // the same answer on every rank
+  if (bounded) {
+    stride64 = (unsigned long long)B[0]->pit_bound_all;
+  } else {
+    std::vector<std::vector<unsigned long long>> mine(n, std::vector<unsigned long long>(1));
+    for (int i = 0; i < n; ++i) mine[i][0] = W[i].npits;
+    std::vector<unsigned long long> np_all;
+    if ((rc = gather_words_host(B, n, mine, 1, np_all))) return rc;
+    for (int b = 0; b < P; ++b) stride64 = std::max(stride64, np_all[b]);
+  }
   if (stride64 * (unsigned long long)P >= 0x7FFFFFFFull)
     return set_error(LITAP_EARG, "litap_bands_shed: too many pits for 31-bit pit numbers");
   const unsigned stride = (unsigned)stride64;
@@ -947,12 +969,14 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
     KERNEL("k_bg_build", k_bg_build<<<blk(Nn), 256, 0, st>>>((const char*)rrecv[i], rec, P, NC, G));
     unsigned* flag = reinterpret_cast<unsigned*>(cnt + 1);
     bool open = true;
-    for (int round = 0; round < 64 && open; ++round) {
-      CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
-      KERNEL("k_bg_resolve", k_bg_resolve<<<blk(Nn), 256, 0, st>>>(G.jres, Nn, flag));
+    for (int round = 0; round < 64 && open; round += 4) {   // four doubling rounds per look at the flag (a round on a resolved graph is a no-op)
+      for (int k = 0; k < 4; ++k) {
+        if (k == 3) CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+        KERNEL("k_bg_resolve", k_bg_resolve<<<blk(Nn), 256, 0, st>>>(G.jres, Nn, flag));
+      }
       unsigned h = 0;
       CUDA_TRY(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, st));
-      CUDA_TRY(cudaStreamSynchronize(st));
+      STREAM_SYNC(st);
       open = h != 0;
     }
     if (open) KERNEL("k_bg_close", k_bg_close<<<blk(Nn), 256, 0, st>>>(G.jres, Nn));
@@ -990,7 +1014,7 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
       KERNEL("k_band_ring_row", k_band_ring_row<<<cblk, 256, 0, st>>>(g->d, g->own_lo - 1, g->shed, g->upslope, g->ridge));
   }
   cudaEventRecord(c.ev[3], st);
-  CUDA_TRY(cudaStreamSynchronize(st));
+  STREAM_SYNC(st);
   cudaEventElapsedTime(&c.tm.shed_ms, c.ev[2], c.ev[3]);
   // upslope is a 32-bit count (include/litap.h): a DEM of 2^32 or more cells (65536 x 65536 is exactly 2^32) could hold a
   // basin whose count wraps.  A wrapped count also wraps at the basin's pit, and then the pit counts no longer add up to

@@ -467,7 +467,7 @@ int run_ddir(litap_grid* g, int invert) {
     KERNEL("k_patch_mark", k_patch_mark<<<c.sm_count * 4, 256, 0, st>>>(g->dd_list, (unsigned long long)g->dd_cap, g->ddir,
                                                                        d, g->row_off, g->dd_keys, ctr));
     CUDA_TRY(cudaMemcpyAsync(&h, ctr, sizeof(h), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    STREAM_SYNC(st);
     if (h.nflat <= g->dd_cap) break;
     if (attempt) return set_error(LITAP_ECUDA, "internal: flat worklist overflow after regrowth");
     rc = ddir_ensure(g, (size_t)h.nflat + 4096);  // unusually flat DEM: regrow the worklist and redo
@@ -485,7 +485,7 @@ int run_ddir(litap_grid* g, int invert) {
     if (rc) return rc;
     KERNEL("k_patch_apply", k_patch_apply<<<nblk(h.npatch), 256, 0, st>>>(K, nd, h.npatch, g->ddir, d, g->row_off,
                                                                          g->own_lo, g->own_hi));
-    CUDA_TRY(cudaStreamSynchronize(st));  // scratch goes back to the pool
+    STREAM_SYNC(st);  // scratch goes back to the pool
   }
   return LITAP_OK;
 }
@@ -504,7 +504,7 @@ int ddir_band_begin(litap_grid* g) {
 int ddir_band_counts(litap_grid* g, unsigned long long* nflat, unsigned* npatch) {
   DdirCounters h;
   CUDA_TRY(cudaMemcpyAsync(&h, g->dd_ctr, sizeof(h), cudaMemcpyDeviceToHost, ctx().stream));
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+  STREAM_SYNC(ctx().stream);
   if (nflat) *nflat = h.nflat;
   if (npatch) *npatch = h.npatch;
   return LITAP_OK;

@@ -68,6 +68,7 @@ struct litap_grid {
   // row band of a larger DEM (bands.cu): nbands == 0 for a whole DEM
   int band = 0, nbands = 0;
   long long gnr = 0;                        // rows of the whole DEM
+  int64_t pit_bound_all = -1;               // the same bound for the band with the most flat cells (all bands agree on it)
   int64_t pit_bound = -1;                   // >= number of pits of the ddir on the grid (flat cells of the D8 stencil), -1 unknown
   int edge_top_row = -1, edge_bot_row = -1; // local row holding the first / last DEM row, -1 if not in this grid
   // calc_ddir2 worklists (ddir.cu)
@@ -157,6 +158,12 @@ struct PoolScratch {
     cudaError_t _e = (expr);                                                                \
     if (_e != cudaSuccess)                                                                  \
       return set_error(LITAP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));    \
+  } while (0)
+// a host wait on the stream inside a stage (counted: litap_timings.host_syncs)
+#define STREAM_SYNC(st)                        \
+  do {                                         \
+    CUDA_TRY(cudaStreamSynchronize(st));       \
+    ++ctx().tm.host_syncs;                     \
   } while (0)
 #define LAUNCH_CHECK()                                                                      \
   do {                                                                                      \

@@ -496,7 +496,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
     KERNEL("k_count_pits", k_count_pits<<<grid, 256, 0, st>>>(g->ddir, d, counters));
     unsigned long long npits64 = 0;
     CUDA_TRY(cudaMemcpyAsync(&npits64, counters, 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    STREAM_SYNC(st);
     np = npits64 ? (size_t)npits64 : 1;
   }
 
@@ -545,7 +545,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
       KERNEL("k_l2_resolve", k_l2_resolve<<<sblk, 256, 0, st>>>(tg, l2.jres, nslots, flag));
     }
     CUDA_TRY(cudaMemcpyAsync(hb, counters + 1, 16, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    STREAM_SYNC(st);
     open = (unsigned)(hb[1] & 0xFFFFFFFFull) != 0;
   }
   const unsigned npits = W.npits = (unsigned)hb[0];
@@ -623,6 +623,6 @@ int run_shed(litap_grid* g) {
   if (rc) return rc;
   rc = shed_phase_final(g, W, shed::BandSeeds());
   if (rc) return rc;
-  CUDA_TRY(cudaStreamSynchronize(ctx().stream));  // scratch is returned to the pool when W dies
+  STREAM_SYNC(ctx().stream);  // scratch is returned to the pool when W dies
   return LITAP_OK;
 }
