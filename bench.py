@@ -492,7 +492,7 @@ def run_ours(a):
     if world > 1:
         g.close()
         lb.lib().litap_pool_trim()
-        fits = (gnr + 2) * (((ncols + 2 + 31 + 31) // 32) * 32) < 2 ** 31 and gnr * ncols * 130 < 170e9
+        fits = (gnr + 2) * (((ncols + 2 + 31 + 31) // 32) * 32) < 2 ** 31 and gnr + 2 <= 65535 and gnr * ncols * 130 < 170e9
         if rank == 0 and fits and not a.no_whole:
             t0 = time.perf_counter()
             w = lb.DeviceGrid(gnr + 2, ncols + 2)

@@ -57,6 +57,7 @@ typedef struct litap_timings {
   float relz_ms;    /* calc_relz + calc_length (device part of litap_relz) */
   float uced_ms;    /* calc_upslopes(type = "uced") */
   int uced_ranges;  /* cell ranges the contributions were processed in (1 unless they exceed the memory budget) */
+  float pitstat_ms; /* pit_stat1 (device part of litap_pit_stat) */
   int host_syncs;   /* host waits on the device inside the stages since the last *_flow_form / stage call began */
   double uced_pairs; /* (head, cell below it) contributions = long double sums computed */
 } litap_timings;
@@ -103,6 +104,20 @@ int litap_weti(const double* elev, const uint8_t* ddir, const uint32_t* upslope,
  * uced: NaN = NA (cells without a shed, pits nothing flows into).  Bit-identical with the reference's
  * long double sum() per track and its order of additions. */
 int litap_uced(const double* elev, const uint8_t* ddir, const int32_t* shed, int64_t NR, int64_t NC, double* uced);
+
+/* pit_stat1(db, shed = ..., method)  R/flow_03_pit_stat_fast.R:1-162 (flow_mapper: R/flow_mapper.R:181,222,378,416; pit
+ * removal: R/flow_04_remove_pit_fast.R:19,44,90,136,240,270): the pour point of every shed (lowest ridge cell / neighbour
+ * pair that tips into another shed) and the statistics of its pit.  shed = the column named by `shed` (0 = NA); ridge as
+ * returned by litap_shed (1 = ridge cell); edge_map 0 / 1; method 0 = "litap", 1 = "landmapr".
+ * out[k] (k < 21, may be NULL) receives column litap_pit_stat_names()[k] -- shedno shed_area edge_pit pit_area pit_vol
+ * pit_elev pit_seqno pit_row pit_col pre_vol varatio in_seqno in_row in_col in_elev out_seqno out_row out_col out_elev
+ * drains_to pour_elev, seqno / row / col in the buffered grid's 1-based numbering, NaN = NA --, one row per shed with
+ * a pour point in shedno order, at most cap rows; *nrows = rows of the table.  pit_vol is R's long double sum() in
+ * the reference's row order. */
+int litap_pit_stat(const double* elev, const uint8_t* ddir, const int32_t* shed, const uint32_t* upslope,
+                   const uint8_t* ridge, const uint8_t* edge_map, int64_t NR, int64_t NC, int method,
+                   int64_t cap, double* const* out, int64_t* nrows);
+const char* const* litap_pit_stat_names(int* n);
 
 /* slope_gc: gradients towards east / north with their zero signs settled, magnitudes (0 -> 0.00001),
  * row / column curvatures, hillslope run labels per row and per column.  f64 outputs NaN = NA;

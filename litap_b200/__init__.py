@@ -15,6 +15,7 @@ from .api import (  # noqa: F401
     calc_shed4,
     calc_upslopes,
     calc_weti2,
+    pit_stat1,
     slope_gc,
     flow_form,
     invert,

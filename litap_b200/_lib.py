@@ -13,7 +13,7 @@ SYMBOLS = [
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
     "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_uced", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
-    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_flt_info", "litap_grid_read_flt", "litap_grid_write_raw", "litap_grid_slope_gc", "litap_grid_flow_form",
+    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_pit_stat", "litap_pit_stat_names", "litap_flt_info", "litap_grid_read_flt", "litap_grid_write_raw", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
@@ -39,7 +39,7 @@ class Timings(C.Structure):
                 ("total_ms", C.c_float), ("plateau_rounds", C.c_int), ("weti_queued", C.c_int),
                 ("flat_cells", C.c_int64),
                 ("patch_cells", C.c_int64), ("npits", C.c_int64), ("kernel_launches", C.c_int64),
-                ("gc_ms", C.c_float), ("relz_ms", C.c_float), ("uced_ms", C.c_float), ("uced_ranges", C.c_int), ("host_syncs", C.c_int),
+                ("gc_ms", C.c_float), ("relz_ms", C.c_float), ("uced_ms", C.c_float), ("uced_ranges", C.c_int), ("pitstat_ms", C.c_float), ("host_syncs", C.c_int),
                 ("uced_pairs", C.c_double)]
 
     def asdict(self):
@@ -58,6 +58,9 @@ def load():
     vp, i64, dbl, ci = C.c_void_p, C.c_int64, C.c_double, C.c_int
     L.litap_init.argtypes = [ci]
     L.litap_shutdown.restype = None
+    L.litap_pit_stat.argtypes = [vp] * 6 + [i64, i64, C.c_int, i64, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    L.litap_pit_stat_names.restype = C.POINTER(C.c_char_p)
+    L.litap_pit_stat_names.argtypes = [C.POINTER(C.c_int)]
     L.litap_flt_info.argtypes = [C.c_char_p, C.POINTER(RasterInfo)]
     L.litap_grid_read_flt.argtypes = [C.c_char_p, C.c_double, C.POINTER(C.c_void_p), C.POINTER(RasterInfo)]
     L.litap_grid_write_raw.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(RasterInfo)]

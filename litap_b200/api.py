@@ -150,6 +150,37 @@ def calc_upslopes(db, type="uced"):
     return out
 
 
+def pit_stat_names():
+    n = C.c_int(0)
+    p = lib().litap_pit_stat_names(C.byref(n))
+    return tuple(p[i].decode() for i in range(n.value))
+
+
+def pit_stat1(db, w=None, shed="shedno", method="landmapr", verbose=False):
+    """R/flow_03_pit_stat_fast.R:1-162.  Needs elev, ddir, upslope, ridge, edge_map and the column named by `shed`;
+    returns the stats table as a dict of columns (one row per shed with a pour point, in shedno order; seqno / row /
+    col in the buffered grid's numbering).  w (a subset of sheds) filters the rows like the reference does."""
+    NR, NC = _dims(db)
+    e = _f64(db["elev"])
+    d = _ddir_u8(db["ddir_u8"] if "ddir_u8" in db else db["ddir"])
+    s = _i32_na0(db[shed])
+    u = np.ascontiguousarray(np.nan_to_num(np.asarray(db["upslope"], dtype=np.float64), nan=0.0), dtype=np.uint32)
+    r = np.ascontiguousarray(np.nan_to_num(np.asarray(db["ridge"], dtype=np.float64), nan=2.0), dtype=np.uint8)
+    g = np.ascontiguousarray(np.nan_to_num(np.asarray(db["edge_map"], dtype=np.float64), nan=0.0), dtype=np.uint8)
+    names = pit_stat_names()
+    cap = max(1, int(np.unique(s[s > 0]).size))
+    out = {k: np.full(cap, np.nan) for k in names}
+    ptrs = (C.c_void_p * len(names))(*[out[k].ctypes.data for k in names])
+    n = C.c_int64(0)
+    check(lib().litap_pit_stat(e.ctypes.data, d.ctypes.data, s.ctypes.data, u.ctypes.data, r.ctypes.data, g.ctypes.data,
+                               NR, NC, {"litap": 0, "landmapr": 1}[method], cap, ptrs, C.byref(n)))
+    out = {k: v[:n.value] for k, v in out.items()}
+    if w is not None:
+        keep = np.isin(out["shedno"], np.asarray(list(w), dtype=np.float64))
+        out = {k: v[keep] for k, v in out.items()}
+    return out
+
+
 def calc_form(db, grid, verbose=False):
     """R/form_01_calc_form.R:4-67.  Returns seqno,row,col,slope_pct,slope_deg,aspect,prof,plan,buffer."""
     NR, NC = _dims(db)

@@ -124,8 +124,8 @@ extern "C" int litap_grid_create(int64_t NR, int64_t NC, litap_grid** out) {
   *out = nullptr;
   if (NR < 3 || NC < 3) return set_error(LITAP_EARG, "grid must be at least 3 x 3 buffered cells (1 x 1 DEM + NA ring)");
   GridDims d = make_dims(NR, NC);
-  if ((double)NR * d.pitch >= 2147483648.0)
-    return set_error(LITAP_EARG, "grid too large for one device: NR*pitch must be < 2^31 cells; shard into row bands");
+  if ((double)NR * d.pitch >= 2147483648.0 || NR > 65535)   // cell ids are 31-bit; rows are the y dimension of most launches
+    return set_error(LITAP_EARG, "grid too large for one device: NR*pitch must be < 2^31 cells and NR <= 65535; shard into row bands");
   int rc = ensure_init();
   if (rc) return rc;
   litap_grid* g = new litap_grid();

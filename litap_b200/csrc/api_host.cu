@@ -248,6 +248,43 @@ extern "C" int litap_uced(const double* elev, const uint8_t* ddir, const int32_t
   return LITAP_OK;
 }
 
+extern "C" int litap_pit_stat(const double* elev, const uint8_t* ddir, const int32_t* shed, const uint32_t* upslope,
+                              const uint8_t* ridge, const uint8_t* edge_map, int64_t NR, int64_t NC, int method, int64_t cap,
+                              double* const* out, int64_t* nrows) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
+  Wall w;
+  GridGuard gg;
+  if (!ddir || !shed || !upslope || !ridge || !edge_map || !out || !nrows) return set_error(LITAP_EARG, "litap_pit_stat: NULL argument");
+  if (method != 0 && method != 1) return set_error(LITAP_EARG, "litap_pit_stat: method must be 0 (litap) or 1 (landmapr)");
+  RC(begin_call(NR, NC, elev, gg));
+  litap_grid* g = gg.g;
+  Ctx& c = ctx();
+  int64_t l0 = c.launches;
+  g->ddir = grid_alloc_array<uint8_t>(g->d, 0);
+  g->shed = grid_alloc_array<int32_t>(g->d, 0);
+  g->upslope = grid_alloc_array<uint32_t>(g->d, 0);
+  g->ridge = grid_alloc_array<uint8_t>(g->d, 0);
+  uint8_t* edge = grid_alloc_array<uint8_t>(g->d, 0);
+  struct EdgeFree { uint8_t* p; ~EdgeFree() { grid_free_array(p); } } ef{edge};
+  if (!g->ddir || !g->shed || !g->upslope || !g->ridge || !edge) return set_error(LITAP_ENOMEM, "device allocation failed (pit_stat inputs)");
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  RC(up(g->elev, g->d, elev));
+  RC(up(g->ddir, g->d, ddir));
+  RC(up(g->shed, g->d, shed));
+  RC(up(g->upslope, g->d, upslope));
+  RC(up(g->ridge, g->d, ridge));
+  RC(up(edge, g->d, edge_map));
+  RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  RC(run_pit_stat(g, edge, method, cap, out, nrows));
+  CUDA_TRY(cudaEventRecord(c.ev[7], c.stream));
+  CUDA_TRY(cudaEventSynchronize(c.ev[7]));
+  cudaEventElapsedTime(&c.tm.pitstat_ms, c.ev[6], c.ev[7]);
+  c.tm.kernel_launches = c.launches - l0;
+  c.tm.total_ms = w.ms();
+  return LITAP_OK;
+}
+
 extern "C" int litap_slope_gc(const double* elev, int64_t NR, int64_t NC, double grid, double* sgre, double* sgr,
                               double* sgcn, double* sgc, double* scr, double* scc, uint8_t* hill_r_dir,
                               uint8_t* hill_c_dir, int32_t* hill_r_n, int32_t* hill_r_cell, int32_t* hill_c_n,

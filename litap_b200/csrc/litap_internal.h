@@ -200,6 +200,7 @@ int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi);  // for
 void form_forget_trig();                               // form.cu (pool-owned table dropped at shutdown)
 int run_weti(litap_grid* g, double grid_m);            // weti.cu
 int run_uced(litap_grid* g);                           // uced.cu
+int run_pit_stat(litap_grid* g, const uint8_t* edge, int method, int64_t cap, double* const* out, int64_t* nrows);  // pitstat.cu
 int run_slope_gc(litap_grid* g, double grid_m);        // gc.cu
 int run_synth(litap_grid* g, int64_t row0, int64_t gnr, uint32_t seed, double quant, int na_permille);  // synth.cu
 int run_checksum(const void* arr, int elem_size, const GridDims& d, uint64_t* out);                     // synth.cu

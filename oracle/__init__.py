@@ -44,6 +44,8 @@ def lib():
                                    C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                    C.c_double, C.POINTER(C.c_void_p)])
         L.oracle_uced.argtypes = [_f64p, _u8p, _i32p, C.c_int64, C.c_int64, _f64p, C.POINTER(C.c_int64)]
+        L.oracle_pit_stat.argtypes = [_f64p, _u8p, _i32p, _i64p, _u8p, _u8p, C.c_int64, C.c_int64, C.c_int, C.c_int64,
+                                      C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.oracle_r_round.argtypes = [C.c_double, C.c_int]
         L.oracle_r_round.restype = C.c_double
         L.oracle_synth_dem.argtypes = [_f64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_uint32,
@@ -127,6 +129,27 @@ def uced(elev_b, ddir_b, shed_b):
     lib().oracle_uced(e, d, s, e.shape[0], e.shape[1], out, C.byref(w))
     uced.work = w.value
     return out
+
+
+PITSTAT_NAMES = ("shedno", "shed_area", "edge_pit", "pit_area", "pit_vol", "pit_elev", "pit_seqno", "pit_row", "pit_col",
+                 "pre_vol", "varatio", "in_seqno", "in_row", "in_col", "in_elev", "out_seqno", "out_row", "out_col", "out_elev",
+                 "drains_to", "pour_elev")
+
+
+def pit_stat(elev_b, ddir_b, shed_b, upslope_b, ridge_b, edge_b, method="landmapr"):
+    """pit_stat1 on buffered grids (R/flow_03_pit_stat_fast.R:1-162) -> dict of PITSTAT_NAMES columns (rows in shedno order)."""
+    e = np.ascontiguousarray(elev_b, dtype=np.float64)
+    d = np.ascontiguousarray(ddir_b, dtype=np.uint8)
+    s = np.ascontiguousarray(shed_b, dtype=np.int32)
+    u = np.ascontiguousarray(upslope_b, dtype=np.int64)
+    r = np.ascontiguousarray(ridge_b, dtype=np.uint8)
+    g = np.ascontiguousarray(edge_b, dtype=np.uint8)
+    cap = max(1, len(np.unique(s[s > 0])))
+    out = {k: np.full(cap, np.nan) for k in PITSTAT_NAMES}
+    ptrs = (C.c_void_p * len(PITSTAT_NAMES))(*[out[k].ctypes.data for k in PITSTAT_NAMES])
+    n = C.c_int64(0)
+    lib().oracle_pit_stat(e, d, s, u, r, g, e.shape[0], e.shape[1], {"litap": 0, "landmapr": 1}[method], cap, ptrs, C.byref(n))
+    return {k: v[:n.value] for k, v in out.items()}
 
 
 GC_F64 = ("sgre", "sgr", "sgcn", "sgc", "scr", "scc")

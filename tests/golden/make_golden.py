@@ -186,7 +186,7 @@ def main():
     # ---- shipped full-grid run (grid=5, max_area=1, max_depth=0.1)
     for name, rel in (("dem_fill", "flow/dem_fill.rds"), ("dem_inverted", "flow/dem_inverted.rds"),
                       ("dem_form", "form/dem_form.rds"), ("dem_length", "form/dem_length.rds"),
-                      ("stats_pond", "flow/stats_pond.rds")):
+                      ("stats_pond", "flow/stats_pond.rds"), ("stats_inverted", "flow/stats_inverted.rds")):
         df = read_rds(f"{REF}/inst/extdata/testELEV/{rel}")
         cols = {n: col_to_f64(v) for n, v in df.items() if isinstance(v, np.ndarray)}
         np.savez_compressed(f"{OUT}/{name}.npz", **cols)

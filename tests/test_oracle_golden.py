@@ -293,3 +293,26 @@ def side_columns(shed, drec1):
     ok = drec1 > 0
     ds[ok] = seq_shed[drec1[ok] - 1]
     return seq_shed, ds
+
+
+def test_pit_stat_oracle_reproduces_stats_inverted(golden):
+    """pit_stat1 (R/flow_03_pit_stat_fast.R:1-162): the shipped flow/stats_inverted.rds is a plain pit_stat1 table
+    (method "landmapr", the default) of flow/dem_inverted.rds: 8 sheds x 20 columns, exact doubles (pit_vol and varatio
+    include R's long double sum)."""
+    import pitstat_fixture as pf
+    i = pf.inverted_inputs(golden)
+    t = oracle.pit_stat(i["elev"], i["ddir"], i["shed"], i["upslope"], i["ridge"], i["edge_map"], "landmapr")
+    pf.assert_equals_golden(t, golden)
+    # method "litap" (the lowest neighbour instead of LandMapR's last one) picks the same pour points on this DEM and keeps
+    # the cell LandMapR omits
+    t2 = oracle.pit_stat(i["elev"], i["ddir"], i["shed"], i["upslope"], i["ridge"], i["edge_map"], "litap")
+    assert (t2["in_seqno"] == t["in_seqno"]).all() and (t2["pit_area"] >= t["pit_area"]).all()
+
+
+def test_pit_stat_oracle_single_shed():
+    e = oracle.add_buffer(np.array([[3., 2, 3], [2, 1, 2], [3, 2, 3]]))
+    d = oracle.ddir(e)["ddir"]
+    s = oracle.shed(e, d)
+    t = oracle.pit_stat(e, d, s["shed"], s["upslope"], s["ridge"], np.zeros_like(d), "litap")
+    assert len(t["shedno"]) == 1 and t["shedno"][0] == 1 and t["pit_elev"][0] == 1 and t["pit_seqno"][0] == 13
+    assert np.isnan(t["pour_elev"][0]) and t["shed_area"][0] == 1 and t["edge_pit"][0] == 1
