@@ -737,18 +737,47 @@ __global__ void k_gather64(const unsigned long long* __restrict__ src, const uin
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[i] = src[idx[i]];
 }
-// rank of every real pit (1-based); also counts them
-__global__ void k_bg_rank(const uint32_t* __restrict__ order, const unsigned long long* __restrict__ kfin, size_t m,
-                          uint32_t* __restrict__ rank, unsigned long long* count) {
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool real = false;
-  if (i < m) {
-    const uint32_t gp = order[i];
-    real = kfin[gp] != 0;
-    rank[gp] = real ? (uint32_t)i + 1 : 0;
+// lists = P sorted key lists of `stride` entries each, list b = [kfin desc (0 = empty slot, last) | the seqno keys in
+// the same order].  Number of entries of list b that come before the key (f, x): kfin greater, or equal with a lower seqno
+__device__ __forceinline__ unsigned keys_before(const unsigned long long* __restrict__ lists, int b, unsigned stride,
+                                                unsigned long long f, unsigned long long x) {
+  const unsigned long long* kf = lists + (size_t)b * 2 * stride;
+  const unsigned long long* kx = kf + stride;
+  unsigned lo = 0, hi = stride;
+  while (lo < hi) {
+    const unsigned mid = (lo + hi) >> 1;
+    const unsigned long long mf = kf[mid];
+    const bool before = mf > f || (mf == f && kx[mid] < x);
+    if (before) lo = mid + 1; else hi = mid;
   }
-  const unsigned bal = __ballot_sync(0xffffffffu, real);
-  if ((threadIdx.x & 31) == 0 && bal) atomicAdd(count, (unsigned long long)__popc(bal));
+  return lo;
+}
+// global rank (1-based, 0 = empty slot) of the band's own slots: place in the own sorted list + keys before it elsewhere
+__global__ void k_bg_rank_own(const unsigned long long* __restrict__ lists, int P, int own, unsigned stride,
+                              const uint32_t* __restrict__ order, uint32_t* __restrict__ rank_own) {
+  const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= stride) return;
+  const unsigned long long* mf = lists + (size_t)own * 2 * stride;
+  const unsigned long long f = mf[j], x = mf[stride + j];
+  uint32_t r = 0;
+  if (f != 0) {
+    r = j + 1;
+    for (int b = 0; b < P; ++b)
+      if (b != own) r += keys_before(lists, b, stride, f, x);
+  }
+  rank_own[order[j]] = r;
+}
+// pits of the whole DEM = non-empty entries of all lists
+__global__ void k_bg_count_real(const unsigned long long* __restrict__ lists, int P, unsigned stride, unsigned long long* count) {
+  for (int b = threadIdx.x; b < P; b += blockDim.x) {
+    const unsigned long long* kf = lists + (size_t)b * 2 * stride;
+    unsigned lo = 0, hi = stride;
+    while (lo < hi) {
+      const unsigned mid = (lo + hi) >> 1;
+      if (kf[mid] != 0) lo = mid + 1; else hi = mid;
+    }
+    atomicAdd(count, (unsigned long long)lo);
+  }
 }
 // final shed number of every local pit id: real pits look up their global rank, portals the rank of the
 // pit their flow ends in; and the seeds (flow entering at the entry cells of this band)
@@ -933,12 +962,25 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
   if ((rc = all_gather(B, n, ksend.data(), krecv.data(), (size_t)stride * 8))) return rc;
   if ((rc = all_gather(B, n, isend.data(), irecv.data(), (size_t)stride * 8))) return rc;
 
-  // ---- phase B: the same boundary graph and the same global pit ranking on every band
+  // ---- phase B: the same boundary graph on every band; the global pit ranking is shared out: a band sorts the keys
+  // of ITS pits, the sorted lists are all-gathered, and a pit's rank is its place in its own list plus, by binary
+  // search, the number of keys before it in every other list (round 1: every band sorted all M keys, 1.6 ms of an
+  // 8-band step at 32768^2)
   unsigned long long npits_global = 0;
   std::vector<uint32_t*> xt(n), xb(n);
+  struct PhaseB {
+    Graph G;
+    unsigned long long *kfin, *cnt;
+    uint32_t *ord, *grank;
+  };
+  std::vector<PhaseB> Q(n);
+  std::vector<void*> lsend(n), lrecv(n), gsend(n), grecv(n);
+  int idx_bits = 1;   // seqnos of the whole DEM need few bits (one more keeps the all-ones "none" last)
+  while (idx_bits < 63 && (((unsigned long long)(B[0]->gnr + 2) * (unsigned long long)NC) >> idx_bits) != 0) ++idx_bits;
+  ++idx_bits;
   for (int i = 0; i < n; ++i) {
     litap_grid* g = B[i];
-    Graph G;
+    Graph& G = Q[i].G;
     G.nxt = S.get<uint32_t>(Nn);
     G.jres = S.get<uint32_t>(Nn);
     G.X = S.get<uint32_t>(Nn);
@@ -948,22 +990,26 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
     G.pkidx = S.get<unsigned long long>(Nn);
     unsigned long long* kmax = (unsigned long long*)krecv[i];
     unsigned long long* kidx = (unsigned long long*)irecv[i];
-    unsigned long long* kfin = S.get<unsigned long long>(M);
-    unsigned long long* k64b = S.get<unsigned long long>(M);
-    unsigned long long* k64c = S.get<unsigned long long>(M);
-    uint32_t* ord_a = S.get<uint32_t>(M);
-    uint32_t* ord_b = S.get<uint32_t>(M);
-    uint32_t* grank = S.get<uint32_t>(M);
-    unsigned long long* cnt = S.get<unsigned long long>(2);
+    unsigned long long* kfin = Q[i].kfin = S.get<unsigned long long>(M);
+    unsigned long long* k64b = S.get<unsigned long long>(stride);
+    unsigned long long* k64c = S.get<unsigned long long>(stride);
+    uint32_t* ord_a = Q[i].ord = S.get<uint32_t>(stride);
+    uint32_t* ord_b = S.get<uint32_t>(stride);
+    Q[i].grank = S.get<uint32_t>(M);
+    unsigned long long* cnt = Q[i].cnt = S.get<unsigned long long>(2);
+    lsend[i] = S.get<unsigned long long>((size_t)2 * stride);
+    lrecv[i] = S.get<unsigned long long>((size_t)2 * M);
+    gsend[i] = S.get<uint32_t>(stride);
+    grecv[i] = Q[i].grank;
     xt[i] = S.get<uint32_t>(NC);
     xb[i] = S.get<uint32_t>(NC);
     size_t t1 = 0, t2 = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, t1, kidx, k64b, ord_a, ord_b, (int)M, 0, 64, st);
-    cub::DeviceRadixSort::SortPairsDescending(nullptr, t2, k64b, k64c, ord_b, ord_a, (int)M, 0, 64, st);
+    cub::DeviceRadixSort::SortPairs(nullptr, t1, kidx, k64b, ord_a, ord_b, (int)stride, 0, 64, st);
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, t2, k64b, k64c, ord_b, ord_a, (int)stride, 0, 64, st);
     size_t tn = std::max(t1, t2) + 256;
     void* tmp = S.get<unsigned char>(tn);
     if (!G.nxt || !G.jres || !G.X || !G.indeg || !G.src || !G.pkmax || !G.pkidx || !kfin || !k64b || !k64c || !ord_a ||
-        !ord_b || !grank || !cnt || !xt[i] || !xb[i] || !tmp)
+        !ord_b || !Q[i].grank || !cnt || !lsend[i] || !lrecv[i] || !gsend[i] || !xt[i] || !xb[i] || !tmp)
       return set_error(LITAP_ENOMEM, "device allocation failed (boundary graph)");
     CUDA_TRY(cudaMemsetAsync(cnt, 0, 16, st));
     KERNEL("k_bg_build", k_bg_build<<<blk(Nn), 256, 0, st>>>((const char*)rrecv[i], rec, P, NC, G));
@@ -988,21 +1034,34 @@ extern "C" int litap_bands_shed(litap_grid** B, int n) {
     KERNEL("k_bg_keys_max", k_bg_keys_max<<<blk(Nn), 256, 0, st>>>(G, Nn, kfin));
     KERNEL("k_bg_keys_own", k_bg_keys_own<<<blk(M), 256, 0, st>>>(kmax, kfin, kidx, M));
     KERNEL("k_bg_keys_idx", k_bg_keys_idx<<<blk(Nn), 256, 0, st>>>(G, Nn, kfin, kidx));
-    // canonical numbering (R/flow_02_calc_shed.R:32-38): stable LSD, seqno asc then max elevation desc
-    KERNEL("k_iota32", k_iota32<<<blk(M), 256, 0, st>>>(ord_a, M));
+    // canonical numbering (R/flow_02_calc_shed.R:32-38) of this band's slots: stable LSD, seqno asc then max elevation desc
+    const size_t base = (size_t)g->band * stride;
+    unsigned long long* ls = (unsigned long long*)lsend[i];
+    KERNEL("k_iota32", k_iota32<<<blk(stride), 256, 0, st>>>(ord_a, stride));
     size_t tcap = tn;
-    CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tcap, kidx, k64b, ord_a, ord_b, (int)M, 0, 64, st));
-    KERNEL("k_gather64", k_gather64<<<blk(M), 256, 0, st>>>(kfin, ord_b, k64b, M));
+    { ProfScope _p("cub_sort_pits_idx"); CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tcap, kidx + base, k64b, ord_a, ord_b, (int)stride, 0, idx_bits, st)); }
+    KERNEL("k_gather64", k_gather64<<<blk(stride), 256, 0, st>>>(kfin + base, ord_b, k64b, stride));
     tcap = tn;
-    CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tcap, k64b, k64c, ord_b, ord_a, (int)M, 0, 64, st));
+    { ProfScope _p("cub_sort_pits_key"); CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tcap, k64b, ls, ord_b, ord_a, (int)stride, 0, 64, st)); }
+    KERNEL("k_gather64", k_gather64<<<blk(stride), 256, 0, st>>>(kidx + base, ord_a, ls + stride, stride));
     c.launches += 4;
-    KERNEL("k_bg_rank", k_bg_rank<<<blk(M), 256, 0, st>>>(ord_a, kfin, M, grank, cnt));
+  }
+  if ((rc = all_gather(B, n, lsend.data(), lrecv.data(), (size_t)2 * stride * 8))) return rc;
+  for (int i = 0; i < n; ++i) {
+    KERNEL("k_bg_rank_own", k_bg_rank_own<<<blk(stride), 256, 0, st>>>((const unsigned long long*)lrecv[i], P, B[i]->band, stride,
+                                                                     Q[i].ord, (uint32_t*)gsend[i]));
+    KERNEL("k_bg_count_real", k_bg_count_real<<<1, 32, 0, st>>>((const unsigned long long*)lrecv[i], P, stride, Q[i].cnt));
+  }
+  if ((rc = all_gather(B, n, gsend.data(), grecv.data(), (size_t)stride * 4))) return rc;
+  for (int i = 0; i < n; ++i) {
+    litap_grid* g = B[i];
+    Graph& G = Q[i].G;
     if (W[i].npits)
-      KERNEL("k_band_fill_rank", k_band_fill_rank<<<blk(W[i].npits), 256, 0, st>>>(BI[i], g->d, W[i].pits, W[i].npits, grank, G.jres));
+      KERNEL("k_band_fill_rank", k_band_fill_rank<<<blk(W[i].npits), 256, 0, st>>>(BI[i], g->d, W[i].pits, W[i].npits, Q[i].grank, G.jres));
     // flow entering this band
     KERNEL("k_band_seeds_extract", k_band_seeds_extract<<<cblk, 256, 0, st>>>(BI[i], NC, G.X, xt[i], xb[i]));
     KERNEL("k_band_seed_walk", k_band_seed_walk<<<dim3(cblk, 2), 256, 0, st>>>(W[i].tg, BI[i], g->ddir, W[i].l2, W[i].nslots, G.X));
-    CUDA_TRY(cudaMemcpyAsync(&npits_global, cnt, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&npits_global, Q[i].cnt, 8, cudaMemcpyDeviceToHost, st));
     // ---- phase C: labels, upslope, ridge
     BandSeeds seeds;
     seeds.x_top = g->halo_top ? xt[i] : nullptr;

@@ -588,10 +588,14 @@ int shed_phase_rank(shed::ShedWork& W) {
   size_t tmpn = tmp1 > tmp2 ? tmp1 : tmp2;
   void* tmp = S.get<unsigned char>(tmpn ? tmpn : 256);
   if (!tmp) return set_error(LITAP_ENOMEM, "device allocation failed (sort scratch)");
-  // stable LSD: first by the tie-break (cell id asc), then by max elevation desc
-  CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmpn, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st));
+  // stable LSD: first by the tie-break (cell id asc), then by max elevation desc.  Cell ids need few bits: only those
+  // are sorted (one more, so that the all-ones "none" still sorts last)
+  int idx_bits = 1;
+  while (idx_bits < 32 && ((unsigned long long)W.tg.d.cells >> idx_bits) != 0) ++idx_bits;
+  idx_bits = idx_bits < 31 ? idx_bits + 1 : 32;
+  { ProfScope _p("cub_sort_pits_idx"); CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmpn, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, idx_bits, st)); }
   KERNEL("k_gather_u64", k_gather_u64<<<pblk, 256, 0, st>>>(pits.rootmax, ord_b, key64_a, npits));
-  CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tmpn, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st));
+  { ProfScope _p("cub_sort_pits_key"); CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tmpn, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st)); }
   KERNEL("k_scatter_rank", k_scatter_rank<<<pblk, 256, 0, st>>>(ord_a, pits.rank, npits));
   c.launches += 4;  // cub passes (at least)
   return LITAP_OK;
