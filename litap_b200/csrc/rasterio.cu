@@ -21,6 +21,11 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
+#include <vector>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
 #include "cellmath.h"
 #include "litap_internal.h"
 
@@ -100,9 +105,10 @@ extern "C" int litap_grid_read_flt(const char* path, double missing_value, litap
   RC(litap_flt_info(path, &info));
   if (info_out) *info_out = info;
   const std::string flt = with_ext(path, ".flt");
-  FILE* f = fopen(flt.c_str(), "rb");
-  if (!f) return set_error(LITAP_EARG, "litap_grid_read_flt: cannot open " + flt);
-  struct Closer { FILE* f; ~Closer() { if (f) fclose(f); } } closer{f};
+  const int fd = open(flt.c_str(), O_RDONLY);
+  if (fd < 0) return set_error(LITAP_EARG, "litap_grid_read_flt: cannot open " + flt);
+  struct Closer { int fd; ~Closer() { if (fd >= 0) close(fd); } } closer{fd};
+  const int nthreads = std::max(1, std::min(8, (int)std::thread::hardware_concurrency()));
   litap_grid* g = nullptr;
   RC(litap_grid_create(info.nrow + 2, info.ncol + 2, &g));   // elev starts as NaN everywhere: the NA ring of add_buffer()
   struct Guard { litap_grid* g; ~Guard() { if (g) litap_grid_destroy(g); } } guard{g};
@@ -122,8 +128,28 @@ extern "C" int litap_grid_read_flt(const char* path, double missing_value, litap
   for (int64_t r = 0; r < info.nrow; r += per, b ^= 1) {
     const int nr = (int)std::min<int64_t>(per, info.nrow - r);
     CUDA_TRY(cudaEventSynchronize(ev[b]));   // the copy engine is done with this buffer (and the kernel with dev[b])
-    if (fread(buf[b], rowb, nr, f) != (size_t)nr)
-      return set_error(LITAP_EARG, "litap_grid_read_flt: " + flt + " is shorter than its header says");
+    {   // the chunk comes off the file through several pread()s at once (one reader manages ~5 GB/s from the page cache)
+      const size_t bytes = rowb * nr, off0 = (size_t)r * rowb;
+      const size_t slice = ((bytes + nthreads - 1) / nthreads + 4095) & ~(size_t)4095;
+      std::vector<std::thread> th;
+      std::vector<int> ok(nthreads, 1);
+      for (int t = 0; t < nthreads; ++t) {
+        const size_t lo = std::min(bytes, slice * t), hi = std::min(bytes, slice * (t + 1));
+        if (hi <= lo) continue;
+        th.emplace_back([&, t, lo, hi] {
+          char* dst = (char*)buf[b] + lo;
+          size_t done = 0;
+          while (done < hi - lo) {
+            const ssize_t got = pread(fd, dst + done, hi - lo - done, (off_t)(off0 + lo + done));
+            if (got <= 0) { ok[t] = 0; return; }
+            done += (size_t)got;
+          }
+        });
+      }
+      for (auto& x : th) x.join();
+      for (int t = 0; t < nthreads; ++t)
+        if (!ok[t]) return set_error(LITAP_EARG, "litap_grid_read_flt: " + flt + " is shorter than its header says");
+    }
     CUDA_TRY(cudaMemcpyAsync(dev[b], buf[b], rowb * nr, cudaMemcpyHostToDevice, st));
     dim3 grid((unsigned)((info.ncol + 255) / 256), (unsigned)nr);
     KERNEL("k_flt_rows", k_flt_rows<<<grid, 256, 0, st>>>(dev[b], g->elev, g->d, (int)r, nr, (int)info.ncol, (float)info.nodata,
@@ -144,9 +170,9 @@ extern "C" int litap_grid_write_raw(litap_grid* g, const char* name, const char*
   const GridDims d = g->d;
   const int nrow = d.NR - 2, ncol = d.NC - 2;
   const int osize = as_flt ? 4 : a.esize;
-  FILE* f = fopen(path, "wb");
-  if (!f) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: cannot create ") + path);
-  struct Closer { FILE* f; ~Closer() { if (f) fclose(f); } } closer{f};
+  const int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+  if (fd < 0) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: cannot create ") + path);
+  struct Closer { int fd; ~Closer() { if (fd >= 0) close(fd); } } closer{fd};
   Ctx& c = ctx();
   cudaStream_t st = c.stream;
   void* buf[2];
@@ -155,17 +181,53 @@ extern "C" int litap_grid_write_raw(litap_grid* g, const char* name, const char*
   RC(hostcopy_staging(1, buf, ev, &cap));
   const size_t rowb = (size_t)ncol * osize;
   if (rowb > cap) return set_error(LITAP_EARG, "litap_grid_write_raw: a row does not fit the staging buffer");
-  const int per = (int)std::min<size_t>(32768, std::max<size_t>(1, cap / rowb));   // rows are blocks of the grid's y dimension
+  const int per = (int)std::min<size_t>(32768, std::max<size_t>(1, cap / rowb));
   PoolScratch S;
-  char* dev[2] = {S.get<char>((size_t)per * rowb), S.get<char>((size_t)per * rowb)};
-  if (!dev[0] || !dev[1]) return set_error(LITAP_ENOMEM, "device allocation failed (raster rows)");
+  char* dev[2] = {nullptr, nullptr};
+  if (as_flt) {
+    dev[0] = S.get<char>((size_t)per * rowb);
+    dev[1] = S.get<char>((size_t)per * rowb);
+    if (!dev[0] || !dev[1]) return set_error(LITAP_ENOMEM, "device allocation failed (raster rows)");
+  }
+  // a chunk that has arrived in its pinned buffer goes to the file from several threads at once (pwrite at disjoint
+  // offsets): one thread filling fresh page-cache pages manages ~4 GB/s, which made the writer 15 x slower than PCIe
   int pending_rows[2] = {0, 0};
+  size_t pending_off[2] = {0, 0};
+  const int nthreads = std::max(1, std::min(8, (int)std::thread::hardware_concurrency()));
+  // writes to ONE file serialise on its inode lock, so the threads store through a shared mapping instead (page faults
+  // of different pages proceed in parallel); pwrite is the fallback where the file cannot be mapped
+  const size_t total = rowb * (size_t)nrow;
+  char* map = nullptr;
+  if (total && ftruncate(fd, (off_t)total) == 0) {
+    void* m = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (m != MAP_FAILED) map = (char*)m;
+  }
+  struct Unmap { char*& m; size_t n; ~Unmap() { if (m) munmap(m, n); } } unmap{map, total};
   auto drain = [&](int b) -> int {
     if (!pending_rows[b]) return LITAP_OK;
     CUDA_TRY(cudaEventSynchronize(ev[b]));
-    if (fwrite(buf[b], rowb, pending_rows[b], f) != (size_t)pending_rows[b])
-      return set_error(LITAP_EARG, std::string("litap_grid_write_raw: short write to ") + path);
+    const size_t bytes = rowb * pending_rows[b];
+    const size_t slice = ((bytes + nthreads - 1) / nthreads + 4095) & ~(size_t)4095;
+    std::vector<std::thread> th;
+    std::vector<int> ok(nthreads, 1);
+    for (int t = 0; t < nthreads; ++t) {
+      const size_t lo = std::min(bytes, slice * t), hi = std::min(bytes, slice * (t + 1));
+      if (hi <= lo) continue;
+      th.emplace_back([&, t, lo, hi] {
+        const char* src = (const char*)buf[b] + lo;
+        if (map) { memcpy(map + pending_off[b] + lo, src, hi - lo); return; }
+        size_t done = 0;
+        while (done < hi - lo) {
+          const ssize_t w = pwrite(fd, src + done, hi - lo - done, (off_t)(pending_off[b] + lo + done));
+          if (w <= 0) { ok[t] = 0; return; }
+          done += (size_t)w;
+        }
+      });
+    }
+    for (auto& x : th) x.join();
     pending_rows[b] = 0;
+    for (int t = 0; t < nthreads; ++t)
+      if (!ok[t]) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: short write to ") + path);
     return LITAP_OK;
   };
   int b = 0;
@@ -184,6 +246,7 @@ extern "C" int litap_grid_write_raw(litap_grid* g, const char* name, const char*
     }
     CUDA_TRY(cudaEventRecord(ev[b], st));
     pending_rows[b] = nr;
+    pending_off[b] = (size_t)r * rowb;
   }
   RC(drain(b));
   RC(drain(b ^ 1));
