@@ -172,6 +172,10 @@ int litap_grid_read_flt(const char* path, double missing_value, litap_grid** out
  * (as_flt = 0: f64 / i32 / u32 / u8; NA = NaN or 0) or narrowed to float32 (as_flt = 1), plus <path minus extension>.hdr.
  * georef (may be NULL) supplies xllcorner / yllcorner / cellsize for the header. */
 int litap_grid_write_raw(litap_grid* g, const char* name, const char* path, int as_flt, const litap_raster_info* georef);
+/* n results at once, one writer per file (up to 8 side by side): a fresh file fills its page-cache pages at ~4 GB/s however
+ * many threads store into it, several files do so independently */
+int litap_grid_write_raw_many(litap_grid* g, int n, const char* const* names, const char* const* paths, int as_flt,
+                              const litap_raster_info* georef);
 
 /* ---- device-resident entry points (bench / large DEMs that never exist on the host) -------- */
 

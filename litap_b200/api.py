@@ -343,6 +343,14 @@ class DeviceGrid:
         g.georef = info
         return g
 
+    def write_raw_many(self, paths, as_flt=False):
+        """{result name: path}: all of them at once, one writer per file (save_output for a whole stage)."""
+        names = list(paths)
+        na = (C.c_char_p * len(names))(*[k.encode() for k in names])
+        pa = (C.c_char_p * len(names))(*[os.fsencode(paths[k]) for k in names])
+        check(lib().litap_grid_write_raw_many(self._h, len(names), na, pa, int(bool(as_flt)),
+                                              C.byref(self.georef) if self.georef is not None else None))
+
     def write_raw(self, name, path, as_flt=False):
         """One result without its ring (remove_buffer) as a raw little-endian binary file (+ .hdr)."""
         check(lib().litap_grid_write_raw(self._h, name.encode(), os.fsencode(path), int(bool(as_flt)),

@@ -102,6 +102,7 @@ extern "C" void litap_shutdown(void) {
   pool_release_all();
   form_forget_trig();
   hostcopy_forget_staging();
+  rasterio_forget();
   for (auto& ev : c.ev) if (ev) { cudaEventDestroy(ev); ev = nullptr; }
   if (g_own_stream) cudaStreamDestroy(c.stream);
   if (g_hi_stream) { cudaStreamDestroy(g_hi_stream); cudaEventDestroy(g_ev_fork); cudaEventDestroy(g_ev_join); g_hi_stream = nullptr; }

@@ -125,6 +125,7 @@ int h2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
 int hostcopy_flush();    // pageable destinations are complete after this
 void hostcopy_reset();   // start of a call: forget chunks a failed call left pending
 void hostcopy_forget_staging();
+void rasterio_forget();   // rasterio.cu: writer lanes (litap_shutdown)
 int hostcopy_staging(int which, void* buf[2], cudaEvent_t ev[2], size_t* bytes);   // pinned pairs for file I/O (rasterio.cu)
 
 template <typename T>

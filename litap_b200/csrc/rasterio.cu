@@ -162,102 +162,146 @@ extern "C" int litap_grid_read_flt(const char* path, double missing_value, litap
   return LITAP_OK;
 }
 
-extern "C" int litap_grid_write_raw(litap_grid* g, const char* name, const char* path, int as_flt, const litap_raster_info* georef) {
-  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
-  if (!g || !name || !path) return set_error(LITAP_EARG, "litap_grid_write_raw: NULL");
-  const ArrRef a = grid_find_array(g, name);
-  if (!a.p) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: no such result on the grid: ") + name);
-  const GridDims d = g->d;
-  const int nrow = d.NR - 2, ncol = d.NC - 2;
-  const int osize = as_flt ? 4 : a.esize;
-  const int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
-  if (fd < 0) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: cannot create ") + path);
-  struct Closer { int fd; ~Closer() { if (fd >= 0) close(fd); } } closer{fd};
-  Ctx& c = ctx();
-  cudaStream_t st = c.stream;
-  void* buf[2];
-  cudaEvent_t ev[2];
+// ---- writer ------------------------------------------------------------------------------------------------------
+// One file = one worker with its own stream, pair of pinned buffers and events (nothing of the library's shared state
+// is touched, so several workers run side by side).  The kernel instantiates the page-cache pages of ONE fresh file at
+// ~4 GB/s whatever the number of threads storing into it (per-inode serialisation), so the way to write faster is to
+// write several files at once: litap_grid_write_raw_many.
+namespace {
+struct WriteJob {
+  const void* arr; int esize; const char* name; const char* path; int as_flt;
+  int rc = LITAP_OK; std::string err;
+};
+struct WriteLane {            // per worker
+  cudaStream_t st = nullptr;
+  void* buf[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  char* dev[2] = {nullptr, nullptr};   // float32 packing buffers (as_flt), from the pool, allocated by the caller thread
   size_t cap = 0;
-  RC(hostcopy_staging(1, buf, ev, &cap));
+};
+#define WJ_CUDA(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { J.rc = LITAP_ECUDA; J.err = std::string(#expr) + ": " + cudaGetErrorString(_e); return; } } while (0)
+
+void write_one(const GridDims d, const litap_raster_info* georef, WriteLane& L, WriteJob& J) {
+  const int nrow = d.NR - 2, ncol = d.NC - 2;
+  const int osize = J.as_flt ? 4 : J.esize;
   const size_t rowb = (size_t)ncol * osize;
-  if (rowb > cap) return set_error(LITAP_EARG, "litap_grid_write_raw: a row does not fit the staging buffer");
-  const int per = (int)std::min<size_t>(32768, std::max<size_t>(1, cap / rowb));
-  PoolScratch S;
-  char* dev[2] = {nullptr, nullptr};
-  if (as_flt) {
-    dev[0] = S.get<char>((size_t)per * rowb);
-    dev[1] = S.get<char>((size_t)per * rowb);
-    if (!dev[0] || !dev[1]) return set_error(LITAP_ENOMEM, "device allocation failed (raster rows)");
-  }
-  // a chunk that has arrived in its pinned buffer goes to the file from several threads at once (pwrite at disjoint
-  // offsets): one thread filling fresh page-cache pages manages ~4 GB/s, which made the writer 15 x slower than PCIe
+  if (rowb > L.cap) { J.rc = LITAP_EARG; J.err = "litap_grid_write_raw: a row does not fit the staging buffer"; return; }
+  const int fd = open(J.path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+  if (fd < 0) { J.rc = LITAP_EARG; J.err = std::string("litap_grid_write_raw: cannot create ") + J.path; return; }
+  struct Closer { int fd; ~Closer() { close(fd); } } closer{fd};
+  const int per = (int)std::min<size_t>(32768, std::max<size_t>(1, L.cap / rowb));
   int pending_rows[2] = {0, 0};
-  size_t pending_off[2] = {0, 0};
-  const int nthreads = std::max(1, std::min(8, (int)std::thread::hardware_concurrency()));
-  // writes to ONE file serialise on its inode lock, so the threads store through a shared mapping instead (page faults
-  // of different pages proceed in parallel); pwrite is the fallback where the file cannot be mapped
-  const size_t total = rowb * (size_t)nrow;
-  char* map = nullptr;
-  if (total && ftruncate(fd, (off_t)total) == 0) {
-    void* m = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
-    if (m != MAP_FAILED) map = (char*)m;
-  }
-  struct Unmap { char*& m; size_t n; ~Unmap() { if (m) munmap(m, n); } } unmap{map, total};
-  auto drain = [&](int b) -> int {
-    if (!pending_rows[b]) return LITAP_OK;
-    CUDA_TRY(cudaEventSynchronize(ev[b]));
-    const size_t bytes = rowb * pending_rows[b];
-    const size_t slice = ((bytes + nthreads - 1) / nthreads + 4095) & ~(size_t)4095;
-    std::vector<std::thread> th;
-    std::vector<int> ok(nthreads, 1);
-    for (int t = 0; t < nthreads; ++t) {
-      const size_t lo = std::min(bytes, slice * t), hi = std::min(bytes, slice * (t + 1));
-      if (hi <= lo) continue;
-      th.emplace_back([&, t, lo, hi] {
-        const char* src = (const char*)buf[b] + lo;
-        if (map) { memcpy(map + pending_off[b] + lo, src, hi - lo); return; }
-        size_t done = 0;
-        while (done < hi - lo) {
-          const ssize_t w = pwrite(fd, src + done, hi - lo - done, (off_t)(pending_off[b] + lo + done));
-          if (w <= 0) { ok[t] = 0; return; }
-          done += (size_t)w;
-        }
-      });
+  auto drain = [&](int b) -> bool {
+    if (!pending_rows[b]) return true;
+    if (cudaEventSynchronize(L.ev[b]) != cudaSuccess) { J.rc = LITAP_ECUDA; J.err = "litap_grid_write_raw: copy failed"; return false; }
+    const char* src = (const char*)L.buf[b];
+    size_t left = rowb * pending_rows[b];
+    while (left) {
+      const ssize_t w = write(fd, src, left);
+      if (w <= 0) { J.rc = LITAP_EARG; J.err = std::string("litap_grid_write_raw: short write to ") + J.path; return false; }
+      src += w; left -= (size_t)w;
     }
-    for (auto& x : th) x.join();
     pending_rows[b] = 0;
-    for (int t = 0; t < nthreads; ++t)
-      if (!ok[t]) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: short write to ") + path);
-    return LITAP_OK;
+    return true;
   };
   int b = 0;
   for (int r = 0; r < nrow; r += per, b ^= 1) {
     const int nr = std::min(per, nrow - r);
-    RC(drain(b));   // the chunk this buffer held goes to the file while the other buffer's chunk crosses PCIe
-    dim3 grid((unsigned)((ncol + 255) / 256), (unsigned)nr);
-    if (as_flt) {
-      if (a.esize == 8) KERNEL("k_pack_rows", k_pack_rows<<<grid, 256, 0, st>>>((const double*)a.p, (float*)dev[b], d, r, nr, ncol));
-      else if (a.esize == 4) KERNEL("k_pack_rows", k_pack_rows<<<grid, 256, 0, st>>>((const int32_t*)a.p, (float*)dev[b], d, r, nr, ncol));
-      else KERNEL("k_pack_rows", k_pack_rows<<<grid, 256, 0, st>>>((const uint8_t*)a.p, (float*)dev[b], d, r, nr, ncol));
-      CUDA_TRY(cudaMemcpyAsync(buf[b], dev[b], rowb * nr, cudaMemcpyDeviceToHost, st));
+    if (!drain(b)) return;   // the chunk this buffer held goes to the file while the other buffer's chunk crosses PCIe
+    if (J.as_flt) {
+      dim3 grid((unsigned)((ncol + 255) / 256), (unsigned)nr);
+      if (J.esize == 8) k_pack_rows<<<grid, 256, 0, L.st>>>((const double*)J.arr, (float*)L.dev[b], d, r, nr, ncol);
+      else if (J.esize == 4) k_pack_rows<<<grid, 256, 0, L.st>>>((const int32_t*)J.arr, (float*)L.dev[b], d, r, nr, ncol);
+      else k_pack_rows<<<grid, 256, 0, L.st>>>((const uint8_t*)J.arr, (float*)L.dev[b], d, r, nr, ncol);
+      WJ_CUDA(cudaGetLastError());
+      WJ_CUDA(cudaMemcpyAsync(L.buf[b], L.dev[b], rowb * nr, cudaMemcpyDeviceToHost, L.st));
     } else {   // own dtype: the copy engine strips the ring and the pitch
-      const char* src = (const char*)a.p + ((size_t)(1 + r) * d.pitch + 1) * a.esize;
-      CUDA_TRY(cudaMemcpy2DAsync(buf[b], rowb, src, (size_t)d.pitch * a.esize, rowb, nr, cudaMemcpyDeviceToHost, st));
+      const char* src = (const char*)J.arr + ((size_t)(1 + r) * d.pitch + 1) * J.esize;
+      WJ_CUDA(cudaMemcpy2DAsync(L.buf[b], rowb, src, (size_t)d.pitch * J.esize, rowb, nr, cudaMemcpyDeviceToHost, L.st));
     }
-    CUDA_TRY(cudaEventRecord(ev[b], st));
+    WJ_CUDA(cudaEventRecord(L.ev[b], L.st));
     pending_rows[b] = nr;
-    pending_off[b] = (size_t)r * rowb;
   }
-  RC(drain(b));
-  RC(drain(b ^ 1));
+  if (!drain(b) || !drain(b ^ 1)) return;
   // header: what is in the file and where it lies
-  const std::string hdr = with_ext(path, ".hdr");
+  const std::string hdr = with_ext(J.path, ".hdr");
   FILE* h = fopen(hdr.c_str(), "w");
-  if (!h) return set_error(LITAP_EARG, "litap_grid_write_raw: cannot create " + hdr);
-  const bool is_float = as_flt || a.esize == 8;
+  if (!h) { J.rc = LITAP_EARG; J.err = "litap_grid_write_raw: cannot create " + hdr; return; }
+  const bool is_float = J.as_flt || J.esize == 8;
   fprintf(h, "ncols %d\nnrows %d\nxllcorner %.10g\nyllcorner %.10g\ncellsize %.10g\nNODATA_value %s\nbyteorder LSBFIRST\n", ncol, nrow,
           georef ? georef->xll : 0.0, georef ? georef->yll : 0.0, georef ? georef->cellsize : 1.0, is_float ? "nan" : "0");
-  fprintf(h, "nbits %d\npixeltype %s\nlayer %s\n", osize * 8, is_float ? "FLOAT" : (a.esize == 4 && !strcmp(name, "shed") ? "SIGNEDINT" : "UNSIGNEDINT"), name);
+  fprintf(h, "nbits %d\npixeltype %s\nlayer %s\n", osize * 8,
+          is_float ? "FLOAT" : (J.esize == 4 && !strcmp(J.name, "shed") ? "SIGNEDINT" : "UNSIGNEDINT"), J.name);
   fclose(h);
+}
+
+// pinned buffers and streams of the writer lanes, kept between calls (freed by litap_shutdown through rasterio_forget)
+constexpr int MAX_LANES = 8;
+constexpr size_t LANE_BUF = 16u << 20;
+WriteLane g_lanes[MAX_LANES];
+int lanes_init(int n) {
+  for (int i = 0; i < n; ++i) {
+    WriteLane& L = g_lanes[i];
+    if (!L.st) CUDA_TRY(cudaStreamCreateWithFlags(&L.st, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      if (!L.buf[b]) CUDA_TRY(cudaHostAlloc(&L.buf[b], LANE_BUF, cudaHostAllocDefault));
+      if (!L.ev[b]) CUDA_TRY(cudaEventCreateWithFlags(&L.ev[b], cudaEventDisableTiming));
+    }
+    L.cap = LANE_BUF;
+  }
   return LITAP_OK;
+}
+}  // namespace
+
+void rasterio_forget() {   // litap_shutdown
+  for (WriteLane& L : g_lanes) {
+    for (int b = 0; b < 2; ++b) {
+      if (L.buf[b]) { cudaFreeHost(L.buf[b]); L.buf[b] = nullptr; }
+      if (L.ev[b]) { cudaEventDestroy(L.ev[b]); L.ev[b] = nullptr; }
+    }
+    if (L.st) { cudaStreamDestroy(L.st); L.st = nullptr; }
+  }
+}
+
+extern "C" int litap_grid_write_raw_many(litap_grid* g, int n, const char* const* names, const char* const* paths, int as_flt,
+                                         const litap_raster_info* georef) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
+  if (!g || n < 1 || !names || !paths) return set_error(LITAP_EARG, "litap_grid_write_raw_many: bad arguments");
+  std::vector<WriteJob> jobs(n);
+  for (int k = 0; k < n; ++k) {
+    if (!names[k] || !paths[k]) return set_error(LITAP_EARG, "litap_grid_write_raw_many: NULL name / path");
+    const ArrRef a = grid_find_array(g, names[k]);
+    if (!a.p) return set_error(LITAP_EARG, std::string("litap_grid_write_raw: no such result on the grid: ") + names[k]);
+    jobs[k].arr = a.p; jobs[k].esize = a.esize; jobs[k].name = names[k]; jobs[k].path = paths[k]; jobs[k].as_flt = as_flt;
+  }
+  const int nl = std::min(n, MAX_LANES);
+  RC(lanes_init(nl));
+  CUDA_TRY(cudaStreamSynchronize(ctx().stream));   // the results are complete before the lanes' streams read them
+  PoolScratch S;
+  const GridDims d = g->d;
+  if (as_flt) {
+    const size_t rowb = (size_t)(d.NC - 2) * 4;
+    const size_t per = std::min<size_t>(32768, std::max<size_t>(1, LANE_BUF / std::max<size_t>(rowb, 1)));
+    for (int i = 0; i < nl; ++i)
+      for (int b = 0; b < 2; ++b) {
+        g_lanes[i].dev[b] = S.get<char>(per * rowb);
+        if (!g_lanes[i].dev[b]) return set_error(LITAP_ENOMEM, "device allocation failed (raster rows)");
+      }
+  }
+  const int device = ctx().device;
+  std::vector<std::thread> th;
+  for (int i = 0; i < nl; ++i)
+    th.emplace_back([&, i] {
+      cudaSetDevice(device);
+      for (int k = i; k < n; k += nl) write_one(d, georef, g_lanes[i], jobs[k]);
+      cudaStreamSynchronize(g_lanes[i].st);
+    });
+  for (auto& x : th) x.join();
+  for (int k = 0; k < n; ++k)
+    if (jobs[k].rc) return set_error(jobs[k].rc, jobs[k].err);
+  return LITAP_OK;
+}
+
+extern "C" int litap_grid_write_raw(litap_grid* g, const char* name, const char* path, int as_flt, const litap_raster_info* georef) {
+  return litap_grid_write_raw_many(g, 1, &name, &path, as_flt, georef);
 }

@@ -42,11 +42,35 @@ calc_shed4 <- function(db, verbose = FALSE) {
   db$ridge <- r$ridge
   # side columns the reference's calc_upslopes() leaves in its result
   # (R/flow_02_calc_shed.R:62-68); not saved (cols_order) but part of its own snapshot test
-  ok <- !is.na(db$initial_shed)
-  db$seqno_shed <- NA_integer_
-  db$seqno_shed[ok] <- stats::ave(db$seqno[ok], db$initial_shed[ok], FUN = seq_along)
+  # group_by(shedno) numbers the NA group as well (cells without a shed count 1, 2, ... among themselves)
+  grp <- ifelse(is.na(db$initial_shed), 0, db$initial_shed)
+  db$seqno_shed <- as.integer(stats::ave(db$seqno, grp, FUN = seq_along))
   db$drec_shed <- db$seqno_shed[db$drec]
   db
+}
+
+# calc_upslopes(db, type = "uced") (R/flow_02_calc_shed.R:60-79): what pit removal calls at
+# R/flow_04_remove_pit_fast.R:73,345.  type = "upslope" is part of calc_shed4() above.
+calc_upslopes <- function(db, type = c("upslope", "uced")) {
+  type <- match.arg(type)
+  if (type != "uced") stop("calc_upslopes(type = \"upslope\") is computed by calc_shed4()", call. = FALSE)
+  d <- litap_dims(db)
+  db$uced <- .Call("litap_R_uced", as.double(db$elev), db$ddir, db$shedno, d[1], d[2])
+  db
+}
+
+# pit_stat1() (R/flow_03_pit_stat_fast.R:1-162): pour point and pit statistics of every shed
+pit_stat1 <- function(db, w = NULL, shed = "shedno", method, verbose = FALSE) {
+  d <- litap_dims(db)
+  if (verbose) message("    Assessing pour points on the GPU")
+  r <- .Call("litap_R_pit_stat", as.double(db$elev), db$ddir, db[[shed]], db$upslope, db$ridge, db$edge_map,
+             d[1], d[2], as.integer(method == "landmapr"))
+  stats <- tibble::as_tibble(r)
+  stats$edge_pit <- stats$edge_pit == 1
+  if (!is.null(w)) stats <- stats[stats$shedno %in% w, ]
+  if ("pond_shed" %in% names(db))
+    stats <- dplyr::left_join(stats, dplyr::distinct(dplyr::select(db, "shedno", "pond_shed")), by = "shedno")
+  stats
 }
 
 calc_form <- function(db, grid, verbose = FALSE) {

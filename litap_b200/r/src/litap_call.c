@@ -146,6 +146,75 @@ SEXP litap_R_weti(SEXP elev, SEXP ddir, SEXP upslope, SEXP nrow, SEXP ncol, SEXP
   return out;
 }
 
+/* integer-like column (numeric or integer, NA allowed) -> int32 with 0 = NA */
+static int32_t* col_to_i32(SEXP v, R_xlen_t n) {
+  int32_t* o = (int32_t*)R_alloc((size_t)n, sizeof(int32_t));
+  if (TYPEOF(v) == REALSXP) {
+    const double* p = REAL(v);
+    for (R_xlen_t i = 0; i < n; ++i) o[i] = ISNAN(p[i]) ? 0 : (int32_t)p[i];
+  } else {
+    const int* p = INTEGER(v);   /* INTSXP and LGLSXP share the layout */
+    for (R_xlen_t i = 0; i < n; ++i) o[i] = p[i] == NA_INTEGER ? 0 : (int32_t)p[i];
+  }
+  return o;
+}
+static uint8_t* col_to_u8(SEXP v, R_xlen_t n, uint8_t na) {
+  uint8_t* o = (uint8_t*)R_alloc((size_t)n, 1);
+  if (TYPEOF(v) == REALSXP) {
+    const double* p = REAL(v);
+    for (R_xlen_t i = 0; i < n; ++i) o[i] = ISNAN(p[i]) ? na : (uint8_t)p[i];
+  } else {
+    const int* p = INTEGER(v);
+    for (R_xlen_t i = 0; i < n; ++i) o[i] = p[i] == NA_INTEGER ? na : (uint8_t)p[i];
+  }
+  return o;
+}
+
+/* calc_upslopes(db, type = "uced"): .Call("litap_R_uced", db$elev, db$ddir, db$shedno, nrow, ncol) -> uced */
+SEXP litap_R_uced(SEXP elev, SEXP ddir, SEXP shedno, SEXP nrow, SEXP ncol) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n || XLENGTH(ddir) != n || XLENGTH(shedno) != n)
+    Rf_error("litap_R_uced: elev/ddir/shedno must have nrow*ncol entries");
+  uint8_t* d = ddir_to_u8(ddir, n);
+  int32_t* s = col_to_i32(shedno, n);
+  SEXP out = PROTECT(Rf_allocVector(REALSXP, n));
+  fail_if(litap_uced(REAL(elev), d, s, NR, NC, REAL(out)), "calc_upslopes(type = \"uced\")");
+  UNPROTECT(1);
+  return out;
+}
+
+/* pit_stat1(db, shed = , method = ): .Call("litap_R_pit_stat", elev, ddir, shed column, upslope, ridge, edge_map, nrow,
+ * ncol, method (0 litap / 1 landmapr)) -> named list of the 21 columns (doubles; seqno / row / col buffered) */
+SEXP litap_R_pit_stat(SEXP elev, SEXP ddir, SEXP shed, SEXP upslope, SEXP ridge, SEXP edge_map, SEXP nrow, SEXP ncol,
+                      SEXP method) {
+  const R_xlen_t NR = (R_xlen_t)Rf_asReal(nrow), NC = (R_xlen_t)Rf_asReal(ncol), n = NR * NC;
+  if (TYPEOF(elev) != REALSXP || XLENGTH(elev) != n || XLENGTH(ddir) != n || XLENGTH(shed) != n || XLENGTH(upslope) != n ||
+      XLENGTH(ridge) != n || XLENGTH(edge_map) != n)
+    Rf_error("litap_R_pit_stat: every column must have nrow*ncol entries");
+  uint8_t* d = ddir_to_u8(ddir, n);
+  int32_t* s = col_to_i32(shed, n);
+  uint32_t* up = (uint32_t*)col_to_i32(upslope, n);
+  uint8_t* rg = col_to_u8(ridge, n, 2);
+  uint8_t* em = col_to_u8(edge_map, n, 0);
+  int32_t mx = 0;
+  for (R_xlen_t i = 0; i < n; ++i) if (s[i] > mx) mx = s[i];
+  const int64_t cap = mx > 0 ? mx : 1;            /* at most one row per shed number */
+  int ncolumns = 0;
+  const char* const* names = litap_pit_stat_names(&ncolumns);
+  double** col = (double**)R_alloc((size_t)ncolumns, sizeof(double*));
+  for (int k = 0; k < ncolumns; ++k) col[k] = (double*)R_alloc((size_t)cap, sizeof(double));
+  int64_t rows = 0;
+  fail_if(litap_pit_stat(REAL(elev), d, s, up, rg, em, NR, NC, Rf_asInteger(method), cap, col, &rows), "pit_stat1");
+  SEXP out = PROTECT(named_list(ncolumns, (const char**)names));
+  for (int k = 0; k < ncolumns; ++k) {
+    SEXP v = Rf_allocVector(REALSXP, (R_xlen_t)rows);
+    SET_VECTOR_ELT(out, k, v);
+    memcpy(REAL(v), col[k], (size_t)rows * sizeof(double));
+  }
+  UNPROTECT(1);
+  return out;
+}
+
 /* slope_gc(db, grid): the six gradients / curvatures as doubles, hill_*_dir as doubles (2/4, 1/3),
  * hill_*_n / hill_*_cell as integers; NA where the library reports 0 / NaN */
 SEXP litap_R_slope_gc(SEXP elev, SEXP nrow, SEXP ncol, SEXP grid) {
@@ -256,6 +325,7 @@ static const R_CallMethodDef call_methods[] = {
     {"litap_R_ddir", (DL_FUNC)&litap_R_ddir, 4},     {"litap_R_shed", (DL_FUNC)&litap_R_shed, 4},
     {"litap_R_form", (DL_FUNC)&litap_R_form, 4},     {"litap_R_weti", (DL_FUNC)&litap_R_weti, 6},
     {"litap_R_slope_gc", (DL_FUNC)&litap_R_slope_gc, 4}, {"litap_R_relz", (DL_FUNC)&litap_R_relz, 8},
+    {"litap_R_uced", (DL_FUNC)&litap_R_uced, 5},     {"litap_R_pit_stat", (DL_FUNC)&litap_R_pit_stat, 9},
     {"litap_R_init", (DL_FUNC)&litap_R_init, 1},     {"litap_R_shutdown", (DL_FUNC)&litap_R_shutdown, 0},
     {"litap_R_timings", (DL_FUNC)&litap_R_timings, 0}, {NULL, NULL, 0}};
 

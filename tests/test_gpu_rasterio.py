@@ -92,3 +92,23 @@ def test_multi_chunk_and_errors(tmp_path):
     os.remove(p + ".hdr")
     with pytest.raises(lb.LitapError):
         lb.DeviceGrid.read_flt(p + ".flt")
+
+
+def test_write_raw_many(tmp_path):
+    """a whole stage's results at once (one writer per file) = the files written one by one"""
+    g = lb.DeviceGrid(700 + 2, 515 + 2)
+    g.synth(seed=4)
+    g.flow_form(5.0)
+    names = ("ddir", "flatcell", "shed", "upslope", "ridge", "slope_pct", "slope_deg", "aspect", "prof", "plan", "elev")
+    g.write_raw_many({k: str(tmp_path / ("m_" + k + ".bin")) for k in names})
+    for k in names:
+        g.write_raw(k, str(tmp_path / ("s_" + k + ".bin")))
+        a = open(str(tmp_path / ("m_" + k + ".bin")), "rb").read()
+        b = open(str(tmp_path / ("s_" + k + ".bin")), "rb").read()
+        assert a == b and len(a) == 700 * 515 * g._DT.get(k, np.float64)().itemsize, k
+        assert open(str(tmp_path / ("m_" + k + ".hdr"))).read() == open(str(tmp_path / ("s_" + k + ".hdr"))).read()
+    g.write_raw_many({"slope_pct": str(tmp_path / "f.flt"), "upslope": str(tmp_path / "u.flt")}, as_flt=True)
+    assert (np.fromfile(str(tmp_path / "u.flt"), "<f4").reshape(700, 515) == g.download("upslope")[1:-1, 1:-1].astype(np.float32)).all()
+    with pytest.raises(lb.LitapError):
+        g.write_raw_many({"nope": str(tmp_path / "x.bin")})
+    g.close()
