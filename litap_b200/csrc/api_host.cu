@@ -91,7 +91,11 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   if (want_form && !(grid > 0)) return set_error(LITAP_EARG, "grid must be > 0");
   // The DEM goes up in row chunks; calc_form runs on each chunk as soon as its rows (and the row
   // below) are resident, and its five outputs go back on a second stream while the next chunk is
-  // still uploading and while calc_ddir2 / calc_shed4 run: both PCIe directions stay busy.
+  // still uploading and while calc_ddir2 / calc_shed4 run: both PCIe directions stay busy.  That holds for
+  // pinned / registered destinations (plain asynchronous copies).  Pageable destinations are staged by THIS
+  // thread (hostcopy.cu): the transfers of a chunk's outputs still overlap the copy engine's next upload and the
+  // kernels already queued, but later stages are enqueued only once the thread gets back from its host copies.
+  // Nothing waits for the device in the middle of the call: the host syncs once, at the end.
   // form is computed on the elevations as given (form_mapper never sees the inverted DEM).
   const GridDims d = g->d;
   double* fouts[5] = {slope_pct, slope_deg, aspect, prof, plan};
@@ -99,7 +103,10 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   RC(P.init());
   const int nchunk = d.NR >= 8 * 256 ? 8 : 1;
   const int crows = ((d.NR + nchunk - 1) / nchunk + 31) / 32 * 32;
-  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  cudaEvent_t up0 = nullptr, up1 = nullptr;   // first / last upload (destroyed by the Pipe)
+  RC(P.mark(c.stream));
+  up0 = P.ev.back();
+  const size_t ev_base = P.ev.size();
   int form_done = 0;  // rows [0, form_done) of the form outputs are computed
   for (int a = 0; a < d.NR; a += crows) {
     const int b = a + crows < d.NR ? a + crows : d.NR;
@@ -118,12 +125,9 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
                   (size_t)d.pitch * 8, (size_t)d.NC * 8, hi - form_done, P.copy));
     form_done = hi;
   }
-  RC(timed_sync(&c.tm.h2d_ms, c.ev[6], c.ev[7]));  // uploads + the form kernels between them
-  for (size_t i = 0; i + 1 < P.ev.size(); i += 2) {
-    float ms = 0;
-    cudaEventElapsedTime(&ms, P.ev[i], P.ev[i + 1]);
-    c.tm.form_ms += ms;
-  }
+  const size_t ev_end = P.ev.size();
+  RC(P.mark(c.stream));
+  up1 = P.ev.back();
   RC(litap_grid_ddir(g, invert));
   if (want_shed) RC(litap_grid_shed(g));
   CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
@@ -137,6 +141,15 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   }
   CUDA_TRY(cudaStreamSynchronize(P.copy));
   RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));  // what is left of the downloads after the last stage
+  {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, up0, up1);   // first upload .. last upload, with the form kernels between them
+    c.tm.h2d_ms = ms;
+    for (size_t i = ev_base; i + 1 < ev_end; i += 2) {
+      cudaEventElapsedTime(&ms, P.ev[i], P.ev[i + 1]);
+      c.tm.form_ms += ms;
+    }
+  }
   c.tm.kernel_launches = c.launches - l0;
   c.tm.total_ms = w.ms();
   return LITAP_OK;
