@@ -3,6 +3,10 @@
 // outputs.  No result is ever computed on the host.
 #include <chrono>
 #include <vector>
+#include <condition_variable>
+#include <mutex>
+#include <string>
+#include <thread>
 #include "litap_internal.h"
 
 namespace {
@@ -40,7 +44,7 @@ int timed_sync(float* slot, cudaEvent_t a, cudaEvent_t b) {
 // that refers to caller memory because the destructor drains the stream first)
 struct Pipe {
   cudaStream_t copy = nullptr;
-  std::vector<cudaEvent_t> ev;
+  std::vector<cudaEvent_t> ev, aux;
   int init() {
     CUDA_TRY(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
     return LITAP_OK;
@@ -55,6 +59,7 @@ struct Pipe {
   ~Pipe() {
     if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
     for (cudaEvent_t e : ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : aux) cudaEventDestroy(e);
   }
 };
 
@@ -101,12 +106,83 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   double* fouts[5] = {slope_pct, slope_deg, aspect, prof, plan};
   Pipe P;
   RC(P.init());
+  // the form outputs are rounded numbers: they travel as int32 (20 instead of 40 B/cell) and are widened by the host
+  // threads of hostcopy.cu while they are copied out of the staging buffers (bit-identical: form.cu k_form_pack checks
+  // every value, hostexpand.cpp reproduces the quotient); LITAP_FORM_PACK=0 sends the doubles themselves
+  const char* pack_env = getenv("LITAP_FORM_PACK");   // read per call (the tests compare both ways)
+  const bool pack_off = pack_env && pack_env[0] == '0';
+  const bool pack = want_form && !pack_off && (size_t)d.NC * 4 <= (64u << 20);
+  int32_t* packed[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int* pack_flags = nullptr;
+  struct PackFree {
+    int32_t** p; int** f;
+    ~PackFree() { for (int i = 0; i < 5; ++i) grid_free_array(p[i]); if (*f) pool_free(*f); }
+  } pack_free{packed, &pack_flags};
+  if (pack) {
+    for (int i = 0; i < 5; ++i)
+      if (fouts[i] && !(packed[i] = grid_alloc_array<int32_t>(d, -1))) return set_error(LITAP_ENOMEM, "device allocation failed (packed form outputs)");
+    pack_flags = (int*)pool_alloc(5 * sizeof(int));
+    if (!pack_flags) return set_error(LITAP_ENOMEM, "device allocation failed (pack flags)");
+    CUDA_TRY(cudaMemsetAsync(pack_flags, 0, 5 * sizeof(int), c.stream));
+  }
   const int nchunk = d.NR >= 8 * 256 ? 8 : 1;
   const int crows = ((d.NR + nchunk - 1) / nchunk + 31) / 32 * 32;
   cudaEvent_t up0 = nullptr, up1 = nullptr;   // first / last upload (destroyed by the Pipe)
   RC(P.mark(c.stream));
   up0 = P.ev.back();
   const size_t ev_base = P.ev.size();
+  // The downloads of the form outputs are driven by a helper thread: staged copies (pageable destinations, packed
+  // outputs) keep a host thread busy with the copying / widening, and this thread has the uploads, calc_ddir2 and
+  // calc_shed4 (with their host read-backs) to enqueue meanwhile.  The helper owns the download staging buffers of
+  // hostcopy.cu until it is joined; this thread only uses the upload pair and plain asynchronous copies before that.
+  struct Chunk { int lo, hi; cudaEvent_t ready; };
+  std::vector<Chunk> chunks;
+  chunks.reserve(nchunk + 1);
+  std::mutex mu;
+  std::condition_variable cv;
+  size_t produced = 0;
+  bool closed = false;
+  int helper_rc = LITAP_OK;
+  std::string helper_err;
+  const int device = c.device;
+  cudaStream_t copy_stream = P.copy;
+  std::thread helper;
+  struct Joiner {   // whatever way the call ends, the helper is told to stop and joined before the staging state is touched
+    std::thread& t; std::mutex& mu; std::condition_variable& cv; bool& closed;
+    ~Joiner() {
+      if (!t.joinable()) return;
+      { std::lock_guard<std::mutex> lk(mu); closed = true; }
+      cv.notify_all();
+      t.join();
+    }
+  } joiner{helper, mu, cv, closed};
+  if (want_form)
+    helper = std::thread([&] {
+      cudaSetDevice(device);
+      for (size_t j = 0;; ++j) {
+        Chunk ch;
+        {
+          std::unique_lock<std::mutex> lk(mu);
+          cv.wait(lk, [&] { return produced > j || closed; });
+          if (produced <= j) break;
+          ch = chunks[j];
+        }
+        int rc = LITAP_OK;
+        if (cudaStreamWaitEvent(copy_stream, ch.ready, 0) != cudaSuccess) rc = set_error(LITAP_ECUDA, "cudaStreamWaitEvent failed");
+        for (int i = 0; i < 5 && !rc; ++i) {
+          if (!fouts[i]) continue;
+          if (pack)
+            rc = d2h_2d_i32_expand(fouts[i] + (size_t)ch.lo * d.NC, (size_t)d.NC * 8, packed[i] + (size_t)ch.lo * d.pitch,
+                                   (size_t)d.pitch * 4, (size_t)d.NC, ch.hi - ch.lo, i == 2 ? 2 : 1, copy_stream);
+          else
+            rc = d2h_2d(fouts[i] + (size_t)ch.lo * d.NC, (size_t)d.NC * 8, g->form[i] + (size_t)ch.lo * d.pitch,
+                        (size_t)d.pitch * 8, (size_t)d.NC * 8, ch.hi - ch.lo, copy_stream);
+        }
+        if (rc) { helper_rc = rc; helper_err = litap_last_error(); return; }
+      }
+      const int rc = hostcopy_flush();
+      if (rc) { helper_rc = rc; helper_err = litap_last_error(); }
+    });
   int form_done = 0;  // rows [0, form_done) of the form outputs are computed
   for (int a = 0; a < d.NR; a += crows) {
     const int b = a + crows < d.NR ? a + crows : d.NR;
@@ -118,29 +194,60 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
     RC(P.mark(c.stream));
     RC(run_form_rows(g, grid, form_done, hi));
     RC(P.mark(c.stream));
-    CUDA_TRY(cudaStreamWaitEvent(P.copy, P.ev.back(), 0));
-    for (int i = 0; i < 5; ++i)
-      if (fouts[i])
-        RC(d2h_2d(fouts[i] + (size_t)form_done * d.NC, (size_t)d.NC * 8, g->form[i] + (size_t)form_done * d.pitch,
-                  (size_t)d.pitch * 8, (size_t)d.NC * 8, hi - form_done, P.copy));
+    if (pack) RC(run_form_pack(g, packed, form_done, hi, pack_flags));
+    cudaEvent_t ready;
+    CUDA_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+    P.aux.push_back(ready);
+    CUDA_TRY(cudaEventRecord(ready, c.stream));
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      chunks.push_back({form_done, hi, ready});
+      produced = chunks.size();
+    }
+    cv.notify_all();
     form_done = hi;
   }
+  { std::lock_guard<std::mutex> lk(mu); closed = true; }
+  cv.notify_all();
   const size_t ev_end = P.ev.size();
   RC(P.mark(c.stream));
   up1 = P.ev.back();
   RC(litap_grid_ddir(g, invert));
   if (want_shed) RC(litap_grid_shed(g));
   CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
-  RC(down(ddir, g->d, g->ddir));
-  RC(down(flatcell, g->d, g->flat));
+  // results that go into pinned memory are plain asynchronous copies: they can start while the helper is still busy;
+  // pageable destinations need the staging buffers the helper holds
+  struct Small { void* dst; const void* src; size_t esize; };
+  std::vector<Small> small;
+  small.push_back({ddir, g->ddir, 1});
+  small.push_back({flatcell, g->flat, 1});
   if (want_shed) {
-    RC(down(shed, g->d, g->shed));
-    RC(down(upslope, g->d, g->upslope));
-    RC(down(ridge, g->d, g->ridge));
+    small.push_back({shed, g->shed, 4});
+    small.push_back({upslope, g->upslope, 4});
+    small.push_back({ridge, g->ridge, 1});
     if (npits) *npits = g->npits;
   }
+  auto send_small = [&](const Small& x) -> int {
+    if (!x.dst) return LITAP_OK;
+    if (!x.src) return set_error(LITAP_ECUDA, "internal: result array missing on the device");
+    return d2h_2d(x.dst, (size_t)d.NC * x.esize, x.src, (size_t)d.pitch * x.esize, (size_t)d.NC * x.esize, d.NR, c.stream);
+  };
+  for (const Small& x : small)
+    if (x.dst && !hostcopy_is_pageable(x.dst)) RC(send_small(x));
+  if (helper.joinable()) helper.join();
+  if (helper_rc) return set_error(helper_rc, helper_err);
+  for (const Small& x : small)
+    if (x.dst && hostcopy_is_pageable(x.dst)) RC(send_small(x));
   CUDA_TRY(cudaStreamSynchronize(P.copy));
   RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));  // what is left of the downloads after the last stage
+  if (pack) {   // an output with a value its integer does not reproduce (|k| >= 2^31) goes again, as doubles
+    int hf[5] = {0, 0, 0, 0, 0};
+    CUDA_TRY(cudaMemcpy(hf, pack_flags, sizeof(hf), cudaMemcpyDeviceToHost));
+    bool again = false;
+    for (int i = 0; i < 5; ++i)
+      if (fouts[i] && hf[i]) { RC(down(fouts[i], g->d, g->form[i])); again = true; }
+    if (again) RC(timed_sync(&c.tm.d2h_ms, c.ev[6], c.ev[7]));
+  }
   {
     float ms = 0;
     cudaEventElapsedTime(&ms, up0, up1);   // first upload .. last upload, with the form kernels between them

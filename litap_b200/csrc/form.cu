@@ -277,3 +277,43 @@ int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi) {
 
 // called by litap_shutdown through pool_release_all(): the table is pool-owned
 void form_forget_trig() { g_trig = nullptr; g_qtab = nullptr; g_qtab_grid = 0.0; }
+
+// ---- packed downloads (litap_flow_form): every output of calc_form is a rounded number -- k / 1000, whole degrees for
+// aspect --, so rows [row_lo, row_hi) can cross PCIe as the int32 k (half the bytes) and be widened on the host with the
+// same correctly rounded quotient (hostexpand.cpp).  NA -> INT32_MIN, -0 -> INT32_MIN + 1.  A value that its integer does
+// not reproduce bit for bit (|k| >= 2^31: slopes above 2 million per cent) raises the output's flag; the caller then
+// downloads that output as fp64.
+struct PackPtrs { const double* in[5]; int32_t* out[5]; };
+__global__ void __launch_bounds__(256) k_form_pack(GridDims d, PackPtrs P, int row_lo, int row_hi, int* __restrict__ flags) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = row_lo + blockIdx.y;
+  if (c >= d.NC || r >= row_hi) return;
+  const size_t id = (size_t)r * d.pitch + c;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    if (!P.out[i]) continue;
+    const double v = P.in[i][id];
+    int32_t k;
+    bool ok = true;
+    if (is_nan(v)) k = INT32_MIN;
+    else if (v == 0.0) k = __double_as_longlong(v) < 0 ? INT32_MIN + 1 : 0;
+    else {
+      const double kd = i == 2 ? v : rint(v * 1000.0);
+      ok = fabs(kd) < 2147483000.0;
+      k = ok ? (int32_t)kd : 0;
+      const double back = i == 2 ? (double)k : (double)k / 1000.0;
+      ok = ok && __double_as_longlong(back) == __double_as_longlong(v);
+    }
+    if (!ok) flags[i] = 1;
+    P.out[i][id] = k;
+  }
+}
+int run_form_pack(litap_grid* g, int32_t* const* out, int row_lo, int row_hi, int* flags) {
+  const GridDims d = g->d;
+  if (row_lo >= row_hi) return LITAP_OK;
+  PackPtrs P;
+  for (int i = 0; i < 5; ++i) { P.in[i] = g->form[i]; P.out[i] = out[i]; }
+  dim3 grid((d.NC + 255) / 256, row_hi - row_lo);
+  KERNEL("k_form_pack", k_form_pack<<<grid, 256, 0, ctx().stream>>>(d, P, row_lo, row_hi, flags));
+  return LITAP_OK;
+}

@@ -18,6 +18,8 @@
 #include <vector>
 #include "litap_internal.h"
 
+extern "C" void litap_host_expand_i32(const int32_t* src, double* dst, size_t n, int kind);   // hostexpand.cpp
+
 namespace {
 #define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
 constexpr size_t HC_STAGE = 64u << 20;
@@ -70,7 +72,7 @@ bool pageable(const void* p) {
 }
 // A chunk that is on its way into a staging buffer: the host copy happens when the buffer is needed again or at
 // hostcopy_flush(), so that the copy of one chunk overlaps the transfer of the next one across calls too.
-struct Pending { bool on = false; char* dst = nullptr; size_t dpitch = 0, width = 0, nrows = 0, bytes = 0; };
+struct Pending { bool on = false; char* dst = nullptr; size_t dpitch = 0, width = 0, nrows = 0, bytes = 0; int kind = 0; };   // kind 1 / 2: int32 -> fp64
 Pending g_pend[2];
 int g_next = 0;
 double g_wait_ms = 0, g_copy_ms = 0, g_bytes = 0;
@@ -84,13 +86,36 @@ int complete(int b) {
   const auto t1 = std::chrono::steady_clock::now();
   const int nt = copy_threads();
   const char* s = (const char*)g_stage[b];
-  if (!p.nrows) host_copy(p.dst, s, p.bytes, nt);
+  if (p.kind) {   // packed download: width int32 per row in the staging buffer -> width doubles per row of the destination
+    const size_t ncol = p.width, total = ncol * p.nrows;
+    const int32_t* src = (const int32_t*)s;
+    auto piece = [&](size_t lo, size_t hi) {   // elements [lo, hi) of the dense chunk, row by row where the destination is pitched
+      if (p.dpitch == ncol * 8) { litap_host_expand_i32(src + lo, (double*)p.dst + lo, hi - lo, p.kind); return; }
+      while (lo < hi) {
+        const size_t r = lo / ncol, c = lo % ncol, n = std::min(hi - lo, ncol - c);
+        litap_host_expand_i32(src + lo, (double*)(p.dst + r * p.dpitch) + c, n, p.kind);
+        lo += n;
+      }
+    };
+    if (nt <= 1 || total < (1u << 18)) piece(0, total);
+    else {
+      std::vector<std::thread> th;
+      const size_t per = ((total + nt - 1) / nt + 15) & ~(size_t)15;
+      for (int t = 1; t < nt; ++t) {
+        const size_t lo = std::min(total, per * t), hi = std::min(total, per * (t + 1));
+        if (hi > lo) th.emplace_back([=] { piece(lo, hi); });
+      }
+      piece(0, std::min(total, per));
+      for (auto& x : th) x.join();
+    }
+  }
+  else if (!p.nrows) host_copy(p.dst, s, p.bytes, nt);
   else if (p.dpitch == p.width) host_copy(p.dst, s, p.nrows * p.width, nt);
   else for (size_t r = 0; r < p.nrows; ++r) memcpy(p.dst + r * p.dpitch, s + r * p.width, p.width);
   const auto t2 = std::chrono::steady_clock::now();
   g_wait_ms += std::chrono::duration<double, std::milli>(t1 - t0).count();
   g_copy_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
-  g_bytes += p.nrows ? (double)p.nrows * p.width : (double)p.bytes;
+  g_bytes += p.kind ? (double)p.nrows * p.width * 4 : p.nrows ? (double)p.nrows * p.width : (double)p.bytes;
   return LITAP_OK;
 }
 }  // namespace
@@ -118,7 +143,7 @@ int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
     else CUDA_TRY(cudaMemcpyAsync(g_stage[b], s, bytes, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaEventRecord(g_stage_ev[b], st));
     Pending& p = g_pend[b];
-    p.on = true; p.dst = (char*)dst + row * dpitch + off; p.dpitch = dpitch; p.width = width; p.nrows = nrows; p.bytes = bytes;
+    p.on = true; p.dst = (char*)dst + row * dpitch + off; p.dpitch = dpitch; p.width = width; p.nrows = nrows; p.bytes = bytes; p.kind = 0;
     g_next ^= 1;
     return LITAP_OK;
   };
@@ -128,6 +153,30 @@ int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
   } else {
     for (size_t r = 0; r < rows; ++r)
       for (size_t o = 0; o < width; o += stage) RC(send(r, o, 0, std::min(stage, width - o)));
+  }
+  return LITAP_OK;
+}
+
+// rows x ncol int32 from pitched device memory, widened to fp64 (kind 1: k / 1000, kind 2: k; INT32_MIN = NA) on their way
+// into dense-or-pitched host memory.  Always staged (pinned destinations too): the host threads do the widening.
+int d2h_2d_i32_expand(double* dst, size_t dpitch, const int32_t* src, size_t spitch, size_t ncol, size_t rows, int kind, cudaStream_t st) {
+  if (!rows || !ncol) return LITAP_OK;
+  RC(stage_init());
+  const size_t width = ncol * 4;
+  if (width > HC_STAGE) return set_error(LITAP_EARG, "packed download: a row does not fit the staging buffer");
+  if (pageable(dst)) advise_hugepages(dst, (rows - 1) * dpitch + ncol * 8);
+  size_t stage = HC_STAGE;
+  if (const char* e = getenv("LITAP_STAGE_KB")) stage = std::min(HC_STAGE, std::max<size_t>(width, (size_t)atol(e) << 10));
+  const size_t per = std::max<size_t>(1, stage / width);
+  for (size_t r = 0; r < rows; r += per) {
+    const size_t nr = std::min(per, rows - r);
+    const int b = g_next;
+    RC(complete(b));
+    CUDA_TRY(cudaMemcpy2DAsync(g_stage[b], width, (const char*)src + r * spitch, spitch, width, nr, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(g_stage_ev[b], st));
+    Pending& p = g_pend[b];
+    p.on = true; p.dst = (char*)dst + r * dpitch; p.dpitch = dpitch; p.width = ncol; p.nrows = nr; p.bytes = 0; p.kind = kind;
+    g_next ^= 1;
   }
   return LITAP_OK;
 }
@@ -191,6 +240,8 @@ int hostcopy_staging(int which, void* buf[2], cudaEvent_t ev[2], size_t* bytes) 
   *bytes = HC_STAGE;
   return LITAP_OK;
 }
+
+bool hostcopy_is_pageable(const void* p) { return pageable(p); }
 
 // completes the staged downloads (older buffer first)
 int hostcopy_flush() {

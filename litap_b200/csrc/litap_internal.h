@@ -121,7 +121,9 @@ void pool_free(void* p);
 void pool_release_all();
 // hostcopy.cu: device -> caller memory; pageable destinations go through pinned staging buffers + host threads
 int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st);
+int d2h_2d_i32_expand(double* dst, size_t dpitch, const int32_t* src, size_t spitch, size_t ncol, size_t rows, int kind, cudaStream_t st);
 int h2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows, cudaStream_t st);
+bool hostcopy_is_pageable(const void* p);   // would d2h_2d stage a copy into p?
 int hostcopy_flush();    // pageable destinations are complete after this
 void hostcopy_reset();   // start of a call: forget chunks a failed call left pending
 void hostcopy_forget_staging();
@@ -198,6 +200,7 @@ int run_ddir(litap_grid* g, int invert);               // ddir.cu
 int run_shed(litap_grid* g);                           // shed.cu
 int run_form(litap_grid* g, double grid_m);            // form.cu
 int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi);  // form.cu: a row range (pipelined upload)
+int run_form_pack(litap_grid* g, int32_t* const* out, int row_lo, int row_hi, int* flags);  // form.cu: outputs as int32 (packed downloads)
 void form_forget_trig();                               // form.cu (pool-owned table dropped at shutdown)
 int run_weti(litap_grid* g, double grid_m);            // weti.cu
 int run_uced(litap_grid* g);                           // uced.cu

@@ -237,3 +237,29 @@ def test_flt_header_parser_needs_no_device(tmp_path):
     (tmp_path / "bad.hdr").write_text("cellsize 1\n")
     assert lb.lib().litap_flt_info(str(tmp_path / "bad.hdr").encode(), C.byref(info)) != 0
     assert b"ncols" in lb.lib().litap_last_error()
+
+
+def test_host_expand_i32_equals_division():
+    """hostexpand.cpp (packed form downloads): the AVX2 + FMA widening k -> k / 1000 must be the IEEE quotient for every
+    int32 pattern class, NA (INT32_MIN) -> NaN, INT32_MIN + 1 -> -0, unaligned destinations included."""
+    import litap_b200 as lb
+    L = lb.lib()
+    i32 = np.ctypeslib.ndpointer(np.int32, flags="C")
+    f64 = np.ctypeslib.ndpointer(np.float64)
+    for fn in (L.litap_host_expand_i32, L.litap_host_expand_i32_ref):
+        fn.argtypes = [i32, f64, C.c_size_t, C.c_int]
+        fn.restype = None
+    rng = np.random.default_rng(3)
+    k = np.concatenate([rng.integers(-2**31 + 2, 2**31 - 1, 3_000_000), np.arange(-70_000, 70_000),
+                        rng.integers(-360_000, 360_000, 1_000_000), [-2**31, -2**31 + 1, 0, 2**31 - 1]]).astype(np.int32)
+    for kind in (1, 2):
+        for off in (0, 1, 3):
+            a = np.zeros(k.size + 4)
+            b = np.zeros(k.size + 4)
+            L.litap_host_expand_i32(k, a[off:off + k.size], k.size, kind)
+            L.litap_host_expand_i32_ref(k, b[off:off + k.size], k.size, kind)
+            assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), (kind, off)
+        want = k.astype(np.float64) / (1000.0 if kind == 1 else 1.0)
+        ok = (k != -2**31) & (k != -2**31 + 1)
+        assert np.array_equal(b[3:3 + k.size][ok], want[ok])
+        assert np.isnan(b[3:3 + k.size][k == -2**31]).all() and np.signbit(b[3:3 + k.size][k == -2**31 + 1]).all()
