@@ -377,7 +377,10 @@ def run_ours(a):
         e2e_ms = float(t.item()) / es
         e2e = {"value": cells_job / (e2e_ms * 1e-3) / 1e6, "unit": "Mcells/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": es,
-               "api": "litap_flow_form (C ABI, pinned host buffers)"}
+               "api": "litap_flow_form (C ABI, pinned host buffers)",
+               "wire_d2h_bytes_per_step": (d2h - 20 * NR * NC) if os.environ.get("LITAP_FORM_PACK", "1") != "0" else d2h,
+               "note": "d2h_bytes_per_step = bytes delivered into the caller's arrays; the five calc_form outputs cross PCIe "
+                       "as int32 thousandths and are widened to fp64 by host threads (bit-identical), unless LITAP_FORM_PACK=0"}
         del pinned
         # the same call with PAGEABLE buffers, fresh result arrays every call: what an R caller (fresh R vectors) sees
         e_page = np.array(e_np)
