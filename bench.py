@@ -464,6 +464,17 @@ def run_ours(a):
                         "the cells upslope of them, not one pass over the DEM; alg. bytes = elev 8 + ddir 1 + shed 4 + uced 8"}
         lb.lib().litap_pool_trim()
 
+    # ---- pit_stat1 (not part of the composite metric): pour points of the DEM's initial sheds
+    pitstat = None
+    if world == 1 and not a.no_weti:
+        g.pit_stat("landmapr")
+        tbl = g.pit_stat("landmapr")
+        tp = lb.timings()
+        pitstat = {"ms": tp["pitstat_ms"], "Mcells_per_s": n * n / tp["pitstat_ms"] / 1e3, "sheds": int(len(tbl["shedno"])),
+                   "method": "landmapr", "note": "device part of pit_stat1 on the resident grid (table of 21 columns back to the host included)"}
+        del tbl
+        lb.lib().litap_pool_trim()
+
     # ---- calc_relz + calc_length (not part of the composite metric) on the flow field of a
     # 4096^2 DEM through the host-buffer C ABI (11 input grids up, 39 double grids down)
     relz = None
@@ -572,7 +583,7 @@ def run_ours(a):
                        "npits": stage["npits"], "flat_cells": stage["flat_cells"]},
             "clocks": clocks, "e2e": e2e if e2e is not None else ({"value": None, "note": e2e_note} if e2e_note else None),
             "gpu_launches": nl, "checks": checks, "extra": extra,
-            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "file_to_files": files, "weti": weti, "slope_gc": gc, "uced": uced, "relz": relz,
+            "roofline": roof, "roofline_frac_by_kernel": rf_all, "per_kernel": per_kernel, "file_to_files": files, "weti": weti, "slope_gc": gc, "uced": uced, "pit_stat": pitstat, "relz": relz,
             "cpu_baseline": cpu}) + "\n").encode())
     if world == 1:
         g.close()

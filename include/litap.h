@@ -191,7 +191,10 @@ int litap_grid_ddir(litap_grid* g, int invert);
 int litap_grid_shed(litap_grid* g);
 int litap_grid_form(litap_grid* g, double grid_m);
 int litap_grid_weti(litap_grid* g, double grid_m);
-int litap_grid_uced(litap_grid* g);   /* needs ddir and shed on the grid (litap_grid_ddir + litap_grid_shed); result "uced" */
+int litap_grid_uced(litap_grid* g);
+/* pit_stat1 on the shed / upslope / ridge columns litap_grid_shed left on the grid (shed = "initial_shed"); edge_map is
+ * derived from the elevations on the device.  Table as for litap_pit_stat. */
+int litap_grid_pit_stat(litap_grid* g, int method, int64_t cap, double* const* out, int64_t* nrows);   /* needs ddir and shed on the grid (litap_grid_ddir + litap_grid_shed); result "uced" */
 int litap_grid_slope_gc(litap_grid* g, double grid_m);
 /* calc_form + calc_ddir2 + calc_shed4 as one call: form overlaps the flow stages on a second stream */
 int litap_grid_flow_form(litap_grid* g, double grid_m, int invert);

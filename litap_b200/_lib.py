@@ -13,7 +13,7 @@ SYMBOLS = [
     "litap_set_stream", "litap_profile_enable", "litap_profile_report",
     "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_uced", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
-    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_pit_stat", "litap_pit_stat_names", "litap_flt_info", "litap_grid_read_flt", "litap_grid_write_raw", "litap_grid_write_raw_many", "litap_grid_slope_gc", "litap_grid_flow_form",
+    "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_pit_stat", "litap_pit_stat_names", "litap_grid_pit_stat", "litap_flt_info", "litap_grid_read_flt", "litap_grid_write_raw", "litap_grid_write_raw_many", "litap_grid_slope_gc", "litap_grid_flow_form",
     "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
@@ -59,6 +59,7 @@ def load():
     L.litap_init.argtypes = [ci]
     L.litap_shutdown.restype = None
     L.litap_pit_stat.argtypes = [vp] * 6 + [i64, i64, C.c_int, i64, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    L.litap_grid_pit_stat.argtypes = [vp, C.c_int, i64, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     L.litap_pit_stat_names.restype = C.POINTER(C.c_char_p)
     L.litap_pit_stat_names.argtypes = [C.POINTER(C.c_int)]
     L.litap_flt_info.argtypes = [C.c_char_p, C.POINTER(RasterInfo)]

@@ -388,6 +388,16 @@ class DeviceGrid:
     def uced(self):
         check(lib().litap_grid_uced(self._h))
 
+    def pit_stat(self, method="landmapr"):
+        """pit_stat1 on the grid's own initial sheds (after shed()): dict of columns, one row per shed with a pour point."""
+        names = pit_stat_names()
+        cap = max(1, int(self.npits))
+        out = {k: np.full(cap, np.nan) for k in names}
+        ptrs = (C.c_void_p * len(names))(*[out[k].ctypes.data for k in names])
+        n = C.c_int64(0)
+        check(lib().litap_grid_pit_stat(self._h, {"litap": 0, "landmapr": 1}[method], cap, ptrs, C.byref(n)))
+        return {k: v[:n.value] for k, v in out.items()}
+
     def slope_gc(self, grid):
         check(lib().litap_grid_slope_gc(self._h, float(grid)))
 

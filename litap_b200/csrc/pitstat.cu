@@ -272,6 +272,21 @@ __global__ void __launch_bounds__(PT) k_ps_first_pit(In I, unsigned* out) {
   if (I.ddir[id] == 5 && !is_nan(I.elev[id])) atomicMin(out, (unsigned)id);
 }
 
+// edge_map of load_file() (R/LITAP_load.R:255-267): cells with a buffer (ring) or missing neighbour
+__global__ void __launch_bounds__(PT) k_ps_edge_map(const double* __restrict__ elev, GridDims d, uint8_t* __restrict__ edge) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y;
+  if (c >= d.NC) return;
+  const size_t id = (size_t)r * d.pitch + c;
+  uint8_t e = 0;
+  if (r > 0 && c > 0 && r < d.NR - 1 && c < d.NC - 1 && !is_nan(elev[id])) {
+#pragma unroll
+    for (int n = 1; n <= 9; ++n)
+      if (n != 5 && is_nan(elev[id + nb_off(n, d.pitch)])) e = 1;
+  }
+  edge[id] = e;
+}
+
 }  // namespace pitstat
 
 namespace {
@@ -450,5 +465,30 @@ int run_pit_stat(litap_grid* g, const uint8_t* edge, int method, int64_t cap, do
   for (int k = 0; k < NCOL; ++k)
     if (out[k]) CUDA_TRY(cudaMemcpyAsync(out[k], O.c[k], (size_t)wr * 8, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
+  return LITAP_OK;
+}
+
+// pit_stat1 on a resident grid: the shed / upslope / ridge columns calc_shed4 left on it (shed = "initial_shed"), the
+// edge_map derived from the elevations on the device
+extern "C" int litap_grid_pit_stat(litap_grid* g, int method, int64_t cap, double* const* out, int64_t* nrows) {
+  ApiLock api_lock_;   // one host thread at a time (include/litap.h)
+  if (!g || !out || !nrows) return set_error(LITAP_EARG, "litap_grid_pit_stat: NULL");
+  if (method != 0 && method != 1) return set_error(LITAP_EARG, "litap_grid_pit_stat: method must be 0 (litap) or 1 (landmapr)");
+  if (g->nbands > 0) return set_error(LITAP_EARG, "litap_grid_pit_stat: not available on a row band (run it on a whole-DEM grid)");
+  if (!g->ddir || !g->shed || !g->upslope || !g->ridge) return set_error(LITAP_EARG, "litap_grid_pit_stat: needs ddir, shed, upslope and ridge on the grid");
+  Ctx& c = ctx();
+  const int64_t l0 = c.launches;
+  uint8_t* edge = grid_alloc_array<uint8_t>(g->d, 0);
+  if (!edge) return set_error(LITAP_ENOMEM, "device allocation failed (edge_map)");
+  struct EdgeFree { uint8_t* p; ~EdgeFree() { cudaStreamSynchronize(ctx().stream); grid_free_array(p); } } ef{edge};
+  CUDA_TRY(cudaEventRecord(c.ev[6], c.stream));
+  dim3 cgrid(nblk(g->d.NC, pitstat::PT), g->d.NR);
+  KERNEL("k_ps_edge_map", pitstat::k_ps_edge_map<<<cgrid, pitstat::PT, 0, c.stream>>>(g->elev, g->d, edge));
+  int rc = run_pit_stat(g, edge, method, cap, out, nrows);
+  if (rc) return rc;
+  CUDA_TRY(cudaEventRecord(c.ev[7], c.stream));
+  CUDA_TRY(cudaEventSynchronize(c.ev[7]));
+  cudaEventElapsedTime(&c.tm.pitstat_ms, c.ev[6], c.ev[7]);
+  c.tm.kernel_launches = c.launches - l0;
   return LITAP_OK;
 }

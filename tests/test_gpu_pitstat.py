@@ -60,3 +60,16 @@ def test_pit_stat_single_shed_and_subset():
     sub = lb.pit_stat1(db, w=[2, 5, 9], method="litap")
     assert sub["shedno"].tolist() == [2.0, 5.0, 9.0]
     assert (sub["pour_elev"] == full["pour_elev"][np.isin(full["shedno"], [2, 5, 9])]).all()
+
+
+def test_pit_stat_on_the_grid():
+    """litap_grid_pit_stat: the columns calc_shed4 left on a resident grid, edge_map derived on the device."""
+    g = lb.DeviceGrid(302, 259)
+    g.synth(seed=6, na_permille=5)
+    g.ddir(); g.shed()
+    e, d, s, u, r = (g.download(k) for k in ("elev", "ddir", "shed", "upslope", "ridge"))
+    for m in ("litap", "landmapr"):
+        want = oracle.pit_stat(e, d, s, u.astype(np.int64), r, pf.edge_map_of(e), m)
+        pf.same_table(g.pit_stat(m), want)
+    assert lb.timings()["pitstat_ms"] > 0
+    g.close()
