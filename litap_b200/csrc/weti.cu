@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(WT) k_weti_queries(Arrays A, GridDims d, unsig
 
 // linear map elevation -> bucket, monotone: a cell in a lower bucket is visited before one in a higher bucket
 struct BucketMap { double emax, scale; };
-__device__ __forceinline__ BucketMap bucket_map(const Arrays& A) {
+__device__ __forceinline__ BucketMap bucket_map_compute(const Arrays& A) {
   BucketMap m;
   m.emax = f64_from_orderable(~A.qhi[0]);
   const double emin = f64_from_orderable(~A.qhi[A.nq - 1]);
@@ -204,11 +204,20 @@ __device__ __forceinline__ int bucket_of(const BucketMap& m, double e) {
   if (!(t < (double)(NT - 1))) return NT - 1;
   return (int)t;
 }
+// the map is computed once (k_weti_table stores it behind the table) and loaded by the 67 M lookups
+__device__ __forceinline__ BucketMap bucket_map(const Arrays& A) {
+  const double2 v = __ldg(reinterpret_cast<const double2*>(A.table + NT + 4));
+  BucketMap m;
+  m.emax = v.x;
+  m.scale = v.y;
+  return m;
+}
 // table[b] = number of queries in buckets < b
 __global__ void k_weti_table(Arrays A, unsigned* __restrict__ table) {
   const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > (unsigned)NT) return;
-  const BucketMap m = bucket_map(A);
+  const BucketMap m = bucket_map_compute(A);
+  if (b == 0) *reinterpret_cast<double2*>(table + NT + 4) = make_double2(m.emax, m.scale);
   unsigned lo = 0, hi = A.nq;
   while (lo < hi) {
     const unsigned mid = (lo + hi) >> 1;
@@ -305,12 +314,10 @@ __device__ __forceinline__ void warp_push(const Arrays& A, unsigned& pushq, cons
 // ------------------------------------------------------------------------------------------------
 // topology word and state of every cell: S, donors in visiting order, successors, pending counter; seeds;
 // last-setter slots
-__global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K) {
-  __shared__ uint32_t s_ids[WT];
-  __shared__ unsigned long long s_tps[WT];
-  __shared__ unsigned s_n;
-  if (threadIdx.x == 0) s_n = 0;
-  __syncthreads();
+__global__ void __launch_bounds__(WT, 4) k_weti_nodes(Arrays A, GridDims d, WetiK K) {
+  bool seed = false;          // a cell without donors: ready from the start
+  uint32_t seed_id = 0;
+  unsigned long long seed_tp = 0;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const int r = blockIdx.y;
   if (c < d.NC) {
@@ -339,7 +346,10 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
         const size_t nid = id + nb_off(n, d.pitch);
         const uint8_t nc = A.cls[nid];
         if (nc == CLS_A) {
-          if (weti_tan(e[n], f, 10 - n, K) > 0) dmask |= 1u << n;   // the same test that sets the donor's succ bit
+          // the same test that sets the donor's succ bit: tan > 0.  A difference above 1e-280 cannot underflow on its way
+          // through / d * l (cell sizes are within 1e-30 .. 1e30 or the reciprocals are off), so only tiny ones are computed
+          const double df = e[n] - f;
+          if (df > 1e-280 ? K.rorth != 0.0 || weti_tan(e[n], f, 10 - n, K) > 0 : weti_tan(e[n], f, 10 - n, K) > 0) dmask |= 1u << n;
         } else if (nc == CLS_B && A.ddir[nid] == 10 - n) {
           if (visited_before(A, e[n], nid, f, id)) { dmask |= 1u << n; bdon |= 1u << n; }
         }
@@ -367,11 +377,7 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
         if ((bdon >> n) & 1) tp |= 1ull << (TP_BM + pos[n]);
       }
       tp |= (unsigned long long)nd | ((unsigned long long)succ << (TP_SUCC - 1)) | ((unsigned long long)cls << TP_CLS);
-      if (nd == 0) {
-        const unsigned k = atomicAdd(&s_n, 1u);
-        s_ids[k] = (uint32_t)id;
-        s_tps[k] = tp;
-      }
+      if (nd == 0) { seed = true; seed_id = (uint32_t)id; seed_tp = tp; }
       const double unset = __longlong_as_double((long long)UNSET);
       double4* sp = reinterpret_cast<double4*>(A.st + id * ST_N);
       sp[0] = make_double4(unset, unset, f, S);
@@ -385,24 +391,24 @@ __global__ void __launch_bounds__(WT) k_weti_nodes(Arrays A, GridDims d, WetiK K
     }
     A.topo[id] = tp;
   }
-  __syncthreads();
-  // seeds of this block -> one ready queue (overflow goes on to the next)
-  unsigned n = s_n;
-  if (!n) return;
-  __shared__ unsigned s_base;
-  unsigned q = (blockIdx.y * gridDim.x + blockIdx.x) % NQ;
-  unsigned at = 0;
-  while (n) {
-    if (threadIdx.x == 0) s_base = atomicAdd(&A.qtail[q].v, n);
-    __syncthreads();
-    const unsigned base = s_base;
-    const unsigned fit = base >= A.qcap ? 0u : min(n, A.qcap - base);
-    for (unsigned k = threadIdx.x; k < fit; k += blockDim.x)
-      A.order[(size_t)q * A.qcap + base + k] = make_ulonglong2(s_tps[at + k], (unsigned long long)s_ids[at + k]);
-    at += fit;
-    n -= fit;
+  // seeds of this warp -> one ready queue, one atomic per warp (an entry that does not fit goes on to the next queue)
+  unsigned q = (blockIdx.y * gridDim.x + blockIdx.x + (threadIdx.x >> 5)) % NQ;
+  const int lane = threadIdx.x & 31;
+  for (int tries = 0; tries < NQ; ++tries) {
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, seed);
+    if (!m) break;
+    const int leader = __ffs(m) - 1;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(&A.qtail[q].v, (unsigned)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (seed) {
+      const unsigned idx = base + __popc(m & ((1u << lane) - 1));
+      if (idx < A.qcap) {
+        A.order[(size_t)q * A.qcap + idx] = make_ulonglong2(seed_tp, (unsigned long long)seed_id);
+        seed = false;
+      }
+    }
     q = (q + 1) % NQ;
-    __syncthreads();
   }
 }
 
@@ -775,7 +781,7 @@ int run_weti(litap_grid* g, double grid_m) {
   A.order = S.get<ulonglong2>((size_t)NQ * qcap);
   A.qcap = qcap;
   unsigned char* ctlmem = S.get<unsigned char>(sizeof(Ctl) + 2 * NQ * sizeof(QCount) + 256);
-  unsigned* table = S.get<unsigned>(NT + 1);
+  unsigned* table = S.get<unsigned>(NT + 4 + 4);   // [NT + 1] counts, then (16-byte aligned) the bucket map
   if (!A.topo || !A.st || !A.cls || !A.order || !ctlmem || !table)
     return set_error(LITAP_ENOMEM, "device allocation failed (weti scratch)");
   A.qtail = reinterpret_cast<QCount*>(ctlmem);
