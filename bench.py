@@ -558,7 +558,50 @@ def run_ours(a):
                      "cells_with_a_shed": cells64, "sum_upslope_at_pits": pits64,
                      "conservation": cells64 == pits64 == 65536 * 65536,
                      "note": "upslope is a 32-bit count: litap_bands_shed refuses a DEM in which a basin reaches 2^32 cells "
-                             "(this conservation test, inside the library); e2e at this size: see profiles/"}
+                             "(this conservation test, inside the library)"}
+            # end to end at this size: every band's rows up from pinned host memory, the step, every result down.  The ten
+            # results of a band are 31.7 GB; they go through ONE pinned buffer per rank (the largest result, 4.3 GB) in
+            # turn, so that the host needs 8 x 8.6 GB of pinned memory instead of 8 x 36 GB: same bytes over PCIe.
+            if not a.no_e2e:
+                import psutil
+                r0, nown = g64.rows(0)
+                NC64 = 65536 + 2
+                need = (8192 + 3) * NC64 * 8 + nown * NC64 * 8
+                if need * world * 2 < psutil.virtual_memory().available:
+                    hin = torch.empty((8192 + 3, NC64), dtype=torch.float64).pin_memory()
+                    _lib.check(lb.lib().litap_grid_download(g64._h[0], b"elev", hin.numpy().ctypes.data))
+                    rows64 = hin.numpy()[1:]
+                    hout = torch.empty((nown, NC64), dtype=torch.float64).pin_memory()
+                    views = {"ddir": np.uint8, "flatcell": np.uint8, "shed": np.int32, "upslope": np.uint32, "ridge": np.uint8,
+                             "slope_pct": np.float64, "slope_deg": np.float64, "aspect": np.float64, "prof": np.float64,
+                             "plan": np.float64}
+                    flat = hout.numpy().reshape(-1).view(np.uint8)
+
+                    def e2e64():
+                        g64.upload_rows(rows64)
+                        g64.flow_form(GRID_M)
+                        for k, dt in views.items():
+                            nb = nown * NC64 * np.dtype(dt).itemsize
+                            g64.download_into(k, flat[:nb].view(dt).reshape(nown, NC64))
+
+                    e2e64()
+                    barrier()
+                    ev0.record(stream)
+                    e2e64()
+                    ev1.record(stream)
+                    barrier()
+                    t = torch.tensor([ev0.elapsed_time(ev1)], device="cuda")
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    up_b = rows64.nbytes * world
+                    dn_b = sum(nown * NC64 * np.dtype(dt).itemsize for dt in views.values()) * world
+                    extra["e2e"] = {"ms_per_step": float(t.item()), "value": 65536 * 65536 / (float(t.item()) * 1e-3) / 1e6,
+                                    "unit": "Mcells/s", "h2d_bytes_per_step": up_b, "d2h_bytes_per_step": dn_b, "steps": 1,
+                                    "GBps_total": (up_b + dn_b) / (float(t.item()) * 1e-3) / 1e9,
+                                    "note": "per-band pinned host buffers; the ten results of a band pass through one pinned "
+                                            "buffer in turn (host memory), same bytes over PCIe"}
+                    del hin, hout
+                else:
+                    extra["e2e"] = {"value": None, "note": "skipped: not enough free host memory for the pinned buffers"}
             g64.close()
 
     if rank == 0:
