@@ -118,8 +118,6 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   uint32_t khi[CPT], klo[CPT];
   int term[CPT];  // 4 * local index of the terminal; 0 = NA (the ring corner is never a terminal)
   const uint32_t a_khi = smem_addr(s_khi), a_klo = smem_addr(s_klo), a_kid = smem_addr(s_kid);
-  // neighbouring cells of a row mostly drain to the same terminal: a thread folds runs of equal terminals among its 8
-  // cells before it touches shared memory (the REDs of a catchment all hit one address and serialise there)
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
@@ -127,43 +125,18 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
     const unsigned long long key = f64_orderable(ev[k]);
     khi[k] = (uint32_t)(key >> 32);
     klo[k] = (uint32_t)key;
-  }
-  {
-    uint32_t run = khi[0];
-#pragma unroll
-    for (int k = 0; k < CPT; ++k) {
-      if (k) run = term[k] == term[k - 1] ? max(run, khi[k]) : khi[k];
-      if (term[k] && (k == CPT - 1 || term[k + 1] != term[k])) red_max_u32(a_khi + term[k], run);
-    }
+    if (term[k]) red_max_u32(a_khi + term[k], khi[k]);
   }
   __syncthreads();
-  {
-    uint32_t run = 0;
-    int rt = 0;   // terminal of the open run (0 = none)
 #pragma unroll
-    for (int k = 0; k < CPT; ++k) {
-      if (!(term[k] && khi[k] == lds_u32(a_khi + term[k]))) term[k] = 0;  // out of the race
-      if (term[k]) {
-        if (rt == term[k]) run = max(run, klo[k]);
-        else { if (rt) red_max_u32(a_klo + rt, run); rt = term[k]; run = klo[k]; }
-      }
-    }
-    if (rt) red_max_u32(a_klo + rt, run);
+  for (int k = 0; k < CPT; ++k) {
+    if (term[k] && khi[k] == lds_u32(a_khi + term[k])) red_max_u32(a_klo + term[k], klo[k]);
+    else term[k] = 0;  // out of the race
   }
   __syncthreads();
-  {
-    uint32_t run = 0;
-    int rt = 0;
 #pragma unroll
-    for (int k = 0; k < CPT; ++k) {
-      if (term[k] && klo[k] == lds_u32(a_klo + term[k])) {
-        const uint32_t cid = (uint32_t)(cell0 + k);
-        if (rt == term[k]) run = min(run, cid);
-        else { if (rt) red_min_u32(a_kid + rt, run); rt = term[k]; run = cid; }
-      }
-    }
-    if (rt) red_min_u32(a_kid + rt, run);
-  }
+  for (int k = 0; k < CPT; ++k)
+    if (term[k] && klo[k] == lds_u32(a_klo + term[k])) red_min_u32(a_kid + term[k], (uint32_t)(cell0 + k));
 
   // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
   unsigned rk[CPT];

@@ -220,18 +220,13 @@ __device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* 
       }
     }
     if (!__syncthreads_or(any)) break;  // also separates this round's reads from its writes
-    // (cells of a thread that point at the same cell 2^k steps downstream are added up first: one RED per run)
-    unsigned run = 0;
-    int rt = -1;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
       if (p[k] & OVER) continue;
       sts_u16(own_ptr + 2 * k, b[k]);
-      if (rt == p[k]) run += sv[k];
-      else { if (rt >= 0) red_add_u32(a_cnt + 4 * rt, run); rt = p[k]; run = sv[k]; }
+      red_add_u32(a_cnt + 4 * p[k], sv[k]);
       p[k] = (int)b[k];
     }
-    if (rt >= 0) red_add_u32(a_cnt + 4 * rt, run);
     __syncthreads();
   }
 }
