@@ -4,6 +4,8 @@
 #include <chrono>
 #include <vector>
 #include <condition_variable>
+#include <deque>
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -142,23 +144,48 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
   std::condition_variable cv;
   size_t produced = 0;
   bool closed = false;
+  // the small results (ddir, flatcell, shed, upslope, ridge) that go into pinned memory travel in pieces of <= 32 MB which
+  // the helper slips between its staged chunks: one long copy queued by this thread would hold the D2H engine for
+  // milliseconds and stall the staged downloads behind it (20 of 58 ms at 8192^2 before)
+  struct Piece { void* dst; const void* src; size_t dpitch, spitch, width, rows; };
+  std::deque<Piece> pieces;
+  bool small_published = false;
+  cudaEvent_t flow_done = nullptr;
   int helper_rc = LITAP_OK;
   std::string helper_err;
   const int device = c.device;
   cudaStream_t copy_stream = P.copy;
   std::thread helper;
   struct Joiner {   // whatever way the call ends, the helper is told to stop and joined before the staging state is touched
-    std::thread& t; std::mutex& mu; std::condition_variable& cv; bool& closed;
+    std::thread& t; std::mutex& mu; std::condition_variable& cv; bool& closed; bool& published;
     ~Joiner() {
       if (!t.joinable()) return;
-      { std::lock_guard<std::mutex> lk(mu); closed = true; }
+      { std::lock_guard<std::mutex> lk(mu); closed = true; published = true; }
       cv.notify_all();
       t.join();
     }
-  } joiner{helper, mu, cv, closed};
+  } joiner{helper, mu, cv, closed, small_published};
   if (want_form)
     helper = std::thread([&] {
       cudaSetDevice(device);
+      bool waited = false;
+      auto send_pieces = [&](size_t maxn) -> int {
+        std::vector<Piece> take;
+        {
+          std::lock_guard<std::mutex> lk(mu);
+          if (!small_published) return LITAP_OK;
+          while (take.size() < maxn && !pieces.empty()) { take.push_back(pieces.front()); pieces.pop_front(); }
+        }
+        if (take.empty()) return LITAP_OK;
+        if (!waited) {
+          if (cudaStreamWaitEvent(copy_stream, flow_done, 0) != cudaSuccess) return set_error(LITAP_ECUDA, "cudaStreamWaitEvent failed");
+          waited = true;
+        }
+        for (const Piece& q : take)
+          if (cudaMemcpy2DAsync(q.dst, q.dpitch, q.src, q.spitch, q.width, q.rows, cudaMemcpyDeviceToHost, copy_stream) != cudaSuccess)
+            return set_error(LITAP_ECUDA, "cudaMemcpy2DAsync failed (small results)");
+        return LITAP_OK;
+      };
       for (size_t j = 0;; ++j) {
         Chunk ch;
         {
@@ -177,10 +204,16 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
           else
             rc = d2h_2d(fouts[i] + (size_t)ch.lo * d.NC, (size_t)d.NC * 8, g->form[i] + (size_t)ch.lo * d.pitch,
                         (size_t)d.pitch * 8, (size_t)d.NC * 8, ch.hi - ch.lo, copy_stream);
+          if (!rc) rc = send_pieces(1);
         }
         if (rc) { helper_rc = rc; helper_err = litap_last_error(); return; }
       }
-      const int rc = hostcopy_flush();
+      {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return small_published; });
+      }
+      int rc = send_pieces((size_t)-1);
+      if (!rc) rc = hostcopy_flush();
       if (rc) { helper_rc = rc; helper_err = litap_last_error(); }
     });
   int form_done = 0;  // rows [0, form_done) of the form outputs are computed
@@ -232,8 +265,27 @@ extern "C" int litap_flow_form(const double* elev, int64_t NR, int64_t NC, doubl
     if (!x.src) return set_error(LITAP_ECUDA, "internal: result array missing on the device");
     return d2h_2d(x.dst, (size_t)d.NC * x.esize, x.src, (size_t)d.pitch * x.esize, (size_t)d.NC * x.esize, d.NR, c.stream);
   };
-  for (const Small& x : small)
-    if (x.dst && !hostcopy_is_pageable(x.dst)) RC(send_small(x));
+  if (helper.joinable()) {   // pinned destinations: in pieces, through the helper
+    CUDA_TRY(cudaEventCreateWithFlags(&flow_done, cudaEventDisableTiming));
+    P.aux.push_back(flow_done);
+    CUDA_TRY(cudaEventRecord(flow_done, c.stream));
+    std::deque<Piece> mine;
+    for (const Small& x : small) {
+      if (!x.dst || hostcopy_is_pageable(x.dst)) continue;
+      if (!x.src) return set_error(LITAP_ECUDA, "internal: result array missing on the device");
+      const size_t rowb = (size_t)d.NC * x.esize;
+      const size_t per = std::max<size_t>(1, ((size_t)32 << 20) / rowb);
+      for (size_t r = 0; r < (size_t)d.NR; r += per) {
+        const size_t nr = std::min(per, (size_t)d.NR - r);
+        mine.push_back({(char*)x.dst + r * rowb, (const char*)x.src + r * (size_t)d.pitch * x.esize, rowb, (size_t)d.pitch * x.esize, rowb, nr});
+      }
+    }
+    { std::lock_guard<std::mutex> lk(mu); pieces.swap(mine); small_published = true; }
+    cv.notify_all();
+  } else {
+    for (const Small& x : small)
+      if (x.dst && !hostcopy_is_pageable(x.dst)) RC(send_small(x));
+  }
   if (helper.joinable()) helper.join();
   if (helper_rc) return set_error(helper_rc, helper_err);
   for (const Small& x : small)
