@@ -23,11 +23,12 @@ extern "C" void litap_host_expand_i32(const int32_t* src, double* dst, size_t n,
 namespace {
 #define RC(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
 constexpr size_t HC_STAGE = 64u << 20;
-void* g_stage[2] = {nullptr, nullptr};
-cudaEvent_t g_stage_ev[2] = {nullptr, nullptr};
+constexpr int NSTAGE = 4;   // download staging buffers: the copy engine runs up to three chunks ahead of the host threads
+void* g_stage[NSTAGE] = {};
+cudaEvent_t g_stage_ev[NSTAGE] = {};
 
 int stage_init() {
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < NSTAGE; ++b) {
     if (!g_stage[b]) CUDA_TRY(cudaHostAlloc(&g_stage[b], HC_STAGE, cudaHostAllocDefault));
     if (!g_stage_ev[b]) CUDA_TRY(cudaEventCreateWithFlags(&g_stage_ev[b], cudaEventDisableTiming));
   }
@@ -73,7 +74,7 @@ bool pageable(const void* p) {
 // A chunk that is on its way into a staging buffer: the host copy happens when the buffer is needed again or at
 // hostcopy_flush(), so that the copy of one chunk overlaps the transfer of the next one across calls too.
 struct Pending { bool on = false; char* dst = nullptr; size_t dpitch = 0, width = 0, nrows = 0, bytes = 0; int kind = 0; };   // kind 1 / 2: int32 -> fp64
-Pending g_pend[2];
+Pending g_pend[NSTAGE];
 int g_next = 0;
 double g_wait_ms = 0, g_copy_ms = 0, g_bytes = 0;
 
@@ -144,7 +145,7 @@ int d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
     CUDA_TRY(cudaEventRecord(g_stage_ev[b], st));
     Pending& p = g_pend[b];
     p.on = true; p.dst = (char*)dst + row * dpitch + off; p.dpitch = dpitch; p.width = width; p.nrows = nrows; p.bytes = bytes; p.kind = 0;
-    g_next ^= 1;
+    g_next = (g_next + 1) % NSTAGE;
     return LITAP_OK;
   };
   if (width <= stage) {
@@ -176,7 +177,7 @@ int d2h_2d_i32_expand(double* dst, size_t dpitch, const int32_t* src, size_t spi
     CUDA_TRY(cudaEventRecord(g_stage_ev[b], st));
     Pending& p = g_pend[b];
     p.on = true; p.dst = (char*)dst + r * dpitch; p.dpitch = dpitch; p.width = ncol; p.nrows = nr; p.bytes = 0; p.kind = kind;
-    g_next ^= 1;
+    g_next = (g_next + 1) % NSTAGE;
   }
   return LITAP_OK;
 }
@@ -233,8 +234,7 @@ int hostcopy_staging(int which, void* buf[2], cudaEvent_t ev[2], size_t* bytes) 
     for (int b = 0; b < 2; ++b) { buf[b] = g_up[b]; ev[b] = g_up_ev[b]; }
   } else {
     RC(stage_init());
-    RC(complete(g_next));
-    RC(complete(g_next ^ 1));
+    for (int k = 0; k < NSTAGE; ++k) RC(complete((g_next + k) % NSTAGE));
     for (int b = 0; b < 2; ++b) { buf[b] = g_stage[b]; ev[b] = g_stage_ev[b]; }
   }
   *bytes = HC_STAGE;
@@ -245,8 +245,7 @@ bool hostcopy_is_pageable(const void* p) { return pageable(p); }
 
 // completes the staged downloads (older buffer first)
 int hostcopy_flush() {
-  RC(complete(g_next));
-  RC(complete(g_next ^ 1));
+  for (int k = 0; k < NSTAGE; ++k) RC(complete((g_next + k) % NSTAGE));   // oldest first
   static const bool debug = getenv("LITAP_COPY_DEBUG") != nullptr;
   if (debug && g_bytes > 0)
     fprintf(stderr, "[hostcopy] cumulative: %.0f MB, waiting for the device %.1f ms, host copies %.1f ms\n", g_bytes / 1e6, g_wait_ms, g_copy_ms);
@@ -254,14 +253,18 @@ int hostcopy_flush() {
 }
 // a call that failed half way may have left chunks pending: their destination belongs to that call, drop them
 void hostcopy_reset() {
-  if (g_pend[0].on || g_pend[1].on) cudaDeviceSynchronize();
-  g_pend[0].on = g_pend[1].on = false;
+  bool any = false;
+  for (int b = 0; b < NSTAGE; ++b) any = any || g_pend[b].on;
+  if (any) cudaDeviceSynchronize();
+  for (int b = 0; b < NSTAGE; ++b) g_pend[b].on = false;
 }
 
 void hostcopy_forget_staging() {   // litap_shutdown
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < NSTAGE; ++b) {
     if (g_stage[b]) { cudaFreeHost(g_stage[b]); g_stage[b] = nullptr; }
     if (g_stage_ev[b]) { cudaEventDestroy(g_stage_ev[b]); g_stage_ev[b] = nullptr; }
+  }
+  for (int b = 0; b < 2; ++b) {
     if (g_up[b]) { cudaFreeHost(g_up[b]); g_up[b] = nullptr; }
     if (g_up_ev[b]) { cudaEventDestroy(g_up_ev[b]); g_up_ev[b] = nullptr; }
   }
