@@ -4,7 +4,7 @@
 // numpy arrays): pageable and usually fresh pages.  cudaMemcpy into such memory is staged by the driver
 // on one thread and ends up bound by page faults (~4 GB/s measured on the B200 box).  d2h_2d() looks at the
 // destination: pinned / registered memory gets the plain asynchronous copy; pageable memory is filled
-// through two pinned staging buffers in turn, a few host threads copying chunk j out while chunk j + 1
+// through four pinned staging buffers in turn, a few host threads copying chunk j out while chunk j + 1
 // crosses PCIe (3-4 x faster for the 39 columns of litap_relz).  The staged path returns when the data
 // is in place (it is synchronous for the host, like a pageable cudaMemcpyAsync already is).
 #include <algorithm>
