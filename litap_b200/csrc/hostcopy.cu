@@ -13,6 +13,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <sys/mman.h>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include <unistd.h>
 #include <vector>
@@ -41,16 +44,72 @@ int copy_threads() {
   if (hw > 0) t = std::min(t, hw);
   return std::max(t, 1);
 }
+// A small pool of host threads that stays alive between chunks: a staged chunk is a few tens of MB, i.e. ~1 ms of
+// copying / widening for 12 threads, and creating and joining them for every chunk cost a quarter of that.
+// run(n, f) calls f(0) .. f(n - 1), f(0) on the calling thread, and returns when all are done.  One caller at a time
+// (the library is driven by one thread, or by the download helper of litap_flow_form while that thread enqueues).
+class CopyPool {
+ public:
+  void run(int n, const std::function<void(int)>& f) {
+    if (n <= 1) { if (n == 1) f(0); return; }
+    std::lock_guard<std::mutex> one(user_);
+    grow(n - 1);
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      fn_ = &f; parts_ = n; next_ = 1; left_ = n - 1; ++gen_;
+    }
+    cv_.notify_all();
+    f(0);
+    std::unique_lock<std::mutex> lk(mu_);
+    done_.wait(lk, [&] { return left_ == 0; });
+    fn_ = nullptr;
+  }
+  void stop() {
+    { std::lock_guard<std::mutex> lk(mu_); quit_ = true; }
+    cv_.notify_all();
+    for (auto& t : th_) t.join();
+    th_.clear();
+    quit_ = false;
+  }
+  ~CopyPool() { stop(); }
+
+ private:
+  void grow(int n) {
+    while ((int)th_.size() < n) th_.emplace_back([this] { work(); });
+  }
+  void work() {
+    unsigned long long seen = 0;
+    for (;;) {
+      std::unique_lock<std::mutex> lk(mu_);
+      cv_.wait(lk, [&] { return quit_ || (gen_ != seen && next_ < parts_); });
+      if (quit_) return;
+      if (gen_ != seen && next_ >= parts_) { seen = gen_; continue; }
+      const int i = next_++;
+      if (next_ >= parts_) seen = gen_;
+      const std::function<void(int)>* f = fn_;
+      lk.unlock();
+      (*f)(i);
+      lk.lock();
+      if (--left_ == 0) done_.notify_all();
+    }
+  }
+  std::mutex user_, mu_;
+  std::condition_variable cv_, done_;
+  std::vector<std::thread> th_;
+  const std::function<void(int)>* fn_ = nullptr;
+  int parts_ = 0, next_ = 0, left_ = 0;
+  unsigned long long gen_ = 0;
+  bool quit_ = false;
+};
+CopyPool g_pool_threads;
+
 void host_copy(char* dst, const char* src, size_t bytes, int nt) {
   if (nt <= 1 || bytes < (4u << 20)) { memcpy(dst, src, bytes); return; }
-  std::vector<std::thread> th;
   const size_t per = ((bytes + nt - 1) / nt + 4095) & ~(size_t)4095;
-  for (int t = 1; t < nt; ++t) {
+  g_pool_threads.run(nt, [=](int t) {
     const size_t lo = std::min(bytes, per * t), hi = std::min(bytes, per * (t + 1));
-    if (hi > lo) th.emplace_back([=] { memcpy(dst + lo, src + lo, hi - lo); });
-  }
-  memcpy(dst, src, std::min(bytes, per));
-  for (auto& x : th) x.join();
+    if (hi > lo) memcpy(dst + lo, src + lo, hi - lo);
+  });
 }
 // Fresh anonymous memory is faulted in page by page while it is written; asking for transparent huge pages on the
 // 2 MB-aligned inside of the destination makes that 512 x fewer faults where the system allows it
@@ -100,14 +159,11 @@ int complete(int b) {
     };
     if (nt <= 1 || total < (1u << 18)) piece(0, total);
     else {
-      std::vector<std::thread> th;
       const size_t per = ((total + nt - 1) / nt + 15) & ~(size_t)15;
-      for (int t = 1; t < nt; ++t) {
+      g_pool_threads.run(nt, [&](int t) {
         const size_t lo = std::min(total, per * t), hi = std::min(total, per * (t + 1));
-        if (hi > lo) th.emplace_back([=] { piece(lo, hi); });
-      }
-      piece(0, std::min(total, per));
-      for (auto& x : th) x.join();
+        if (hi > lo) piece(lo, hi);
+      });
     }
   }
   else if (!p.nrows) host_copy(p.dst, s, p.bytes, nt);
@@ -260,6 +316,7 @@ void hostcopy_reset() {
 }
 
 void hostcopy_forget_staging() {   // litap_shutdown
+  g_pool_threads.stop();
   for (int b = 0; b < NSTAGE; ++b) {
     if (g_stage[b]) { cudaFreeHost(g_stage[b]); g_stage[b] = nullptr; }
     if (g_stage_ev[b]) { cudaEventDestroy(g_stage_ev[b]); g_stage_ev[b] = nullptr; }
