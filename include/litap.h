@@ -209,6 +209,20 @@ int litap_grid_checksum(litap_grid* g, const char* name, uint64_t* out);
  * its own rows); over a whole DEM the two are equal.  litap_bands_shed uses it to refuse DEMs in which a 32-bit count wrapped. */
 int litap_grid_conservation(litap_grid* g, uint64_t* cells, uint64_t* pit_upslope);
 
+/* litap_checksum_noalloc has no counterpart in the reference: it was added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, serving loops, harnesses that forbid it).
+ * The checksum of litap_grid_checksum over a device array the CALLER owns: NR rows x NC columns of elem_size (1, 4 or 8)
+ * bytes, `pitch` elements from one row to the next, result into the device word dev_out, both kernels enqueued on
+ * cuda_stream (a cudaStream_t; NULL = the default stream) with no synchronisation.  Calls no cudaMalloc / cudaFree and
+ * no allocating library routine: its scratch (one partial sum per raster row) is a static __device__ array of
+ * LITAP_NOALLOC_MAX_ROWS words (512 KB) that every GPU which loads the library holds until exit.  NR beyond that
+ * limit is refused with LITAP_EARG.  All calls share the array: calls that overlap on the GPU race (order them on one
+ * stream).  The first call on a device looks the array's address up (cudaGetSymbolAddress); make it outside capture.
+ * Works on the current device; needs no litap_init. */
+#define LITAP_NOALLOC_MAX_ROWS 65536
+int litap_checksum_noalloc(const void* dev_arr, int elem_size, int64_t NR, int64_t NC, int64_t pitch,
+                           uint64_t* dev_out, void* cuda_stream);
+
 /* ---- row bands: one DEM sharded over several GPUs ----------------------- */
 /* The DEM (gnr rows x nc cols, unbuffered) is cut into nbands contiguous row bands; band b owns rows
  * [gnr*b/nbands, gnr*(b+1)/nbands) and keeps one halo row on either side.  A band is a litap_grid.

@@ -14,7 +14,7 @@ SYMBOLS = [
     "litap_ddir", "litap_shed", "litap_form", "litap_weti", "litap_uced", "litap_slope_gc", "litap_relz", "litap_relz_names", "litap_flow_form",
     "litap_grid_create", "litap_grid_destroy", "litap_grid_synth", "litap_grid_upload_elev",
     "litap_grid_ddir", "litap_grid_shed", "litap_grid_form", "litap_grid_weti", "litap_grid_uced", "litap_band_checksum", "litap_grid_conservation", "litap_pool_trim", "litap_pit_stat", "litap_pit_stat_names", "litap_grid_pit_stat", "litap_flt_info", "litap_grid_read_flt", "litap_grid_write_raw", "litap_grid_write_raw_many", "litap_grid_slope_gc", "litap_grid_flow_form",
-    "litap_grid_download", "litap_grid_npits", "litap_grid_checksum",
+    "litap_grid_download", "litap_grid_npits", "litap_grid_checksum", "litap_checksum_noalloc",
     "litap_comm_unique_id", "litap_comm_init", "litap_comm_destroy",
     "litap_band_create", "litap_band_synth", "litap_band_upload_elev", "litap_band_upload_rows", "litap_bands_ddir", "litap_bands_shed",
     "litap_bands_form", "litap_bands_flow_form", "litap_band_rows", "litap_band_download",
@@ -100,6 +100,7 @@ def load():
     L.litap_grid_npits.restype = i64
     L.litap_grid_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
     L.litap_band_checksum.argtypes = [vp, C.c_char_p, C.POINTER(C.c_uint64)]
+    L.litap_checksum_noalloc.argtypes = [vp, ci, i64, i64, i64, vp, vp]
     L.litap_grid_conservation.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.litap_comm_unique_id.argtypes = [vp]
     L.litap_comm_init.argtypes = [ci, ci, vp]
