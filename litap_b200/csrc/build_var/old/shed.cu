@@ -1,0 +1,632 @@
+// shed.cu — calc_shed4 + calc_upslopes("upslope") on the device (R/flow_02_calc_shed.R:10-145).
+//
+//   k_count_pits    pits = cells with ddir == 5                                   (:12-20)
+//   k_shed_local    per tile: local terminals (pointer jumping), per-terminal max-elevation key,
+//                   local flow counts; writes the level-2 edges of the 252 border cells
+//   k_l2_*          level-2 graph over border slots: resolve every border cell to its pit
+//                   (pointer jumping with path compression), accumulate external inflow
+//                   (in-degree + chase with atomics), merge the per-shed keys               (:25-29)
+//   cub radix sort  rank pits by (max elev desc, seqno of that cell asc)                  (:32-38)
+//   k_shed_final    per tile: final shed label, upslope count (local accumulation seeded with
+//                   the external inflow) and ridge flag                                 (:42-57)
+//
+// Algorithmic traffic: ddir is read twice (1 B), elev once (8 B), shed + upslope + ridge written
+// once (9 B) => 19 B/cell; the level-2 arrays are ~1.9 B/cell and stay in L2.
+#include <algorithm>
+#include <vector>
+#include <cub/cub.cuh>
+#include "shed_tile.cuh"
+
+namespace shed {
+
+__device__ __forceinline__ unsigned long long f64_orderable(double x) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(x);
+  return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+
+__global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsigned long long* count) {
+  unsigned n = 0;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  if (c < d.NC)
+    for (int r = 1 + blockIdx.y; r < d.NR; r += gridDim.y) n += ddir[(size_t)r * d.pitch + c] == 5;
+  for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if ((threadIdx.x & 31) == 0 && n) atomicAdd(count, (unsigned long long)n);
+}
+
+// ------------------------------------------------------------------------------------------------
+// shared memory of k_shed_local: ptr, dir, cnt, key hi / lo / idx (no aliasing: fewer barriers)
+constexpr size_t SMEM_A = (size_t)LC * (2 + 1 + 4 + 4 + 4 + 4) + 64;
+
+#ifndef SHED_MINB
+#define SHED_MINB 6
+#endif
+__global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
+                                                      const double* __restrict__ elev, uint32_t* __restrict__ lab,
+                                                      uint16_t* __restrict__ tword, uint32_t* __restrict__ lcnt,
+                                                      L2 l2, Pits pits, unsigned long long* pit_cursor) {
+  // static shared arrays: the compiler addresses them with immediate offsets (with dynamic shared
+  // memory it rebuilt the shared-window base, 4 instructions, in front of most accesses)
+  __shared__ unsigned s_cnt[LC];
+  __shared__ uint32_t s_khi[LC];   // key, high word
+  __shared__ uint32_t s_klo[LC];   // key, low word
+  __shared__ uint32_t s_kid[LC];   // lowest cell id attaining the key; later the pit id
+  __shared__ uint16_t s_ptr[LC];
+  __shared__ uint8_t s_dir[LC];
+  __shared__ unsigned s_npit;
+  __shared__ unsigned long long s_pitbase;
+
+  const TileCtx t = tile_ctx();
+  const int r = t.r_base + owned_ly(), c0 = t.c_base + owned_lx0();
+  const bool row_ok = r < g.d.NR;
+  const int base = owned_local(0);
+  const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
+  const size_t cell0 = (size_t)r * g.d.pitch + c0;  // k-th owned cell: cell0 + k (an 8-element boundary)
+  if (threadIdx.x == 0) s_npit = 0;
+  int p[CPT];
+  const unsigned dvp = tile_setup(g, t, ddir, s_ptr, s_dir, p);
+  // elevations of the owned cells (64 contiguous bytes): issued now, consumed after the pointer-doubling loop
+  double ev[CPT];
+  if (row_ok) {
+#pragma unroll
+    for (int k = 0; k < CPT; k += 2) {
+      const double2 v = __ldg(reinterpret_cast<const double2*>(elev + cell0 + k));
+      ev[k] = v.x;
+      ev[k + 1] = v.y;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    const bool valid = ((dvp >> (4 * k)) & 15u) != 0;
+    if (!valid) ev[k] = 0.0;
+    const int i = base + k;
+    s_cnt[i] = valid ? 1u : 0u;  // out-of-grid and NA cells carry no weight
+    s_khi[i] = 0u;
+    s_klo[i] = 0u;
+    s_kid[i] = 0xFFFFFFFFu;
+  }
+  __syncthreads();
+  const unsigned pit_mask_src = dvp;  // dv == 5 <-> pit
+  tile_jump_accumulate(s_ptr, s_cnt, p);
+  // here: all REDs into s_cnt are complete (the loop ends with a barrier or with the all-done vote)
+
+  // ---- exits hand their count to the entry cell's slot (base of the level-2 sum); pits keep theirs
+  unsigned pcnt[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    const int dv = (dvp >> (4 * k)) & 15u;
+    const int i = base + k;
+    pcnt[k] = s_cnt[i];
+    // own initial pointer word had T_EXIT <=> the final one has it and points at the cell itself
+    if ((p[k] & (OVER | T_EXIT)) == (OVER | T_EXIT) && (p[k] & PIDX) == i) {
+      const long long es = slot_of_rc(r + nb_dr(dv), c0 + k + nb_dc(dv), g.tilesX);
+      if (es >= 0) atomicAdd(&l2.ext[es], pcnt[k]);
+    }
+  }
+  if (row_ok) {  // kept for k_shed_final: local terminal word and in-tile flow count of every cell (pads included)
+    uint4 w;
+    w.x = (unsigned)p[0] & 0xFFFFu | (unsigned)p[1] << 16;
+    w.y = (unsigned)p[2] & 0xFFFFu | (unsigned)p[3] << 16;
+    w.z = (unsigned)p[4] & 0xFFFFu | (unsigned)p[5] << 16;
+    w.w = (unsigned)p[6] & 0xFFFFu | (unsigned)p[7] << 16;
+    *reinterpret_cast<uint4*>(tword + cell0) = w;
+    *reinterpret_cast<uint4*>(lcnt + cell0) = make_uint4(pcnt[0], pcnt[1], pcnt[2], pcnt[3]);
+    *reinterpret_cast<uint4*>(lcnt + cell0 + 4) = make_uint4(pcnt[4], pcnt[5], pcnt[6], pcnt[7]);
+  }
+
+  // ---- per-terminal key: max elevation, then lowest cell id attaining it; three rounds of native
+  // 32-bit shared REDs (high word, low word among the high-word winners, id among the winners)
+  uint32_t khi[CPT], klo[CPT];
+  int term[CPT];  // 4 * local index of the terminal; 0 = NA (the ring corner is never a terminal)
+  const uint32_t a_khi = smem_addr(s_khi), a_klo = smem_addr(s_klo), a_kid = smem_addr(s_kid);
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    const bool ok = (p[k] & OVER) && (p[k] & (T_PIT | T_EXIT));
+    term[k] = ok ? 4 * (p[k] & PIDX) : 0;
+    const unsigned long long key = f64_orderable(ev[k]);
+    khi[k] = (uint32_t)(key >> 32);
+    klo[k] = (uint32_t)key;
+    if (term[k]) red_max_u32(a_khi + term[k], khi[k]);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    if (term[k] && khi[k] == lds_u32(a_khi + term[k])) red_max_u32(a_klo + term[k], klo[k]);
+    else term[k] = 0;  // out of the race
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k)
+    if (term[k] && klo[k] == lds_u32(a_klo + term[k])) red_min_u32(a_kid + term[k], (uint32_t)(cell0 + k));
+
+  // ---- pit ids (order of ids is irrelevant: the canonical numbering comes from the sort)
+  unsigned rk[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    rk[k] = 0xFFFFFFFFu;
+    if (((pit_mask_src >> (4 * k)) & 15u) == 5u) rk[k] = atomicAdd(&s_npit, 1u);
+  }
+  __syncthreads();  // keys complete, s_npit complete
+  if (threadIdx.x == 0 && s_npit) s_pitbase = atomicAdd(pit_cursor, (unsigned long long)s_npit);
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    if (rk[k] == 0xFFFFFFFFu) continue;
+    const int i = base + k;
+    const uint32_t pid = (uint32_t)(s_pitbase + rk[k]);
+    const unsigned long long key = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
+    pits.rootmax[pid] = key;
+    pits.pitkmax[pid] = key;
+    pits.pitkidx[pid] = s_kid[i];
+    pits.rootidx[pid] = 0xFFFFFFFFu;
+    pits.cell[pid] = (uint32_t)(cell0 + k);
+    pits.cnt[pid] = pcnt[k];
+    lab[cell0 + k] = pid;  // read back by k_shed_final of this tile
+    s_cnt[i] = pid;        // from here on s_cnt[pit] is its pid (counts are consumed)
+  }
+  __syncthreads();
+
+  // ---- level-2 edges and key partials: one thread per border slot
+  if (threadIdx.x < BUSED) {
+    int bx, by;
+    slot_to_local((int)threadIdx.x, bx, by);
+    const int i = by * LW + bx;
+    const int pw = s_ptr[i];
+    uint32_t edge = ID_NA;
+    unsigned long long pk = 0;
+    uint32_t pi = 0xFFFFFFFFu;
+    if ((pw & OVER) && (pw & (T_PIT | T_EXIT))) {
+      const int tt = pw & PIDX;
+      if (pw & T_PIT) edge = ID_ROOT | s_cnt[tt];
+      else {  // exit: continue at the entry cell of the neighbouring tile
+        const int dv = s_dir[tt];
+        const int ty_ = tt / LW, tx_ = tt - ty_ * LW;
+        edge = (uint32_t)((size_t)(t.r_base + ty_ + nb_dr(dv)) * g.d.pitch + (t.c_base + tx_ + nb_dc(dv)));
+        if (tt == i) {  // this border cell is the exit itself
+          pk = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
+          pi = s_kid[i];
+        }
+      }
+    }
+    l2.jump0[tile_slot0 + threadIdx.x] = edge;
+    l2.jres[tile_slot0 + threadIdx.x] = edge;
+    l2.pkmax[tile_slot0 + threadIdx.x] = pk;
+    l2.pkidx[tile_slot0 + threadIdx.x] = pi;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool is_cell(uint32_t v) { return !(v & ID_ROOT); }  // ID_NA has the flag bit too
+
+__global__ void k_l2_resolve(TileGeom g, uint32_t* __restrict__ jres, size_t nslots, unsigned* unresolved) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool open = false;
+  if (s < nslots) {
+    uint32_t v = jres[s];
+    if (is_cell(v)) {
+      for (int hop = 0; hop < 8 && is_cell(v); ++hop) {
+        long long s2 = slot_of_id(v, g);
+        v = s2 < 0 ? ID_NA : jres[s2];
+      }
+      jres[s] = v;
+      open = is_cell(v);
+    }
+  }
+  if (__syncthreads_or(open) && threadIdx.x == 0) atomicAdd(unresolved, 1u);
+}
+__global__ void k_l2_close_cycles(uint32_t* __restrict__ jres, size_t nslots) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots && is_cell(jres[s])) jres[s] = ID_NA;
+}
+__global__ void k_l2_indeg(TileGeom g, const uint32_t* __restrict__ jump0, size_t nslots, uint32_t* __restrict__ indeg) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  uint32_t v = jump0[s];
+  if (!is_cell(v)) return;
+  long long s2 = slot_of_id(v, g);
+  if (s2 >= 0) atomicAdd(&indeg[s2], 1u);
+}
+__global__ void k_l2_src(const uint32_t* __restrict__ indeg, size_t nslots, uint8_t* __restrict__ src) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots) src[s] = indeg[s] == 0;
+}
+__global__ void k_l2_chase(TileGeom g, const uint32_t* __restrict__ jump0, const uint8_t* __restrict__ src,
+                           size_t nslots, uint32_t* ext, uint32_t* indeg) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || !src[s]) return;
+  uint32_t carry = *reinterpret_cast<volatile uint32_t*>(&ext[s]);
+  while (true) {
+    uint32_t v = jump0[s];
+    if (!is_cell(v)) break;
+    long long t = slot_of_id(v, g);
+    if (t < 0) break;
+    if (carry) atomicAdd(&ext[t], carry);
+    __threadfence();
+    if (atomicSub(&indeg[t], 1u) != 1u) break;
+    __threadfence();
+    carry = atomicAdd(&ext[t], 0u);
+    s = (size_t)t;
+  }
+}
+// shed keys: exits' partials merged into their root; then the index among the maxima
+__global__ void k_keys_max(const L2 l2, size_t nslots, Pits pits) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  unsigned long long pk = l2.pkmax[s];
+  uint32_t root = l2.jres[s];
+  if (pk && root != ID_NA && (root & ID_ROOT)) atomicMax(&pits.rootmax[root & ~ID_ROOT], pk);
+}
+__global__ void k_keys_idx(const L2 l2, size_t nslots, Pits pits, unsigned npits) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots) {
+    unsigned long long pk = l2.pkmax[s];
+    uint32_t root = l2.jres[s];
+    if (pk && root != ID_NA && (root & ID_ROOT)) {
+      uint32_t pid = root & ~ID_ROOT;
+      if (pk == pits.rootmax[pid]) atomicMin(&pits.rootidx[pid], l2.pkidx[s]);
+    }
+  }
+  if (s < npits && pits.pitkmax[s] == pits.rootmax[s]) atomicMin(&pits.rootidx[s], pits.pitkidx[s]);
+}
+__global__ void k_iota(uint32_t* a, unsigned n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = i;
+}
+__global__ void k_gather_u64(const unsigned long long* __restrict__ src, const uint32_t* __restrict__ idx,
+                             unsigned long long* __restrict__ dst, unsigned n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[idx[i]];
+}
+__global__ void k_scatter_rank(const uint32_t* __restrict__ order, uint32_t* __restrict__ rank, unsigned n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rank[order[i]] = i + 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_shed_final: labels, upslope and ridge of one tile from what k_shed_local left behind — the
+// local terminal of every cell (tword) and its in-tile flow count (upslope array) — plus the level-2
+// results.  Flow entering the tile (external inflow of a border cell; flow entering a row band at its
+// first / last own row) is walked down its in-tile path to the local terminal: at most BUSED + 2 TW
+// short serial walks per tile instead of a second pointer-doubling pass over all its cells.
+__device__ __forceinline__ uint32_t rank_of_edge(uint32_t v, const uint32_t* __restrict__ rank) {
+  return (v != ID_NA && (v & ID_ROOT)) ? rank[v & ~ID_ROOT] : 0u;
+}
+__device__ __forceinline__ bool tw_labelled(unsigned w) { return (w & OVER) && (w & (T_PIT | T_EXIT)); }
+
+// add x to every cell from local cell i down to its local terminal (inclusive)
+__device__ __forceinline__ void tile_walk_add(uint32_t a_cnt, const uint8_t* s_dir, const uint16_t* s_tw, int i, unsigned x) {
+  const unsigned w = s_tw[i];
+  if (!x || !tw_labelled(w)) return;  // NA chains and cycles carry no upslope
+  const int term = w & PIDX;
+  for (int step = 0; step < LC; ++step) {
+    red_add_u32(a_cnt + 4 * i, x);
+    if (i == term) break;
+    i += loc_off(s_dir[i]);
+  }
+}
+
+__global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
+                                                      const uint32_t* __restrict__ rank,
+                                                      const uint16_t* __restrict__ tword, int32_t* shed_out,
+                                                      uint32_t* upslope, uint8_t* __restrict__ ridge, BandSeeds seeds) {
+  __shared__ unsigned s_cnt[LC];
+  __shared__ uint32_t s_tlab[LC];  // label of a terminal
+  __shared__ uint32_t s_lab[LC];   // label of every local cell
+  __shared__ uint16_t s_tw[LC];
+  __shared__ uint8_t s_dir[LC];
+  const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
+
+  const TileCtx t = tile_ctx();
+  const int r = t.r_base + owned_ly(), c0 = t.c_base + owned_lx0();
+  const bool row_ok = r < g.d.NR;
+  const int base = owned_local(0);
+  const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
+  const size_t cell0 = (size_t)r * g.d.pitch + c0;  // k-th owned cell: cell0 + k (an 8-element boundary)
+  unsigned tw[CPT];
+  {
+    unsigned long long draw = 0;
+    uint4 wraw = make_uint4(0, 0, 0, 0), n0 = wraw, n1 = wraw;
+    if (row_ok) {
+      draw = __ldg(reinterpret_cast<const unsigned long long*>(ddir + cell0));
+      wraw = __ldg(reinterpret_cast<const uint4*>(tword + cell0));
+      n0 = *reinterpret_cast<const uint4*>(upslope + cell0);
+      n1 = *reinterpret_cast<const uint4*>(upslope + cell0 + 4);
+    }
+    const unsigned wv[4] = {wraw.x, wraw.y, wraw.z, wraw.w};
+    const unsigned nv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+      const int i = base + k;
+      const bool in = c0 + k < g.d.NC;  // (row_ok is folded into the zero loads)
+      const unsigned w = in ? (wv[k >> 1] >> (16 * (k & 1))) & 0xFFFFu : 0u;
+      tw[k] = w;
+      s_dir[i] = in ? (uint8_t)(draw >> (8 * k)) : (uint8_t)0;
+      s_tw[i] = (uint16_t)w;
+      s_cnt[i] = in ? nv[k] : 0u;
+    }
+  }
+  // ---- labels of the terminals, gathered now (two dependent global loads each) and stored after the
+  // walks: pits look up their own rank, exits the rank of their resolved root
+  uint32_t pitlab[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    pitlab[k] = 0xFFFFFFFFu;
+    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k)
+      pitlab[k] = rank[lab_in[cell0 + k]];
+  }
+  int bi = -1;  // this thread's border slot as a local index
+  uint32_t bext = 0, blab = 0;
+  if (threadIdx.x < BUSED) {
+    int bx, by;
+    slot_to_local((int)threadIdx.x, bx, by);
+    bi = by * LW + bx;
+    bext = l2.ext[tile_slot0 + threadIdx.x];
+    blab = rank_of_edge(l2.jres[tile_slot0 + threadIdx.x], rank);
+  }
+  __syncthreads();
+  const uint32_t a_cnt = smem_addr(s_cnt);
+  // ---- flow entering the tile, walked down to the local terminal
+  if (bi >= 0) tile_walk_add(a_cnt, s_dir, s_tw, bi, bext);
+  if (seeds.x_top || seeds.x_bot) {
+    const int lt = seeds.row_top - t.r_base, lb = seeds.row_bot - t.r_base;
+    if (threadIdx.x < TW && t.c_base + (int)threadIdx.x + 1 < g.d.NC) {
+      const int cc = t.c_base + (int)threadIdx.x + 1;
+      if (seeds.x_top && lt >= 1 && lt <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lt * LW + (int)threadIdx.x + 1, seeds.x_top[cc]);
+      if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lb * LW + (int)threadIdx.x + 1, seeds.x_bot[cc]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < CPT; ++k)
+    if (pitlab[k] != 0xFFFFFFFFu) s_tlab[base + k] = pitlab[k];
+  if (bi >= 0) {
+    const int pw = s_tw[bi];
+    if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == bi) s_tlab[bi] = blab;
+  }
+  // ---- labels of the ring cells (for the ridge test): border cells of the neighbouring tiles
+  for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
+    int ry, rx;
+    if (q < LW) { ry = 0; rx = q; }
+    else if (q < 2 * LW) { ry = LH - 1; rx = q - LW; }
+    else if (q < 2 * LW + TH) { ry = q - 2 * LW + 1; rx = 0; }
+    else { ry = q - 2 * LW - TH + 1; rx = LW - 1; }
+    const int r = t.r_base + ry, cc = t.c_base + rx;
+    uint32_t lb = 0;
+    if (r >= 1 && cc >= 1 && in_grid(g, r, cc)) {
+      const long long s = slot_of_rc(r, cc, g.tilesX);
+      if (s >= 0) lb = rank_of_edge(l2.jres[s], rank);
+    }
+    s_lab[ry * LW + rx] = lb;
+  }
+  __syncthreads();
+  uint32_t mylab[CPT];
+  const uint32_t a_tlab = smem_addr(s_tlab);
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    mylab[k] = tw_labelled(tw[k]) ? lds_u32(a_tlab + 4 * (tw[k] & PIDX)) : 0u;
+    s_lab[base + k] = mylab[k];
+  }
+  __syncthreads();
+
+  // ---- outputs.  ridge = more than one distinct non-NA label in the 3 x 3 window
+  // (R/flow_02_calc_shed.R:48-57) <=> max label != min non-zero label; with 0 -> 0xFFFFFFFF by
+  // "label - 1" the minimum skips NA cells.  Column triples (rows above / at / below) of the 10
+  // window columns of the thread's 8 cells, then 3 adjacent columns per cell.
+  if (!row_ok) return;
+  uint32_t cmx[CPT + 2], cmn[CPT + 2];
+#pragma unroll
+  for (int j = 0; j < CPT + 2; ++j) {
+    const uint32_t a = s_lab[base - LW - 1 + j], b = s_lab[base - 1 + j], cc = s_lab[base + LW - 1 + j];
+    cmx[j] = __vimax3_u32(a, b, cc);
+    cmn[j] = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
+  }
+  uint32_t up[CPT];
+  unsigned long long rg8 = 0;
+  const bool row_in = r < g.d.NR - 1;
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) {
+    const uint32_t lb = mylab[k];
+    unsigned rg = 2;  // NA on the ring
+    if (row_in && c0 + k < g.d.NC - 1) {
+      const uint32_t mx = __vimax3_u32(cmx[k], cmx[k + 1], cmx[k + 2]), mn = __vimin3_u32(cmn[k], cmn[k + 1], cmn[k + 2]);
+      rg = (mx != 0u) & (mn + 1u != mx);
+    }
+    up[k] = lb ? s_cnt[base + k] : 0u;
+    rg8 |= (unsigned long long)rg << (8 * k);
+  }
+  // pad columns (>= NC) get label 0 / upslope 0 / ridge NA: one aligned vector per array
+  *reinterpret_cast<uint4*>(shed_out + cell0) = make_uint4(mylab[0], mylab[1], mylab[2], mylab[3]);
+  *reinterpret_cast<uint4*>(shed_out + cell0 + 4) = make_uint4(mylab[4], mylab[5], mylab[6], mylab[7]);
+  *reinterpret_cast<uint4*>(upslope + cell0) = make_uint4(up[0], up[1], up[2], up[3]);
+  *reinterpret_cast<uint4*>(upslope + cell0 + 4) = make_uint4(up[4], up[5], up[6], up[7]);
+  *reinterpret_cast<unsigned long long*>(ridge + cell0) = rg8;
+}
+
+// ring row 0 / column 0 (never inside a tile) and, for uniformity, the other two ring lines
+__global__ void k_ring_fill(GridDims d, int32_t* __restrict__ shed_out, uint32_t* __restrict__ upslope,
+                            uint8_t* __restrict__ ridge, int keep_last_row) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  int line = blockIdx.y;
+  if (line == 1 && keep_last_row) return;  // south halo of a row band: its pit cells still hold their ids
+  int r, c;
+  if (line == 0) { r = 0; c = t; }
+  else if (line == 1) { r = d.NR - 1; c = t; }
+  else if (line == 2) { r = t; c = 0; }
+  else { r = t; c = d.NC - 1; }
+  if (r >= d.NR || c >= d.NC) return;
+  size_t o = (size_t)r * d.pitch + c;
+  shed_out[o] = 0;
+  upslope[o] = 0;
+  ridge[o] = 2;
+}
+
+}  // namespace shed
+
+// ------------------------------------------------------------------------------------------------
+// host side: calc_shed4 in phases (the row-band driver in bands.cu runs exchanges between them)
+//   shed_phase_local   tiles + level-2 graph: every border cell resolved to a pit id, external
+//                      inflow of every border cell, per-pit key (max elevation, lowest cell)
+//   shed_phase_rank    single device: canonical numbering of the pits (two radix sorts)
+//   shed_phase_final   labels, upslope, ridge
+int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
+  using namespace shed;
+  Ctx& c = ctx();
+  const GridDims d = g->d;
+  cudaStream_t st = c.stream;
+  if (!g->shed) g->shed = grid_alloc_array<int32_t>(d, -1);
+  if (!g->upslope) g->upslope = grid_alloc_array<uint32_t>(d, -1);
+  if (!g->ridge) g->ridge = grid_alloc_array<uint8_t>(d, -1);
+  if (!g->shed || !g->upslope || !g->ridge) return set_error(LITAP_ENOMEM, "device allocation failed (shed outputs)");
+
+  static_assert(SMEM_A <= 48 * 1024, "tile arrays are static shared memory");
+  TileGeom& tg = W.tg;
+  tg.d = d;
+  tg.tilesX = (d.NC - 1 + TW - 1) / TW;
+  tg.tilesY = (d.NR - 1 + TH - 1) / TH;
+  const size_t nslots = W.nslots = (size_t)tg.tilesX * tg.tilesY * BSLOTS;
+
+  PoolScratch& S = W.S;
+  unsigned long long* counters = W.counters = S.get<unsigned long long>(4);
+  if (!counters) return set_error(LITAP_ENOMEM, "device allocation failed (shed scratch)");
+  CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), st));
+  // capacity of the pit arrays: the flat-cell count of the D8 stencil when calc_ddir2 ran on this grid
+  // (pits are a subset; a row band adds its portals), else an exact count (one more pass over ddir and a host sync)
+  size_t np = 1;
+  if (g->pit_bound >= 0) np = g->pit_bound ? (size_t)g->pit_bound : 1;
+  else {
+    dim3 grid((d.NC - 1 + 255) / 256, d.NR - 1 < 256 ? d.NR - 1 : 256);
+    KERNEL("k_count_pits", k_count_pits<<<grid, 256, 0, st>>>(g->ddir, d, counters));
+    unsigned long long npits64 = 0;
+    CUDA_TRY(cudaMemcpyAsync(&npits64, counters, 8, cudaMemcpyDeviceToHost, st));
+    STREAM_SYNC(st);
+    np = npits64 ? (size_t)npits64 : 1;
+  }
+
+  L2& l2 = W.l2;
+  l2.jump0 = S.get<uint32_t>(nslots);
+  l2.jres = S.get<uint32_t>(nslots);
+  l2.pkmax = S.get<unsigned long long>(nslots);
+  l2.pkidx = S.get<uint32_t>(nslots);
+  l2.ext = S.get<uint32_t>(nslots);
+  l2.indeg = S.get<uint32_t>(nslots);
+  l2.src = S.get<uint8_t>(nslots);
+  Pits& pits = W.pits;
+  pits.rootmax = S.get<unsigned long long>(np);
+  pits.pitkmax = S.get<unsigned long long>(np);
+  pits.pitkidx = S.get<uint32_t>(np);
+  pits.rootidx = S.get<uint32_t>(np);
+  pits.rank = S.get<uint32_t>(np);
+  pits.cell = S.get<uint32_t>(np);
+  pits.cnt = S.get<uint32_t>(np);
+  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.ext || !l2.indeg || !l2.src || !pits.rootmax ||
+      !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !pits.cell || !pits.cnt)
+    return set_error(LITAP_ENOMEM, "device allocation failed (shed level-2 arrays)");
+  CUDA_TRY(cudaMemsetAsync(l2.ext, 0, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.indeg, 0, nslots * 4, st));
+  // slots BUSED.. of every tile are never written by k_shed_local: keep them NA / empty
+  CUDA_TRY(cudaMemsetAsync(l2.jump0, 0xFF, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.jres, 0xFF, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
+
+  dim3 tgrid(tg.tilesX, tg.tilesY);
+  W.tword = S.get<uint16_t>((size_t)d.cells + 64);  // pitched and offset like the grid arrays (aligned 16-byte vectors)
+  if (!W.tword) return set_error(LITAP_ENOMEM, "device allocation failed (shed terminal words)");
+  W.tword += LITAP_XOFF;
+  KERNEL("k_shed_local", k_shed_local<<<tgrid, NT, 0, st>>>(tg, g->ddir, g->elev, reinterpret_cast<uint32_t*>(g->shed), W.tword,
+                                         g->upslope, l2, pits, counters + 1));
+
+  const unsigned sblk = (unsigned)((nslots + 255) / 256);
+  // ---- resolve border cells to pits; a drec cycle across tiles never resolves -> NA after the cap
+  // (two rounds per host check; the same read-back brings the pit count = the pit cursor of k_shed_local)
+  unsigned* flag = reinterpret_cast<unsigned*>(counters + 2);
+  bool open = true;
+  unsigned long long hb[2] = {0, 0};
+  for (int round = 0; round < 64 && open; round += 2) {
+    for (int k = 0; k < 2; ++k) {
+      CUDA_TRY(cudaMemsetAsync(flag, 0, 4, st));
+      KERNEL("k_l2_resolve", k_l2_resolve<<<sblk, 256, 0, st>>>(tg, l2.jres, nslots, flag));
+    }
+    CUDA_TRY(cudaMemcpyAsync(hb, counters + 1, 16, cudaMemcpyDeviceToHost, st));
+    STREAM_SYNC(st);
+    open = (unsigned)(hb[1] & 0xFFFFFFFFull) != 0;
+  }
+  const unsigned npits = W.npits = (unsigned)hb[0];
+  if (open) {
+    KERNEL("k_l2_close_cycles", k_l2_close_cycles<<<sblk, 256, 0, st>>>(l2.jres, nslots));
+  }
+  // ---- external inflow of every border cell
+  KERNEL("k_l2_indeg", k_l2_indeg<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.indeg));
+  KERNEL("k_l2_src", k_l2_src<<<sblk, 256, 0, st>>>(l2.indeg, nslots, l2.src));
+  KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, l2.src, nslots, l2.ext, l2.indeg));
+  // ---- per-pit keys
+  if (npits) {
+    const unsigned kblk = (unsigned)((std::max(nslots, (size_t)npits) + 255) / 256);
+    KERNEL("k_keys_max", k_keys_max<<<sblk, 256, 0, st>>>(l2, nslots, pits));
+    KERNEL("k_keys_idx", k_keys_idx<<<kblk, 256, 0, st>>>(l2, nslots, pits, npits));
+  }
+  return LITAP_OK;
+}
+
+int shed_phase_rank(shed::ShedWork& W) {
+  using namespace shed;
+  Ctx& c = ctx();
+  cudaStream_t st = c.stream;
+  const unsigned npits = W.npits;
+  if (!npits) return LITAP_OK;
+  PoolScratch& S = W.S;
+  Pits& pits = W.pits;
+  uint32_t* ord_a = S.get<uint32_t>(npits);
+  uint32_t* ord_b = S.get<uint32_t>(npits);
+  uint32_t* key32_b = S.get<uint32_t>(npits);
+  unsigned long long* key64_a = S.get<unsigned long long>(npits);
+  unsigned long long* key64_b = S.get<unsigned long long>(npits);
+  if (!ord_a || !ord_b || !key32_b || !key64_a || !key64_b)
+    return set_error(LITAP_ENOMEM, "device allocation failed (shed sort buffers)");
+  const unsigned pblk = (npits + 255) / 256;
+  KERNEL("k_iota", k_iota<<<pblk, 256, 0, st>>>(ord_a, npits));
+  size_t tmp1 = 0, tmp2 = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp1, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, 32, st);
+  cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp2, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st);
+  size_t tmpn = tmp1 > tmp2 ? tmp1 : tmp2;
+  void* tmp = S.get<unsigned char>(tmpn ? tmpn : 256);
+  if (!tmp) return set_error(LITAP_ENOMEM, "device allocation failed (sort scratch)");
+  // stable LSD: first by the tie-break (cell id asc), then by max elevation desc.  Cell ids need few bits: only those
+  // are sorted (one more, so that the all-ones "none" still sorts last)
+  int idx_bits = 1;
+  while (idx_bits < 32 && ((unsigned long long)W.tg.d.cells >> idx_bits) != 0) ++idx_bits;
+  idx_bits = idx_bits < 31 ? idx_bits + 1 : 32;
+  { ProfScope _p("cub_sort_pits_idx"); CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmpn, pits.rootidx, key32_b, ord_a, ord_b, (int)npits, 0, idx_bits, st)); }
+  KERNEL("k_gather_u64", k_gather_u64<<<pblk, 256, 0, st>>>(pits.rootmax, ord_b, key64_a, npits));
+  { ProfScope _p("cub_sort_pits_key"); CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tmpn, key64_a, key64_b, ord_b, ord_a, (int)npits, 0, 64, st)); }
+  KERNEL("k_scatter_rank", k_scatter_rank<<<pblk, 256, 0, st>>>(ord_a, pits.rank, npits));
+  c.launches += 4;  // cub passes (at least)
+  return LITAP_OK;
+}
+
+int shed_phase_final(litap_grid* g, shed::ShedWork& W, const shed::BandSeeds& seeds) {
+  using namespace shed;
+  Ctx& c = ctx();
+  const GridDims d = g->d;
+  cudaStream_t st = c.stream;
+  {
+    int m = d.NR > d.NC ? d.NR : d.NC;
+    dim3 grid((m + 255) / 256, 4);
+    KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge, g->halo_bot ? 1 : 0));
+  }
+  dim3 tgrid(W.tg.tilesX, W.tg.tilesY);
+  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, 0, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, W.tword, g->shed, g->upslope,
+                                                                g->ridge, seeds));
+  return LITAP_OK;
+}
+
+int run_shed(litap_grid* g) {
+  shed::ShedWork W;
+  int rc = shed_phase_local(g, W);
+  if (rc) return rc;
+  g->npits = (int64_t)W.npits;
+  ctx().tm.npits = g->npits;
+  rc = shed_phase_rank(W);
+  if (rc) return rc;
+  rc = shed_phase_final(g, W, shed::BandSeeds());
+  if (rc) return rc;
+  STREAM_SYNC(ctx().stream);  // scratch is returned to the pool when W dies
+  return LITAP_OK;
+}

@@ -23,9 +23,8 @@ LITAP_HD bool is_nan(double x) { return x != x; }
 // exact ties resolved to the lowest direction code.  nb[n] = elevation of neighbour n (nb[5] unused).
 // Returns 0 (NA) for a NaN centre, 5 for a flat cell / pit.
 //
-// The IEEE division by sqrt(2) is only needed to order a diagonal against an orthogonal
-// neighbour (or two unequal diagonals) when they are within a few ulp; otherwise raw
-// differences decide.  The slow path below is the reference's loop verbatim.
+// d8_slow is the reference's loop verbatim (eight differences, four IEEE divisions); d8_dir gets the same
+// answer from one exact division per cell.
 LITAP_HD int d8_slow(double e, const double* nb) {
   const double sqrt2 = 1.4142135623730951;  // == sqrt(2.0) in binary64
   double best = 0.0;
@@ -40,35 +39,83 @@ LITAP_HD int d8_slow(double e, const double* nb) {
   return d;
 }
 
-LITAP_HD int d8_dir(double e, const double* nb) {
-  if (is_nan(e)) return 0;
-  // orthogonal candidates 2,4,6,8 and diagonal candidates 1,3,7,9, first maximum each
-  double mo = 0.0, md = 0.0, md2 = 0.0;  // md2: largest diagonal difference strictly below md
-  int io = 5, id = 5;
+// RN(a / RN(sqrt 2)) for 2^-900 < a < 2^900 (and a == 0) without the generic division: y = RN(1 / RN(sqrt 2)),
+// two Newton corrections with exact residuals (Markstein 1990, as div_rcp below with the constants folded in).
+#if defined(__CUDACC__)
+__device__ __constant__ double c_sqrt2[2] = {1.4142135623730951, 0.7071067811865475};  // constant-bank operands
+#endif
+LITAP_HD double div_sqrt2(double a) {
+#if defined(__CUDA_ARCH__)
+  const double s = c_sqrt2[0], y = c_sqrt2[1];
+#else
+  const double s = 1.4142135623730951, y = 0.7071067811865475;  // 0x1.6a09e667f3bcdp+0, 0x1.6a09e667f3bccp-1
+#endif
+  double q = a * y;
+  double r = fma(-q, s, a);
+  q = fma(r, y, q);
+  r = fma(-q, s, a);
+  return fma(r, y, q);
+}
+
+// (m, i) = d > 0 ? (d, n) : (0, 5): the first step of a "first maximum" chain.  Spelled out in PTX on the device because
+// the compiler turns the C form into an fmax with NaN quieting (six instructions instead of three).
+LITAP_HD void d8_first(double d, int n, double& m, int& i) {
+#if defined(__CUDA_ARCH__)
+  asm("{\n .reg .pred p;\n setp.gt.f64 p, %2, 0d0000000000000000;\n selp.f64 %0, %2, 0d0000000000000000, p;\n"
+      " selp.s32 %1, %3, 5, p;\n}"
+      : "=d"(m), "=r"(i)
+      : "d"(d), "r"(n));
+#else
+  const bool p = d > 0.0;
+  m = p ? d : 0.0;
+  i = p ? n : 5;
+#endif
+}
+
+// Branch-free fast path: first maximum (strict >, lowest code on ties) of the four orthogonal and of the four diagonal
+// raw differences; the division is monotone, so the largest diagonal quotient is RN(md / sqrt 2) - ONE exact division
+// per cell.  A smaller diagonal difference can round to the same quotient only if it is the double just below md
+// (the quotients of consecutive doubles are 0.707 or 1.414 ulp apart, so three in a row never share one); such a window
+// - and one whose md is outside the range of exact residuals - takes the reference's loop.  Against the orthogonal
+// maximum the exact quotient decides; on equality the lowest code of the two groups wins.
+// d8_fast returns -1 for a window that needs d8_slow.
+LITAP_HD int d8_fast(double e, const double* nb) {
+  double mo, md;
+  int io, id;
+  const double d2 = e - nb[2], d4 = e - nb[4], d6 = e - nb[6], d8 = e - nb[8];
+  const double d1 = e - nb[1], d3 = e - nb[3], d7 = e - nb[7], d9 = e - nb[9];
+  d8_first(d2, 2, mo, io);
+  if (d4 > mo) { mo = d4; io = 4; }
+  if (d6 > mo) { mo = d6; io = 6; }
+  if (d8 > mo) { mo = d8; io = 8; }
+  d8_first(d1, 1, md, id);
+  if (d3 > md) { md = d3; id = 3; }
+  if (d7 > md) { md = d7; id = 7; }
+  if (d9 > md) { md = d9; id = 9; }
+  // the double below md (md == 0: a NaN, equal to nothing) and md's exponent field (md >= 0)
+  unsigned long long mb;
+#if defined(__CUDA_ARCH__)
+  mb = (unsigned long long)__double_as_longlong(md);
+  const double mdp = __longlong_as_double((long long)(mb - 1ull));
+#else
+  double mdp;
   {
-    double d2 = e - nb[2], d4 = e - nb[4], d6 = e - nb[6], d8 = e - nb[8];
-    if (d2 > mo) { mo = d2; io = 2; }
-    if (d4 > mo) { mo = d4; io = 4; }
-    if (d6 > mo) { mo = d6; io = 6; }
-    if (d8 > mo) { mo = d8; io = 8; }
-    double d1 = e - nb[1], d3 = e - nb[3], d7 = e - nb[7], d9 = e - nb[9];
-    if (d1 > md) { md = d1; id = 1; }
-    if (d3 > md) { md2 = md; md = d3; id = 3; } else if (d3 > md2 && d3 < md) md2 = d3;
-    if (d7 > md) { md2 = md; md = d7; id = 7; } else if (d7 > md2 && d7 < md) md2 = d7;
-    if (d9 > md) { md2 = md; md = d9; id = 9; } else if (d9 > md2 && d9 < md) md2 = d9;
+    __builtin_memcpy(&mb, &md, 8);
+    const unsigned long long u = mb - 1ull;
+    __builtin_memcpy(&mdp, &u, 8);
   }
-  if (id == 5) return io;  // no descending diagonal (io == 5 -> flat)
-  const double tol = 4e-15;
-  bool ambiguous = (md2 > md * (1.0 - tol));  // two unequal diagonals within a few ulp
-  if (io != 5) {
-    double a = md * 0.70710678118654757;  // ~ md / sqrt(2), within 2 ulp
-    double gap = a - mo;
-    if (gap < 0) gap = -gap;
-    if (gap <= tol * mo) ambiguous = true;
-    else if (!ambiguous) return (a > mo) ? id : io;
-  }
-  if (!ambiguous) return id;
-  return d8_slow(e, nb);
+#endif
+  const bool in_range = (unsigned)(mb >> 52) - 123u <= 1800u;   // 2^-900 <= md < 2^901; false for md == 0 (nothing is divided)
+  const bool rare = (d1 == mdp) | (d3 == mdp) | (d7 == mdp) | (d9 == mdp) | ((id != 5) & !in_range);
+  const double q = div_sqrt2(md);
+  const int lowest = io < id ? io : id;
+  int res = q > mo ? id : (q < mo ? io : lowest);
+  if (rare) res = -1;
+  return is_nan(e) ? 0 : res;   // a NaN centre: every difference is NaN, nothing above is taken (never rare)
+}
+LITAP_HD int d8_dir(double e, const double* nb) {
+  const int d = d8_fast(e, nb);
+  return d >= 0 ? d : d8_slow(e, nb);
 }
 
 // ---------------------------------------------------------------------------------------------

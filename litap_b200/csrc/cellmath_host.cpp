@@ -24,6 +24,19 @@ void host_d8(const double* elev, long long NR, long long NC, unsigned char* ddir
       ddir[r * NC + c] = (unsigned char)(slow ? (is_nan(e) ? 0 : d8_slow(e, nb)) : d8_dir(e, nb));
     }
 }
+// n windows of nine doubles (neighbour codes 1..9, code 5 = the cell): d8_dir and the reference loop side by side
+void host_d8_windows(const double* win, long long n, unsigned char* fast, unsigned char* slow, long long* nrare) {
+  long long rare = 0;
+  for (long long i = 0; i < n; ++i) {
+    double nb[10];
+    for (int k = 1; k <= 9; ++k) nb[k] = win[i * 9 + k - 1];
+    const double e = nb[5];
+    rare += d8_fast(e, nb) < 0;
+    fast[i] = (unsigned char)d8_dir(e, nb);
+    slow[i] = (unsigned char)(is_nan(e) ? 0 : d8_slow(e, nb));
+  }
+  *nrare = rare;
+}
 int host_get_dir(long long row, long long col, long long row_f, long long col_f, unsigned opts) {
   return get_dir_int(row, col, row_f, col_f, opts);
 }

@@ -11,6 +11,7 @@
 #include <cub/cub.cuh>
 #include "cellmath.h"
 #include "litap_internal.h"
+#include "rowring.cuh"
 #include "stencil.cuh"
 
 namespace cg = cooperative_groups;
@@ -60,73 +61,166 @@ __global__ void k_invert(double* __restrict__ elev, GridDims d, const unsigned l
 // ---- D8 stencil + flat worklist ------------------------------------------------------------------
 constexpr int D8_CPT = 4;        // columns per thread: 32-byte loads, uchar4 stores
 constexpr int D8_THREADS = 128;  // 512 columns per block
-constexpr int D8_ROWS = 16;
+constexpr int D8_ROWS = 32;      // rows per block
 constexpr int D8_STAGE = 1024;   // flats a block stages in shared memory before appending
 
-__global__ void __launch_bounds__(D8_THREADS) k_d8(const double* __restrict__ elev, GridDims d,
+// the reference's loop for the (very rare) windows d8_fast does not decide: out of line, and fed from global memory
+// (four arguments), so that the stencil body stays small - the unrolled body with the window passed in registers was
+// 45 KB of code and the kernel waited for instructions (stall "no_instruction" 2.2 per issue)
+__device__ __noinline__ int d8_slow_at(const double* __restrict__ elev, int NR, int pitch, int r, int c) {
+  double nb[10];
+#pragma unroll
+  for (int n = 1; n <= 9; ++n) {
+    const int rr = r + nb_dr(n);
+    nb[n] = (rr < 0 || rr >= NR) ? sw_nan() : elev[(size_t)rr * pitch + c + nb_dc(n)];   // column pads are readable
+  }
+  return d8_slow(nb[5], nb);
+}
+// flats of one thread-row that do not fit the block's staging buffer (a very flat block)
+__device__ __noinline__ void d8_flats_direct(unsigned fm, uint32_t id0, unsigned k, uint32_t* s_ids,
+                                             uint32_t* __restrict__ list, unsigned long long cap, DdirCounters* ctr) {
+  for (; fm; fm &= fm - 1) {
+    const uint32_t id = id0 + ((__ffs(fm) - 1) >> 3);
+    if (k < D8_STAGE) s_ids[k] = id;
+    else {
+      unsigned long long g = atomicAdd(&ctr->nflat, 1ull);
+      if (g < cap) list[g] = id;
+    }
+    ++k;
+  }
+}
+
+// one row of the block: directions of the thread's four cells from the three row windows, stores, flats.
+// colmask: 0x01 in byte j where column c0 + j < NC
+__device__ __forceinline__ void d8_row(const RowWin<D8_CPT>& p, const RowWin<D8_CPT>& q, const RowWin<D8_CPT>& n,
+                                       const double* __restrict__ elev, const GridDims& d, int r, int c0, bool live,
+                                       bool own_row, unsigned colmask, size_t i, uint8_t* __restrict__ ddir,
+                                       uint8_t* __restrict__ flat, uint32_t* __restrict__ list, unsigned long long cap,
+                                       DdirCounters* ctr, uint32_t* s_ids, unsigned* s_n) {
+  unsigned od = 0, rare = 0;
+#pragma unroll
+  for (int j = 0; j < D8_CPT; ++j) {
+    double nb[10];
+    nb[7] = p.v[j]; nb[8] = p.v[j + 1]; nb[9] = p.v[j + 2];
+    nb[4] = q.v[j]; nb[5] = q.v[j + 1]; nb[6] = q.v[j + 2];
+    nb[1] = n.v[j]; nb[2] = n.v[j + 1]; nb[3] = n.v[j + 2];
+    const int dd = d8_fast(nb[5], nb);
+    od |= ((unsigned)dd & 0xFFu) << (8 * j);   // a rare window leaves 0xFF
+    rare |= (unsigned)(dd < 0) << j;
+  }
+  if (rare && live) {   // (a thread beyond the row allocation works on whatever its ring columns hold and stores nothing)
+    for (unsigned m = rare; m; m &= m - 1) {
+      const int j = __ffs(m) - 1;
+      const unsigned dd = (unsigned)d8_slow_at(elev, d.NR, d.pitch, r, c0 + j);
+      od = (od & ~(0xFFu << (8 * j))) | (dd << (8 * j));
+    }
+  }
+  // flatcell byte: 2 for an NA cell, 1 for a flat one, else 0; flats inside the grid columns
+  const unsigned eq5 = __vcmpeq4(od, 0x05050505u) & 0x01010101u;
+  const unsigned of = eq5 | (__vcmpeq4(od, 0u) & 0x02020202u);
+  const unsigned fm = eq5 & colmask;
+  if (live) {
+    *reinterpret_cast<unsigned*>(ddir + i) = od;
+    *reinterpret_cast<unsigned*>(flat + i) = of;
+    if (c0 == 1) { ddir[i - 1] = 0; flat[i - 1] = 2; }  // ring column 0 (always NA)
+  }
+  if (fm && own_row) {  // halo rows of a band are not ours
+    const unsigned cnt = (unsigned)__popc(fm);
+    unsigned k = atomicAdd(s_n, cnt);
+    if (k + cnt <= D8_STAGE) {
+      if (fm & 0x00000001u) s_ids[k++] = (uint32_t)i;
+      if (fm & 0x00000100u) s_ids[k++] = (uint32_t)i + 1;
+      if (fm & 0x00010000u) s_ids[k++] = (uint32_t)i + 2;
+      if (fm & 0x01000000u) s_ids[k++] = (uint32_t)i + 3;
+    } else d8_flats_direct(fm, (uint32_t)i, k, s_ids, list, cap, ctr);
+  }
+}
+
+#ifndef D8_MINB
+#define D8_MINB 6
+#endif
+#ifndef D8_STAGES
+#define D8_STAGES 4
+#endif
+// Rows reach the block through the TMA row ring (rowring.cuh, as in k_form): segments of D8_COLS + 4 columns, fetched
+// by 1-D bulk copies D8_STAGES - D8_GROUP .. D8_STAGES rows ahead of the arithmetic.  With the rows prefetched
+// through registers (one row ahead per warp) the kernel had ~18 KB in flight per SM and ran at the latency, not at
+// the issue rate, once the per-cell arithmetic was halved.
+constexpr int D8_COLS = D8_THREADS * D8_CPT;
+constexpr int D8_GROUP = 2;      // ring slots recycled per block barrier
+using D8Ring = RowRing<double, D8_COLS, D8_STAGES>;
+
+// the thread's window columns of ring row k (grid row r0 - 1 + k): own columns at slot elements 2 + 4t .. 5 + 4t; a row
+// outside the grid is read from a slot full of NaN
+__device__ __forceinline__ void d8_take_row(RowWin<D8_CPT>& w, D8Ring& ring, const double* nanrow, int k, bool valid) {
+  const int s = k % D8_STAGES;
+  if (valid) rr_wait(&ring.bar[s], (unsigned)(k / D8_STAGES) & 1u);
+  const double* row = (valid ? ring.row[s] : nanrow) + D8_CPT * threadIdx.x;
+  const double2 a = *reinterpret_cast<const double2*>(row + 2);
+  const double2 b = *reinterpret_cast<const double2*>(row + 4);
+  w.v[0] = row[1];
+  w.v[1] = a.x; w.v[2] = a.y; w.v[3] = b.x; w.v[4] = b.y;
+  w.v[5] = row[6];
+}
+
+__global__ void __launch_bounds__(D8_THREADS, D8_MINB) k_d8(const double* __restrict__ elev, GridDims d,
                                                    uint8_t* __restrict__ ddir, uint8_t* __restrict__ flat,
                                                    uint32_t* __restrict__ list, unsigned long long cap,
                                                    int own_lo, int own_hi, DdirCounters* ctr) {
+  __shared__ D8Ring ring;
+  __shared__ __align__(16) double s_nan[D8Ring::SEG];
   __shared__ uint32_t s_ids[D8_STAGE];
   __shared__ unsigned s_n;
   __shared__ unsigned long long s_base;
-  if (threadIdx.x == 0) s_n = 0;
-  __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int c0 = (blockIdx.x * D8_THREADS + threadIdx.x) * D8_CPT + 1;  // column 1 is the aligned one
+  const int cb = blockIdx.x * D8_COLS + 1;                // first column of the block (column 1 is the aligned one)
+  const int c0 = cb + threadIdx.x * D8_CPT;
   const int r0 = blockIdx.y * D8_ROWS;
   const int rend = min(r0 + D8_ROWS, d.NR);
-  const bool live = c0 < d.pitch - LITAP_XOFF;  // the whole warp-row stays inside the row allocation
-  RowWin<D8_CPT> p, q, n, f;
-  if (live) {
-    sw_issue(p, elev, d, r0 - 1, c0, lane);
-    sw_issue(q, elev, d, r0, c0, lane);
-    sw_issue(n, elev, d, r0 + 1, c0, lane);
-  } else {
-#pragma unroll
-    for (int k = 0; k < D8_CPT + 2; ++k) p.v[k] = q.v[k] = n.v[k] = sw_nan();
-  }
-  sw_finish(p, lane);
-  sw_finish(q, lane);
-  sw_finish(n, lane);
-  for (int r = r0; r < rend; ++r) {
-    if (live && r + 1 < rend) sw_issue(f, elev, d, r + 2, c0, lane);
-    else {
-#pragma unroll
-      for (int k = 0; k < D8_CPT + 2; ++k) f.v[k] = sw_nan();
+  const bool live = c0 < d.pitch - LITAP_XOFF;  // the thread's columns lie inside the row allocation
+  // ring row k = grid row r0 - 1 + k, k = 0 .. kmax; the segment starts at column cb - 2 and must stay inside
+  // pitch + 32 elements of its row
+  const int kmax = rend - r0 + 1;
+  const unsigned seg_bytes = (unsigned)min(D8Ring::SEG, ((d.pitch + 32 - (cb - 2)) / 2) * 2) * sizeof(double);
+  int next_k = 0;  // thread 0: first ring row not yet requested
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < D8_STAGES; ++s) rr_bar_init(&ring.bar[s]);
+    rr_fence_init();
+    s_n = 0;
+    for (; next_k < D8_STAGES && next_k <= kmax; ++next_k) {
+      const int rr = r0 - 1 + next_k;
+      if (rr >= 0 && rr < d.NR)
+        rr_issue(ring.row[next_k % D8_STAGES], elev + (size_t)rr * d.pitch + (cb - 2), seg_bytes, &ring.bar[next_k % D8_STAGES]);
+      else rr_skip(&ring.bar[next_k % D8_STAGES]);
     }
-    uchar4 od, of;
-    uint8_t* pd = reinterpret_cast<uint8_t*>(&od);
-    uint8_t* pf = reinterpret_cast<uint8_t*>(&of);
+  }
+  for (int k = threadIdx.x; k < D8Ring::SEG; k += D8_THREADS) s_nan[k] = sw_nan();
+  __syncthreads();
+  unsigned colmask = 0;
 #pragma unroll
-    for (int j = 0; j < D8_CPT; ++j) {
-      double nb[10];
-      nb[7] = p.v[j]; nb[8] = p.v[j + 1]; nb[9] = p.v[j + 2];
-      nb[4] = q.v[j]; nb[5] = q.v[j + 1]; nb[6] = q.v[j + 2];
-      nb[1] = n.v[j]; nb[2] = n.v[j + 1]; nb[3] = n.v[j + 2];
-      int dd = d8_dir(nb[5], nb);
-      pd[j] = (uint8_t)dd;
-      pf[j] = dd == 0 ? 2 : (dd == 5);
-      if (dd == 5 && c0 + j < d.NC && r >= own_lo && r < own_hi) {  // halo rows of a band are not ours
-        const uint32_t id = (uint32_t)((size_t)r * d.pitch + c0 + j);
-        unsigned k = atomicAdd(&s_n, 1u);
-        if (k < D8_STAGE) s_ids[k] = id;
-        else {  // staging buffer full (very flat block): append directly
-          unsigned long long g = atomicAdd(&ctr->nflat, 1ull);
-          if (g < cap) list[g] = id;
+  for (int j = 0; j < D8_CPT; ++j) colmask |= (unsigned)(c0 + j < d.NC) << (8 * j);
+  RowWin<D8_CPT> p, q, n;  // rows r-1, r, r+1
+  d8_take_row(p, ring, s_nan, 0, r0 - 1 >= 0);
+  d8_take_row(q, ring, s_nan, 1, true);
+  size_t i = (size_t)r0 * d.pitch + c0;
+  for (int r = r0; r < rend; ++r) {
+    const int j = r - r0;
+    if (j > 0 && (j % D8_GROUP) == 0) {
+      __syncthreads();  // every thread has taken ring rows <= j + 1: their slots are free
+      if (threadIdx.x == 0) {
+        for (; next_k <= kmax && next_k - D8_STAGES <= j + 1; ++next_k) {
+          const int rk = r0 - 1 + next_k;
+          if (rk < d.NR)
+            rr_issue(ring.row[next_k % D8_STAGES], elev + (size_t)rk * d.pitch + (cb - 2), seg_bytes,
+                     &ring.bar[next_k % D8_STAGES]);
+          else rr_skip(&ring.bar[next_k % D8_STAGES]);
         }
       }
     }
-    if (live) {
-      const size_t i = (size_t)r * d.pitch + c0;
-      *reinterpret_cast<uchar4*>(ddir + i) = od;
-      *reinterpret_cast<uchar4*>(flat + i) = of;
-      if (c0 == 1) { ddir[i - 1] = 0; flat[i - 1] = 2; }  // ring column 0 (always NA)
-    }
+    d8_take_row(n, ring, s_nan, j + 2, r + 1 < d.NR);
+    d8_row(p, q, n, elev, d, r, c0, live, r >= own_lo && r < own_hi, colmask, i, ddir, flat, list, cap, ctr, s_ids, &s_n);
+    i += d.pitch;
     p = q;
     q = n;
-    n = f;
-    sw_finish(n, lane);
   }
   __syncthreads();
   const unsigned ns = min(s_n, (unsigned)D8_STAGE);

@@ -282,14 +282,26 @@ __global__ void k_scatter_rank(const uint32_t* __restrict__ order, uint32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------
+// Final shed number of every border slot (the rank of the pit its level-2 chain ends in, 0 = none) and, in the label
+// array, of every pit cell (k_shed_local left the pit id there): k_shed_final then needs ONE load per border / ring /
+// pit cell where it used to chase slot -> pit id -> rank, two dependent L2 round trips in front of its barriers.
+__global__ void k_final_labels(const uint32_t* __restrict__ jres, size_t nslots, const uint32_t* __restrict__ rank,
+                               const uint32_t* __restrict__ pitcell, unsigned npits, uint32_t* __restrict__ slab,
+                               uint32_t* __restrict__ lab) {
+  const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots) {
+    const uint32_t v = jres[s];
+    slab[s] = (v != ID_NA && (v & ID_ROOT)) ? rank[v & ~ID_ROOT] : 0u;
+  }
+  if (s < npits) lab[pitcell[s]] = rank[s];
+}
+
+// ------------------------------------------------------------------------------------------------
 // k_shed_final: labels, upslope and ridge of one tile from what k_shed_local left behind — the
 // local terminal of every cell (tword) and its in-tile flow count (upslope array) — plus the level-2
 // results.  Flow entering the tile (external inflow of a border cell; flow entering a row band at its
 // first / last own row) is walked down its in-tile path to the local terminal: at most BUSED + 2 TW
 // short serial walks per tile instead of a second pointer-doubling pass over all its cells.
-__device__ __forceinline__ uint32_t rank_of_edge(uint32_t v, const uint32_t* __restrict__ rank) {
-  return (v != ID_NA && (v & ID_ROOT)) ? rank[v & ~ID_ROOT] : 0u;
-}
 __device__ __forceinline__ bool tw_labelled(unsigned w) { return (w & OVER) && (w & (T_PIT | T_EXIT)); }
 
 // add x to every cell from local cell i down to its local terminal (inclusive)
@@ -305,7 +317,7 @@ __device__ __forceinline__ void tile_walk_add(uint32_t a_cnt, const uint8_t* s_d
 }
 
 __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
-                                                      const uint32_t* __restrict__ rank,
+                                                      const uint32_t* __restrict__ slab,
                                                       const uint16_t* __restrict__ tword, int32_t* shed_out,
                                                       uint32_t* upslope, uint8_t* __restrict__ ridge, BandSeeds seeds) {
   __shared__ unsigned s_cnt[LC];
@@ -313,7 +325,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   __shared__ uint32_t s_lab[LC];   // label of every local cell
   __shared__ uint16_t s_tw[LC];
   __shared__ uint8_t s_dir[LC];
-  const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their pid
+  const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their final label (k_final_labels)
 
   const TileCtx t = tile_ctx();
   const int r = t.r_base + owned_ly(), c0 = t.c_base + owned_lx0();
@@ -344,14 +356,14 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
       s_cnt[i] = in ? nv[k] : 0u;
     }
   }
-  // ---- labels of the terminals, gathered now (two dependent global loads each) and stored after the
-  // walks: pits look up their own rank, exits the rank of their resolved root
+  // ---- labels of the terminals (pits: their own cell of the label array; exits: their border slot) and of the ring
+  // cells (border slots of the neighbouring tiles, for the ridge test): one independent load each, all issued here,
+  // in front of the first barrier, and stored after the walks
   uint32_t pitlab[CPT];
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     pitlab[k] = 0xFFFFFFFFu;
-    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k)
-      pitlab[k] = rank[lab_in[cell0 + k]];
+    if ((tw[k] & (OVER | T_PIT)) == (OVER | T_PIT) && (int)(tw[k] & PIDX) == base + k) pitlab[k] = lab_in[cell0 + k];
   }
   int bi = -1;  // this thread's border slot as a local index
   uint32_t bext = 0, blab = 0;
@@ -360,7 +372,29 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
     slot_to_local((int)threadIdx.x, bx, by);
     bi = by * LW + bx;
     bext = l2.ext[tile_slot0 + threadIdx.x];
-    blab = rank_of_edge(l2.jres[tile_slot0 + threadIdx.x], rank);
+    blab = slab[tile_slot0 + threadIdx.x];
+  }
+  constexpr int NRING = 2 * LW + 2 * TH, RPT = (NRING + NT - 1) / NT;
+  uint32_t rlab[RPT];
+  int rloc[RPT];
+#pragma unroll
+  for (int j = 0; j < RPT; ++j) {
+    const int q = (int)threadIdx.x + j * NT;
+    rloc[j] = -1;
+    rlab[j] = 0;
+    if (q < NRING) {
+      int ry, rx;
+      if (q < LW) { ry = 0; rx = q; }
+      else if (q < 2 * LW) { ry = LH - 1; rx = q - LW; }
+      else if (q < 2 * LW + TH) { ry = q - 2 * LW + 1; rx = 0; }
+      else { ry = q - 2 * LW - TH + 1; rx = LW - 1; }
+      rloc[j] = ry * LW + rx;
+      const int rr = t.r_base + ry, cc = t.c_base + rx;
+      if (rr >= 1 && cc >= 1 && in_grid(g, rr, cc)) {
+        const long long sl = slot_of_rc(rr, cc, g.tilesX);
+        if (sl >= 0) rlab[j] = slab[sl];
+      }
+    }
   }
   __syncthreads();
   const uint32_t a_cnt = smem_addr(s_cnt);
@@ -381,21 +415,9 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
     const int pw = s_tw[bi];
     if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == bi) s_tlab[bi] = blab;
   }
-  // ---- labels of the ring cells (for the ridge test): border cells of the neighbouring tiles
-  for (int q = threadIdx.x; q < 2 * LW + 2 * TH; q += NT) {
-    int ry, rx;
-    if (q < LW) { ry = 0; rx = q; }
-    else if (q < 2 * LW) { ry = LH - 1; rx = q - LW; }
-    else if (q < 2 * LW + TH) { ry = q - 2 * LW + 1; rx = 0; }
-    else { ry = q - 2 * LW - TH + 1; rx = LW - 1; }
-    const int r = t.r_base + ry, cc = t.c_base + rx;
-    uint32_t lb = 0;
-    if (r >= 1 && cc >= 1 && in_grid(g, r, cc)) {
-      const long long s = slot_of_rc(r, cc, g.tilesX);
-      if (s >= 0) lb = rank_of_edge(l2.jres[s], rank);
-    }
-    s_lab[ry * LW + rx] = lb;
-  }
+#pragma unroll
+  for (int j = 0; j < RPT; ++j)
+    if (rloc[j] >= 0) s_lab[rloc[j]] = rlab[j];
   __syncthreads();
   uint32_t mylab[CPT];
   const uint32_t a_tlab = smem_addr(s_tlab);
@@ -611,8 +633,15 @@ int shed_phase_final(litap_grid* g, shed::ShedWork& W, const shed::BandSeeds& se
     dim3 grid((m + 255) / 256, 4);
     KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge, g->halo_bot ? 1 : 0));
   }
+  // the in-degree array of the level-2 chase is free by now: it takes the slots' final labels
+  uint32_t* slab = W.l2.indeg;
+  {
+    const size_t n = std::max(W.nslots, (size_t)W.npits);
+    KERNEL("k_final_labels", k_final_labels<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+        W.l2.jres, W.nslots, W.pits.rank, W.pits.cell, W.npits, slab, reinterpret_cast<uint32_t*>(g->shed)));
+  }
   dim3 tgrid(W.tg.tilesX, W.tg.tilesY);
-  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, 0, st>>>(W.tg, g->ddir, W.l2, W.pits.rank, W.tword, g->shed, g->upslope,
+  KERNEL("k_shed_final", k_shed_final<<<tgrid, NT, 0, st>>>(W.tg, g->ddir, W.l2, slab, W.tword, g->shed, g->upslope,
                                                                 g->ridge, seeds));
   return LITAP_OK;
 }

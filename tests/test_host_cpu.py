@@ -51,6 +51,7 @@ def cellmath():
     f64 = np.ctypeslib.ndpointer(np.float64, flags="C")
     u8 = np.ctypeslib.ndpointer(np.uint8, flags="C")
     L.host_d8.argtypes = [f64, C.c_longlong, C.c_longlong, u8, C.c_int]
+    L.host_d8_windows.argtypes = [f64, C.c_longlong, u8, u8, C.POINTER(C.c_longlong)]
     L.host_form_raw.argtypes = [f64, C.c_longlong, C.c_longlong, C.c_double, f64]
     L.host_get_dir.argtypes = [C.c_longlong] * 4 + [C.c_uint]
     L.host_r_round3.argtypes = [C.c_double]
@@ -71,6 +72,44 @@ def test_d8_fast_path_equals_reference_loop(cellmath, kw):
     o = oracle.ddir(e)
     nf = o["flatcell"] == 0
     assert (a[nf] == o["ddir"][nf]).all() and (a[o["flatcell"] == 1] == 5).all()
+
+
+def test_d8_one_division_equals_reference_loop_on_near_ties(cellmath):
+    """d8_dir divides only the largest diagonal difference by sqrt(2) (exactly, from the reciprocal) and sends windows
+    with a diagonal one ulp below the maximum to the reference loop: windows built around exactly those cases -
+    diagonals within a few ulp of each other, orthogonal differences within a few ulp of diagonal / sqrt(2), ties,
+    NaN neighbours, denormal / huge / infinite differences - must give the loop's (R/LITAP_functions.R:257-273) answer."""
+    rng = np.random.default_rng(7)
+    n = 1_500_000
+    diag = np.array([1, 0, 1, 0, 0, 0, 1, 0, 1], bool)   # codes 1, 3, 7, 9
+    base = (1.0 + rng.random(n)) * 2.0 ** rng.integers(-30, 30, n)
+    d = np.empty((n, 9))
+    for k in range(9):
+        kind = rng.integers(0, 8, n)
+        near = base if diag[k] else base / np.sqrt(2.0)
+        steps = rng.integers(-3, 3, n)
+        v = near.copy()
+        for _ in range(3):   # up to three ulp up or down
+            up = steps > 0
+            dn = steps < 0
+            v = np.where(up, np.nextafter(v, np.inf), np.where(dn, np.nextafter(v, -np.inf), v))
+            steps = steps - np.sign(steps)
+        d[:, k] = np.where(kind < 5, v, np.where(kind == 5, -near, rng.random(n) * near))
+    ext = np.array([0.0, 5e-324, 1e-320, 1e-300, 2.0 ** -901, 2.0 ** -899, 2.0 ** 900, 2.0 ** 902, 1e300, np.inf, -np.inf, np.nan])
+    m = n // 10
+    d[:m] = ext[rng.integers(0, len(ext), (m, 9))]
+    win = -d                     # centre 0: e - nb reproduces the differences exactly
+    win[:, 4] = 0.0
+    win[rng.random(n) < 0.01, 4] = np.nan
+    # a second family on quantised elevations (exact ties inside the groups)
+    q = np.round(600 + rng.integers(0, 40, (n, 9)) / 1000.0, 3)
+    q[rng.random((n, 9)) < 0.02] = np.nan
+    win = np.ascontiguousarray(np.concatenate([win, q]))
+    fast, slow = np.zeros(len(win), np.uint8), np.zeros(len(win), np.uint8)
+    nrare = C.c_longlong(0)
+    cellmath.host_d8_windows(win, len(win), fast, slow, C.byref(nrare))
+    assert (fast == slow).all(), np.flatnonzero(fast != slow)[:5]
+    assert 0 < nrare.value < len(win) // 4   # the guarded windows exist in this set and are a minority
 
 
 def test_form_cell_equals_oracle(cellmath):
