@@ -35,7 +35,14 @@ inline GridDims make_dims(int64_t NR, int64_t NC) {
 #endif
 constexpr int TW = LITAP_TILE, TH = LITAP_TILE;  // interior cells per tile
 constexpr int LW = TW + 2, LH = TH + 2;    // local grid incl. the 1-cell ring
-constexpr int LC = LW * LH;                // local cells (1156 for 32 x 32)
+#ifndef LITAP_LPAD
+#define LITAP_LPAD 1
+#endif
+// row pitch of the local grid in shared memory: odd (35), so that the 32 threads of a warp - 8 tile rows x 4 groups of
+// 8 columns - touch 32 different banks when each accesses the k-th of its own cells (with a pitch of 34 they met in
+// pairs: every own-cell access of the tile kernels took two wavefronts, and k_shed_local is bound by the LSU pipe)
+constexpr int LP = LW + LITAP_LPAD;
+constexpr int LC = LP * LH;                // local cells (1190 for 32 x 32)
 constexpr int BUSED = 2 * TW + 2 * (TH - 2);        // border cells per tile (124)
 constexpr int BSLOTS = (BUSED + 31) / 32 * 32;      // border slots per tile (128)
 constexpr uint32_t ID_NA = 0xFFFFFFFFu;    // "no shed" (NA drec chain / cycle)

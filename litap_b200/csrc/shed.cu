@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   if (threadIdx.x < BUSED) {
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
-    const int i = by * LW + bx;
+    const int i = by * LP + bx;
     const int pw = s_ptr[i];
     uint32_t edge = ID_NA;
     unsigned long long pk = 0;
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
       if (pw & T_PIT) edge = ID_ROOT | s_cnt[tt];
       else {  // exit: continue at the entry cell of the neighbouring tile
         const int dv = s_dir[tt];
-        const int ty_ = tt / LW, tx_ = tt - ty_ * LW;
+        const int ty_ = tt / LP, tx_ = tt - ty_ * LP;
         edge = (uint32_t)((size_t)(t.r_base + ty_ + nb_dr(dv)) * g.d.pitch + (t.c_base + tx_ + nb_dc(dv)));
         if (tt == i) {  // this border cell is the exit itself
           pk = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
@@ -370,7 +370,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   if (threadIdx.x < BUSED) {
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
-    bi = by * LW + bx;
+    bi = by * LP + bx;
     bext = l2.ext[tile_slot0 + threadIdx.x];
     blab = slab[tile_slot0 + threadIdx.x];
   }
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
       else if (q < 2 * LW) { ry = LH - 1; rx = q - LW; }
       else if (q < 2 * LW + TH) { ry = q - 2 * LW + 1; rx = 0; }
       else { ry = q - 2 * LW - TH + 1; rx = LW - 1; }
-      rloc[j] = ry * LW + rx;
+      rloc[j] = ry * LP + rx;
       const int rr = t.r_base + ry, cc = t.c_base + rx;
       if (rr >= 1 && cc >= 1 && in_grid(g, rr, cc)) {
         const long long sl = slot_of_rc(rr, cc, g.tilesX);
@@ -404,8 +404,8 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
     const int lt = seeds.row_top - t.r_base, lb = seeds.row_bot - t.r_base;
     if (threadIdx.x < TW && t.c_base + (int)threadIdx.x + 1 < g.d.NC) {
       const int cc = t.c_base + (int)threadIdx.x + 1;
-      if (seeds.x_top && lt >= 1 && lt <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lt * LW + (int)threadIdx.x + 1, seeds.x_top[cc]);
-      if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lb * LW + (int)threadIdx.x + 1, seeds.x_bot[cc]);
+      if (seeds.x_top && lt >= 1 && lt <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lt * LP + (int)threadIdx.x + 1, seeds.x_top[cc]);
+      if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lb * LP + (int)threadIdx.x + 1, seeds.x_bot[cc]);
     }
   }
 #pragma unroll
@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   uint32_t cmx[CPT + 2], cmn[CPT + 2];
 #pragma unroll
   for (int j = 0; j < CPT + 2; ++j) {
-    const uint32_t a = s_lab[base - LW - 1 + j], b = s_lab[base - 1 + j], cc = s_lab[base + LW - 1 + j];
+    const uint32_t a = s_lab[base - LP - 1 + j], b = s_lab[base - 1 + j], cc = s_lab[base + LP - 1 + j];
     cmx[j] = __vimax3_u32(a, b, cc);
     cmn[j] = __vimin3_u32(a - 1u, b - 1u, cc - 1u);
   }

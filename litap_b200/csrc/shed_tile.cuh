@@ -1,7 +1,7 @@
 // shed_tile.cuh — tile-local building blocks of calc_shed4 on the device (included by shed.cu).
 //
 // The drec forest is processed in tiles of TW x TH interior cells staged in shared memory with a
-// 1-cell ring (local grid LW x LH, 16-bit local indices).  Inside a tile every cell is resolved
+// 1-cell ring (local grid LW x LH, row pitch LP, 16-bit local indices).  Inside a tile every cell is resolved
 // to its local terminal by pointer jumping in shared memory:
 //     pit   (ddir == 5)                       -> a root of the forest
 //     exit  (ddir points out of the tile)     -> continues at the entry cell of the next tile
@@ -33,14 +33,14 @@ struct TileGeom {
 __device__ __forceinline__ int loc_off(int dir) {
   int dr = (dir < 4) - (dir > 6);
   int dc = (int)((0x92490u >> (2 * dir)) & 3u) - 1;  // 2-bit table of (dir-1)%3 for dir 0..9 (dir 0 -> unused)
-  return dr * LW + dc;
+  return dr * LP + dc;
 }
 // k-th interior cell owned by this thread: local row owned_ly(), local column owned_lx0() + k.  Column 1
 // of every grid row is 32-element aligned (LITAP_XOFF) and tiles are 32 columns wide, so the thread's
 // 8 cells start at an 8-element boundary of every per-cell array.
 __device__ __forceinline__ int owned_ly() { return (int)(threadIdx.x / GX) + 1; }
 __device__ __forceinline__ int owned_lx0() { return (int)(threadIdx.x % GX) * CPT + 1; }
-__device__ __forceinline__ int owned_local(int k) { return owned_ly() * LW + owned_lx0() + k; }
+__device__ __forceinline__ int owned_local(int k) { return owned_ly() * LP + owned_lx0() + k; }
 
 // local coordinates of border slot s (0 <= s < BUSED): inverse of border_slot_local
 __device__ __forceinline__ void slot_to_local(int s, int& lx, int& ly) {
@@ -135,7 +135,7 @@ __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx&
   unsigned pack = 0;
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
-    const int lx = lx0 + k, c = t.c_base + lx, i = ly * LW + lx;
+    const int lx = lx0 + k, c = t.c_base + lx, i = ly * LP + lx;
     int dv = (int)((raw >> (8 * k)) & 0xFFull);
     if (c >= g.d.NC || dv > 9) dv = 0;
     int pw = i | OVER;  // NA terminal unless shown otherwise
@@ -147,7 +147,7 @@ __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx&
       if (rr < 1 || cc < 1 || !in_grid(g, rr, cc)) dv = 0;
       else {
         const bool ex = (dc < 0 && lx == 1) || (dc > 0 && lx == TW) || (dr < 0 && ly == 1) || (dr > 0 && ly == TH);
-        pw = ex ? (i | OVER | T_EXIT) : (i + dr * LW + dc);
+        pw = ex ? (i | OVER | T_EXIT) : (i + dr * LP + dc);
       }
     }
     s_ptr[i] = (uint16_t)pw;
