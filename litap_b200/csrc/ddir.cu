@@ -8,6 +8,7 @@
 //                                                         R/flow_01_calc_ddir.R:48-107
 // No raster and no result ever goes through the host: it reads three counters per call.
 #include <cooperative_groups.h>
+#include <cstdlib>
 #include <cub/cub.cuh>
 #include "cellmath.h"
 #include "litap_internal.h"
@@ -76,15 +77,21 @@ __device__ __noinline__ int d8_slow_at(const double* __restrict__ elev, int NR, 
   }
   return d8_slow(nb[5], nb);
 }
+// Worklist entries: cell id, with bit 31 (LIST_DEAD) set when the flat cell has no neighbour at its own elevation - no
+// plateau round can ever give such a cell a direction (96 % of the flat cells of the bench DEM are single-cell pits),
+// so the rounds skip it without touching the rasters; the patch stage looks at every entry.
+constexpr uint32_t LIST_DEAD = 0x80000000u, LIST_ID = 0x7FFFFFFFu;
+
 // flats of one thread-row that do not fit the block's staging buffer (a very flat block)
-__device__ __noinline__ void d8_flats_direct(unsigned fm, uint32_t id0, unsigned k, uint32_t* s_ids,
+__device__ __noinline__ void d8_flats_direct(unsigned fm, uint4 ids, unsigned k, uint32_t* s_ids,
                                              uint32_t* __restrict__ list, unsigned long long cap, DdirCounters* ctr) {
-  for (; fm; fm &= fm - 1) {
-    const uint32_t id = id0 + ((__ffs(fm) - 1) >> 3);
-    if (k < D8_STAGE) s_ids[k] = id;
+  const uint32_t v[4] = {ids.x, ids.y, ids.z, ids.w};
+  for (int j = 0; j < 4; ++j) {
+    if (!((fm >> (8 * j)) & 1u)) continue;
+    if (k < D8_STAGE) s_ids[k] = v[j];
     else {
       unsigned long long g = atomicAdd(&ctr->nflat, 1ull);
-      if (g < cap) list[g] = id;
+      if (g < cap) list[g] = v[j];
     }
     ++k;
   }
@@ -127,12 +134,22 @@ __device__ __forceinline__ void d8_row(const RowWin<D8_CPT>& p, const RowWin<D8_
   if (fm && own_row) {  // halo rows of a band are not ours
     const unsigned cnt = (unsigned)__popc(fm);
     unsigned k = atomicAdd(s_n, cnt);
+    uint32_t ids[D8_CPT];
+#pragma unroll
+    for (int j = 0; j < D8_CPT; ++j) {
+      ids[j] = (uint32_t)i + j;
+      if ((fm >> (8 * j)) & 1u) {   // a neighbour at the cell's own elevation? (none of a flat cell's neighbours is lower)
+        const double e = q.v[j + 1];
+        const bool level = (p.v[j] == e) | (p.v[j + 1] == e) | (p.v[j + 2] == e) | (q.v[j] == e) | (q.v[j + 2] == e) |
+                           (n.v[j] == e) | (n.v[j + 1] == e) | (n.v[j + 2] == e);
+        if (!level) ids[j] |= LIST_DEAD;
+      }
+    }
     if (k + cnt <= D8_STAGE) {
-      if (fm & 0x00000001u) s_ids[k++] = (uint32_t)i;
-      if (fm & 0x00000100u) s_ids[k++] = (uint32_t)i + 1;
-      if (fm & 0x00010000u) s_ids[k++] = (uint32_t)i + 2;
-      if (fm & 0x01000000u) s_ids[k++] = (uint32_t)i + 3;
-    } else d8_flats_direct(fm, (uint32_t)i, k, s_ids, list, cap, ctr);
+#pragma unroll
+      for (int j = 0; j < D8_CPT; ++j)
+        if ((fm >> (8 * j)) & 1u) s_ids[k++] = ids[j];
+    } else d8_flats_direct(fm, make_uint4(ids[0], ids[1], ids[2], ids[3]), k, s_ids, list, cap, ctr);
   }
 }
 
@@ -234,24 +251,39 @@ __global__ void __launch_bounds__(D8_THREADS, D8_MINB) k_d8(const double* __rest
 // R/flow_01_calc_ddir.R:17-41: a flat cell takes the lowest direction n whose neighbour has the
 // same elevation (elev - elev_n >= 0 can only be equality: no neighbour is lower) and already drains.
 // ddir is re-read across rounds of one launch while other SMs write it: L2 loads (ld.cg), never L1 / nc.
+constexpr uint8_t PLATEAU_DEAD = 0x80;   // probe result / candidate byte: the worklist entry needs no further probe
 __device__ __forceinline__ uint8_t plateau_probe_cell(uint32_t id, const uint8_t* ddir,
                                                       const double* __restrict__ elev, const GridDims& d) {
   if (__ldcg(ddir + id) != 5) return 0;
-  const double e = elev[id];
   const int r = id / d.pitch, c = id - r * d.pitch;
+  // the cell and its eight neighbours in ONE round trip: sixteen independent loads (a neighbour outside the grid reads
+  // the cell itself, which is flat and so never qualifies), then the lowest code that qualifies.  With the
+  // neighbours visited one after the other and an early exit, a probe was a chain of up to sixteen dependent loads,
+  // and the whole stage (three passes over 1 % of the cells) cost 0.23 ms at 8192^2.
+  const double e = elev[id];
+  double en[10];
+  uint8_t dn[10];
 #pragma unroll
   for (int k = 1; k <= 9; ++k) {
     if (k == 5) continue;
-    int rr = r + nb_dr(k), cc = c + nb_dc(k);
-    if (rr < 0 || rr >= d.NR || cc < 0 || cc >= d.NC) continue;
-    size_t j = (size_t)rr * d.pitch + cc;
-    double en = elev[j];
-    if (is_nan(en) || !(e - en >= 0)) continue;
-    uint8_t dn = __ldcg(ddir + j);
-    if (dn == 5 || dn == 0) continue;
-    return (uint8_t)k;
+    const int rr = r + nb_dr(k), cc = c + nb_dc(k);
+    const bool in = rr >= 0 && rr < d.NR && cc >= 0 && cc < d.NC;
+    const size_t j = in ? (size_t)rr * d.pitch + cc : (size_t)id;
+    en[k] = elev[j];
+    dn[k] = __ldcg(ddir + j);
   }
-  return 0;
+  uint8_t res = 0;
+  bool level = false;   // a neighbour at the cell's own elevation exists (no neighbour of a flat cell is lower)
+#pragma unroll
+  for (int k = 9; k >= 1; --k) {
+    if (k == 5) continue;
+    const bool eq = !is_nan(en[k]) && (e - en[k] >= 0);
+    level |= eq;
+    if (eq && dn[k] != 5 && dn[k] != 0) res = (uint8_t)k;
+  }
+  // PLATEAU_DEAD: no neighbour at the cell's elevation, so no round can ever give it a direction (a single-cell pit:
+  // 96 % of the flat cells of the bench DEM) - the caller may drop it from the later rounds
+  return level ? res : PLATEAU_DEAD;
 }
 
 // all rounds in one cooperative launch (single-device path): no host round trip per round
@@ -265,17 +297,24 @@ __global__ void __launch_bounds__(256) k_plateau_all(const uint32_t* __restrict_
   for (unsigned round = 0;; ++round) {
     unsigned* flag = &ctr->changed[round & 1];
     bool any = false;
+    // every pass re-reads only the candidate byte (coalesced) of an entry that is settled: single-cell pits after the
+    // first probe, resolved cells once their direction is stored.  Each pass used to pull ~10 sectors per flat cell
+    // from DRAM, three times over, for the 4 % of the entries that can change at all.
     for (unsigned i = t0; i < n; i += stride) {
-      uint8_t res = plateau_probe_cell(list[i], ddir, elev, d);
+      if (round && cand[i] == PLATEAU_DEAD) continue;
+      const uint32_t v = list[i];
+      uint8_t res = (v & LIST_DEAD) ? PLATEAU_DEAD : plateau_probe_cell(v & LIST_ID, ddir, elev, d);
       cand[i] = res;
-      any |= res != 0;
+      any |= (res & 15) != 0;
     }
     if (__syncthreads_or(any) && threadIdx.x == 0) atomicOr(flag, 1u);
     if (t0 == 0) ctr->changed[(round + 1) & 1] = 0;  // next round's flag (nobody reads it before the sync)
     grid.sync();
     if (!*reinterpret_cast<volatile unsigned*>(flag)) break;
-    for (unsigned i = t0; i < n; i += stride)
-      if (cand[i]) ddir[list[i]] = cand[i];
+    for (unsigned i = t0; i < n; i += stride) {
+      const uint8_t cd = cand[i];
+      if (cd & 15) { ddir[list[i] & LIST_ID] = cd; cand[i] = PLATEAU_DEAD; }
+    }
     if (t0 == 0) ctr->rounds = round + 1;
     grid.sync();
   }
@@ -288,7 +327,8 @@ __global__ void k_plateau_probe(const uint32_t* __restrict__ list, unsigned n, c
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   bool any = false;
   if (i < n) {
-    uint8_t res = plateau_probe_cell(list[i], ddir, elev, d);
+    const uint32_t v = list[i];   // (a band's halo rows change between rounds, its elevations do not: dead stays dead)
+    uint8_t res = (v & LIST_DEAD) ? 0 : plateau_probe_cell(v & LIST_ID, ddir, elev, d) & 15;
     cand[i] = res;
     any = res != 0;
   }
@@ -297,7 +337,7 @@ __global__ void k_plateau_probe(const uint32_t* __restrict__ list, unsigned n, c
 __global__ void k_plateau_apply(const uint32_t* __restrict__ list, unsigned n, const uint8_t* __restrict__ cand,
                                 uint8_t* __restrict__ ddir) {
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && cand[i]) ddir[list[i]] = cand[i];
+  if (i < n && cand[i]) ddir[list[i] & LIST_ID] = cand[i];
 }
 
 // ---- flat-pit patches ------------------------------------------------------------------------------
@@ -314,7 +354,7 @@ __global__ void k_patch_mark(const uint32_t* __restrict__ list, unsigned long lo
   const unsigned long long nf = ctr->nflat;
   const unsigned n = (unsigned)(nf < cap ? nf : cap);
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    uint32_t id = list[i];
+    uint32_t id = list[i] & LIST_ID;
     if (ddir[id] != 5) continue;
     const int r = id / d.pitch, c = id - r * d.pitch;
     bool hit = false;
@@ -542,7 +582,9 @@ int run_ddir(litap_grid* g, int invert) {
     int per_sm = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plateau_all, 256, 0));
     if (per_sm < 1) return set_error(LITAP_ECUDA, "k_plateau_all cannot be made resident");
-    coop_blocks = c.sm_count * (per_sm < 2 ? per_sm : 2);
+    int want = 4;   // blocks per SM: enough threads for the worklist, few enough to start beside calc_form's blocks
+    if (const char* e = getenv("LITAP_PLATEAU_BPS")) want = atoi(e) > 0 ? atoi(e) : want;
+    coop_blocks = c.sm_count * (per_sm < want ? per_sm : want);
   }
   DdirCounters h;
   for (int attempt = 0;; ++attempt) {
