@@ -225,26 +225,37 @@ __global__ void k_l2_indeg(TileGeom g, const uint32_t* __restrict__ jump0, size_
   long long s2 = slot_of_id(v, g);
   if (s2 >= 0) atomicAdd(&indeg[s2], 1u);
 }
-__global__ void k_l2_src(const uint32_t* __restrict__ indeg, size_t nslots, uint8_t* __restrict__ src) {
+// sources of the level-2 forest, and per slot ONE word for the chase: inflow known so far (high half, starts as the
+// base handed over by k_shed_local) | inflows still to come (low half)
+__global__ void k_l2_src(const uint32_t* __restrict__ indeg, const uint32_t* __restrict__ ext, size_t nslots,
+                         uint8_t* __restrict__ src, unsigned long long* __restrict__ xi) {
   size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < nslots) src[s] = indeg[s] == 0;
+  if (s >= nslots) return;
+  const uint32_t n = indeg[s];
+  src[s] = n == 0;
+  xi[s] = ((unsigned long long)ext[s] << 32) | n;
 }
+// A thread per source carries its inflow down the chain of border slots; at every slot the LAST inflow to arrive
+// carries the sum on.  One 64-bit atomic per hop adds the carry to the slot's high half and takes one off its
+// pending count; the value it returns tells the thread whether it was the last and what had arrived before it
+// (atomics on one address are ordered, so no fence is needed), and the next edge is loaded under the shadow of the
+// atomic: one memory round trip per hop (there were three: add, fenced decrement, fenced read-back).
 __global__ void k_l2_chase(TileGeom g, const uint32_t* __restrict__ jump0, const uint8_t* __restrict__ src,
-                           size_t nslots, uint32_t* ext, uint32_t* indeg) {
+                           size_t nslots, uint32_t* __restrict__ ext, unsigned long long* xi) {
   size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= nslots || !src[s]) return;
-  uint32_t carry = *reinterpret_cast<volatile uint32_t*>(&ext[s]);
-  while (true) {
-    uint32_t v = jump0[s];
+  uint32_t carry = ext[s];
+  uint32_t v = jump0[s];
+  for (size_t hop = 0; hop < nslots; ++hop) {
     if (!is_cell(v)) break;
-    long long t = slot_of_id(v, g);
+    const long long t = slot_of_id(v, g);
     if (t < 0) break;
-    if (carry) atomicAdd(&ext[t], carry);
-    __threadfence();
-    if (atomicSub(&indeg[t], 1u) != 1u) break;
-    __threadfence();
-    carry = atomicAdd(&ext[t], 0u);
-    s = (size_t)t;
+    const uint32_t vn = jump0[t];
+    const unsigned long long old = atomicAdd(&xi[t], ((unsigned long long)carry << 32) - 1ull);
+    if ((uint32_t)old != 1u) break;   // other inflows are still to come
+    carry += (uint32_t)(old >> 32);
+    ext[t] = carry;
+    v = vn;
   }
 }
 // shed keys: exits' partials merged into their root; then the index among the maxima
@@ -530,6 +541,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   l2.ext = S.get<uint32_t>(nslots);
   l2.indeg = S.get<uint32_t>(nslots);
   l2.src = S.get<uint8_t>(nslots);
+  l2.xi = S.get<unsigned long long>(nslots);
   Pits& pits = W.pits;
   pits.rootmax = S.get<unsigned long long>(np);
   pits.pitkmax = S.get<unsigned long long>(np);
@@ -538,7 +550,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   pits.rank = S.get<uint32_t>(np);
   pits.cell = S.get<uint32_t>(np);
   pits.cnt = S.get<uint32_t>(np);
-  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.ext || !l2.indeg || !l2.src || !pits.rootmax ||
+  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.ext || !l2.indeg || !l2.src || !l2.xi || !pits.rootmax ||
       !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !pits.cell || !pits.cnt)
     return set_error(LITAP_ENOMEM, "device allocation failed (shed level-2 arrays)");
   CUDA_TRY(cudaMemsetAsync(l2.ext, 0, nslots * 4, st));
@@ -576,8 +588,8 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   }
   // ---- external inflow of every border cell
   KERNEL("k_l2_indeg", k_l2_indeg<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.indeg));
-  KERNEL("k_l2_src", k_l2_src<<<sblk, 256, 0, st>>>(l2.indeg, nslots, l2.src));
-  KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, l2.src, nslots, l2.ext, l2.indeg));
+  KERNEL("k_l2_src", k_l2_src<<<sblk, 256, 0, st>>>(l2.indeg, l2.ext, nslots, l2.src, l2.xi));
+  KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, l2.src, nslots, l2.ext, l2.xi));
   // ---- per-pit keys
   if (npits) {
     const unsigned kblk = (unsigned)((std::max(nslots, (size_t)npits) + 255) / 256);

@@ -75,6 +75,7 @@ struct L2 {                    // level-2 arrays, one entry per border slot
   uint32_t* ext;               // external inflow into the border cell (starts as base, accumulated in place)
   uint32_t* indeg;
   uint8_t* src;
+  unsigned long long* xi;      // chase word: inflow so far << 32 | inflows still to come
 };
 struct Pits {                  // one entry per pit id
   unsigned long long* rootmax; // max orderable elevation of the shed
