@@ -528,7 +528,7 @@ __global__ void k_pit_totals(const L2 l2, size_t nslots, uint32_t* __restrict__ 
   if (s >= nslots) return;
   uint32_t v = l2.jump0[s];
   if (v != ID_NA && (v & ID_ROOT)) {
-    uint32_t e = l2.ext[s];
+    uint32_t e = xi_inflow(l2.xi[s]);
     if (e) atomicAdd(&tot[v & ~ID_ROOT], e);
   }
 }
@@ -815,7 +815,7 @@ __global__ void k_band_seed_walk(TileGeom g, BandInfo bi, const uint8_t* __restr
     cc = c2;
   }
   for (size_t hop = 0; s >= 0 && hop < nslots; ++hop) {
-    atomicAdd(&l2.ext[s], x);
+    atomicAdd(&l2.xi[s], (unsigned long long)x << 32);
     const uint32_t v = l2.jump0[s];
     if (!is_cell(v)) return;
     s = slot_of_id(v, g);

@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
     // own initial pointer word had T_EXIT <=> the final one has it and points at the cell itself
     if ((p[k] & (OVER | T_EXIT)) == (OVER | T_EXIT) && (p[k] & PIDX) == i) {
       const long long es = slot_of_rc(r + nb_dr(dv), c0 + k + nb_dc(dv), g.tilesX);
-      if (es >= 0) atomicAdd(&l2.ext[es], pcnt[k]);
+      if (es >= 0) atomicAdd(&l2.xi[es], (unsigned long long)pcnt[k] << 32);
     }
   }
   if (row_ok) {  // kept for k_shed_final: local terminal word and in-tile flow count of every cell (pads included)
@@ -180,7 +180,10 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
       else {  // exit: continue at the entry cell of the neighbouring tile
         const int dv = s_dir[tt];
         const int ty_ = tt / LP, tx_ = tt - ty_ * LP;
-        edge = (uint32_t)((size_t)(t.r_base + ty_ + nb_dr(dv)) * g.d.pitch + (t.c_base + tx_ + nb_dc(dv)));
+        const int er = t.r_base + ty_ + nb_dr(dv), ec = t.c_base + tx_ + nb_dc(dv);
+        edge = (uint32_t)((size_t)er * g.d.pitch + ec);
+        const long long es = slot_of_rc(er, ec, g.tilesX);   // one more in-edge of the entry cell's slot
+        if (es >= 0) atomicAdd(&l2.xi[es], 1ull);
         if (tt == i) {  // this border cell is the exit itself
           pk = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
           pi = s_kid[i];
@@ -217,44 +220,27 @@ __global__ void k_l2_close_cycles(uint32_t* __restrict__ jres, size_t nslots) {
   size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s < nslots && is_cell(jres[s])) jres[s] = ID_NA;
 }
-__global__ void k_l2_indeg(TileGeom g, const uint32_t* __restrict__ jump0, size_t nslots, uint32_t* __restrict__ indeg) {
+// External inflow of every border cell.  A thread per source (a slot without in-edges) carries its inflow down the
+// chain of border slots; at every slot the LAST inflow to arrive carries the sum on.  One 64-bit atomic per hop adds the
+// carry to the slot's inflow field and counts the arrival; the value it returns tells the thread whether it was the
+// last and what had arrived before it (atomics on one address are ordered: no fence), and the next edge is loaded
+// under the shadow of the atomic: one memory round trip per hop.  The in-edge counts and the base inflows come
+// from k_shed_local in the same word (L2::xi), so there is no in-degree pass and no source pass over the slots.
+__global__ void k_l2_chase(TileGeom g, const uint32_t* __restrict__ jump0, size_t nslots, unsigned long long* xi) {
   size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= nslots) return;
-  uint32_t v = jump0[s];
-  if (!is_cell(v)) return;
-  long long s2 = slot_of_id(v, g);
-  if (s2 >= 0) atomicAdd(&indeg[s2], 1u);
-}
-// sources of the level-2 forest, and per slot ONE word for the chase: inflow known so far (high half, starts as the
-// base handed over by k_shed_local) | inflows still to come (low half)
-__global__ void k_l2_src(const uint32_t* __restrict__ indeg, const uint32_t* __restrict__ ext, size_t nslots,
-                         uint8_t* __restrict__ src, unsigned long long* __restrict__ xi) {
-  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots) return;
-  const uint32_t n = indeg[s];
-  src[s] = n == 0;
-  xi[s] = ((unsigned long long)ext[s] << 32) | n;
-}
-// A thread per source carries its inflow down the chain of border slots; at every slot the LAST inflow to arrive
-// carries the sum on.  One 64-bit atomic per hop adds the carry to the slot's high half and takes one off its
-// pending count; the value it returns tells the thread whether it was the last and what had arrived before it
-// (atomics on one address are ordered, so no fence is needed), and the next edge is loaded under the shadow of the
-// atomic: one memory round trip per hop (there were three: add, fenced decrement, fenced read-back).
-__global__ void k_l2_chase(TileGeom g, const uint32_t* __restrict__ jump0, const uint8_t* __restrict__ src,
-                           size_t nslots, uint32_t* __restrict__ ext, unsigned long long* xi) {
-  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || !src[s]) return;
-  uint32_t carry = ext[s];
+  const unsigned long long w = xi[s];
+  if (w & XI_EDGES) return;          // not a source (the in-edge field does not change during the chase)
+  uint32_t carry = xi_inflow(w);     // nothing is ever added to a source
   uint32_t v = jump0[s];
   for (size_t hop = 0; hop < nslots; ++hop) {
     if (!is_cell(v)) break;
     const long long t = slot_of_id(v, g);
     if (t < 0) break;
     const uint32_t vn = jump0[t];
-    const unsigned long long old = atomicAdd(&xi[t], ((unsigned long long)carry << 32) - 1ull);
-    if ((uint32_t)old != 1u) break;   // other inflows are still to come
-    carry += (uint32_t)(old >> 32);
-    ext[t] = carry;
+    const unsigned long long old = atomicAdd(&xi[t], ((unsigned long long)carry << 32) + XI_ARRIVED);
+    if (((old >> 16) & 0xFFFFull) + 1ull != (old & XI_EDGES)) break;   // other inflows are still to come
+    carry += xi_inflow(old);
     v = vn;
   }
 }
@@ -382,7 +368,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
     bi = by * LP + bx;
-    bext = l2.ext[tile_slot0 + threadIdx.x];
+    bext = xi_inflow(l2.xi[tile_slot0 + threadIdx.x]);
     blab = slab[tile_slot0 + threadIdx.x];
   }
   constexpr int NRING = 2 * LW + 2 * TH, RPT = (NRING + NT - 1) / NT;
@@ -538,10 +524,8 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   l2.jres = S.get<uint32_t>(nslots);
   l2.pkmax = S.get<unsigned long long>(nslots);
   l2.pkidx = S.get<uint32_t>(nslots);
-  l2.ext = S.get<uint32_t>(nslots);
-  l2.indeg = S.get<uint32_t>(nslots);
-  l2.src = S.get<uint8_t>(nslots);
   l2.xi = S.get<unsigned long long>(nslots);
+  l2.slab = S.get<uint32_t>(nslots);
   Pits& pits = W.pits;
   pits.rootmax = S.get<unsigned long long>(np);
   pits.pitkmax = S.get<unsigned long long>(np);
@@ -550,11 +534,10 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   pits.rank = S.get<uint32_t>(np);
   pits.cell = S.get<uint32_t>(np);
   pits.cnt = S.get<uint32_t>(np);
-  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.ext || !l2.indeg || !l2.src || !l2.xi || !pits.rootmax ||
+  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.xi || !l2.slab || !pits.rootmax ||
       !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !pits.cell || !pits.cnt)
     return set_error(LITAP_ENOMEM, "device allocation failed (shed level-2 arrays)");
-  CUDA_TRY(cudaMemsetAsync(l2.ext, 0, nslots * 4, st));
-  CUDA_TRY(cudaMemsetAsync(l2.indeg, 0, nslots * 4, st));
+  CUDA_TRY(cudaMemsetAsync(l2.xi, 0, nslots * 8, st));
   // slots BUSED.. of every tile are never written by k_shed_local: keep them NA / empty
   CUDA_TRY(cudaMemsetAsync(l2.jump0, 0xFF, nslots * 4, st));
   CUDA_TRY(cudaMemsetAsync(l2.jres, 0xFF, nslots * 4, st));
@@ -587,9 +570,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
     KERNEL("k_l2_close_cycles", k_l2_close_cycles<<<sblk, 256, 0, st>>>(l2.jres, nslots));
   }
   // ---- external inflow of every border cell
-  KERNEL("k_l2_indeg", k_l2_indeg<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.indeg));
-  KERNEL("k_l2_src", k_l2_src<<<sblk, 256, 0, st>>>(l2.indeg, l2.ext, nslots, l2.src, l2.xi));
-  KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, l2.src, nslots, l2.ext, l2.xi));
+  KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.xi));
   // ---- per-pit keys
   if (npits) {
     const unsigned kblk = (unsigned)((std::max(nslots, (size_t)npits) + 255) / 256);
@@ -645,8 +626,7 @@ int shed_phase_final(litap_grid* g, shed::ShedWork& W, const shed::BandSeeds& se
     dim3 grid((m + 255) / 256, 4);
     KERNEL("k_ring_fill", k_ring_fill<<<grid, 256, 0, st>>>(d, g->shed, g->upslope, g->ridge, g->halo_bot ? 1 : 0));
   }
-  // the in-degree array of the level-2 chase is free by now: it takes the slots' final labels
-  uint32_t* slab = W.l2.indeg;
+  uint32_t* slab = W.l2.slab;
   {
     const size_t n = std::max(W.nslots, (size_t)W.npits);
     KERNEL("k_final_labels", k_final_labels<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(

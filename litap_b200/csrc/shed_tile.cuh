@@ -72,11 +72,15 @@ struct L2 {                    // level-2 arrays, one entry per border slot
   uint32_t* jres;              // resolved (compressed) pointer
   unsigned long long* pkmax;   // exit cells: max orderable elevation draining through it inside its tile (0 = none)
   uint32_t* pkidx;             //             lowest cell id attaining pkmax
-  uint32_t* ext;               // external inflow into the border cell (starts as base, accumulated in place)
-  uint32_t* indeg;
-  uint8_t* src;
-  unsigned long long* xi;      // chase word: inflow so far << 32 | inflows still to come
+  // external inflow of the border cell and the state of the level-2 chase in ONE word: inflow known so far << 32 (starts
+  // as the counts handed over by the exits of the neighbouring tiles) | inflows that have arrived << 16 | in-edges
+  // (border slots whose flow continues at this cell; < 2^16: at most 3 tiles x BUSED).  k_shed_local builds it with
+  // 64-bit atomic adds; only the chase changes the middle field.
+  unsigned long long* xi;
+  uint32_t* slab;              // final shed number of the slot (k_final_labels)
 };
+__device__ __forceinline__ uint32_t xi_inflow(unsigned long long w) { return (uint32_t)(w >> 32); }
+constexpr unsigned long long XI_ARRIVED = 1ull << 16, XI_EDGES = 0xFFFFull;
 struct Pits {                  // one entry per pit id
   unsigned long long* rootmax; // max orderable elevation of the shed
   unsigned long long* pitkmax; // the pit tile's own partial
