@@ -52,8 +52,8 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   __shared__ uint32_t s_kid[LC];   // lowest cell id attaining the key; later the pit id
   __shared__ uint16_t s_ptr[LC];
   __shared__ uint8_t s_dir[LC];
-  __shared__ unsigned s_npit;
-  __shared__ unsigned long long s_pitbase;
+  __shared__ unsigned s_npit, s_nx, s_xcur;   // pits / exit cells of the tile, cursor of its exit records
+  __shared__ unsigned long long s_pitbase, s_xbase;
 
   const TileCtx t = tile_ctx();
   const int r = t.r_base + owned_ly(), c0 = t.c_base + owned_lx0();
@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   const int base = owned_local(0);
   const size_t tile_slot0 = (size_t)(t.ty * g.tilesX + t.tx) * BSLOTS;
   const size_t cell0 = (size_t)r * g.d.pitch + c0;  // k-th owned cell: cell0 + k (an 8-element boundary)
-  if (threadIdx.x == 0) s_npit = 0;
+  if (threadIdx.x == 0) s_npit = s_nx = s_xcur = 0;
   int p[CPT];
   const unsigned dvp = tile_setup(g, t, ddir, s_ptr, s_dir, p);
   // elevations of the owned cells (64 contiguous bytes): issued now, consumed after the pointer-doubling loop
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   // here: all REDs into s_cnt are complete (the loop ends with a barrier or with the all-done vote)
 
   // ---- exits hand their count to the entry cell's slot (base of the level-2 sum); pits keep theirs
-  unsigned pcnt[CPT];
+  unsigned pcnt[CPT], nx = 0;
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
     const int dv = (dvp >> (4 * k)) & 15u;
@@ -100,8 +100,10 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
     if ((p[k] & (OVER | T_EXIT)) == (OVER | T_EXIT) && (p[k] & PIDX) == i) {
       const long long es = slot_of_rc(r + nb_dr(dv), c0 + k + nb_dc(dv), g.tilesX);
       if (es >= 0) atomicAdd(&l2.xi[es], (unsigned long long)pcnt[k] << 32);
+      ++nx;
     }
   }
+  if (nx) atomicAdd(&s_nx, nx);   // exit records of the tile: their space is claimed together with the pit ids
   if (row_ok) {  // kept for k_shed_final: local terminal word and in-tile flow count of every cell (pads included)
     uint4 w;
     w.x = (unsigned)p[0] & 0xFFFFu | (unsigned)p[1] << 16;
@@ -146,7 +148,11 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
     if (((pit_mask_src >> (4 * k)) & 15u) == 5u) rk[k] = atomicAdd(&s_npit, 1u);
   }
   __syncthreads();  // keys complete, s_npit complete
-  if (threadIdx.x == 0 && s_npit) s_pitbase = atomicAdd(pit_cursor, (unsigned long long)s_npit);
+  if (threadIdx.x == 0 && (s_npit | s_nx)) {   // one atomic per tile: pits in the low half of the cursor, exit records in the high half
+    const unsigned long long old = atomicAdd(pit_cursor, (unsigned long long)s_npit | ((unsigned long long)s_nx << 32));
+    s_pitbase = old & 0xFFFFFFFFull;
+    s_xbase = old >> 32;
+  }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < CPT; ++k) {
@@ -166,14 +172,15 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   __syncthreads();
 
   // ---- level-2 edges and key partials: one thread per border slot
+  unsigned long long pk = 0;   // this thread's border cell is an exit itself: its key partial
+  uint32_t pi = 0xFFFFFFFFu;
+  bool is_exit = false;
   if (threadIdx.x < BUSED) {
     int bx, by;
     slot_to_local((int)threadIdx.x, bx, by);
     const int i = by * LP + bx;
     const int pw = s_ptr[i];
     uint32_t edge = ID_NA;
-    unsigned long long pk = 0;
-    uint32_t pi = 0xFFFFFFFFu;
     if ((pw & OVER) && (pw & (T_PIT | T_EXIT))) {
       const int tt = pw & PIDX;
       if (pw & T_PIT) edge = ID_ROOT | s_cnt[tt];
@@ -187,14 +194,15 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
         if (tt == i) {  // this border cell is the exit itself
           pk = ((unsigned long long)s_khi[i] << 32) | s_klo[i];
           pi = s_kid[i];
+          is_exit = true;
         }
       }
     }
     l2.jump0[tile_slot0 + threadIdx.x] = edge;
     l2.jres[tile_slot0 + threadIdx.x] = edge;
-    l2.pkmax[tile_slot0 + threadIdx.x] = pk;
-    l2.pkidx[tile_slot0 + threadIdx.x] = pi;
   }
+  // exit records: the key passes run over the exits only, not over every slot
+  if (is_exit) l2.xrec[s_xbase + atomicAdd(&s_xcur, 1u)] = make_ulonglong2(pk, ((unsigned long long)(tile_slot0 + threadIdx.x) << 32) | pi);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -244,25 +252,28 @@ __global__ void k_l2_chase(TileGeom g, const uint32_t* __restrict__ jump0, size_
     v = vn;
   }
 }
-// shed keys: exits' partials merged into their root; then the index among the maxima
-__global__ void k_keys_max(const L2 l2, size_t nslots, Pits pits) {
-  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots) return;
-  unsigned long long pk = l2.pkmax[s];
-  uint32_t root = l2.jres[s];
-  if (pk && root != ID_NA && (root & ID_ROOT)) atomicMax(&pits.rootmax[root & ~ID_ROOT], pk);
+// shed keys: exits' partials merged into their root; then the index among the maxima (grid-stride over the exit
+// records; their number stays on the device)
+__global__ void k_keys_max(const L2 l2, const unsigned long long* __restrict__ nrec, Pits pits) {
+  const size_t n = (size_t)(*nrec >> 32);   // (the pit cursor: exit records in its high half)
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const ulonglong2 rec = l2.xrec[i];
+    const uint32_t root = l2.jres[rec.y >> 32];
+    if (rec.x && root != ID_NA && (root & ID_ROOT)) atomicMax(&pits.rootmax[root & ~ID_ROOT], rec.x);
+  }
 }
-__global__ void k_keys_idx(const L2 l2, size_t nslots, Pits pits, unsigned npits) {
-  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < nslots) {
-    unsigned long long pk = l2.pkmax[s];
-    uint32_t root = l2.jres[s];
-    if (pk && root != ID_NA && (root & ID_ROOT)) {
-      uint32_t pid = root & ~ID_ROOT;
-      if (pk == pits.rootmax[pid]) atomicMin(&pits.rootidx[pid], l2.pkidx[s]);
+__global__ void k_keys_idx(const L2 l2, const unsigned long long* __restrict__ nrec, Pits pits, unsigned npits) {
+  const size_t n = (size_t)(*nrec >> 32), stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (size_t i = t0; i < n; i += stride) {
+    const ulonglong2 rec = l2.xrec[i];
+    const uint32_t root = l2.jres[rec.y >> 32];
+    if (rec.x && root != ID_NA && (root & ID_ROOT)) {
+      const uint32_t pid = root & ~ID_ROOT;
+      if (rec.x == pits.rootmax[pid]) atomicMin(&pits.rootidx[pid], (uint32_t)rec.y);
     }
   }
-  if (s < npits && pits.pitkmax[s] == pits.rootmax[s]) atomicMin(&pits.rootidx[s], pits.pitkidx[s]);
+  for (size_t s = t0; s < npits; s += stride)
+    if (pits.pitkmax[s] == pits.rootmax[s]) atomicMin(&pits.rootidx[s], pits.pitkidx[s]);
 }
 __global__ void k_iota(uint32_t* a, unsigned n) {
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -522,8 +533,7 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   L2& l2 = W.l2;
   l2.jump0 = S.get<uint32_t>(nslots);
   l2.jres = S.get<uint32_t>(nslots);
-  l2.pkmax = S.get<unsigned long long>(nslots);
-  l2.pkidx = S.get<uint32_t>(nslots);
+  l2.xrec = S.get<ulonglong2>(nslots);
   l2.xi = S.get<unsigned long long>(nslots);
   l2.slab = S.get<uint32_t>(nslots);
   Pits& pits = W.pits;
@@ -534,14 +544,13 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   pits.rank = S.get<uint32_t>(np);
   pits.cell = S.get<uint32_t>(np);
   pits.cnt = S.get<uint32_t>(np);
-  if (!l2.jump0 || !l2.jres || !l2.pkmax || !l2.pkidx || !l2.xi || !l2.slab || !pits.rootmax ||
+  if (!l2.jump0 || !l2.jres || !l2.xrec || !l2.xi || !l2.slab || !pits.rootmax ||
       !pits.pitkmax || !pits.pitkidx || !pits.rootidx || !pits.rank || !pits.cell || !pits.cnt)
     return set_error(LITAP_ENOMEM, "device allocation failed (shed level-2 arrays)");
   CUDA_TRY(cudaMemsetAsync(l2.xi, 0, nslots * 8, st));
   // slots BUSED.. of every tile are never written by k_shed_local: keep them NA / empty
   CUDA_TRY(cudaMemsetAsync(l2.jump0, 0xFF, nslots * 4, st));
   CUDA_TRY(cudaMemsetAsync(l2.jres, 0xFF, nslots * 4, st));
-  CUDA_TRY(cudaMemsetAsync(l2.pkmax, 0, nslots * 8, st));
 
   dim3 tgrid(tg.tilesX, tg.tilesY);
   W.tword = S.get<uint16_t>((size_t)d.cells + 64);  // pitched and offset like the grid arrays (aligned 16-byte vectors)
@@ -573,9 +582,9 @@ int shed_phase_local(litap_grid* g, shed::ShedWork& W) {
   KERNEL("k_l2_chase", k_l2_chase<<<sblk, 256, 0, st>>>(tg, l2.jump0, nslots, l2.xi));
   // ---- per-pit keys
   if (npits) {
-    const unsigned kblk = (unsigned)((std::max(nslots, (size_t)npits) + 255) / 256);
-    KERNEL("k_keys_max", k_keys_max<<<sblk, 256, 0, st>>>(l2, nslots, pits));
-    KERNEL("k_keys_idx", k_keys_idx<<<kblk, 256, 0, st>>>(l2, nslots, pits, npits));
+    const unsigned kblk = (unsigned)ctx().sm_count * 16;
+    KERNEL("k_keys_max", k_keys_max<<<kblk, 256, 0, st>>>(l2, counters + 1, pits));
+    KERNEL("k_keys_idx", k_keys_idx<<<kblk, 256, 0, st>>>(l2, counters + 1, pits, npits));
   }
   return LITAP_OK;
 }

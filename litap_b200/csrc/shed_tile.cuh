@@ -70,8 +70,10 @@ __device__ __forceinline__ long long slot_of_id(uint32_t id, const TileGeom& g) 
 struct L2 {                    // level-2 arrays, one entry per border slot
   uint32_t* jump0;             // original edge: entry cell id | ID_ROOT|pid | ID_NA
   uint32_t* jres;              // resolved (compressed) pointer
-  unsigned long long* pkmax;   // exit cells: max orderable elevation draining through it inside its tile (0 = none)
-  uint32_t* pkidx;             //             lowest cell id attaining pkmax
+  // exit cells, compacted (k_shed_local appends one record per border cell that is an exit itself; the cursor is
+  // counters[3]): x = max orderable elevation draining through it inside its tile, y = slot << 32 | lowest cell id
+  // attaining that maximum
+  ulonglong2* xrec;
   // external inflow of the border cell and the state of the level-2 chase in ONE word: inflow known so far << 32 (starts
   // as the counts handed over by the exits of the neighbouring tiles) | inflows that have arrived << 16 | in-edges
   // (border slots whose flow continues at this cell; < 2^16: at most 3 tiles x BUSED).  k_shed_local builds it with
