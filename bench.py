@@ -31,6 +31,8 @@ SEED, QUANT, GRID_M = 20261104, 1000.0, 5.0
 METRIC = "Mcells/s (ddir+shed+upslope+form)"
 # algorithmic bytes per cell of each hot kernel
 ALG_BYTES = {"k_d8": 9, "k_form": 48, "k_shed_local": 9, "k_shed_final": 10}
+# roofline_frac_by_kernel charges a kernel with the helper launch that prepares its gathers
+KERNEL_GROUP = {"k_shed_final": ("k_final_labels",)}
 
 
 def ncu_traffic(kernel):
@@ -297,6 +299,9 @@ def run_ours(a):
     for k, b in ALG_BYTES.items():
         if k in prof:
             avg = prof[k][1] / prof[k][0]
+            for extra in KERNEL_GROUP.get(k, ()):   # helper launches that belong to the kernel's job
+                if extra in prof:
+                    avg += prof[extra][1] / prof[k][0]
             rf_all[k] = round(b * n * ncols / (avg * 1e-3) / 1e9 / peak, 4)
 
     # ---- calc_weti2 (not part of the composite metric; single-device stage), reported beside it

@@ -2,11 +2,14 @@
 //
 //   k_count_pits    pits = cells with ddir == 5                                   (:12-20)
 //   k_shed_local    per tile: local terminals (pointer jumping), per-terminal max-elevation key,
-//                   local flow counts; writes the level-2 edges of the 252 border cells
+//                   local flow counts; writes the level-2 edges of the 124 border cells, counts the
+//                   in-edges / base inflows of the entry cells they lead to (L2::xi) and appends
+//                   one key record per exit cell
 //   k_l2_*          level-2 graph over border slots: resolve every border cell to its pit
 //                   (pointer jumping with path compression), accumulate external inflow
-//                   (in-degree + chase with atomics), merge the per-shed keys               (:25-29)
+//                   (chase: one 64-bit atomic per hop), merge the per-shed keys (exit records) (:25-29)
 //   cub radix sort  rank pits by (max elev desc, seqno of that cell asc)                  (:32-38)
+//   k_final_labels  final shed number of every border slot and pit cell
 //   k_shed_final    per tile: final shed label, upslope count (local accumulation seeded with
 //                   the external inflow) and ridge flag                                 (:42-57)
 //
