@@ -805,13 +805,16 @@ LITAP_HD double weti_tan(double f, double nv, int n, const WetiK& K) {
 // S = sum(tan, na.rm = TRUE) with R's long double accumulator; e[n] = elevation of neighbour n
 // (e[5] = the cell itself).  *lower gets bit n set for every strictly lower neighbour.
 LITAP_HD double weti_S(const double* e, const WetiK& K, unsigned* lower) {
-  const int W[9] = {7, 8, 9, 4, 5, 6, 1, 2, 3};
   Ld80 s;
   s.m = 0; s.e = 0;
   unsigned lo = 0;
-#pragma unroll
+  // window order 7 8 9 4 5 6 1 2 3.  On the device the loop stays a loop: unrolled (eight emulated long double additions
+  // and eight divisions in a row) it was most of a 65 KB kernel that waited for instructions
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
   for (int k = 0; k < 9; ++k) {
-    const int n = W[k];
+    const int n = 7 - 3 * (k / 3) + k % 3;
     if (n == 5) continue;  // self: tan = 0
     double t = weti_tan(e[5], e[n], n, K);
     if (is_nan(t)) continue;

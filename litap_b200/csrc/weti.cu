@@ -338,13 +338,18 @@ __global__ void __launch_bounds__(WT, 4) k_weti_nodes(Arrays A, GridDims d, Weti
         if (A.cls[tid] != CLS_NA && visited_before(A, f, id, e[dv], tid)) succ = 1u << dv;
       }
       // donors that precede the cell: strictly higher neighbours (they are A cells and push qc*tan, :74-75) and B
-      // neighbours whose drec is this cell and that are visited first (they push their whole qa, :82-83)
+      // neighbours whose drec is this cell and that are visited first (they push their whole qa, :82-83).
+      // (Loops over the neighbours / the donors, not unrolled: code size, see weti_S.)
       unsigned dmask = 0, bdon = 0;
+      unsigned clsw = 0;   // classes of the eight neighbours, 2 bits each: eight independent loads in flight
 #pragma unroll
+      for (int n = 1; n <= 9; ++n)
+        if (n != 5) clsw |= (unsigned)A.cls[id + nb_off(n, d.pitch)] << (2 * n);
+#pragma unroll 1
       for (int n = 1; n <= 9; ++n) {
         if (n == 5) continue;
         const size_t nid = id + nb_off(n, d.pitch);
-        const uint8_t nc = A.cls[nid];
+        const uint8_t nc = (uint8_t)((clsw >> (2 * n)) & 3u);
         if (nc == CLS_A) {
           // the same test that sets the donor's succ bit: tan > 0.  A difference above 1e-280 cannot underflow on its way
           // through / d * l (cell sizes are within 1e-30 .. 1e30 or the reciprocals are off), so only tiny ones are computed
@@ -354,27 +359,22 @@ __global__ void __launch_bounds__(WT, 4) k_weti_nodes(Arrays A, GridDims d, Weti
           if (visited_before(A, e[n], nid, f, id)) { dmask |= 1u << n; bdon |= 1u << n; }
         }
       }
-      // position of a donor in the visiting order = number of donors visited before it (static indices: registers)
-      int pos[10];
-#pragma unroll
-      for (int n = 1; n <= 9; ++n) pos[n] = 0;
-#pragma unroll
-      for (int a = 1; a <= 9; ++a) {
-        if (a == 5) continue;
-#pragma unroll
-        for (int b = a + 1; b <= 9; ++b) {
-          if (b == 5) continue;
-          if (((dmask >> a) & 1) && ((dmask >> b) & 1)) {
-            if (visited_before(A, e[a], id + nb_off(a, d.pitch), e[b], id + nb_off(b, d.pitch))) ++pos[b]; else ++pos[a];
-          }
+      // position of a donor in the visiting order = number of donors visited before it, 4 bits per neighbour code
+      unsigned long long posw = 0;
+      for (unsigned ma = dmask; ma; ma &= ma - 1) {
+        const int a = __ffs(ma) - 1;
+        for (unsigned mb = ma & (ma - 1); mb; mb &= mb - 1) {
+          const int b = __ffs(mb) - 1;
+          const bool ab = visited_before(A, e[a], id + nb_off(a, d.pitch), e[b], id + nb_off(b, d.pitch));
+          posw += 1ull << (4 * (ab ? b : a));
         }
       }
       const int nd = __popc(dmask);
-#pragma unroll
-      for (int n = 1; n <= 9; ++n) {
-        if (n == 5 || !((dmask >> n) & 1)) continue;
-        tp |= (unsigned long long)n << (TP_DON + 4 * pos[n]);
-        if ((bdon >> n) & 1) tp |= 1ull << (TP_BM + pos[n]);
+      for (unsigned m = dmask; m; m &= m - 1) {
+        const int n = __ffs(m) - 1;
+        const int pos = (int)(posw >> (4 * n)) & 15;
+        tp |= (unsigned long long)n << (TP_DON + 4 * pos);
+        if ((bdon >> n) & 1) tp |= 1ull << (TP_BM + pos);
       }
       tp |= (unsigned long long)nd | ((unsigned long long)succ << (TP_SUCC - 1)) | ((unsigned long long)cls << TP_CLS);
       if (nd == 0) { seed = true; seed_id = (uint32_t)id; seed_tp = tp; }
