@@ -14,7 +14,7 @@
 
 // neighbour code n (1..9) -> row / col step; R/LITAP_functions.R:212-220, rows grow southward
 LITAP_HD int nb_dr(int n) { return n <= 3 ? 1 : (n <= 6 ? 0 : -1); }
-LITAP_HD int nb_dc(int n) { return (n - 1) % 3 - 1; }
+LITAP_HD int nb_dc(int n) { return (int)((0x92490u >> (2 * n)) & 3u) - 1; }   // (n - 1) % 3 - 1 for n = 1..9, as a 2-bit table
 
 LITAP_HD bool is_nan(double x) { return x != x; }
 
@@ -794,7 +794,7 @@ LITAP_HD double div_rcp_prepare(double b) {
   const double ab = b < 0 ? -b : b;
   return (ab > 1e-30 && ab < 1e30) ? 1.0 / b : 0.0;
 }
-LITAP_HD bool weti_is_diag(int n) { return n == 1 || n == 3 || n == 7 || n == 9; }
+LITAP_HD bool weti_is_diag(int n) { return (0x28Au >> n) & 1u; }   // n in {1, 3, 7, 9}
 // tan_k of a cell at elevation f towards a neighbour at elevation nv in direction n (:64-65);
 // NaN neighbour -> NaN, neighbour not lower -> 0
 LITAP_HD double weti_tan(double f, double nv, int n, const WetiK& K) {
@@ -814,7 +814,7 @@ LITAP_HD double weti_S(const double* e, const WetiK& K, unsigned* lower) {
 #pragma unroll 1
 #endif
   for (int k = 0; k < 9; ++k) {
-    const int n = 7 - 3 * (k / 3) + k % 3;
+    const int n = (int)((0x321654987ull >> (4 * k)) & 15ull);
     if (n == 5) continue;  // self: tan = 0
     double t = weti_tan(e[5], e[n], n, K);
     if (is_nan(t)) continue;
