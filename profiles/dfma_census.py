@@ -36,7 +36,8 @@ print("# explicit fma() call sites in the sources:", explicit)
 print("# a kernel whose DFMAs all belong to division / sqrt expansions has MUFU.RCP64H / RSQ64H seeds; kernels that call")
 print("# div_rcp / div1000 / the quick paths of cellmath.h (explicit fma()) are marked in the last column")
 FMA_USERS = {"k_form": "form_cell_quick / fast (explicit fma, guarded; the doubt queue falls back to the reference tree)",
-             "k_form_edges": "same as k_form", "k_weti_nodes": "div_rcp", "k_weti_flow": "div_rcp", "k_weti_cls": "div_rcp",
+             "k_form_edges": "same as k_form", "k_d8": "div_sqrt2 (exact quotient of the largest diagonal difference: 4 explicit fma per cell x 4 cells) + the IEEE divisions of d8_slow_at",
+             "d8_slow_at": "IEEE divisions of the reference loop (out-of-line slow path of k_d8)", "k_weti_nodes": "div_rcp", "k_weti_flow": "div_rcp", "k_weti_cls": "div_rcp",
              "k_weti_final": "log() of libdevice", "k_relz_cells": "r_round1 (div1000-style exact quotient)"}
 print(f"{'kernel':44s} {'DFMA':>6s} {'DMUL':>6s} {'DADD':>6s} {'RCP64H':>7s} {'RSQ64H':>7s} {'UBLKCP':>7s}  explicit fma()")
 for k, c in stats.items():
