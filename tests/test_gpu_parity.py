@@ -184,6 +184,31 @@ def test_tiny_and_tile_edge_shapes(shape):
     assert_form_parity(e, 5.0, str(shape))
 
 
+def test_d8_near_ties_on_device():
+    """k_d8 divides only the largest diagonal difference by sqrt(2) and sends a window to the reference loop when another
+    diagonal difference is the double just below it (the only case in which a smaller difference can round to the same
+    quotient), or when the difference is tiny / huge.  A DEM drawn from a few values built for exactly that - diagonal
+    differences one or two ulp apart, orthogonal differences within a few ulp of diagonal / sqrt(2), denormal and 1e300
+    steps - must come out as the reference's loop (R/LITAP_functions.R:257-273) has it."""
+    rng = np.random.default_rng(20261105)
+    u = 2.0 ** -52
+    top = 1.5
+    diag = [0.25, 0.25 + u, 0.25 + 2 * u, 0.25 + 3 * u]            # top - diag = 1.25, 1.25 - 1 ulp, ...
+    q = 1.25 / np.sqrt(2.0)
+    orth = [top - q, np.nextafter(top - q, 0), np.nextafter(top - q, 2), np.nextafter(np.nextafter(top - q, 0), 0)]
+    vals = np.array([top, top, top] + diag + orth)
+    e = oracle.add_buffer(vals[rng.integers(0, len(vals), (200, 260))])
+    assert_flow_parity(e, "near ties")
+    # the same pattern scaled into the ranges the exact-residual division does not cover
+    for scale in (2.0 ** -1000, 2.0 ** 950):
+        es = oracle.add_buffer(vals[rng.integers(0, len(vals), (64, 70))] * scale)
+        o = oracle.ddir(es)
+        db = lb.add_buffer(es[1:-1, 1:-1])
+        db["elev"] = np.ascontiguousarray(es).ravel()
+        d = lb.calc_ddir2(db)
+        assert (d["ddir_u8"].reshape(es.shape) == o["ddir"]).all(), f"scale {scale}"
+
+
 def test_degenerate_surfaces():
     flat = oracle.add_buffer(np.full((70, 70), 5.0))          # one big flat pit patch
     assert_flow_parity(flat, "flat")
