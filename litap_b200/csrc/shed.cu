@@ -38,7 +38,7 @@ __global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsig
 
 // ------------------------------------------------------------------------------------------------
 // shared memory of k_shed_local: ptr, dir, cnt, key hi / lo / idx (no aliasing: fewer barriers)
-constexpr size_t SMEM_A = (size_t)LC * (2 + 1 + 4 + 4 + 4 + 4) + 64;
+constexpr size_t SMEM_A = (size_t)LC * (sizeof(ptr_t) + 1 + 4 + 4 + 4 + 4) + 64;
 
 #ifndef SHED_MINB
 #define SHED_MINB 6
@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const 
   __shared__ uint32_t s_khi[LC];   // key, high word
   __shared__ uint32_t s_klo[LC];   // key, low word
   __shared__ uint32_t s_kid[LC];   // lowest cell id attaining the key; later the pit id
-  __shared__ uint16_t s_ptr[LC];
+  __shared__ ptr_t s_ptr[LC];
   __shared__ uint8_t s_dir[LC];
   __shared__ unsigned s_npit, s_nx, s_xcur;   // pits / exit cells of the tile, cursor of its exit records
   __shared__ unsigned long long s_pitbase, s_xbase;

@@ -22,6 +22,14 @@ static_assert(TW % CPT == 0 && NT == GX * TH, "a thread owns CPT consecutive col
 // local pointer word (16 bit): low 11 bits = local index, OVER = the walk has reached / passed the
 // terminal whose index is in the low bits, T_PIT / T_EXIT = kind of that terminal (neither = NA)
 constexpr int OVER = 0x8000, T_PIT = 0x4000, T_EXIT = 0x2000, PIDX = 0x07FF;
+// the pointer words of a tile in shared memory: 32-bit slots (the words themselves stay 16-bit, as stored per cell for
+// k_shed_final).  With 16-bit slots two threads' own-cell stores shared a bank word (1.7 wavefronts per store); 32-bit
+// slots with the odd row pitch are conflict-free
+#ifndef SHED_PTR16
+typedef uint32_t ptr_t;
+#else
+typedef uint16_t ptr_t;
+#endif
 static_assert(LC <= PIDX + 1, "local indices must fit 11 bits");
 
 struct TileGeom {
@@ -136,7 +144,7 @@ __device__ __forceinline__ unsigned long long load_owned_u8(const TileGeom& g, c
 // to no tile: the NA ring) are NA terminals.  Returns the 8 direction codes packed 4 bits each; p[k]
 // gets the pointer word of the k-th owned cell.
 __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx& t, const uint8_t* __restrict__ ddir,
-                                               uint16_t* s_ptr, uint8_t* s_dir, int* p) {
+                                               ptr_t* s_ptr, uint8_t* s_dir, int* p) {
   const int ly = owned_ly(), r = t.r_base + ly, lx0 = owned_lx0();
   const unsigned long long raw = load_owned_u8(g, t, ddir);
   unsigned pack = 0;
@@ -157,7 +165,7 @@ __device__ __forceinline__ unsigned tile_setup(const TileGeom& g, const TileCtx&
         pw = ex ? (i | OVER | T_EXIT) : (i + dr * LP + dc);
       }
     }
-    s_ptr[i] = (uint16_t)pw;
+    s_ptr[i] = (ptr_t)pw;
     s_dir[i] = (uint8_t)dv;
     p[k] = pw;
     pack |= (unsigned)dv << (4 * k);
@@ -198,6 +206,9 @@ __device__ __forceinline__ unsigned lds_u32(uint32_t a) {
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
   return v;
 }
+__device__ __forceinline__ void sts_u32(uint32_t a, unsigned v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
 __device__ __forceinline__ void sts_u16(uint32_t a, unsigned v) {
   asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
@@ -211,17 +222,17 @@ __device__ __forceinline__ void red_min_u32(uint32_t a, unsigned v) {
   asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
 
-__device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* s_cnt, int* p) {
+__device__ __forceinline__ void tile_jump_accumulate(ptr_t* s_ptr, unsigned* s_cnt, int* p) {
   const int base = owned_local(0);
   const uint32_t a_ptr = smem_addr(s_ptr), a_cnt = smem_addr(s_cnt);
-  const uint32_t own_ptr = a_ptr + 2 * base, own_cnt = a_cnt + 4 * base;
+  const uint32_t own_ptr = a_ptr + (uint32_t)sizeof(ptr_t) * base, own_cnt = a_cnt + 4 * base;
   for (int round = 0; round < MAX_ROUNDS; ++round) {
     unsigned b[CPT], sv[CPT];
     bool any = false;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
       if (!(p[k] & OVER)) {
-        b[k] = lds_u16(a_ptr + 2 * p[k]);
+        b[k] = sizeof(ptr_t) == 2 ? lds_u16(a_ptr + 2 * p[k]) : lds_u32(a_ptr + 4 * p[k]);
         sv[k] = lds_u32(own_cnt + 4 * k);
         any = true;
       }
@@ -230,7 +241,7 @@ __device__ __forceinline__ void tile_jump_accumulate(uint16_t* s_ptr, unsigned* 
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
       if (p[k] & OVER) continue;
-      sts_u16(own_ptr + 2 * k, b[k]);
+      if (sizeof(ptr_t) == 2) sts_u16(own_ptr + 2 * k, b[k]); else sts_u32(own_ptr + 4 * k, b[k]);
       red_add_u32(a_cnt + 4 * p[k], sv[k]);
       p[k] = (int)b[k];
     }
