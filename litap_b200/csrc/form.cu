@@ -5,6 +5,7 @@
 #include <cmath>
 #include "cellmath.h"
 #include "litap_internal.h"
+#include <cstdlib>
 #include "rowring.cuh"
 #include "stencil.cuh"
 
@@ -257,7 +258,24 @@ int run_form_rows(litap_grid* g, double grid_m, int row_lo, int row_hi) {
     FormQ Q;
     Q.inv2g = K.inv2g;
     Q.gz = 8.0 * 4.440892098500626e-16 * 57295.78 / (grid_m * grid_m);
-    KERNEL("k_form", k_form<<<grid, FORM_THREADS, 0, st>>>(g->elev, d, K, Q, g_trig, g_qtab, P, row_lo, row_hi));
+    // LITAP_FORM_BPS (tuning): cap k_form's resident blocks per SM with unused dynamic shared memory, so that the flow
+    // stages of litap_*_flow_form (other pipes of the SM: ALU / shared memory, k_form is fp64-bound) stay co-resident
+    static int dyn_smem = -1;
+    if (dyn_smem < 0) {
+      dyn_smem = 0;
+      if (const char* e = getenv("LITAP_FORM_BPS")) {
+        const int bps = atoi(e);
+        cudaFuncAttributes fa;
+        if (bps > 0 && cudaFuncGetAttributes(&fa, k_form) == cudaSuccess) {
+          const int per_block = (227 * 1024) / bps - 1024;   // shared memory of one block such that bps + 1 do not fit
+          const int share = (227 * 1024) / (bps + 1);
+          int want = share + 1024 - (int)fa.sharedSizeBytes;
+          if (want > per_block - (int)fa.sharedSizeBytes) want = per_block - (int)fa.sharedSizeBytes;
+          if (want > 0 && cudaFuncSetAttribute(k_form, cudaFuncAttributeMaxDynamicSharedMemorySize, want) == cudaSuccess) dyn_smem = want;
+        }
+      }
+    }
+    KERNEL("k_form", k_form<<<grid, FORM_THREADS, dyn_smem, st>>>(g->elev, d, K, Q, g_trig, g_qtab, P, row_lo, row_hi));
   }
   // R/form_01_calc_form.R:54-57 in buffered 0-based coordinates, in this order:
   //   col 1 <- col 2 ; col NC-2 <- col NC-3 ; row 1 <- row 2 ; row NR-2 <- row NR-3

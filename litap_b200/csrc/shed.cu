@@ -316,14 +316,16 @@ __global__ void k_final_labels(const uint32_t* __restrict__ jres, size_t nslots,
 __device__ __forceinline__ bool tw_labelled(unsigned w) { return (w & OVER) && (w & (T_PIT | T_EXIT)); }
 
 // add x to every cell from local cell i down to its local terminal (inclusive)
-__device__ __forceinline__ void tile_walk_add(uint32_t a_cnt, const uint8_t* s_dir, const uint16_t* s_tw, int i, unsigned x) {
-  const unsigned w = s_tw[i];
+// s_td: per local cell, terminal word (low half) | direction code << 16 - one 32-bit slot, so that the own-cell stores
+// are conflict-free (separate u16 / u8 arrays took 2 and 3 wavefronts per store) and a walk step is one load
+__device__ __forceinline__ void tile_walk_add(uint32_t a_cnt, const uint32_t* s_td, int i, unsigned x) {
+  const unsigned w = s_td[i] & 0xFFFFu;
   if (!x || !tw_labelled(w)) return;  // NA chains and cycles carry no upslope
   const int term = w & PIDX;
   for (int step = 0; step < LC; ++step) {
     red_add_u32(a_cnt + 4 * i, x);
     if (i == term) break;
-    i += loc_off(s_dir[i]);
+    i += loc_off((int)(s_td[i] >> 16));
   }
 }
 
@@ -334,8 +336,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   __shared__ unsigned s_cnt[LC];
   __shared__ uint32_t s_tlab[LC];  // label of a terminal
   __shared__ uint32_t s_lab[LC];   // label of every local cell
-  __shared__ uint16_t s_tw[LC];
-  __shared__ uint8_t s_dir[LC];
+  __shared__ uint32_t s_td[LC];
   const uint32_t* lab_in = reinterpret_cast<const uint32_t*>(shed_out);      // pit cells hold their final label (k_final_labels)
 
   const TileCtx t = tile_ctx();
@@ -362,8 +363,7 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
       const bool in = c0 + k < g.d.NC;  // (row_ok is folded into the zero loads)
       const unsigned w = in ? (wv[k >> 1] >> (16 * (k & 1))) & 0xFFFFu : 0u;
       tw[k] = w;
-      s_dir[i] = in ? (uint8_t)(draw >> (8 * k)) : (uint8_t)0;
-      s_tw[i] = (uint16_t)w;
+      s_td[i] = w | (in ? (unsigned)((draw >> (8 * k)) & 0xFFull) << 16 : 0u);
       s_cnt[i] = in ? nv[k] : 0u;
     }
   }
@@ -410,20 +410,20 @@ __global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t*
   __syncthreads();
   const uint32_t a_cnt = smem_addr(s_cnt);
   // ---- flow entering the tile, walked down to the local terminal
-  if (bi >= 0) tile_walk_add(a_cnt, s_dir, s_tw, bi, bext);
+  if (bi >= 0) tile_walk_add(a_cnt, s_td, bi, bext);
   if (seeds.x_top || seeds.x_bot) {
     const int lt = seeds.row_top - t.r_base, lb = seeds.row_bot - t.r_base;
     if (threadIdx.x < TW && t.c_base + (int)threadIdx.x + 1 < g.d.NC) {
       const int cc = t.c_base + (int)threadIdx.x + 1;
-      if (seeds.x_top && lt >= 1 && lt <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lt * LP + (int)threadIdx.x + 1, seeds.x_top[cc]);
-      if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_dir, s_tw, lb * LP + (int)threadIdx.x + 1, seeds.x_bot[cc]);
+      if (seeds.x_top && lt >= 1 && lt <= TH) tile_walk_add(a_cnt, s_td, lt * LP + (int)threadIdx.x + 1, seeds.x_top[cc]);
+      if (seeds.x_bot && lb >= 1 && lb <= TH) tile_walk_add(a_cnt, s_td, lb * LP + (int)threadIdx.x + 1, seeds.x_bot[cc]);
     }
   }
 #pragma unroll
   for (int k = 0; k < CPT; ++k)
     if (pitlab[k] != 0xFFFFFFFFu) s_tlab[base + k] = pitlab[k];
   if (bi >= 0) {
-    const int pw = s_tw[bi];
+    const int pw = (int)(s_td[bi] & 0xFFFFu);
     if ((pw & (OVER | T_EXIT)) == (OVER | T_EXIT) && (pw & PIDX) == bi) s_tlab[bi] = blab;
   }
 #pragma unroll
