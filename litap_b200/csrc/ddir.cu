@@ -62,7 +62,10 @@ __global__ void k_invert(double* __restrict__ elev, GridDims d, const unsigned l
 // ---- D8 stencil + flat worklist ------------------------------------------------------------------
 constexpr int D8_CPT = 4;        // columns per thread: 32-byte loads, uchar4 stores
 constexpr int D8_THREADS = 128;  // 512 columns per block
-constexpr int D8_ROWS = 32;      // rows per block
+#ifndef D8_ROWS_PER_BLOCK
+#define D8_ROWS_PER_BLOCK 32
+#endif
+constexpr int D8_ROWS = D8_ROWS_PER_BLOCK;      // rows per block
 constexpr int D8_STAGE = 1024;   // flats a block stages in shared memory before appending
 
 // the reference's loop for the (very rare) windows d8_fast does not decide: out of line, and fed from global memory
@@ -164,7 +167,10 @@ __device__ __forceinline__ void d8_row(const RowWin<D8_CPT>& p, const RowWin<D8_
 // through registers (one row ahead per warp) the kernel had ~18 KB in flight per SM and ran at the latency, not at
 // the issue rate, once the per-cell arithmetic was halved.
 constexpr int D8_COLS = D8_THREADS * D8_CPT;
-constexpr int D8_GROUP = 2;      // ring slots recycled per block barrier
+#ifndef D8_GROUP_ROWS
+#define D8_GROUP_ROWS 2
+#endif
+constexpr int D8_GROUP = D8_GROUP_ROWS;      // ring slots recycled per block barrier
 using D8Ring = RowRing<double, D8_COLS, D8_STAGES>;
 
 // the thread's window columns of ring row k (grid row r0 - 1 + k): own columns at slot elements 2 + 4t .. 5 + 4t; a row

@@ -41,7 +41,7 @@ __global__ void k_count_pits(const uint8_t* __restrict__ ddir, GridDims d, unsig
 constexpr size_t SMEM_A = (size_t)LC * (sizeof(ptr_t) + 1 + 4 + 4 + 4 + 4) + 64;
 
 #ifndef SHED_MINB
-#define SHED_MINB 6
+#define SHED_MINB 8
 #endif
 __global__ void __launch_bounds__(NT, SHED_MINB) k_shed_local(TileGeom g, const uint8_t* __restrict__ ddir,
                                                       const double* __restrict__ elev, uint32_t* __restrict__ lab,
@@ -329,7 +329,10 @@ __device__ __forceinline__ void tile_walk_add(uint32_t a_cnt, const uint32_t* s_
   }
 }
 
-__global__ void __launch_bounds__(NT, 8) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
+#ifndef SHEDF_MINB
+#define SHEDF_MINB 8
+#endif
+__global__ void __launch_bounds__(NT, SHEDF_MINB) k_shed_final(TileGeom g, const uint8_t* __restrict__ ddir, const L2 l2,
                                                       const uint32_t* __restrict__ slab,
                                                       const uint16_t* __restrict__ tword, int32_t* shed_out,
                                                       uint32_t* upslope, uint8_t* __restrict__ ridge, BandSeeds seeds) {
